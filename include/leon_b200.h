@@ -1,0 +1,143 @@
+/* leon_b200 — C ABI of the B200-native Leon compression hot path (libleon_b200.so).
+ *
+ * The reference (GATB/leon) has no FFI: its boundary is the C++ class `Leon : Tool` and the functors it hands to
+ * `Dispatcher::iterate`.  Every entry point below replaces one of those call sites and is
+ * what a cgo/JNI/ctypes/C++ host would bind.  Citations are relative to
+ * /root/reference/thirdparty/gatb-core/gatb-core/src/gatb/ (C/ = tools/compression/, K/ = kmer/impl/).
+ *
+ * Conventions: plain pointers and sizes only; every call returns 0 or a negative LEON_E_* code and leaves a
+ * message retrievable with leon_last_error(); nothing throws or aborts across the boundary.  A context is
+ * single-owner (not re-entrant).  Inputs are owned by the caller and must stay valid until the call returns;
+ * outputs are owned by the context (pinned host memory) and stay valid until the next leon_compress() /
+ * leon_encode() on that context or leon_destroy().  There is NO CPU fallback: without a CUDA device or with
+ * the extension missing every compute call fails with LEON_E_CUDA.
+ */
+#ifndef LEON_B200_H
+#define LEON_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LEON_B200_ABI_VERSION 1
+
+enum {
+    LEON_OK = 0,
+    LEON_E_ARG = -1,      /* bad argument / unsupported option value */
+    LEON_E_CUDA = -2,     /* CUDA runtime error (message has the CUDA string) */
+    LEON_E_NOMEM = -3,    /* host or device allocation failed */
+    LEON_E_STATE = -4,    /* phase called out of order */
+    LEON_E_OVERFLOW = -5  /* an internal capacity bound was exceeded (message says which) */
+};
+
+/* Option subset of the `leon -c` command line that reaches the hot path (C/Leon.cpp:102-140, 342-431). */
+typedef struct leon_opts {
+    int32_t kmer_size;        /* -kmer-size, default 31; 2..31 uses 64-bit keys, 32..63 uses 128-bit keys */
+    int32_t reads_per_block;  /* -reads (hidden), default 50000: block = that many consecutive reads */
+    int32_t has_qual;         /* 1: FASTQ with qualities kept; 0: FASTA, -noqual or -seq-only */
+    int32_t lossless;         /* -lossless: qualities copied, no smoothing */
+    int32_t abundance_set;    /* -abundance X given: disables the auto cutoff (its value is unused) */
+    int32_t device;           /* CUDA device ordinal */
+    int32_t anchor_batch;     /* reads per anchor-resolution batch (0 = default); any value gives identical output */
+    int32_t reserved[9];
+} leon_opts;
+
+/* A set of reads: concatenated ASCII bases (upper-case ACGTN for reference parity) + R+1 offsets
+ * (what K/../bank Sequence::getDataBuffer()/getDataSize() give the reference, C/DnaCoder.cpp:279-296),
+ * and, when has_qual, the quality characters at the same offsets. */
+typedef struct leon_reads {
+    const uint8_t  *bases;
+    const uint64_t *offsets;   /* offsets[0] = 0, offsets[R] = total bases */
+    const uint8_t  *quals;     /* NULL when qualities are not kept */
+    uint64_t        nreads;
+} leon_reads;
+
+/* Result of phase 1 (replaces SortingCountAlgorithm<>::execute as used by C/Leon.cpp:449-459 and the two values
+ * Leon reads back from it at C/Leon.cpp:247-280). */
+typedef struct leon_count_result {
+    int32_t  cutoff;              /* histogram/cutoff (auto cutoff, floor 4) */
+    uint64_t nb_solids_cutoff;    /* histogram/nbsolidsforcutoff */
+    uint64_t nb_solid_total;      /* #distinct canonical k-mers with abundance >= 2 */
+    uint64_t nb_distinct;         /* #distinct canonical k-mers */
+    uint64_t nb_kmers;            /* #valid k-mer occurrences counted */
+    const uint64_t *histogram;    /* [10001] abundance histogram (bin 10000 = clamp), host memory */
+} leon_count_result;
+
+/* Everything `leon -c` stores for the sequence stream (C/Leon.cpp:965-1081 endDnaCompression, writeBloom,
+ * writeAnchorDict; C/Leon.cpp:653-710 writeBlock; C/Leon.cpp:581-651 writeBlockLena before zlib). */
+typedef struct leon_result {
+    leon_count_result count;
+    /* dataset leon/bloom + its "size" attribute */
+    const uint8_t *bloom;          uint64_t bloom_nbytes;   uint64_t bloom_bits;
+    /* datasets leon/anchors/anchorsDict, anchorAdress */
+    const uint8_t *anchors_dict;   uint64_t anchors_dict_nbytes;   uint64_t anchor_count;
+    /* datasets leon/dna/dna_<id> (concatenated), blocksizes ([2*nblocks]: bytes, nreads), nb_blocks = 2*nblocks */
+    uint64_t nblocks;
+    const uint64_t *blocksizes;
+    const uint8_t *dna;            uint64_t dna_nbytes;
+    /* text handed to zlib for leon/qual/qual_<id> (concatenated), and its per-block sizes; empty without qualities */
+    const uint8_t *qual_text;      uint64_t qual_nbytes;
+    const uint64_t *qual_block_sizes;
+    /* metadata datasets */
+    uint64_t read_count, total_dna_size;
+    int32_t  min_read_size, max_read_size;
+    /* per-read encoding decisions, for parity checks: anchor position (-1 = read coded without anchor), address */
+    const int32_t  *anchor_pos;
+    const uint32_t *anchor_addr;
+    uint64_t reads_without_anchor;
+} leon_result;
+
+/* Device-side phase timings of the last leon_compress()/phase calls, CUDA events on the context's stream. */
+typedef struct leon_timings {
+    float h2d_ms, count_ms, sort_ms, bloom_ms, anchor_ms, walk_ms, qual_ms, entropy_ms, d2h_ms, total_ms;
+    uint64_t kernel_launches;     /* kernels launched by the library since leon_create */
+    uint32_t sort_passes;         /* radix passes executed by the counting sort */
+    uint32_t anchor_batches, anchor_rounds;
+    float sort_pass_ms;           /* average duration of one scatter pass of the counting sort */
+    uint64_t sort_keys;           /* keys per pass */
+    float reserved[6];
+} leon_timings;
+
+typedef struct leon_ctx leon_ctx;
+
+int         leon_b200_abi_version(void);
+/* Creates a context on opts->device.  Replaces Leon::Leon + Leon::execute option capture (C/Leon.cpp:81-224). */
+int         leon_create(const leon_opts *opts, leon_ctx **out);
+void        leon_destroy(leon_ctx *ctx);
+const char *leon_last_error(const leon_ctx *ctx);   /* ctx may be NULL: error of a failed leon_create */
+
+/* Pinned host memory for inputs, so that uploads are true DMA (optional: any host pointer is accepted). */
+void       *leon_alloc_pinned(size_t nbytes);
+void        leon_free_pinned(void *p);
+
+/* One-shot: phases 1-4 for an in-memory read set.  Replaces Leon::executeCompression's sequence stream
+ * (C/Leon.cpp:449-459 DSK, :903-962 startDnaCompression, :965-1081 endDnaCompression). */
+int leon_compress(leon_ctx *ctx, const leon_reads *reads, leon_result *out);
+
+/* The same work phase by phase (what the CLI and multi-step hosts call): */
+int leon_upload(leon_ctx *ctx, const leon_reads *reads);                 /* H2D of the read set */
+int leon_count(leon_ctx *ctx, leon_count_result *out);                   /* K/SortingCountAlgorithm.cpp:499-644 as used by Leon */
+int leon_bloom_build(leon_ctx *ctx, const uint8_t **bits, uint64_t *nbytes, uint64_t *reduced_bits); /* C/Leon.cpp:226-338 */
+int leon_encode(leon_ctx *ctx, leon_result *out);                        /* C/DnaCoder.cpp:279-405 over all blocks + range coding */
+/* Device-only run on the already uploaded read set (phases 1-4, outputs left in HBM); used to time the path with
+ * inputs resident in HBM.  leon_fetch() then copies the outputs to host. */
+int leon_run_device(leon_ctx *ctx);
+int leon_fetch(leon_ctx *ctx, leon_result *out);
+
+int leon_get_timings(const leon_ctx *ctx, leon_timings *out);
+
+/* Test hooks (parity tests only): Bloom queries on the device filter for host-provided forward k-mers.
+ * kmers: n x (lo, hi) u64 pairs.  out4[i] = BloomNeighborCoherent::contains4 mask (COL Bloom.hpp:645-798),
+ * out1[i] = contains() of the canonical form (Bloom.hpp:597-642). */
+int leon_debug_bloom_query(leon_ctx *ctx, const uint64_t *kmers, uint64_t n, int right, uint8_t *out4, uint8_t *out1);
+/* out12[i*12..]: canon lo/hi, hashpart lo/hi, racine, prefval, simplehash16(hashpart,1..6) as computed on the device. */
+int leon_debug_hashes(leon_ctx *ctx, const uint64_t *kmers, uint64_t n, uint64_t *out12);
+/* Copies a named device buffer of the last run to host (names listed in DESIGN.md); returns bytes via *nbytes. */
+int leon_debug_fetch(leon_ctx *ctx, const char *name, void *dst, uint64_t cap, uint64_t *nbytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,8 @@
+"""leon_b200 — B200-native Leon compression hot path.
+
+The product is libleon_b200.so (hand-written sm_100a CUDA behind the C ABI of include/leon_b200.h).
+This package is the thin Python host mirror used by the parity tests and bench.py: it binds the C ABI with
+ctypes and keeps the names of the reference's interface (`-kmer-size`, `-reads`, `-lossless`, `-abundance`, ...).
+It contains no compute and no fallback: if the library or a CUDA device is missing, calls raise.
+"""
+from .api import Leon, LeonError, load_library, ABI_SYMBOLS  # noqa: F401

@@ -1,0 +1,242 @@
+"""ctypes binding of include/leon_b200.h (no torch types, no compute on the Python side)."""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libleon_b200.so")
+
+ABI_SYMBOLS = [
+    "leon_b200_abi_version", "leon_create", "leon_destroy", "leon_last_error", "leon_alloc_pinned", "leon_free_pinned",
+    "leon_compress", "leon_upload", "leon_count", "leon_bloom_build", "leon_encode", "leon_run_device", "leon_fetch",
+    "leon_get_timings", "leon_debug_bloom_query", "leon_debug_hashes", "leon_debug_fetch",
+]
+
+
+class LeonError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("leon_b200 error %d: %s" % (code, msg))
+        self.code = code
+
+
+class Opts(C.Structure):
+    _fields_ = [("kmer_size", C.c_int32), ("reads_per_block", C.c_int32), ("has_qual", C.c_int32), ("lossless", C.c_int32),
+                ("abundance_set", C.c_int32), ("device", C.c_int32), ("anchor_batch", C.c_int32), ("reserved", C.c_int32 * 9)]
+
+
+class Reads(C.Structure):
+    _fields_ = [("bases", C.c_void_p), ("offsets", C.c_void_p), ("quals", C.c_void_p), ("nreads", C.c_uint64)]
+
+
+class CountResult(C.Structure):
+    _fields_ = [("cutoff", C.c_int32), ("nb_solids_cutoff", C.c_uint64), ("nb_solid_total", C.c_uint64),
+                ("nb_distinct", C.c_uint64), ("nb_kmers", C.c_uint64), ("histogram", C.POINTER(C.c_uint64))]
+
+
+class Result(C.Structure):
+    _fields_ = [
+        ("count", CountResult),
+        ("bloom", C.POINTER(C.c_uint8)), ("bloom_nbytes", C.c_uint64), ("bloom_bits", C.c_uint64),
+        ("anchors_dict", C.POINTER(C.c_uint8)), ("anchors_dict_nbytes", C.c_uint64), ("anchor_count", C.c_uint64),
+        ("nblocks", C.c_uint64), ("blocksizes", C.POINTER(C.c_uint64)),
+        ("dna", C.POINTER(C.c_uint8)), ("dna_nbytes", C.c_uint64),
+        ("qual_text", C.POINTER(C.c_uint8)), ("qual_nbytes", C.c_uint64), ("qual_block_sizes", C.POINTER(C.c_uint64)),
+        ("read_count", C.c_uint64), ("total_dna_size", C.c_uint64),
+        ("min_read_size", C.c_int32), ("max_read_size", C.c_int32),
+        ("anchor_pos", C.POINTER(C.c_int32)), ("anchor_addr", C.POINTER(C.c_uint32)),
+        ("reads_without_anchor", C.c_uint64),
+    ]
+
+
+class Timings(C.Structure):
+    _fields_ = [(n, C.c_float) for n in ("h2d_ms", "count_ms", "sort_ms", "bloom_ms", "anchor_ms", "walk_ms", "qual_ms",
+                                         "entropy_ms", "d2h_ms", "total_ms")] + \
+               [("kernel_launches", C.c_uint64), ("sort_passes", C.c_uint32), ("anchor_batches", C.c_uint32),
+                ("anchor_rounds", C.c_uint32), ("sort_pass_ms", C.c_float), ("sort_keys", C.c_uint64),
+                ("reserved", C.c_float * 6)]
+
+
+_lib = None
+
+
+def load_library(path=LIB_PATH):
+    """Loads libleon_b200.so; raises if it was not built (no fallback of any kind)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(path):
+        raise LeonError(-2, "%s not built: run `python -c 'import __graft_entry__ as g; g.build()'`" % path)
+    L = C.CDLL(path)
+    L.leon_create.argtypes = [C.POINTER(Opts), C.POINTER(C.c_void_p)]
+    L.leon_destroy.argtypes = [C.c_void_p]
+    L.leon_last_error.restype = C.c_char_p
+    L.leon_last_error.argtypes = [C.c_void_p]
+    L.leon_alloc_pinned.restype = C.c_void_p
+    L.leon_alloc_pinned.argtypes = [C.c_size_t]
+    L.leon_free_pinned.argtypes = [C.c_void_p]
+    L.leon_compress.argtypes = [C.c_void_p, C.POINTER(Reads), C.POINTER(Result)]
+    L.leon_upload.argtypes = [C.c_void_p, C.POINTER(Reads)]
+    L.leon_count.argtypes = [C.c_void_p, C.POINTER(CountResult)]
+    L.leon_bloom_build.argtypes = [C.c_void_p, C.POINTER(C.POINTER(C.c_uint8)), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    L.leon_encode.argtypes = [C.c_void_p, C.POINTER(Result)]
+    L.leon_run_device.argtypes = [C.c_void_p]
+    L.leon_fetch.argtypes = [C.c_void_p, C.POINTER(Result)]
+    L.leon_get_timings.argtypes = [C.c_void_p, C.POINTER(Timings)]
+    L.leon_debug_bloom_query.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.c_void_p]
+    L.leon_debug_hashes.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+    L.leon_debug_fetch.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
+    _lib = L
+    return L
+
+
+def _arr(ptr, n, dtype, copy=True):
+    if not n or not ptr:
+        return np.zeros(0, dtype)
+    a = np.ctypeslib.as_array(ptr, shape=(int(n),))
+    return a.astype(dtype, copy=True) if copy else a
+
+
+class PinnedArray:
+    """numpy view over pinned host memory obtained from leon_alloc_pinned."""
+
+    def __init__(self, nbytes, dtype=np.uint8):
+        L = load_library()
+        self._L = L
+        self.nbytes = int(nbytes)
+        self.ptr = L.leon_alloc_pinned(max(self.nbytes, 1))
+        if not self.ptr:
+            raise LeonError(-3, "leon_alloc_pinned(%d) failed" % nbytes)
+        buf = (C.c_uint8 * max(self.nbytes, 1)).from_address(self.ptr)
+        self.array = np.frombuffer(buf, dtype=np.uint8, count=self.nbytes).view(dtype)
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            self._L.leon_free_pinned(self.ptr)
+            self.ptr = None
+
+
+class Leon:
+    """Host-side mirror of the reference's `Leon` tool for the sequence stream of `leon -c`.
+
+    Option names follow the command line of the reference (C/Leon.cpp:102-140): kmer_size = -kmer-size,
+    reads_per_block = -reads, lossless = -lossless, abundance = -abundance (only its presence matters, as in the
+    reference), seq_only/noqual decide whether qualities are kept.
+    """
+
+    def __init__(self, kmer_size=31, reads_per_block=50000, lossless=False, abundance=None, has_qual=False, device=0,
+                 anchor_batch=0):
+        self.L = load_library()
+        self.opts = Opts(kmer_size, reads_per_block, int(has_qual), int(lossless), int(abundance is not None), device,
+                         anchor_batch)
+        self.ctx = C.c_void_p()
+        rc = self.L.leon_create(C.byref(self.opts), C.byref(self.ctx))
+        if rc != 0:
+            raise LeonError(rc, self.L.leon_last_error(None).decode())
+        self._keep = None
+
+    def close(self):
+        if self.ctx:
+            self.L.leon_destroy(self.ctx)
+            self.ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            raise LeonError(rc, self.L.leon_last_error(self.ctx).decode())
+
+    def _reads(self, bases, offsets, quals):
+        bases = np.ascontiguousarray(bases, np.uint8)
+        offsets = np.ascontiguousarray(offsets, np.uint64)
+        q = np.ascontiguousarray(quals, np.uint8) if (self.opts.has_qual and quals is not None) else None
+        self._keep = (bases, offsets, q)
+        return Reads(bases.ctypes.data, offsets.ctypes.data, q.ctypes.data if q is not None else None, len(offsets) - 1)
+
+    @staticmethod
+    def _result(r, copy=True):
+        hq = r.qual_nbytes > 0
+        return dict(
+            cutoff=int(r.count.cutoff), nb_solids_cutoff=int(r.count.nb_solids_cutoff),
+            nb_solid_total=int(r.count.nb_solid_total), nb_distinct=int(r.count.nb_distinct), nb_kmers=int(r.count.nb_kmers),
+            histogram=_arr(r.count.histogram, 10001, np.uint64, copy),
+            bloom=_arr(r.bloom, r.bloom_nbytes, np.uint8, copy), bloom_bits=int(r.bloom_bits),
+            anchors_dict=_arr(r.anchors_dict, r.anchors_dict_nbytes, np.uint8, copy), anchor_count=int(r.anchor_count),
+            nblocks=int(r.nblocks), blocksizes=_arr(r.blocksizes, 2 * r.nblocks, np.uint64, copy),
+            dna=_arr(r.dna, r.dna_nbytes, np.uint8, copy),
+            qual_text=_arr(r.qual_text, r.qual_nbytes, np.uint8, copy),
+            qual_block_sizes=_arr(r.qual_block_sizes, r.nblocks if hq else 0, np.uint64, copy),
+            read_count=int(r.read_count), total_dna_size=int(r.total_dna_size),
+            min_read_size=int(r.min_read_size), max_read_size=int(r.max_read_size),
+            anchor_pos=_arr(r.anchor_pos, r.read_count, np.int32, copy),
+            anchor_addr=_arr(r.anchor_addr, r.read_count, np.uint32, copy),
+            reads_without_anchor=int(r.reads_without_anchor),
+        )
+
+    # one-shot, host buffers in / host buffers out
+    def compress(self, bases, offsets, quals=None, copy=True):
+        rd = self._reads(bases, offsets, quals)
+        r = Result()
+        self._check(self.L.leon_compress(self.ctx, C.byref(rd), C.byref(r)))
+        return self._result(r, copy)
+
+    # phase by phase
+    def upload(self, bases, offsets, quals=None):
+        rd = self._reads(bases, offsets, quals)
+        self._check(self.L.leon_upload(self.ctx, C.byref(rd)))
+
+    def count(self):
+        r = CountResult()
+        self._check(self.L.leon_count(self.ctx, C.byref(r)))
+        return dict(cutoff=int(r.cutoff), nb_solids_cutoff=int(r.nb_solids_cutoff), nb_solid_total=int(r.nb_solid_total),
+                    nb_distinct=int(r.nb_distinct), nb_kmers=int(r.nb_kmers), histogram=_arr(r.histogram, 10001, np.uint64))
+
+    def bloom_build(self):
+        bits = C.POINTER(C.c_uint8)()
+        nbytes, red = C.c_uint64(), C.c_uint64()
+        self._check(self.L.leon_bloom_build(self.ctx, C.byref(bits), C.byref(nbytes), C.byref(red)))
+        return _arr(bits, nbytes.value, np.uint8), int(red.value)
+
+    def encode(self):
+        r = Result()
+        self._check(self.L.leon_encode(self.ctx, C.byref(r)))
+        return self._result(r)
+
+    def run_device(self):
+        self._check(self.L.leon_run_device(self.ctx))
+
+    def fetch(self, copy=True):
+        r = Result()
+        self._check(self.L.leon_fetch(self.ctx, C.byref(r)))
+        return self._result(r, copy)
+
+    def timings(self):
+        t = Timings()
+        self._check(self.L.leon_get_timings(self.ctx, C.byref(t)))
+        return {n: getattr(t, n) for n, _ in Timings._fields_ if n != "reserved"}
+
+    def debug_bloom_query(self, kmers_lo_hi, right):
+        k = np.ascontiguousarray(kmers_lo_hi, np.uint64).reshape(-1, 2)
+        n = len(k)
+        o4, o1 = np.zeros(n, np.uint8), np.zeros(n, np.uint8)
+        self._check(self.L.leon_debug_bloom_query(self.ctx, k.ctypes.data, n, int(right), o4.ctypes.data, o1.ctypes.data))
+        return o4, o1
+
+    def debug_hashes(self, kmers_lo_hi):
+        k = np.ascontiguousarray(kmers_lo_hi, np.uint64).reshape(-1, 2)
+        out = np.zeros((len(k), 12), np.uint64)
+        self._check(self.L.leon_debug_hashes(self.ctx, k.ctypes.data, len(k), out.ctypes.data))
+        return out
+
+    def debug_fetch(self, name, dtype=np.uint8):
+        nb = C.c_uint64()
+        self._check(self.L.leon_debug_fetch(self.ctx, name.encode(), None, 0, C.byref(nb)))
+        out = np.zeros(nb.value, np.uint8)
+        if nb.value:
+            self._check(self.L.leon_debug_fetch(self.ctx, name.encode(), out.ctypes.data, nb.value, C.byref(nb)))
+        return out.view(dtype)

@@ -1,0 +1,317 @@
+// Phase 3a — anchor selection with the reference's sequential semantics, computed in parallel.
+//
+// Reference (one thread, reads in file order; C/DnaCoder.cpp:563-576 findExistingAnchor, C/Leon.cpp:1105-1243
+// findAndInsertAnchor, COL/Hash16.hpp): read i takes the FIRST position whose canonical k-mer is already in the
+// dictionary D; if none, the first Bloom-positive k-mer in the order [n/2, n/2+10) -> [0, n/2) -> [n/2+10, n) is
+// inserted with address |D| and becomes the anchor; if none, the read has no anchor.
+//
+// Here reads are handled in ordered batches.  Every dictionary entry carries the index of the read that inserted it
+// ("time"); read i may only see entries with time < i.  Per batch:
+//   A  lookup against D (entries of earlier batches)            -> reads with a hit can never insert
+//   P  the no-hit reads, in order, with their Bloom candidate c_j
+//   R  resolve who inserts: j inserts  <=>  no earlier inserter l < j has c_l among the k-mers of read j.
+//      Rounds of deterministic reservations: j is decided once every earlier reader of each of its k-mers is
+//      decided; the smallest undecided j always is, so it terminates with exactly the serial answer.
+//   I  inserters get addresses |D| + rank, in read order, and enter D with time = read index
+//   B  second lookup for the other reads of the batch, restricted to positions before their current hit (the
+//      reference returns the first POSITION, so an anchor inserted by an earlier read of the same batch can win)
+#pragma once
+#include "common.cuh"
+#include "kmer_math.cuh"
+#include "count.cuh"
+
+namespace lbanchor {
+
+using lbcount::pack32;
+using lbcount::window_kmer;
+
+#define LB_EMPTY32 0xffffffffu
+#define LB_EMPTY64 0xffffffffffffffffull
+
+template <typename K> struct DictDev {
+    K *keys;
+    uint32_t *addr;
+    uint32_t *time;      // LB_EMPTY32 = free slot
+    uint64_t mask;       // capacity - 1 (power of two)
+};
+
+template <typename K> LB_HD uint64_t dict_hash(K key) { return hash64(kmer_fold64(key), 0x9E3779B97F4A7C15ULL); }
+
+// forward-strand k-mers of positions [start, end) of a read, 32 per step, N read as A (C/DnaCoder.cpp:519-535).
+// f(p, kmer, active) is called by all 32 lanes together and returns a warp-uniform "stop".
+template <typename K, typename F>
+LB_D void warp_for_kmers(const uint8_t *__restrict__ s, uint64_t L, int k, uint64_t start, uint64_t end, int lane, F &f)
+{
+    if (start >= end) return;
+    uint64_t i0 = start + lane, i1 = start + 32 + lane;
+    uint64_t w0 = pack32(i0 < L ? base_code_n_as_a(s[i0]) : 0u);
+    uint64_t w1 = pack32(i1 < L ? base_code_n_as_a(s[i1]) : 0u);
+    for (uint64_t base = start; base < end; base += 32) {
+        uint64_t i2 = base + 64 + lane;
+        uint64_t w2 = pack32(i2 < L ? base_code_n_as_a(s[i2]) : 0u);
+        uint64_t p = base + lane;
+        K kmer = window_kmer<K>(w0, w1, w2, lane, k);
+        if (f(p, kmer, p < end)) return;
+        w0 = w1; w1 = w2;
+    }
+}
+
+template <typename K> LB_D bool dict_find(const DictDev<K> &d, K key, uint32_t before, uint32_t *addr)
+{
+    uint64_t s = dict_hash(key) & d.mask;
+    while (true) {
+        uint32_t t = d.time[s];
+        if (t == LB_EMPTY32) return false;
+        if (d.keys[s] == key) {
+            if (t < before) { *addr = d.addr[s]; return true; }
+            return false;   // keys are unique in D
+        }
+        s = (s + 1) & d.mask;
+    }
+}
+
+template <typename K> struct LookupFn {
+    const DictDev<K> &d; int k; uint32_t r; uint64_t lim; int lane;
+    int64_t pos; uint32_t addr;
+    LB_D bool operator()(uint64_t p, K kmer, bool active)
+    {
+        uint32_t a = 0;
+        bool hit = active && p < lim && dict_find(d, kmer_canon(kmer, k), r, &a);
+        unsigned bal = __ballot_sync(0xffffffffu, hit);
+        if (bal) {
+            int first = __ffs(bal) - 1;
+            pos = (int64_t)(p - lane + first);
+            addr = __shfl_sync(0xffffffffu, a, first);
+            return true;
+        }
+        return false;
+    }
+};
+
+// passes A and B.  apos[r] < 0: search all positions; apos[r] >= 0: only positions before it.
+template <typename K>
+__global__ void __launch_bounds__(256) k_anchor_lookup(const uint8_t *__restrict__ bases, const uint64_t *__restrict__ offsets,
+                                                       uint64_t lo, uint64_t hi, int k, DictDev<K> d, int32_t *apos,
+                                                       uint32_t *aaddr, const uint8_t *__restrict__ skip)
+{
+    const int lane = threadIdx.x & 31;
+    uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+    for (uint64_t r = lo + warp; r < hi; r += nwarps) {
+        if (skip && skip[r]) continue;
+        uint64_t o = offsets[r], L = offsets[r + 1] - o;
+        if (L < (uint64_t)k) continue;
+        uint64_t n = L - k + 1;
+        int32_t cur = apos[r];
+        uint64_t lim = cur >= 0 ? (uint64_t)cur : n;
+        LookupFn<K> f{d, k, (uint32_t)r, lim, lane, -1, 0};
+        warp_for_kmers<K>(bases + o, L, k, 0, lim, lane, f);
+        if (lane == 0 && f.pos >= 0) { apos[r] = (int32_t)f.pos; aaddr[r] = f.addr; }
+    }
+}
+
+// P list: reads of the batch that have k-mers but no hit yet
+struct PIn {
+    const uint64_t *offsets; const int32_t *apos; uint64_t lo; int k;
+    __device__ uint32_t operator()(uint64_t i) const
+    {
+        uint64_t r = lo + i;
+        return (offsets[r + 1] - offsets[r] >= (uint64_t)k && apos[r] < 0) ? 1u : 0u;
+    }
+};
+struct POut {
+    uint32_t *plist; uint64_t lo;
+    __device__ void operator()(uint64_t i, uint32_t ex, uint32_t v) const { if (v) plist[ex] = (uint32_t)(lo + i); }
+};
+
+template <typename K> struct CandFn {
+    const BloomDev &b; const uint64_t *tbl; int k; int lane;
+    int64_t pos; K key;
+    LB_D bool operator()(uint64_t p, K kmer, bool active)
+    {
+        K c = kmer_canon(kmer, k);
+        bool hit = active && bloom_contains<K>(b, c, tbl);
+        unsigned bal = __ballot_sync(0xffffffffu, hit);
+        if (bal) {
+            int first = __ffs(bal) - 1;
+            pos = (int64_t)(p - lane + first);
+            uint64_t l = __shfl_sync(0xffffffffu, kmer_low64(c), first);
+            uint64_t h = __shfl_sync(0xffffffffu, kmer_high64(c), first);
+            kmer_make(key, l, h);
+            return true;
+        }
+        return false;
+    }
+};
+
+// Bloom candidate of every P read, search order of C/Leon.cpp:1139-1187
+template <typename K>
+__global__ void __launch_bounds__(256) k_candidates(const uint8_t *__restrict__ bases, const uint64_t *__restrict__ offsets,
+                                                    const uint32_t *__restrict__ plist, uint32_t m, int k, BloomDev b,
+                                                    const uint64_t *__restrict__ tbl_g, int32_t *cand_pos, K *cand_key)
+{
+    __shared__ uint64_t tbl[256];
+    tbl[threadIdx.x] = tbl_g[threadIdx.x];
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t j = warp; j < m; j += nwarps) {
+        uint64_t r = plist[j];
+        uint64_t o = offsets[r], L = offsets[r + 1] - o;
+        uint64_t n = L - k + 1;
+        uint64_t iMin = n / 2, iMax = n / 2 + 10;
+        if (iMax > n) iMax = n;
+        CandFn<K> f{b, tbl, k, lane, -1, K(0)};
+        warp_for_kmers<K>(bases + o, L, k, iMin, iMax, lane, f);
+        if (f.pos < 0) warp_for_kmers<K>(bases + o, L, k, 0, iMin, lane, f);
+        if (f.pos < 0) warp_for_kmers<K>(bases + o, L, k, iMax, n, lane, f);
+        if (lane == 0) { cand_pos[j] = (int32_t)f.pos; cand_key[j] = f.key; }
+    }
+}
+
+// ---- batch-local table over candidate values ------------------------------------------------------------------
+template <typename K> struct CandTable {
+    uint64_t *proxy;     // 64-bit stand-in used for the CAS (the key itself for 64-bit k-mers); LB_EMPTY64 = free
+    K *keys;
+    uint32_t *ins;       // P index of the decided inserter of this value (at most one), LB_EMPTY32 if none yet
+    uint32_t *fu;        // smallest undecided P index having this value as candidate (per round)
+    uint64_t mask;
+};
+
+template <typename K> LB_HD uint64_t cand_proxy(K key, uint64_t salt)
+{
+    uint64_t p = sizeof(K) == 8 ? kmer_low64(key) : (hash64(kmer_low64(key), salt) ^ kmer_high64(key));
+    return p == LB_EMPTY64 ? 0x5bd1e995ull : p;
+}
+
+// state of a P entry
+enum { ST_UNDECIDED = 0, ST_INSERTER = 1, ST_BLOCKED = 2, ST_NOCAND = 3 };
+
+template <typename K>
+__global__ void k_cand_build(const int32_t *__restrict__ cand_pos, const K *__restrict__ cand_key, uint32_t m, CandTable<K> t,
+                             uint64_t salt, uint32_t *cand_slot, uint8_t *state)
+{
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= m) return;
+    if (cand_pos[j] < 0) { state[j] = ST_NOCAND; cand_slot[j] = LB_EMPTY32; return; }
+    state[j] = ST_UNDECIDED;
+    K key = cand_key[j];
+    uint64_t px = cand_proxy(key, salt);
+    uint64_t s = hash64(px, 0x2545F4914F6CDD1DULL) & t.mask;
+    while (true) {
+        unsigned long long old = atomicCAS((unsigned long long *)&t.proxy[s], (unsigned long long)LB_EMPTY64, (unsigned long long)px);
+        if (old == LB_EMPTY64) { t.keys[s] = key; break; }
+        if (old == px) break;
+        s = (s + 1) & t.mask;
+    }
+    cand_slot[j] = (uint32_t)s;
+}
+
+// two different wide k-mers with the same proxy would share a slot: detected here, the build is redone with a new salt
+template <typename K>
+__global__ void k_cand_verify(const K *__restrict__ cand_key, const uint32_t *__restrict__ cand_slot, uint32_t m, CandTable<K> t,
+                              uint32_t *collision)
+{
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= m || cand_slot[j] == LB_EMPTY32) return;
+    if (t.keys[cand_slot[j]] != cand_key[j]) *collision = 1;
+}
+
+__global__ void k_round_fu(const uint8_t *__restrict__ state, const uint32_t *__restrict__ cand_slot, uint32_t m, uint32_t *fu)
+{
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= m || state[j] != ST_UNDECIDED) return;
+    atomicMin(&fu[cand_slot[j]], j);
+}
+
+template <typename K> struct DecideFn {
+    const CandTable<K> &t; int k; uint32_t j; uint64_t salt;
+    bool blocked, wait;
+    LB_D bool operator()(uint64_t, K kmer, bool active)
+    {
+        bool b = false, w = false;
+        if (active) {
+            K c = kmer_canon(kmer, k);
+            uint64_t px = cand_proxy(c, salt);
+            uint64_t s = hash64(px, 0x2545F4914F6CDD1DULL) & t.mask;
+            while (true) {
+                uint64_t q = t.proxy[s];
+                if (q == LB_EMPTY64) break;
+                if (q == px && t.keys[s] == c) {
+                    b = t.ins[s] < j;
+                    w = t.fu[s] < j;
+                    break;
+                }
+                s = (s + 1) & t.mask;
+            }
+        }
+        blocked |= __any_sync(0xffffffffu, b);
+        wait |= __any_sync(0xffffffffu, w);
+        return blocked;
+    }
+};
+
+template <typename K>
+__global__ void __launch_bounds__(256) k_round_decide(const uint8_t *__restrict__ bases, const uint64_t *__restrict__ offsets,
+                                                      const uint32_t *__restrict__ plist, uint32_t m, int k, CandTable<K> t,
+                                                      uint64_t salt, const uint32_t *__restrict__ cand_slot, uint8_t *state,
+                                                      uint32_t *remaining)
+{
+    const int lane = threadIdx.x & 31;
+    uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t j = warp; j < m; j += nwarps) {
+        if (state[j] != ST_UNDECIDED) continue;
+        uint64_t r = plist[j];
+        uint64_t o = offsets[r], L = offsets[r + 1] - o;
+        uint64_t n = L - k + 1;
+        DecideFn<K> f{t, k, j, salt, false, false};
+        warp_for_kmers<K>(bases + o, L, k, 0, n, lane, f);
+        if (lane == 0) {
+            if (f.blocked) state[j] = ST_BLOCKED;
+            else if (!f.wait) { state[j] = ST_INSERTER; atomicMin(&t.ins[cand_slot[j]], j); }
+            else atomicAdd(remaining, 1u);
+        }
+    }
+}
+
+struct InsIn {
+    const uint8_t *state;
+    __device__ uint32_t operator()(uint64_t j) const { return state[j] == ST_INSERTER ? 1u : 0u; }
+};
+template <typename K> struct InsOut {
+    const uint32_t *plist; const int32_t *cand_pos; const K *cand_key;
+    DictDev<K> d; uint32_t base_addr; K *anchors; int32_t *apos; uint32_t *aaddr; uint8_t *inserter;
+    __device__ void operator()(uint64_t j, uint32_t ex, uint32_t v) const
+    {
+        if (!v) return;
+        uint32_t r = plist[j];
+        uint32_t a = base_addr + ex;
+        K key = cand_key[j];
+        anchors[a] = key;
+        apos[r] = cand_pos[j];
+        aaddr[r] = a;
+        inserter[r] = 1;
+        uint64_t s = dict_hash(key) & d.mask;
+        while (atomicCAS(&d.time[s], LB_EMPTY32, r) != LB_EMPTY32) s = (s + 1) & d.mask;   // keys are distinct
+        d.keys[s] = key;
+        d.addr[s] = a;
+    }
+};
+
+// rehash into a larger dictionary
+template <typename K> __global__ void k_dict_rehash(DictDev<K> from, DictDev<K> to)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i > from.mask) return;
+    uint32_t t = from.time[i];
+    if (t == LB_EMPTY32) return;
+    K key = from.keys[i];
+    uint64_t s = dict_hash(key) & to.mask;
+    while (atomicCAS(&to.time[s], LB_EMPTY32, t) != LB_EMPTY32) s = (s + 1) & to.mask;
+    to.keys[s] = key;
+    to.addr[s] = from.addr[i];
+}
+
+}  // namespace lbanchor

@@ -1,0 +1,852 @@
+// libleon_b200.so — context, phase orchestration and the C ABI of include/leon_b200.h.
+// All compute is in the sm_100a kernels of count.cuh / bloom.cuh / anchors.cuh / walk.cuh / entropy.cuh; the host
+// only sizes buffers, runs the (exact, double precision) auto-cutoff of MI/impl/Histogram.cpp:62-195 and copies
+// results.  There is no CPU implementation of any kernel here: without a device every call fails.
+#include "common.cuh"
+#include "kmer_math.cuh"
+#include "scan.cuh"
+#include "count.cuh"
+#include "bloom.cuh"
+#include "anchors.cuh"
+#include "walk.cuh"
+#include "entropy.cuh"
+#include "simplehash_table.h"
+#include <string.h>
+#include <vector>
+#include <algorithm>
+
+namespace {
+
+constexpr int NUM_SMS = 148;
+
+// Histogram::compute_threshold (MI/impl/Histogram.cpp:62-195) with length 10000; min threshold forced to 4 by
+// Leon (C/Leon.cpp:456).  Pure host arithmetic on 10001 bins.
+void compute_threshold(const uint64_t *h, int min_auto_threshold, int32_t *cutoff_out, uint64_t *nbsolids_out)
+{
+    const size_t length = 10000;
+    std::vector<uint64_t> sm(length + 1, 0);
+    int cutoff = 0;
+    uint64_t nbsolids = 0, sum_allk = 0;
+    sm[1] = (uint64_t)(0.6 * (double)h[1] + 0.4 * (double)h[2]);
+    sum_allk += h[1];
+    int first_inc = -1, idx_max = -1;
+    uint64_t max_val = 0;
+    for (size_t i = 2; i < length; i++) {
+        sum_allk += h[i] * i;
+        sm[i] = (uint64_t)(0.2 * (double)h[i - 1] + 0.6 * (double)h[i] + 0.2 * (double)h[i + 1]);
+        if (first_inc == -1 && sm[i - 1] < sm[i]) first_inc = (int)i - 1;
+        if (first_inc > 0 && sm[i] > max_val) { max_val = sm[i]; idx_max = (int)i; }
+    }
+    sum_allk += h[length] * length;
+    if (first_inc == -1) { *cutoff_out = min_auto_threshold; *nbsolids_out = 0; return; }
+    uint64_t min_val = 10000000000ULL;
+    int idx_min = -1;
+    for (int i = first_inc; i <= idx_max; i++)
+        if (sm[i] < min_val) { min_val = sm[i]; idx_min = i; }
+    if (idx_min != -1) cutoff = idx_min;
+    uint64_t sum_elim = 0;
+    int max_cutoff = 0;
+    for (size_t i = 0; i < length + 1; i++) {
+        sum_elim += h[i] * i;
+        double ratio = (double)sum_elim / sum_allk;
+        if (ratio >= 0.25) { max_cutoff = (int)i + 1; break; }
+    }
+    if (cutoff > max_cutoff) cutoff = max_cutoff;
+    if (cutoff < min_auto_threshold) cutoff = min_auto_threshold;
+    for (size_t i = (size_t)cutoff; i < length + 1; i++) nbsolids += h[i];
+    *cutoff_out = cutoff;
+    *nbsolids_out = nbsolids;
+}
+
+enum Phase { PH_NONE = 0, PH_UPLOADED, PH_COUNTED, PH_BLOOM, PH_ENCODED };
+
+}  // namespace
+
+struct leon_ctx {
+    leon_opts opts;
+    std::string err;
+    cudaStream_t st = nullptr;
+    LaunchCounter lc;
+    Phase phase = PH_NONE;
+    leon_timings tm;
+    cudaEvent_t ev[16];
+    std::vector<uint64_t> qsizes;   // per-block size of the quality text (host)
+
+    // read set
+    uint64_t nreads = 0, nbases = 0, nkmers = 0;
+    DevBuf d_bases, d_offsets, d_quals, d_koff;
+    // counting
+    DevBuf d_keys, d_keys_alt, d_tile_hist, d_tile_off, d_scan, d_histo, d_stats, d_tbl;
+    void *sorted_keys = nullptr;     // points into d_keys or d_keys_alt
+    void *heads = nullptr;           // run heads live in the other one
+    uint64_t nruns = 0;
+    PinBuf h_histo, h_small;
+    leon_count_result cres;
+    int32_t min_abundance = 0;
+    // bloom
+    DevBuf d_bloom;
+    BloomDev bloom;
+    PinBuf h_bloom;
+    // anchors
+    DevBuf d_apos, d_aaddr, d_insflag, d_plist, d_cand_pos, d_cand_key, d_cand_slot, d_state;
+    DevBuf d_ct_proxy, d_ct_keys, d_ct_ins, d_ct_fu;
+    DevBuf d_dict_keys[2], d_dict_addr[2], d_dict_time[2];
+    int dict_cur = 0;
+    uint64_t dict_cap = 0, dict_count = 0;
+    DevBuf d_anchors, d_counters;
+    // walk + entropy
+    DevBuf d_bif, d_err, d_recs, d_symoff, d_tri, d_nsym, d_descs, d_outall, d_outsize, d_dnaoff, d_dna, d_bs, d_qout;
+    DevBuf d_dict_tri, d_dict_desc, d_dict_out, d_dict_size;
+    uint64_t nblocks = 0, dna_nbytes = 0, dict_nbytes = 0;
+    PinBuf h_dna, h_bs, h_dict, h_qual, h_qsizes, h_apos, h_aaddr;
+    uint64_t reads_without_anchor = 0;
+    int32_t min_len = 0, max_len = 0;
+};
+
+namespace {
+
+template <typename T> T fetch_scalar(leon_ctx *c, const T *dptr)
+{
+    c->h_small.reserve(256);
+    CUDA_TRY(cudaMemcpyAsync(c->h_small.p, dptr, sizeof(T), cudaMemcpyDeviceToHost, c->st));
+    CUDA_TRY(cudaStreamSynchronize(c->st));
+    T v;
+    memcpy(&v, c->h_small.p, sizeof(T));
+    return v;
+}
+
+unsigned warp_grid(uint64_t nwarps_wanted)
+{
+    uint64_t blocks = (nwarps_wanted + 7) / 8;
+    uint64_t cap = (uint64_t)NUM_SMS * 16;
+    if (blocks > cap) blocks = cap;
+    if (blocks == 0) blocks = 1;
+    return (unsigned)blocks;
+}
+
+void do_upload(leon_ctx *c, const leon_reads *rd)
+{
+    if (!rd || !rd->offsets || (rd->nreads && !rd->bases)) throw LeonError(LEON_E_ARG, "leon_upload: null read set");
+    if (rd->nreads >= 0xfffffff0ull) throw LeonError(LEON_E_ARG, "leon_upload: more than 2^32-16 reads in one set");
+    if (c->opts.has_qual && !rd->quals) throw LeonError(LEON_E_ARG, "leon_upload: has_qual set but quals is NULL");
+    c->nreads = rd->nreads;
+    c->nbases = rd->offsets[rd->nreads];
+    CUDA_TRY(cudaEventRecord(c->ev[0], c->st));
+    c->d_bases.reserve(c->nbases + 128);
+    c->d_offsets.reserve((c->nreads + 1) * 8);
+    CUDA_TRY(cudaMemcpyAsync(c->d_bases.p, rd->bases, c->nbases, cudaMemcpyHostToDevice, c->st));
+    CUDA_TRY(cudaMemcpyAsync(c->d_offsets.p, rd->offsets, (c->nreads + 1) * 8, cudaMemcpyHostToDevice, c->st));
+    if (c->opts.has_qual) {
+        c->d_quals.reserve(c->nbases + 128);
+        CUDA_TRY(cudaMemcpyAsync(c->d_quals.p, rd->quals, c->nbases, cudaMemcpyHostToDevice, c->st));
+    }
+    CUDA_TRY(cudaEventRecord(c->ev[1], c->st));
+    // min / max read length for the metadata datasets (host side, offsets are already here)
+    int32_t mn = 0x7fffffff, mx = 0;
+    for (uint64_t i = 0; i < rd->nreads; i++) {
+        uint64_t L = rd->offsets[i + 1] - rd->offsets[i];
+        if (L >= 0x7fffffffull) throw LeonError(LEON_E_ARG, "leon_upload: read longer than 2^31-1");
+        if ((int32_t)L < mn) mn = (int32_t)L;
+        if ((int32_t)L > mx) mx = (int32_t)L;
+    }
+    c->min_len = mn; c->max_len = mx;
+    // size of the quality text of every block: sum of (L + 1) over its reads (C/DnaCoder.cpp:428-459)
+    c->qsizes.clear();
+    if (c->opts.has_qual) {
+        uint64_t rpb = (uint64_t)c->opts.reads_per_block;
+        for (uint64_t r0 = 0; r0 < rd->nreads; r0 += rpb) {
+            uint64_t r1 = std::min(rd->nreads, r0 + rpb);
+            c->qsizes.push_back(rd->offsets[r1] - rd->offsets[r0] + (r1 - r0));
+        }
+    }
+    c->phase = PH_UPLOADED;
+}
+
+template <typename K> void do_count(leon_ctx *c)
+{
+    using namespace lbcount;
+    const int k = c->opts.kmer_size;
+    cudaStream_t st = c->st;
+    CUDA_TRY(cudaEventRecord(c->ev[2], st));
+    if (!c->d_tbl.p) {
+        c->d_tbl.reserve(256 * 8);
+        CUDA_TRY(cudaMemcpyAsync(c->d_tbl.p, kSimpleHashTable, 256 * 8, cudaMemcpyHostToDevice, st));
+    }
+    // k-mer slot offsets per read
+    c->d_koff.reserve((c->nreads + 1) * 8);
+    uint64_t *koff = c->d_koff.as<uint64_t>();
+    uint64_t *tot = lbscan::exclusive_scan<uint64_t>(c->nreads, NkIn{c->d_offsets.as<uint64_t>(), k}, NkOut{koff}, c->d_scan, st, c->lc);
+    uint64_t nk = c->nreads ? fetch_scalar(c, tot) : 0;
+    c->nkmers = nk;
+    CUDA_TRY(cudaMemcpyAsync(koff + c->nreads, &c->nkmers, 8, cudaMemcpyHostToDevice, st));
+
+    c->d_keys.reserve((nk + 1) * sizeof(K));
+    c->d_keys_alt.reserve((nk + 1) * (sizeof(K) > 8 ? sizeof(K) : 8));
+    K *keys = c->d_keys.as<K>(), *alt = c->d_keys_alt.as<K>();
+    if (nk) LB_LAUNCH(c->lc, (k_extract<K>), warp_grid(c->nreads), 256, 0, st, c->d_bases.as<uint8_t>(),
+                      c->d_offsets.as<uint64_t>(), koff, c->nreads, k, keys);
+    CUDA_TRY(cudaEventRecord(c->ev[3], st));
+
+    // LSD radix sort over the ceil(2k/8) low bytes (the sentinel is all ones, so it stays the maximum)
+    uint32_t ntiles = cdiv_u(nk, RS_TILE);
+    if (ntiles == 0) ntiles = 1;
+    c->d_tile_hist.reserve((uint64_t)ntiles * 256 * 4);
+    c->d_tile_off.reserve((uint64_t)ntiles * 256 * 8);
+    int passes = (2 * k + 7) / 8;
+    c->tm.sort_passes = 0;
+    cudaEvent_t pe0 = c->ev[13], pe1 = c->ev[14];
+    float pass_ms = 0;
+    for (int p = 0; p < passes && nk > 1; p++) {
+        int shift = 8 * p;
+        LB_LAUNCH(c->lc, (k_rs_hist<K>), ntiles, RS_THREADS, 0, st, keys, nk, shift, c->d_tile_hist.as<uint32_t>(), ntiles);
+        lbscan::exclusive_scan<uint64_t>((uint64_t)ntiles * 256, HistIn{c->d_tile_hist.as<uint32_t>()},
+                                         HistOut{c->d_tile_off.as<uint64_t>()}, c->d_scan, st, c->lc);
+        CUDA_TRY(cudaEventRecord(pe0, st));
+        LB_LAUNCH(c->lc, (k_rs_scatter<K>), ntiles, RS_THREADS, 0, st, keys, alt, nk, shift, c->d_tile_off.as<uint64_t>(), ntiles);
+        CUDA_TRY(cudaEventRecord(pe1, st));
+        if (p == passes - 1) {  // time one representative scatter pass without stalling the others
+            CUDA_TRY(cudaEventSynchronize(pe1));
+            CUDA_TRY(cudaEventElapsedTime(&pass_ms, pe0, pe1));
+        }
+        std::swap(keys, alt);
+        c->tm.sort_passes++;
+    }
+    c->tm.sort_pass_ms = pass_ms;
+    c->tm.sort_keys = nk;
+    c->sorted_keys = keys;
+    c->heads = alt;
+    CUDA_TRY(cudaEventRecord(c->ev[4], st));
+
+    // run heads -> abundance histogram
+    c->d_histo.reserve(10001 * 8);
+    c->d_stats.reserve(sizeof(CountStats));
+    CUDA_TRY(cudaMemsetAsync(c->d_histo.p, 0, 10001 * 8, st));
+    CUDA_TRY(cudaMemsetAsync(c->d_stats.p, 0, sizeof(CountStats), st));
+    c->nruns = 0;
+    CountStats stats = {0, 0, 0};
+    if (nk) {
+        uint64_t *tot_runs = lbscan::exclusive_scan<uint64_t>(nk, HeadIn64<K>{keys}, HeadOut64{(uint64_t *)alt}, c->d_scan, st, c->lc);
+        c->nruns = fetch_scalar(c, tot_runs);
+        unsigned grid = (unsigned)std::min<uint64_t>((c->nruns + 255) / 256, (uint64_t)NUM_SMS * 8);
+        if (grid == 0) grid = 1;
+        LB_LAUNCH(c->lc, (k_run_stats<K>), grid, 256, 10001 * 4, st, keys, (const uint64_t *)alt, c->nruns, nk,
+                  (unsigned long long *)c->d_histo.p, c->d_stats.as<CountStats>());
+        stats = fetch_scalar(c, c->d_stats.as<CountStats>());
+    }
+    c->h_histo.reserve(10001 * 8);
+    CUDA_TRY(cudaMemcpyAsync(c->h_histo.p, c->d_histo.p, 10001 * 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    CUDA_TRY(cudaEventRecord(c->ev[5], st));
+
+    leon_count_result &r = c->cres;
+    r.histogram = c->h_histo.as<uint64_t>();
+    r.nb_solid_total = stats.nb_solid_total;
+    r.nb_distinct = stats.nb_distinct;
+    r.nb_kmers = stats.nb_valid;
+    compute_threshold(r.histogram, 4, &r.cutoff, &r.nb_solids_cutoff);
+    c->phase = PH_COUNTED;
+}
+
+template <typename K> void do_bloom(leon_ctx *c)
+{
+    cudaStream_t st = c->st;
+    const leon_count_result &r = c->cres;
+    // C/Leon.cpp:247-335: auto cutoff unless -abundance was given; 12 bits per solid k-mer, 1000 if none
+    uint64_t nbs = c->opts.abundance_set ? r.nb_solid_total : r.nb_solids_cutoff;
+    c->min_abundance = c->opts.abundance_set ? 0 : r.cutoff;
+    uint64_t est = (uint64_t)((double)nbs * 12);
+    if (est == 0) est = 1000;
+    uint64_t tai = est + 2 * 4096;                 // COL/Bloom.hpp:438
+    uint64_t nbytes = 1 + tai / 8;                 // COL/Bloom.hpp:187
+    if (tai && !(tai & (tai - 1))) tai--;          // COL/Bloom.hpp:193-198
+    BloomDev &b = c->bloom;
+    b.reduced_tai = tai - 2 * 4096;                // COL/Bloom.hpp:441
+    b.magic = ~0ull / b.reduced_tai;
+    b.nbytes = nbytes;
+    b.k = c->opts.kmer_size;
+    uint64_t alloc = (nbytes + 3) / 4 * 4 + 64;
+    c->d_bloom.reserve(alloc);
+    b.words = c->d_bloom.as<uint32_t>();
+    CUDA_TRY(cudaMemsetAsync(b.words, 0, alloc, st));
+    if (c->nruns) {
+        unsigned grid = (unsigned)std::min<uint64_t>((c->nruns + 255) / 256, (uint64_t)NUM_SMS * 8);
+        LB_LAUNCH(c->lc, (lbbloom::k_insert_runs<K>), grid, 256, 0, st, (const K *)c->sorted_keys, (const uint64_t *)c->heads,
+                  c->nruns, c->nkmers, (uint32_t)c->min_abundance, b, c->d_tbl.as<uint64_t>());
+    }
+    CUDA_TRY(cudaEventRecord(c->ev[6], st));
+    c->phase = PH_BLOOM;
+}
+
+}  // namespace
+
+namespace {
+
+template <typename K> lbanchor::DictDev<K> dict_view(leon_ctx *c, int which)
+{
+    lbanchor::DictDev<K> d;
+    d.keys = c->d_dict_keys[which].as<K>();
+    d.addr = c->d_dict_addr[which].as<uint32_t>();
+    d.time = c->d_dict_time[which].as<uint32_t>();
+    d.mask = c->dict_cap - 1;
+    return d;
+}
+
+template <typename K> void dict_alloc(leon_ctx *c, int which, uint64_t cap)
+{
+    c->d_dict_keys[which].reserve(cap * sizeof(K));
+    c->d_dict_addr[which].reserve(cap * 4);
+    c->d_dict_time[which].reserve(cap * 4);
+    CUDA_TRY(cudaMemsetAsync(c->d_dict_time[which].p, 0xff, cap * 4, c->st));
+}
+
+template <typename K> void dict_ensure(leon_ctx *c, uint64_t want_entries)
+{
+    if (want_entries * 2 <= c->dict_cap) return;
+    uint64_t ncap = c->dict_cap;
+    while (want_entries * 2 > ncap) ncap *= 4;
+    lbanchor::DictDev<K> from = dict_view<K>(c, c->dict_cur);
+    int other = c->dict_cur ^ 1;
+    uint64_t old_cap = c->dict_cap;
+    c->dict_cap = ncap;
+    dict_alloc<K>(c, other, ncap);
+    lbanchor::DictDev<K> to = dict_view<K>(c, other);
+    LB_LAUNCH(c->lc, (lbanchor::k_dict_rehash<K>), cdiv_u(old_cap, 256), 256, 0, c->st, from, to);
+    c->dict_cur = other;
+}
+
+// Phase 3a: anchors for all reads, in ordered batches (see anchors.cuh)
+template <typename K> void do_anchors(leon_ctx *c)
+{
+    using namespace lbanchor;
+    cudaStream_t st = c->st;
+    const int k = c->opts.kmer_size;
+    const uint64_t R = c->nreads;
+    const uint8_t *bases = c->d_bases.as<uint8_t>();
+    const uint64_t *offsets = c->d_offsets.as<uint64_t>();
+
+    c->d_apos.reserve((R + 1) * 4);
+    c->d_aaddr.reserve((R + 1) * 4);
+    c->d_insflag.reserve(R + 1);
+    CUDA_TRY(cudaMemsetAsync(c->d_apos.p, 0xff, (R + 1) * 4, st));     // -1
+    CUDA_TRY(cudaMemsetAsync(c->d_aaddr.p, 0, (R + 1) * 4, st));
+    CUDA_TRY(cudaMemsetAsync(c->d_insflag.p, 0, R + 1, st));
+    int32_t *apos = c->d_apos.as<int32_t>();
+    uint32_t *aaddr = c->d_aaddr.as<uint32_t>();
+    uint8_t *insflag = c->d_insflag.as<uint8_t>();
+    c->d_anchors.reserve((R + 1) * sizeof(K));
+    c->d_counters.reserve(64);
+    uint32_t *counters = c->d_counters.as<uint32_t>();   // [0] collision, [1] remaining
+    c->dict_cap = 1 << 16;
+    c->dict_cur = 0;
+    c->dict_count = 0;
+    dict_alloc<K>(c, 0, c->dict_cap);
+    c->tm.anchor_batches = 0;
+    c->tm.anchor_rounds = 0;
+
+    uint64_t S = c->opts.anchor_batch > 0 ? (uint64_t)c->opts.anchor_batch : 32768;
+    const bool adaptive = c->opts.anchor_batch <= 0;
+    for (uint64_t lo = 0; lo < R;) {
+        uint64_t hi = std::min(R, lo + S);
+        uint64_t nb = hi - lo;
+        c->tm.anchor_batches++;
+        // A: lookup against the dictionary of earlier batches
+        if (c->dict_count)
+            LB_LAUNCH(c->lc, (k_anchor_lookup<K>), warp_grid(nb), 256, 0, st, bases, offsets, lo, hi, k,
+                      dict_view<K>(c, c->dict_cur), apos, aaddr, (const uint8_t *)nullptr);
+        // P: no-hit reads in order
+        c->d_plist.reserve(nb * 4);
+        uint32_t *plist = c->d_plist.as<uint32_t>();
+        uint32_t *mtot = lbscan::exclusive_scan<uint32_t>(nb, PIn{offsets, apos, lo, k}, POut{plist, lo}, c->d_scan, st, c->lc);
+        uint32_t m = fetch_scalar(c, mtot);
+        uint32_t nins = 0;
+        if (m) {
+            c->d_cand_pos.reserve((uint64_t)m * 4);
+            c->d_cand_key.reserve((uint64_t)m * sizeof(K));
+            c->d_cand_slot.reserve((uint64_t)m * 4);
+            c->d_state.reserve(m);
+            int32_t *cand_pos = c->d_cand_pos.as<int32_t>();
+            K *cand_key = c->d_cand_key.as<K>();
+            uint32_t *cand_slot = c->d_cand_slot.as<uint32_t>();
+            uint8_t *state = c->d_state.as<uint8_t>();
+            LB_LAUNCH(c->lc, (k_candidates<K>), warp_grid(m), 256, 0, st, bases, offsets, plist, m, k, c->bloom,
+                      c->d_tbl.as<uint64_t>(), cand_pos, cand_key);
+            // table over candidate values
+            uint64_t tcap = 1024;
+            while (tcap < 2ull * m) tcap <<= 1;
+            c->d_ct_proxy.reserve(tcap * 8);
+            c->d_ct_keys.reserve(tcap * sizeof(K));
+            c->d_ct_ins.reserve(tcap * 4);
+            c->d_ct_fu.reserve(tcap * 4);
+            CandTable<K> t{c->d_ct_proxy.as<uint64_t>(), c->d_ct_keys.as<K>(), c->d_ct_ins.as<uint32_t>(),
+                           c->d_ct_fu.as<uint32_t>(), tcap - 1};
+            uint64_t salt = 0x1234567;
+            for (int attempt = 0;; attempt++) {
+                CUDA_TRY(cudaMemsetAsync(t.proxy, 0xff, tcap * 8, st));
+                CUDA_TRY(cudaMemsetAsync(t.ins, 0xff, tcap * 4, st));
+                LB_LAUNCH(c->lc, (k_cand_build<K>), cdiv_u(m, 256), 256, 0, st, cand_pos, cand_key, m, t, salt, cand_slot, state);
+                if (sizeof(K) == 8) break;
+                CUDA_TRY(cudaMemsetAsync(counters, 0, 4, st));
+                LB_LAUNCH(c->lc, (k_cand_verify<K>), cdiv_u(m, 256), 256, 0, st, cand_key, cand_slot, m, t, counters);
+                if (!fetch_scalar(c, counters)) break;
+                if (attempt > 8) throw LeonError(LEON_E_OVERFLOW, "anchor candidate table: repeated proxy collisions");
+                salt = salt * 6364136223846793005ULL + 1442695040888963407ULL;
+            }
+            // R: rounds of deterministic reservations
+            while (true) {
+                c->tm.anchor_rounds++;
+                CUDA_TRY(cudaMemsetAsync(t.fu, 0xff, tcap * 4, st));
+                CUDA_TRY(cudaMemsetAsync(counters + 1, 0, 4, st));
+                LB_LAUNCH(c->lc, k_round_fu, cdiv_u(m, 256), 256, 0, st, state, cand_slot, m, t.fu);
+                LB_LAUNCH(c->lc, (k_round_decide<K>), warp_grid(m), 256, 0, st, bases, offsets, plist, m, k, t, salt, cand_slot,
+                          state, counters + 1);
+                if (!fetch_scalar(c, counters + 1)) break;
+            }
+            // I: addresses in read order, insertion into D
+            dict_ensure<K>(c, c->dict_count + m);
+            InsOut<K> io{plist, cand_pos, cand_key, dict_view<K>(c, c->dict_cur), (uint32_t)c->dict_count,
+                         c->d_anchors.as<K>(), apos, aaddr, insflag};
+            uint32_t *itot = lbscan::exclusive_scan<uint32_t>(m, InsIn{state}, io, c->d_scan, st, c->lc);
+            nins = fetch_scalar(c, itot);
+            c->dict_count += nins;
+            // B: anchors of this batch can pre-empt later reads of the batch at earlier positions
+            if (nins)
+                LB_LAUNCH(c->lc, (k_anchor_lookup<K>), warp_grid(nb), 256, 0, st, bases, offsets, lo, hi, k,
+                          dict_view<K>(c, c->dict_cur), apos, aaddr, (const uint8_t *)insflag);
+        }
+        if (adaptive) {
+            if ((uint64_t)nins * 50 < nb && S < (1ull << 20)) S *= 2;
+        }
+        lo = hi;
+    }
+    CUDA_TRY(cudaEventRecord(c->ev[7], st));
+}
+
+__global__ void k_count_noanchor(const int32_t *__restrict__ apos, uint64_t n, unsigned long long *out)
+{
+    unsigned long long v = 0;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+        v += apos[i] < 0;
+    for (int d = 16; d; d >>= 1) v += __shfl_down_sync(0xffffffffu, v, d);
+    if ((threadIdx.x & 31) == 0 && v) atomicAdd(out, v);
+}
+
+template <typename K> void do_encode(leon_ctx *c)
+{
+    using namespace lbent;
+    cudaStream_t st = c->st;
+    const int k = c->opts.kmer_size;
+    const uint64_t R = c->nreads;
+    const uint32_t rpb = (uint32_t)c->opts.reads_per_block;
+    const uint8_t *bases = c->d_bases.as<uint8_t>();
+    const uint64_t *offsets = c->d_offsets.as<uint64_t>();
+    const uint64_t *koff = c->d_koff.as<uint64_t>();
+
+    do_anchors<K>(c);
+    int32_t *apos = c->d_apos.as<int32_t>();
+    uint32_t *aaddr = c->d_aaddr.as<uint32_t>();
+
+    c->d_err.reserve((c->nkmers + 1) * 4);
+    // qualities first: the smoothing pass borrows the error-position buffer as its prefix-count scratch
+    if (c->opts.has_qual) {
+        c->d_qout.reserve(c->nbases + R + 16);
+        if (R)
+            LB_LAUNCH(c->lc, (lbwalk::k_quals<K>), warp_grid(R), 256, 0, st, bases, c->d_quals.as<uint8_t>(), offsets, koff, R,
+                      c->bloom, c->d_tbl.as<uint64_t>(), c->opts.lossless, c->d_err.as<uint32_t>(), c->d_qout.as<uint8_t>());
+    }
+    CUDA_TRY(cudaEventRecord(c->ev[8], st));
+
+    // walk
+    c->d_bif.reserve(c->nkmers + 1);
+    c->d_recs.reserve((R + 1) * sizeof(lbwalk::ReadRec));
+    if (R)
+        LB_LAUNCH(c->lc, (lbwalk::k_walk<K>), warp_grid(R), 256, 0, st, bases, offsets, koff, R, c->bloom, c->d_tbl.as<uint64_t>(),
+                  apos, c->d_bif.as<uint8_t>(), c->d_err.as<uint32_t>(), c->d_recs.as<lbwalk::ReadRec>());
+    CUDA_TRY(cudaEventRecord(c->ev[9], st));
+
+    // per-block entropy coding
+    c->nblocks = R ? (R + rpb - 1) / rpb : 0;
+    c->dna_nbytes = 0;
+    c->d_counters.reserve(64);
+    uint32_t *ovf = c->d_counters.as<uint32_t>() + 2;
+    CUDA_TRY(cudaMemsetAsync(c->d_counters.p, 0, 64, st));
+    if (c->nblocks) {
+        c->d_symoff.reserve((R + 1) * 8);
+        uint64_t *symtot = lbscan::exclusive_scan<uint64_t>(R, SymBoundIn{offsets, apos, c->d_recs.as<ReadRec>()},
+                                                            SymBoundOut{c->d_symoff.as<uint64_t>()}, c->d_scan, st, c->lc);
+        uint64_t total_bound = fetch_scalar(c, symtot);
+        // the scan scratch is reused below, keep the total in the counters buffer
+        uint64_t *symtot_keep = (uint64_t *)(c->d_counters.as<uint8_t>() + 16);
+        CUDA_TRY(cudaMemcpyAsync(symtot_keep, &total_bound, 8, cudaMemcpyHostToDevice, st));
+        c->d_tri.reserve((total_bound + 1) * sizeof(uint4));
+        c->d_nsym.reserve(c->nblocks * 8);
+        c->d_descs.reserve(c->nblocks * sizeof(StreamDesc));
+        c->d_outall.reserve(2 * total_bound + 16 * c->nblocks + 16);
+        c->d_outsize.reserve(c->nblocks * 8);
+        c->d_dnaoff.reserve(c->nblocks * 8);
+        c->d_bs.reserve(c->nblocks * 16);
+        LB_LAUNCH(c->lc, k_model_scan, (unsigned)c->nblocks, 32, 0, st, bases, offsets, koff, R, rpb, apos, aaddr,
+                  c->d_recs.as<ReadRec>(), c->d_bif.as<uint8_t>(), c->d_err.as<uint32_t>(), c->d_symoff.as<uint64_t>(),
+                  c->d_tri.as<uint4>(), c->d_nsym.as<uint64_t>());
+        LB_LAUNCH(c->lc, k_block_descs, cdiv_u(c->nblocks, 128), 128, 0, st, c->d_symoff.as<uint64_t>(), symtot_keep,
+                  c->d_nsym.as<uint64_t>(), R, rpb, c->nblocks, c->d_descs.as<StreamDesc>());
+        LB_LAUNCH(c->lc, k_range_encode, (unsigned)c->nblocks, 32, 0, st, c->d_tri.as<uint4>(), c->d_descs.as<StreamDesc>(),
+                  c->d_outall.as<uint8_t>(), c->d_outsize.as<uint64_t>(), 0, ovf);
+        uint64_t *dtot = lbscan::exclusive_scan<uint64_t>(c->nblocks, SizeIn{c->d_outsize.as<uint64_t>()},
+                                                          SizeOut{c->d_dnaoff.as<uint64_t>()}, c->d_scan, st, c->lc);
+        c->dna_nbytes = fetch_scalar(c, dtot);
+        c->d_dna.reserve(c->dna_nbytes + 16);
+        LB_LAUNCH(c->lc, k_gather_streams, (unsigned)c->nblocks, 256, 0, st, c->d_outall.as<uint8_t>(), c->d_descs.as<StreamDesc>(),
+                  c->d_outsize.as<uint64_t>(), c->d_dnaoff.as<uint64_t>(), c->d_dna.as<uint8_t>());
+        LB_LAUNCH(c->lc, k_blocksizes, cdiv_u(c->nblocks, 128), 128, 0, st, c->d_outsize.as<uint64_t>(), R, rpb, c->nblocks,
+                  c->d_bs.as<uint64_t>());
+    }
+
+    // anchor dictionary stream: one coder over all anchors, flushed once (C/Leon.cpp:1034-1042,1245-1260)
+    {
+        uint64_t A = c->dict_count;
+        uint64_t nsym = A * (uint64_t)k;
+        if (nsym >= 0xffffff00ull) throw LeonError(LEON_E_OVERFLOW, "anchor dictionary stream longer than 2^32 symbols");
+        c->d_dict_tri.reserve((nsym + 1) * sizeof(uint4));
+        c->d_dict_desc.reserve(sizeof(StreamDesc));
+        c->d_dict_out.reserve(2 * nsym + 64);
+        c->d_dict_size.reserve(8);
+        if (A)
+            lbscan::exclusive_scan<lbscan::U32x4>(A, DictCountIn<K>{c->d_anchors.as<K>(), k},
+                                                  DictTriOut<K>{c->d_anchors.as<K>(), k, c->d_dict_tri.as<uint4>()}, c->d_scan, st, c->lc);
+        StreamDesc d{0, nsym, 0, 2 * nsym + 16};
+        CUDA_TRY(cudaMemcpyAsync(c->d_dict_desc.p, &d, sizeof d, cudaMemcpyHostToDevice, st));
+        LB_LAUNCH(c->lc, k_range_encode, 1, 32, 0, st, c->d_dict_tri.as<uint4>(), c->d_dict_desc.as<StreamDesc>(),
+                  c->d_dict_out.as<uint8_t>(), c->d_dict_size.as<uint64_t>(), 1, ovf);
+        c->dict_nbytes = fetch_scalar(c, c->d_dict_size.as<uint64_t>());
+    }
+    if (fetch_scalar(c, ovf)) throw LeonError(LEON_E_OVERFLOW, "range coder output exceeded its capacity bound");
+    {
+        unsigned long long *cnt = (unsigned long long *)(c->d_counters.as<uint8_t>() + 32);
+        if (R) LB_LAUNCH(c->lc, k_count_noanchor, (unsigned)std::min<uint64_t>((R + 255) / 256, 1024), 256, 0, st, apos, R, cnt);
+        c->reads_without_anchor = fetch_scalar(c, cnt);
+    }
+    CUDA_TRY(cudaEventRecord(c->ev[10], st));
+    c->phase = PH_ENCODED;
+}
+
+void do_fetch(leon_ctx *c, leon_result *out)
+{
+    cudaStream_t st = c->st;
+    const uint64_t R = c->nreads;
+    CUDA_TRY(cudaEventRecord(c->ev[11], st));
+    c->h_bloom.reserve(c->bloom.nbytes + 8);
+    CUDA_TRY(cudaMemcpyAsync(c->h_bloom.p, c->bloom.words, c->bloom.nbytes, cudaMemcpyDeviceToHost, st));
+    c->h_dict.reserve(c->dict_nbytes + 8);
+    CUDA_TRY(cudaMemcpyAsync(c->h_dict.p, c->d_dict_out.p, c->dict_nbytes, cudaMemcpyDeviceToHost, st));
+    c->h_dna.reserve(c->dna_nbytes + 8);
+    c->h_bs.reserve(c->nblocks * 16 + 8);
+    if (c->nblocks) {
+        CUDA_TRY(cudaMemcpyAsync(c->h_dna.p, c->d_dna.p, c->dna_nbytes, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaMemcpyAsync(c->h_bs.p, c->d_bs.p, c->nblocks * 16, cudaMemcpyDeviceToHost, st));
+    }
+    c->h_apos.reserve((R + 1) * 4);
+    c->h_aaddr.reserve((R + 1) * 4);
+    if (R) {
+        CUDA_TRY(cudaMemcpyAsync(c->h_apos.p, c->d_apos.p, R * 4, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaMemcpyAsync(c->h_aaddr.p, c->d_aaddr.p, R * 4, cudaMemcpyDeviceToHost, st));
+    }
+    uint64_t qbytes = 0;
+    c->h_qsizes.reserve(c->nblocks * 8 + 8);
+    if (c->opts.has_qual && R) {
+        qbytes = c->nbases + R;
+        c->h_qual.reserve(qbytes + 8);
+        CUDA_TRY(cudaMemcpyAsync(c->h_qual.p, c->d_qout.p, qbytes, cudaMemcpyDeviceToHost, st));
+    }
+    CUDA_TRY(cudaStreamSynchronize(st));
+    memset(out, 0, sizeof *out);
+    out->count = c->cres;
+    out->bloom = c->h_bloom.as<uint8_t>(); out->bloom_nbytes = c->bloom.nbytes; out->bloom_bits = c->bloom.reduced_tai;
+    out->anchors_dict = c->h_dict.as<uint8_t>(); out->anchors_dict_nbytes = c->dict_nbytes; out->anchor_count = c->dict_count;
+    out->nblocks = c->nblocks; out->blocksizes = c->h_bs.as<uint64_t>();
+    out->dna = c->h_dna.as<uint8_t>(); out->dna_nbytes = c->dna_nbytes;
+    out->qual_text = c->h_qual.as<uint8_t>(); out->qual_nbytes = qbytes; out->qual_block_sizes = c->h_qsizes.as<uint64_t>();
+    out->read_count = R; out->total_dna_size = c->nbases;
+    out->min_read_size = c->min_len; out->max_read_size = c->max_len;
+    out->anchor_pos = c->h_apos.as<int32_t>(); out->anchor_addr = c->h_aaddr.as<uint32_t>();
+    out->reads_without_anchor = c->reads_without_anchor;
+    if (c->opts.has_qual && !c->qsizes.empty()) memcpy(c->h_qsizes.p, c->qsizes.data(), c->qsizes.size() * 8);
+    CUDA_TRY(cudaEventRecord(c->ev[12], st));
+    CUDA_TRY(cudaEventSynchronize(c->ev[12]));
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------------------
+// C ABI
+// ------------------------------------------------------------------------------------------------------------
+static thread_local std::string g_create_error;
+
+#define LB_API_BEGIN try {
+#define LB_API_END(ctx)                                                      \
+    }                                                                        \
+    catch (const LeonError &e) { (ctx)->err = e.msg; return e.code; }        \
+    catch (const std::exception &e) { (ctx)->err = e.what(); return LEON_E_NOMEM; } \
+    return LEON_OK;
+
+#define LB_DISPATCH(ctx, fn)                                                  \
+    do {                                                                      \
+        if ((ctx)->opts.kmer_size <= 31) fn<uint64_t>(ctx); else fn<u128>(ctx); \
+    } while (0)
+
+static void fill_timings(leon_ctx *c)
+{
+    auto el = [&](int a, int b) { float ms = 0; if (cudaEventElapsedTime(&ms, c->ev[a], c->ev[b]) != cudaSuccess) { cudaGetLastError(); ms = 0; } return ms; };
+    c->tm.h2d_ms = el(0, 1);
+    c->tm.count_ms = el(2, 5);
+    c->tm.sort_ms = el(3, 4);
+    c->tm.bloom_ms = el(5, 6);
+    c->tm.anchor_ms = el(6, 7);
+    c->tm.qual_ms = el(7, 8);
+    c->tm.walk_ms = el(8, 9);
+    c->tm.entropy_ms = el(9, 10);
+    c->tm.d2h_ms = el(11, 12);
+    c->tm.total_ms = el(2, 10);
+    c->tm.kernel_launches = c->lc.n;
+}
+
+extern "C" {
+
+int leon_b200_abi_version(void) { return LEON_B200_ABI_VERSION; }
+
+int leon_create(const leon_opts *opts, leon_ctx **out)
+{
+    if (!opts || !out) { g_create_error = "leon_create: null argument"; return LEON_E_ARG; }
+    *out = nullptr;
+    if (opts->kmer_size < 2 || opts->kmer_size > 63) { g_create_error = "leon_create: kmer_size must be in [2,63]"; return LEON_E_ARG; }
+    if (opts->reads_per_block <= 0) { g_create_error = "leon_create: reads_per_block must be positive"; return LEON_E_ARG; }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        g_create_error = std::string("leon_create: no CUDA device (") + cudaGetErrorString(e) + "); there is no CPU fallback";
+        return LEON_E_CUDA;
+    }
+    if (opts->device < 0 || opts->device >= ndev) { g_create_error = "leon_create: bad device ordinal"; return LEON_E_ARG; }
+    leon_ctx *c = new (std::nothrow) leon_ctx();
+    if (!c) { g_create_error = "leon_create: out of memory"; return LEON_E_NOMEM; }
+    c->opts = *opts;
+    memset(&c->tm, 0, sizeof c->tm);
+    memset(&c->cres, 0, sizeof c->cres);
+    memset(&c->bloom, 0, sizeof c->bloom);
+    try {
+        CUDA_TRY(cudaSetDevice(opts->device));
+        CUDA_TRY(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
+        for (int i = 0; i < 16; i++) CUDA_TRY(cudaEventCreate(&c->ev[i]));
+        for (int i = 0; i < 16; i++) CUDA_TRY(cudaEventRecord(c->ev[i], c->st));
+    } catch (const LeonError &er) {
+        g_create_error = er.msg;
+        delete c;
+        return er.code;
+    }
+    *out = c;
+    return LEON_OK;
+}
+
+void leon_destroy(leon_ctx *c)
+{
+    if (!c) return;
+    cudaSetDevice(c->opts.device);
+    if (c->st) cudaStreamSynchronize(c->st);
+    DevBuf *dev[] = {&c->d_bases, &c->d_offsets, &c->d_quals, &c->d_koff, &c->d_keys, &c->d_keys_alt, &c->d_tile_hist, &c->d_tile_off,
+                     &c->d_scan, &c->d_histo, &c->d_stats, &c->d_tbl, &c->d_bloom, &c->d_apos, &c->d_aaddr, &c->d_insflag, &c->d_plist,
+                     &c->d_cand_pos, &c->d_cand_key, &c->d_cand_slot, &c->d_state, &c->d_ct_proxy, &c->d_ct_keys, &c->d_ct_ins,
+                     &c->d_ct_fu, &c->d_dict_keys[0], &c->d_dict_keys[1], &c->d_dict_addr[0], &c->d_dict_addr[1], &c->d_dict_time[0],
+                     &c->d_dict_time[1], &c->d_anchors, &c->d_counters, &c->d_bif, &c->d_err, &c->d_recs, &c->d_symoff, &c->d_tri,
+                     &c->d_nsym, &c->d_descs, &c->d_outall, &c->d_outsize, &c->d_dnaoff, &c->d_dna, &c->d_bs, &c->d_qout,
+                     &c->d_dict_tri, &c->d_dict_desc, &c->d_dict_out, &c->d_dict_size};
+    for (DevBuf *b : dev) b->release();
+    PinBuf *pin[] = {&c->h_histo, &c->h_small, &c->h_bloom, &c->h_dna, &c->h_bs, &c->h_dict, &c->h_qual, &c->h_qsizes, &c->h_apos, &c->h_aaddr};
+    for (PinBuf *b : pin) b->release();
+    for (int i = 0; i < 16; i++) cudaEventDestroy(c->ev[i]);
+    if (c->st) cudaStreamDestroy(c->st);
+    delete c;
+}
+
+const char *leon_last_error(const leon_ctx *c) { return c ? c->err.c_str() : g_create_error.c_str(); }
+
+void *leon_alloc_pinned(size_t nbytes)
+{
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, nbytes ? nbytes : 1, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+void leon_free_pinned(void *p) { if (p) cudaFreeHost(p); }
+
+int leon_upload(leon_ctx *c, const leon_reads *reads)
+{
+    if (!c) return LEON_E_ARG;
+    LB_API_BEGIN
+    CUDA_TRY(cudaSetDevice(c->opts.device));
+    do_upload(c, reads);
+    LB_API_END(c)
+}
+
+int leon_count(leon_ctx *c, leon_count_result *out)
+{
+    if (!c) return LEON_E_ARG;
+    LB_API_BEGIN
+    if (c->phase < PH_UPLOADED) throw LeonError(LEON_E_STATE, "leon_count: no read set uploaded");
+    CUDA_TRY(cudaSetDevice(c->opts.device));
+    LB_DISPATCH(c, do_count);
+    if (out) *out = c->cres;
+    LB_API_END(c)
+}
+
+int leon_bloom_build(leon_ctx *c, const uint8_t **bits, uint64_t *nbytes, uint64_t *reduced_bits)
+{
+    if (!c) return LEON_E_ARG;
+    LB_API_BEGIN
+    if (c->phase < PH_COUNTED) throw LeonError(LEON_E_STATE, "leon_bloom_build: leon_count has not run");
+    CUDA_TRY(cudaSetDevice(c->opts.device));
+    LB_DISPATCH(c, do_bloom);
+    if (bits) {
+        c->h_bloom.reserve(c->bloom.nbytes + 8);
+        CUDA_TRY(cudaMemcpyAsync(c->h_bloom.p, c->bloom.words, c->bloom.nbytes, cudaMemcpyDeviceToHost, c->st));
+        CUDA_TRY(cudaStreamSynchronize(c->st));
+        *bits = c->h_bloom.as<uint8_t>();
+    }
+    if (nbytes) *nbytes = c->bloom.nbytes;
+    if (reduced_bits) *reduced_bits = c->bloom.reduced_tai;
+    LB_API_END(c)
+}
+
+int leon_fetch(leon_ctx *c, leon_result *out)
+{
+    if (!c || !out) return LEON_E_ARG;
+    LB_API_BEGIN
+    if (c->phase < PH_ENCODED) throw LeonError(LEON_E_STATE, "leon_fetch: nothing encoded yet");
+    CUDA_TRY(cudaSetDevice(c->opts.device));
+    do_fetch(c, out);
+    fill_timings(c);
+    LB_API_END(c)
+}
+
+int leon_encode(leon_ctx *c, leon_result *out)
+{
+    if (!c) return LEON_E_ARG;
+    LB_API_BEGIN
+    if (c->phase < PH_BLOOM) throw LeonError(LEON_E_STATE, "leon_encode: leon_bloom_build has not run");
+    CUDA_TRY(cudaSetDevice(c->opts.device));
+    LB_DISPATCH(c, do_encode);
+    if (out) do_fetch(c, out);
+    fill_timings(c);
+    LB_API_END(c)
+}
+
+int leon_run_device(leon_ctx *c)
+{
+    if (!c) return LEON_E_ARG;
+    LB_API_BEGIN
+    if (c->phase < PH_UPLOADED) throw LeonError(LEON_E_STATE, "leon_run_device: no read set uploaded");
+    CUDA_TRY(cudaSetDevice(c->opts.device));
+    LB_DISPATCH(c, do_count);
+    LB_DISPATCH(c, do_bloom);
+    LB_DISPATCH(c, do_encode);
+    CUDA_TRY(cudaStreamSynchronize(c->st));
+    fill_timings(c);
+    LB_API_END(c)
+}
+
+int leon_compress(leon_ctx *c, const leon_reads *reads, leon_result *out)
+{
+    if (!c || !out) return LEON_E_ARG;
+    LB_API_BEGIN
+    CUDA_TRY(cudaSetDevice(c->opts.device));
+    do_upload(c, reads);
+    LB_DISPATCH(c, do_count);
+    LB_DISPATCH(c, do_bloom);
+    LB_DISPATCH(c, do_encode);
+    do_fetch(c, out);
+    fill_timings(c);
+    LB_API_END(c)
+}
+
+int leon_get_timings(const leon_ctx *c, leon_timings *out)
+{
+    if (!c || !out) return LEON_E_ARG;
+    *out = c->tm;
+    return LEON_OK;
+}
+
+int leon_debug_bloom_query(leon_ctx *c, const uint64_t *kmers, uint64_t n, int right, uint8_t *out4, uint8_t *out1)
+{
+    if (!c || !kmers || !out4 || !out1) return LEON_E_ARG;
+    LB_API_BEGIN
+    if (c->phase < PH_BLOOM) throw LeonError(LEON_E_STATE, "leon_debug_bloom_query: no Bloom filter built");
+    CUDA_TRY(cudaSetDevice(c->opts.device));
+    DevBuf dk, d4, d1;
+    dk.reserve(n * 16 + 16); d4.reserve(n + 16); d1.reserve(n + 16);
+    try {
+        CUDA_TRY(cudaMemcpyAsync(dk.p, kmers, n * 16, cudaMemcpyHostToDevice, c->st));
+        if (n) {
+            if (c->opts.kmer_size <= 31)
+                LB_LAUNCH(c->lc, (lbbloom::k_debug_query<uint64_t>), warp_grid(n), 256, 0, c->st, dk.as<uint64_t>(), n, right, c->bloom,
+                          c->d_tbl.as<uint64_t>(), d4.as<uint8_t>(), d1.as<uint8_t>());
+            else
+                LB_LAUNCH(c->lc, (lbbloom::k_debug_query<u128>), warp_grid(n), 256, 0, c->st, dk.as<uint64_t>(), n, right, c->bloom,
+                          c->d_tbl.as<uint64_t>(), d4.as<uint8_t>(), d1.as<uint8_t>());
+        }
+        CUDA_TRY(cudaMemcpyAsync(out4, d4.p, n, cudaMemcpyDeviceToHost, c->st));
+        CUDA_TRY(cudaMemcpyAsync(out1, d1.p, n, cudaMemcpyDeviceToHost, c->st));
+        CUDA_TRY(cudaStreamSynchronize(c->st));
+    } catch (...) { dk.release(); d4.release(); d1.release(); throw; }
+    dk.release(); d4.release(); d1.release();
+    LB_API_END(c)
+}
+
+int leon_debug_hashes(leon_ctx *c, const uint64_t *kmers, uint64_t n, uint64_t *out12)
+{
+    if (!c || !kmers || !out12) return LEON_E_ARG;
+    LB_API_BEGIN
+    if (c->phase < PH_BLOOM) throw LeonError(LEON_E_STATE, "leon_debug_hashes: no Bloom filter built");
+    CUDA_TRY(cudaSetDevice(c->opts.device));
+    DevBuf dk, d_o;
+    dk.reserve(n * 16 + 16); d_o.reserve(n * 96 + 16);
+    try {
+        CUDA_TRY(cudaMemcpyAsync(dk.p, kmers, n * 16, cudaMemcpyHostToDevice, c->st));
+        if (n) {
+            if (c->opts.kmer_size <= 31)
+                LB_LAUNCH(c->lc, (lbbloom::k_debug_hashes<uint64_t>), cdiv_u(n, 128), 128, 0, c->st, dk.as<uint64_t>(), n, c->bloom,
+                          c->d_tbl.as<uint64_t>(), d_o.as<uint64_t>());
+            else
+                LB_LAUNCH(c->lc, (lbbloom::k_debug_hashes<u128>), cdiv_u(n, 128), 128, 0, c->st, dk.as<uint64_t>(), n, c->bloom,
+                          c->d_tbl.as<uint64_t>(), d_o.as<uint64_t>());
+        }
+        CUDA_TRY(cudaMemcpyAsync(out12, d_o.p, n * 96, cudaMemcpyDeviceToHost, c->st));
+        CUDA_TRY(cudaStreamSynchronize(c->st));
+    } catch (...) { dk.release(); d_o.release(); throw; }
+    dk.release(); d_o.release();
+    LB_API_END(c)
+}
+
+int leon_debug_fetch(leon_ctx *c, const char *name, void *dst, uint64_t cap, uint64_t *nbytes)
+{
+    if (!c || !name || !nbytes) return LEON_E_ARG;
+    LB_API_BEGIN
+    CUDA_TRY(cudaSetDevice(c->opts.device));
+    const void *src = nullptr;
+    uint64_t n = 0;
+    std::string s(name);
+    size_t ksz = c->opts.kmer_size <= 31 ? 8 : 16;
+    if (s == "sorted_keys") { src = c->sorted_keys; n = c->nkmers * ksz; }
+    else if (s == "anchors") { src = c->d_anchors.p; n = c->dict_count * ksz; }
+    else if (s == "recs") { src = c->d_recs.p; n = c->nreads * sizeof(lbwalk::ReadRec); }
+    else if (s == "koff") { src = c->d_koff.p; n = (c->nreads + 1) * 8; }
+    else if (s == "bif") { src = c->d_bif.p; n = c->nkmers; }
+    else if (s == "err") { src = c->d_err.p; n = c->nkmers * 4; }
+    else if (s == "nsym") { src = c->d_nsym.p; n = c->nblocks * 8; }
+    else throw LeonError(LEON_E_ARG, "leon_debug_fetch: unknown buffer name " + s);
+    *nbytes = n;
+    if (dst && src) {
+        if (cap < n) throw LeonError(LEON_E_ARG, "leon_debug_fetch: destination too small");
+        CUDA_TRY(cudaMemcpyAsync(dst, src, n, cudaMemcpyDeviceToHost, c->st));
+        CUDA_TRY(cudaStreamSynchronize(c->st));
+    }
+    LB_API_END(c)
+}
+
+}  // extern "C"

@@ -1,0 +1,162 @@
+"""GPU parity tests (run with -m gpu on a B200): the CUDA path, called through the C ABI, must reproduce the
+reference byte for byte — against the committed golden fixtures (outputs of the compiled reference) and against the
+oracle on seeded inputs — plus size-independent properties at larger sizes."""
+import numpy as np
+import pytest
+
+from golden_util import case_names, load_case
+
+pytestmark = pytest.mark.gpu
+
+
+def _engine(c=None, **kw):
+    import leon_b200
+    if c is not None:
+        kw = dict(kmer_size=c["k"], reads_per_block=c["rpb"], lossless=c["lossless"],
+                  abundance=3 if c["abundance_set"] else None, has_qual=c["has_qual"], **kw)
+    return leon_b200.Leon(**kw)
+
+
+def _same(r, ref, has_qual):
+    for key in ("cutoff", "nb_solids_cutoff", "nb_solid_total", "bloom_bits", "anchor_count", "read_count",
+                "total_dna_size", "reads_without_anchor"):
+        assert r[key] == ref[key], key
+    for key in ("histogram", "bloom", "anchors_dict", "blocksizes", "dna", "anchor_pos"):
+        assert np.array_equal(r[key], ref[key]), key
+    am = ref["anchor_pos"] >= 0
+    assert np.array_equal(r["anchor_addr"][am], ref["anchor_addr"][am])
+    if has_qual:
+        assert np.array_equal(r["qual_text"], ref["qual_text"])
+        assert np.array_equal(r["qual_block_sizes"], ref["qual_block_sizes"])
+
+
+@pytest.mark.parametrize("name", case_names())
+def test_golden_reference_bytes(name):
+    """CUDA output == datasets of the .leon file the compiled reference wrote with -nb-cores 1."""
+    c = load_case(name)
+    eng = _engine(c)
+    r = eng.compress(c["bases"], c["offsets"], c["quals"] if c["has_qual"] else None)
+    eng.close()
+    if c["auto_cutoff"]:
+        assert r["cutoff"] == int(c["cutoff"]) and r["nb_solids_cutoff"] == int(c["nb_solid"])
+    else:
+        assert r["nb_solid_total"] == int(c["nb_solid"])
+    assert r["bloom_bits"] == int(c["bloom_bits"])
+    assert np.array_equal(r["bloom"], c["bloom"])
+    assert r["anchor_count"] == int(c["anchor_count"])
+    assert np.array_equal(r["anchors_dict"], c["anchors_dict"])
+    assert np.array_equal(r["blocksizes"], c["blocksizes"])
+    assert np.array_equal(r["dna"], c["dna_concat"])
+    if c["has_qual"]:
+        assert np.array_equal(r["qual_block_sizes"], c["qual_text_sizes"])
+        assert np.array_equal(r["qual_text"], c["qual_text_concat"])
+    assert r["read_count"] == int(c["meta_readcount"]) and r["total_dna_size"] == int(c["meta_totalDnaSize"])
+    assert r["min_read_size"] == int(c["meta_minSequenceSize"]) and r["max_read_size"] == int(c["meta_maxSequenceSize"])
+
+
+@pytest.mark.parametrize("name,batch", [("fa_k31_blocks", 64), ("fa_k31_blocks", 1000), ("fa_k31_edge", 37),
+                                        ("fq_k31_lossy", 501), ("fa_k63", 128), ("fa_k31_lowcov", 256)])
+def test_anchor_batching_is_invisible(name, batch):
+    """Anchor resolution must equal the serial reference whatever the batch size."""
+    from oracle import oracle_py as O
+    c = load_case(name)
+    ref = O.compress(c["bases"], c["offsets"], c["quals"] if c["has_qual"] else None, kmer_size=c["k"],
+                     reads_per_block=c["rpb"], lossless=c["lossless"], abundance_set=c["abundance_set"])
+    eng = _engine(c, anchor_batch=batch)
+    r = eng.compress(c["bases"], c["offsets"], c["quals"] if c["has_qual"] else None)
+    eng.close()
+    _same(r, ref, c["has_qual"])
+
+
+@pytest.mark.parametrize("k,L,fastq,seed", [(31, 100, False, 1), (31, 150, True, 2), (25, 76, False, 3), (63, 150, False, 4),
+                                            (40, 101, True, 5)])
+def test_oracle_parity_seeded(k, L, fastq, seed):
+    """Seeded synthetic sets of the BASELINE shape (reduced), several blocks, vs the oracle."""
+    from oracle import oracle_py as O
+    from leon_b200 import synth
+    g = synth.make_genome(60000, seed)
+    bases, offs, quals = synth.sample_reads(g, 40000, L, seed + 100, n_rate=0.0005, with_quals=fastq)
+    ref = O.compress(bases, offs, quals, kmer_size=k, reads_per_block=7000)
+    eng = _engine(kmer_size=k, reads_per_block=7000, has_qual=fastq)
+    r = eng.compress(bases, offs, quals)
+    eng.close()
+    _same(r, ref, fastq)
+
+
+def test_bloom_queries_match_oracle():
+    """contains() and contains4() of the device filter == BloomNeighborCoherent restated, on real and random k-mers."""
+    import ctypes as C
+    from oracle import oracle_py as O
+    for name in ("fa_k31_blocks", "fa_k63"):
+        c = load_case(name)
+        k = c["k"]
+        eng = _engine(c)
+        eng.upload(c["bases"], c["offsets"])
+        eng.count()
+        bloom, bits = eng.bloom_build()
+        assert np.array_equal(bloom, c["bloom"])
+        L = O.lib()
+        b = O.Bloom()
+        assert L.lo_bloom_init(C.byref(b), bits, k, 7) == 0   # bits = reduced size: same geometry
+        assert b.nbytes == len(bloom)
+        C.memmove(b.bits, bloom.ctypes.data, len(bloom))
+        rng = np.random.default_rng(7)
+        vals = []
+        s = c["bases"]
+        for _ in range(1500):   # k-mers taken from reads (mostly present) ...
+            p = int(rng.integers(0, len(s) - k))
+            w = bytes(s[p:p + k]).replace(b"N", b"A")
+            vals.append(O.from_u128(L.lo_encode_kmer(w, k)))
+        for _ in range(1500):   # ... and random ones (mostly absent)
+            vals.append(int.from_bytes(rng.bytes(16), "little") & ((1 << (2 * k)) - 1))
+        km = np.array([[v & (2**64 - 1), v >> 64] for v in vals], np.uint64)
+        for right in (0, 1):
+            o4, o1 = eng.debug_bloom_query(km, right)
+            for i, v in enumerate(vals):
+                assert int(o4[i]) == L.lo_bloom_contains4(C.byref(b), O.u128(v), right)
+                rc = O.from_u128(L.lo_revcomp(O.u128(v), k))
+                assert int(o1[i]) == (1 if L.lo_bloom_contains(C.byref(b), O.u128(min(v, rc))) else 0)
+        L.lo_bloom_free(C.byref(b))
+        eng.close()
+
+
+def test_edge_inputs():
+    """Empty set, reads shorter than k, all-N reads, a single read: same bytes as the oracle, no faults."""
+    from oracle import oracle_py as O
+    cases = []
+    cases.append((np.zeros(0, np.uint8), np.zeros(1, np.uint64)))
+    short = np.frombuffer(b"ACGTACGTAC" * 3, np.uint8)
+    cases.append((np.concatenate([short[:10], short[:30], short[:5]]), np.array([0, 10, 40, 45], np.uint64)))
+    cases.append((np.frombuffer(b"N" * 80 + b"ACGT" * 20, np.uint8).copy(), np.array([0, 80, 160], np.uint64)))
+    one = np.frombuffer(b"GATTACAGATTACAGGATCCGATTACATTTAGGACCAGATTACAGATTACAGGATCCGATTACATTTAGGACCA", np.uint8)
+    cases.append((one.copy(), np.array([0, len(one)], np.uint64)))
+    for bases, offs in cases:
+        ref = O.compress(bases, offs, None, kmer_size=31, reads_per_block=2)
+        eng = _engine(kmer_size=31, reads_per_block=2)
+        r = eng.compress(bases, offs)
+        eng.close()
+        _same(r, ref, False)
+
+
+def test_properties_full_shape_reduced_count():
+    """Size-independent properties on a BASELINE-config-2-shaped set too large for byte goldens: block table sums,
+    anchors are Bloom-positive canonical k-mers of their read, and the result is reproducible."""
+    from leon_b200 import synth
+    g = synth.make_genome(1_000_000, 9)
+    bases, offs, _ = synth.sample_reads(g, 300_000, 100, 10)
+    eng = _engine(kmer_size=31, reads_per_block=50000)
+    r1 = eng.compress(bases, offs)
+    r2 = eng.compress(bases, offs)
+    assert r1["nblocks"] == 6
+    assert int(r1["blocksizes"][0::2].sum()) == len(r1["dna"])
+    assert int(r1["blocksizes"][1::2].sum()) == 300_000
+    for key in ("bloom", "anchors_dict", "dna", "blocksizes", "anchor_pos", "anchor_addr"):
+        assert np.array_equal(r1[key], r2[key]), key
+    assert r1["anchor_addr"][r1["anchor_pos"] >= 0].max() == r1["anchor_count"] - 1
+    # addresses are handed out in read order: the first read using address a comes before the first using a+1
+    am = r1["anchor_pos"] >= 0
+    first_use = np.full(r1["anchor_count"], len(am), np.int64)
+    idx = np.nonzero(am)[0]
+    np.minimum.at(first_use, r1["anchor_addr"][am], idx)
+    assert np.all(np.diff(first_use) > 0)
+    eng.close()
