@@ -128,6 +128,19 @@ int leon_fetch(leon_ctx *ctx, leon_result *out);
 
 int leon_get_timings(const leon_ctx *ctx, leon_timings *out);
 
+/* Device time of the main kernels of the last run (CUDA events on the context's stream around each launch). */
+typedef struct leon_kernel_time {
+    char     name[32];
+    float    ms_total;
+    uint32_t launches;
+} leon_kernel_time;
+int leon_get_kernel_times(const leon_ctx *ctx, leon_kernel_time *out, int cap, int *n);
+
+/* Makes the context launch on the caller's CUDA stream (a cudaStream_t; e.g. the host framework's current stream)
+ * instead of its own, so that the caller's events bracket the work.  The reference has no equivalent: its
+ * Dispatcher owns its threads (DP/impl/Command.cpp:119). */
+int leon_set_stream(leon_ctx *ctx, void *stream);
+
 /* Test hooks (parity tests only): Bloom queries on the device filter for host-provided forward k-mers.
  * kmers: n x (lo, hi) u64 pairs.  out4[i] = BloomNeighborCoherent::contains4 mask (COL Bloom.hpp:645-798),
  * out1[i] = contains() of the canonical form (Bloom.hpp:597-642). */

@@ -10,7 +10,7 @@ LIB_PATH = os.path.join(HERE, "libleon_b200.so")
 ABI_SYMBOLS = [
     "leon_b200_abi_version", "leon_create", "leon_destroy", "leon_last_error", "leon_alloc_pinned", "leon_free_pinned",
     "leon_compress", "leon_upload", "leon_count", "leon_bloom_build", "leon_encode", "leon_run_device", "leon_fetch",
-    "leon_get_timings", "leon_debug_bloom_query", "leon_debug_hashes", "leon_debug_fetch",
+    "leon_get_timings", "leon_get_kernel_times", "leon_set_stream", "leon_debug_bloom_query", "leon_debug_hashes", "leon_debug_fetch",
 ]
 
 
@@ -57,6 +57,10 @@ class Timings(C.Structure):
                 ("reserved", C.c_float * 6)]
 
 
+class KernelTime(C.Structure):
+    _fields_ = [("name", C.c_char * 32), ("ms_total", C.c_float), ("launches", C.c_uint32)]
+
+
 _lib = None
 
 
@@ -83,6 +87,8 @@ def load_library(path=LIB_PATH):
     L.leon_run_device.argtypes = [C.c_void_p]
     L.leon_fetch.argtypes = [C.c_void_p, C.POINTER(Result)]
     L.leon_get_timings.argtypes = [C.c_void_p, C.POINTER(Timings)]
+    L.leon_get_kernel_times.argtypes = [C.c_void_p, C.POINTER(KernelTime), C.c_int, C.POINTER(C.c_int)]
+    L.leon_set_stream.argtypes = [C.c_void_p, C.c_void_p]
     L.leon_debug_bloom_query.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.c_void_p]
     L.leon_debug_hashes.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
     L.leon_debug_fetch.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
@@ -219,6 +225,16 @@ class Leon:
         t = Timings()
         self._check(self.L.leon_get_timings(self.ctx, C.byref(t)))
         return {n: getattr(t, n) for n, _ in Timings._fields_ if n != "reserved"}
+
+    def kernel_times(self):
+        """{kernel name: (total ms, launches)} of the last run."""
+        arr = (KernelTime * 64)()
+        n = C.c_int()
+        self._check(self.L.leon_get_kernel_times(self.ctx, arr, 64, C.byref(n)))
+        return {arr[i].name.decode(): (float(arr[i].ms_total), int(arr[i].launches)) for i in range(min(n.value, 64))}
+
+    def set_stream(self, cuda_stream_ptr):
+        self._check(self.L.leon_set_stream(self.ctx, C.c_void_p(cuda_stream_ptr)))
 
     def debug_bloom_query(self, kmers_lo_hi, right):
         k = np.ascontiguousarray(kmers_lo_hi, np.uint64).reshape(-1, 2)

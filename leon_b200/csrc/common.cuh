@@ -5,6 +5,8 @@
 #include <stdio.h>
 #include <string>
 #include <stdexcept>
+#include <vector>
+#include <string.h>
 #include "../../include/leon_b200.h"
 
 struct LeonError {
@@ -63,5 +65,71 @@ struct PinBuf {
     void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
     template <typename T> T *as() const { return (T *)p; }
 };
+
+// Per-kernel device time, CUDA events on the launching stream around selected launches.  Slots are named after
+// the kernel; leon_get_kernel_times() reports total ms and launch count per slot for the last run.
+struct KernelTimer {
+    struct Slot { const char *name; double ms; uint32_t n; };
+    struct Pending { int slot; cudaEvent_t a, b; };
+    std::vector<Slot> slots;
+    std::vector<Pending> pending;
+    std::vector<cudaEvent_t> pool;
+    bool enabled = true;
+    int slot_of(const char *name)
+    {
+        for (size_t i = 0; i < slots.size(); i++) if (slots[i].name == name || !strcmp(slots[i].name, name)) return (int)i;
+        slots.push_back(Slot{name, 0.0, 0});
+        return (int)slots.size() - 1;
+    }
+    cudaEvent_t get()
+    {
+        if (!pool.empty()) { cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
+        cudaEvent_t e;
+        CUDA_TRY(cudaEventCreate(&e));
+        return e;
+    }
+    cudaEvent_t begin(cudaStream_t st)
+    {
+        cudaEvent_t a = get();
+        CUDA_TRY(cudaEventRecord(a, st));
+        return a;
+    }
+    void end(const char *name, cudaEvent_t a, cudaStream_t st)
+    {
+        cudaEvent_t b = get();
+        CUDA_TRY(cudaEventRecord(b, st));
+        pending.push_back(Pending{slot_of(name), a, b});
+    }
+    void reset()
+    {
+        for (auto &p : pending) { pool.push_back(p.a); pool.push_back(p.b); }
+        pending.clear();
+        slots.clear();
+    }
+    void resolve()   // after the stream has been synchronised
+    {
+        for (auto &p : pending) {
+            float ms = 0;
+            if (cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess) { slots[p.slot].ms += ms; slots[p.slot].n++; }
+            else cudaGetLastError();
+            pool.push_back(p.a); pool.push_back(p.b);
+        }
+        pending.clear();
+    }
+    void release()
+    {
+        reset();
+        for (cudaEvent_t e : pool) cudaEventDestroy(e);
+        pool.clear();
+    }
+};
+#define LB_TIMED(timer, name, stream, ...)                                           \
+    do {                                                                             \
+        if ((timer).enabled) {                                                       \
+            cudaEvent_t _ta = (timer).begin(stream);                                 \
+            __VA_ARGS__;                                                             \
+            (timer).end(name, _ta, stream);                                          \
+        } else { __VA_ARGS__; }                                                      \
+    } while (0)
 
 static inline unsigned cdiv_u(uint64_t a, uint64_t b) { return (unsigned)((a + b - 1) / b); }

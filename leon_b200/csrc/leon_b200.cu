@@ -67,6 +67,8 @@ struct leon_ctx {
     std::string err;
     cudaStream_t st = nullptr;
     LaunchCounter lc;
+    KernelTimer kt;
+    bool own_stream = true;
     Phase phase = PH_NONE;
     leon_timings tm;
     cudaEvent_t ev[16];
@@ -167,6 +169,7 @@ template <typename K> void do_count(leon_ctx *c)
     using namespace lbcount;
     const int k = c->opts.kmer_size;
     cudaStream_t st = c->st;
+    c->kt.reset();
     CUDA_TRY(cudaEventRecord(c->ev[2], st));
     if (!c->d_tbl.p) {
         c->d_tbl.reserve(256 * 8);
@@ -183,8 +186,8 @@ template <typename K> void do_count(leon_ctx *c)
     c->d_keys.reserve((nk + 1) * sizeof(K));
     c->d_keys_alt.reserve((nk + 1) * (sizeof(K) > 8 ? sizeof(K) : 8));
     K *keys = c->d_keys.as<K>(), *alt = c->d_keys_alt.as<K>();
-    if (nk) LB_LAUNCH(c->lc, (k_extract<K>), warp_grid(c->nreads), 256, 0, st, c->d_bases.as<uint8_t>(),
-                      c->d_offsets.as<uint64_t>(), koff, c->nreads, k, keys);
+    if (nk) LB_TIMED(c->kt, "k_extract", st, LB_LAUNCH(c->lc, (k_extract<K>), warp_grid(c->nreads), 256, 0, st, c->d_bases.as<uint8_t>(),
+                      c->d_offsets.as<uint64_t>(), koff, c->nreads, k, keys));
     CUDA_TRY(cudaEventRecord(c->ev[3], st));
 
     // LSD radix sort over the ceil(2k/8) low bytes (the sentinel is all ones, so it stays the maximum)
@@ -194,24 +197,15 @@ template <typename K> void do_count(leon_ctx *c)
     c->d_tile_off.reserve((uint64_t)ntiles * 256 * 8);
     int passes = (2 * k + 7) / 8;
     c->tm.sort_passes = 0;
-    cudaEvent_t pe0 = c->ev[13], pe1 = c->ev[14];
-    float pass_ms = 0;
     for (int p = 0; p < passes && nk > 1; p++) {
         int shift = 8 * p;
-        LB_LAUNCH(c->lc, (k_rs_hist<K>), ntiles, RS_THREADS, 0, st, keys, nk, shift, c->d_tile_hist.as<uint32_t>(), ntiles);
+        LB_TIMED(c->kt, "k_rs_hist", st, LB_LAUNCH(c->lc, (k_rs_hist<K>), ntiles, RS_THREADS, 0, st, keys, nk, shift, c->d_tile_hist.as<uint32_t>(), ntiles));
         lbscan::exclusive_scan<uint64_t>((uint64_t)ntiles * 256, HistIn{c->d_tile_hist.as<uint32_t>()},
                                          HistOut{c->d_tile_off.as<uint64_t>()}, c->d_scan, st, c->lc);
-        CUDA_TRY(cudaEventRecord(pe0, st));
-        LB_LAUNCH(c->lc, (k_rs_scatter<K>), ntiles, RS_THREADS, 0, st, keys, alt, nk, shift, c->d_tile_off.as<uint64_t>(), ntiles);
-        CUDA_TRY(cudaEventRecord(pe1, st));
-        if (p == passes - 1) {  // time one representative scatter pass without stalling the others
-            CUDA_TRY(cudaEventSynchronize(pe1));
-            CUDA_TRY(cudaEventElapsedTime(&pass_ms, pe0, pe1));
-        }
+        LB_TIMED(c->kt, "k_rs_scatter", st, LB_LAUNCH(c->lc, (k_rs_scatter<K>), ntiles, RS_THREADS, 0, st, keys, alt, nk, shift, c->d_tile_off.as<uint64_t>(), ntiles));
         std::swap(keys, alt);
         c->tm.sort_passes++;
     }
-    c->tm.sort_pass_ms = pass_ms;
     c->tm.sort_keys = nk;
     c->sorted_keys = keys;
     c->heads = alt;
@@ -229,8 +223,8 @@ template <typename K> void do_count(leon_ctx *c)
         c->nruns = fetch_scalar(c, tot_runs);
         unsigned grid = (unsigned)std::min<uint64_t>((c->nruns + 255) / 256, (uint64_t)NUM_SMS * 8);
         if (grid == 0) grid = 1;
-        LB_LAUNCH(c->lc, (k_run_stats<K>), grid, 256, 10001 * 4, st, keys, (const uint64_t *)alt, c->nruns, nk,
-                  (unsigned long long *)c->d_histo.p, c->d_stats.as<CountStats>());
+        LB_TIMED(c->kt, "k_run_stats", st, LB_LAUNCH(c->lc, (k_run_stats<K>), grid, 256, 10001 * 4, st, keys, (const uint64_t *)alt, c->nruns, nk,
+                  (unsigned long long *)c->d_histo.p, c->d_stats.as<CountStats>()));
         stats = fetch_scalar(c, c->d_stats.as<CountStats>());
     }
     c->h_histo.reserve(10001 * 8);
@@ -270,8 +264,8 @@ template <typename K> void do_bloom(leon_ctx *c)
     CUDA_TRY(cudaMemsetAsync(b.words, 0, alloc, st));
     if (c->nruns) {
         unsigned grid = (unsigned)std::min<uint64_t>((c->nruns + 255) / 256, (uint64_t)NUM_SMS * 8);
-        LB_LAUNCH(c->lc, (lbbloom::k_insert_runs<K>), grid, 256, 0, st, (const K *)c->sorted_keys, (const uint64_t *)c->heads,
-                  c->nruns, c->nkmers, (uint32_t)c->min_abundance, b, c->d_tbl.as<uint64_t>());
+        LB_TIMED(c->kt, "k_insert_runs", st, LB_LAUNCH(c->lc, (lbbloom::k_insert_runs<K>), grid, 256, 0, st, (const K *)c->sorted_keys, (const uint64_t *)c->heads,
+                  c->nruns, c->nkmers, (uint32_t)c->min_abundance, b, c->d_tbl.as<uint64_t>()));
     }
     CUDA_TRY(cudaEventRecord(c->ev[6], st));
     c->phase = PH_BLOOM;
@@ -450,8 +444,8 @@ template <typename K> void do_encode(leon_ctx *c)
     if (c->opts.has_qual) {
         c->d_qout.reserve(c->nbases + R + 16);
         if (R)
-            LB_LAUNCH(c->lc, (lbwalk::k_quals<K>), warp_grid(R), 256, 0, st, bases, c->d_quals.as<uint8_t>(), offsets, koff, R,
-                      c->bloom, c->d_tbl.as<uint64_t>(), c->opts.lossless, c->d_err.as<uint32_t>(), c->d_qout.as<uint8_t>());
+            LB_TIMED(c->kt, "k_quals", st, LB_LAUNCH(c->lc, (lbwalk::k_quals<K>), warp_grid(R), 256, 0, st, bases, c->d_quals.as<uint8_t>(), offsets, koff, R,
+                      c->bloom, c->d_tbl.as<uint64_t>(), c->opts.lossless, c->d_err.as<uint32_t>(), c->d_qout.as<uint8_t>()));
     }
     CUDA_TRY(cudaEventRecord(c->ev[8], st));
 
@@ -459,8 +453,8 @@ template <typename K> void do_encode(leon_ctx *c)
     c->d_bif.reserve(c->nkmers + 1);
     c->d_recs.reserve((R + 1) * sizeof(lbwalk::ReadRec));
     if (R)
-        LB_LAUNCH(c->lc, (lbwalk::k_walk<K>), warp_grid(R), 256, 0, st, bases, offsets, koff, R, c->bloom, c->d_tbl.as<uint64_t>(),
-                  apos, c->d_bif.as<uint8_t>(), c->d_err.as<uint32_t>(), c->d_recs.as<lbwalk::ReadRec>());
+        LB_TIMED(c->kt, "k_walk", st, LB_LAUNCH(c->lc, (lbwalk::k_walk<K>), warp_grid(R), 256, 0, st, bases, offsets, koff, R, c->bloom, c->d_tbl.as<uint64_t>(),
+                  apos, c->d_bif.as<uint8_t>(), c->d_err.as<uint32_t>(), c->d_recs.as<lbwalk::ReadRec>()));
     CUDA_TRY(cudaEventRecord(c->ev[9], st));
 
     // per-block entropy coding
@@ -484,13 +478,13 @@ template <typename K> void do_encode(leon_ctx *c)
         c->d_outsize.reserve(c->nblocks * 8);
         c->d_dnaoff.reserve(c->nblocks * 8);
         c->d_bs.reserve(c->nblocks * 16);
-        LB_LAUNCH(c->lc, k_model_scan, (unsigned)c->nblocks, 32, 0, st, bases, offsets, koff, R, rpb, apos, aaddr,
+        LB_TIMED(c->kt, "k_model_scan", st, LB_LAUNCH(c->lc, k_model_scan, (unsigned)c->nblocks, 32, 0, st, bases, offsets, koff, R, rpb, apos, aaddr,
                   c->d_recs.as<ReadRec>(), c->d_bif.as<uint8_t>(), c->d_err.as<uint32_t>(), c->d_symoff.as<uint64_t>(),
-                  c->d_tri.as<uint4>(), c->d_nsym.as<uint64_t>());
+                  c->d_tri.as<uint4>(), c->d_nsym.as<uint64_t>()));
         LB_LAUNCH(c->lc, k_block_descs, cdiv_u(c->nblocks, 128), 128, 0, st, c->d_symoff.as<uint64_t>(), symtot_keep,
                   c->d_nsym.as<uint64_t>(), R, rpb, c->nblocks, c->d_descs.as<StreamDesc>());
-        LB_LAUNCH(c->lc, k_range_encode, (unsigned)c->nblocks, 32, 0, st, c->d_tri.as<uint4>(), c->d_descs.as<StreamDesc>(),
-                  c->d_outall.as<uint8_t>(), c->d_outsize.as<uint64_t>(), 0, ovf);
+        LB_TIMED(c->kt, "k_range_encode", st, LB_LAUNCH(c->lc, k_range_encode, (unsigned)c->nblocks, 32, 0, st, c->d_tri.as<uint4>(), c->d_descs.as<StreamDesc>(),
+                  c->d_outall.as<uint8_t>(), c->d_outsize.as<uint64_t>(), 0, ovf));
         uint64_t *dtot = lbscan::exclusive_scan<uint64_t>(c->nblocks, SizeIn{c->d_outsize.as<uint64_t>()},
                                                           SizeOut{c->d_dnaoff.as<uint64_t>()}, c->d_scan, st, c->lc);
         c->dna_nbytes = fetch_scalar(c, dtot);
@@ -515,8 +509,8 @@ template <typename K> void do_encode(leon_ctx *c)
                                                   DictTriOut<K>{c->d_anchors.as<K>(), k, c->d_dict_tri.as<uint4>()}, c->d_scan, st, c->lc);
         StreamDesc d{0, nsym, 0, 2 * nsym + 16};
         CUDA_TRY(cudaMemcpyAsync(c->d_dict_desc.p, &d, sizeof d, cudaMemcpyHostToDevice, st));
-        LB_LAUNCH(c->lc, k_range_encode, 1, 32, 0, st, c->d_dict_tri.as<uint4>(), c->d_dict_desc.as<StreamDesc>(),
-                  c->d_dict_out.as<uint8_t>(), c->d_dict_size.as<uint64_t>(), 1, ovf);
+        LB_TIMED(c->kt, "k_range_encode_dict", st, LB_LAUNCH(c->lc, k_range_encode, 1, 32, 0, st, c->d_dict_tri.as<uint4>(), c->d_dict_desc.as<StreamDesc>(),
+                  c->d_dict_out.as<uint8_t>(), c->d_dict_size.as<uint64_t>(), 1, ovf));
         c->dict_nbytes = fetch_scalar(c, c->d_dict_size.as<uint64_t>());
     }
     if (fetch_scalar(c, ovf)) throw LeonError(LEON_E_OVERFLOW, "range coder output exceeded its capacity bound");
@@ -607,6 +601,10 @@ static void fill_timings(leon_ctx *c)
     c->tm.d2h_ms = el(11, 12);
     c->tm.total_ms = el(2, 10);
     c->tm.kernel_launches = c->lc.n;
+    c->kt.resolve();
+    c->tm.sort_pass_ms = 0;
+    for (auto &sl : c->kt.slots)
+        if (!strcmp(sl.name, "k_rs_scatter") && sl.n) c->tm.sort_pass_ms = (float)(sl.ms / sl.n);
 }
 
 extern "C" {
@@ -662,7 +660,8 @@ void leon_destroy(leon_ctx *c)
     PinBuf *pin[] = {&c->h_histo, &c->h_small, &c->h_bloom, &c->h_dna, &c->h_bs, &c->h_dict, &c->h_qual, &c->h_qsizes, &c->h_apos, &c->h_aaddr};
     for (PinBuf *b : pin) b->release();
     for (int i = 0; i < 16; i++) cudaEventDestroy(c->ev[i]);
-    if (c->st) cudaStreamDestroy(c->st);
+    c->kt.release();
+    if (c->st && c->own_stream) cudaStreamDestroy(c->st);
     delete c;
 }
 
@@ -769,6 +768,36 @@ int leon_get_timings(const leon_ctx *c, leon_timings *out)
 {
     if (!c || !out) return LEON_E_ARG;
     *out = c->tm;
+    return LEON_OK;
+}
+
+int leon_set_stream(leon_ctx *c, void *stream)
+{
+    if (!c) return LEON_E_ARG;
+    LB_API_BEGIN
+    CUDA_TRY(cudaSetDevice(c->opts.device));
+    CUDA_TRY(cudaStreamSynchronize(c->st));
+    if (c->own_stream && c->st) CUDA_TRY(cudaStreamDestroy(c->st));
+    c->st = (cudaStream_t)stream;
+    c->own_stream = false;
+    for (int i = 0; i < 16; i++) CUDA_TRY(cudaEventRecord(c->ev[i], c->st));
+    LB_API_END(c)
+}
+
+int leon_get_kernel_times(const leon_ctx *c, leon_kernel_time *out, int cap, int *n)
+{
+    if (!c || !n || (cap > 0 && !out)) return LEON_E_ARG;
+    int m = 0;
+    for (auto &sl : c->kt.slots) {
+        if (m < cap) {
+            memset(&out[m], 0, sizeof out[m]);
+            strncpy(out[m].name, sl.name, sizeof(out[m].name) - 1);
+            out[m].ms_total = (float)sl.ms;
+            out[m].launches = sl.n;
+        }
+        m++;
+    }
+    *n = m;
     return LEON_OK;
 }
 
