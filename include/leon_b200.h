@@ -41,7 +41,9 @@ typedef struct leon_opts {
     int32_t abundance_set;    /* -abundance X given: disables the auto cutoff (its value is unused) */
     int32_t device;           /* CUDA device ordinal */
     int32_t anchor_batch;     /* reads per anchor-resolution batch (0 = default); any value gives identical output */
-    int32_t reserved[9];
+    int32_t dict_on_device;   /* 1: run the serial low/range recurrence of the anchor dictionary dump (C/Leon.cpp:1245-1260) as a
+                                 single-warp kernel instead of on the host thread (same bytes, ~20x slower per step) */
+    int32_t reserved[8];
 } leon_opts;
 
 /* A set of reads: concatenated ASCII bases (upper-case ACGTN for reference parity) + R+1 offsets
@@ -97,7 +99,9 @@ typedef struct leon_timings {
     uint32_t anchor_batches, anchor_rounds;
     float sort_pass_ms;           /* average duration of one scatter pass of the counting sort */
     uint64_t sort_keys;           /* keys per pass */
-    float reserved[6];
+    float dict_host_ms;           /* wall time of the host thread coding the anchor dictionary (0 when on device) */
+    float dict_wait_ms;           /* how long the stream's work had been finished before that thread was */
+    float reserved[4];
 } leon_timings;
 
 typedef struct leon_ctx leon_ctx;

@@ -22,7 +22,8 @@ class LeonError(RuntimeError):
 
 class Opts(C.Structure):
     _fields_ = [("kmer_size", C.c_int32), ("reads_per_block", C.c_int32), ("has_qual", C.c_int32), ("lossless", C.c_int32),
-                ("abundance_set", C.c_int32), ("device", C.c_int32), ("anchor_batch", C.c_int32), ("reserved", C.c_int32 * 9)]
+                ("abundance_set", C.c_int32), ("device", C.c_int32), ("anchor_batch", C.c_int32), ("dict_on_device", C.c_int32),
+                ("reserved", C.c_int32 * 8)]
 
 
 class Reads(C.Structure):
@@ -54,7 +55,7 @@ class Timings(C.Structure):
                                          "entropy_ms", "d2h_ms", "total_ms")] + \
                [("kernel_launches", C.c_uint64), ("sort_passes", C.c_uint32), ("anchor_batches", C.c_uint32),
                 ("anchor_rounds", C.c_uint32), ("sort_pass_ms", C.c_float), ("sort_keys", C.c_uint64),
-                ("reserved", C.c_float * 6)]
+                ("dict_host_ms", C.c_float), ("dict_wait_ms", C.c_float), ("reserved", C.c_float * 4)]
 
 
 class KernelTime(C.Structure):
@@ -132,10 +133,10 @@ class Leon:
     """
 
     def __init__(self, kmer_size=31, reads_per_block=50000, lossless=False, abundance=None, has_qual=False, device=0,
-                 anchor_batch=0):
+                 anchor_batch=0, dict_on_device=False):
         self.L = load_library()
         self.opts = Opts(kmer_size, reads_per_block, int(has_qual), int(lossless), int(abundance is not None), device,
-                         anchor_batch)
+                         anchor_batch, int(dict_on_device))
         self.ctx = C.c_void_p()
         rc = self.L.leon_create(C.byref(self.opts), C.byref(self.ctx))
         if rc != 0:

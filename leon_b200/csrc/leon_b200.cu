@@ -14,6 +14,8 @@
 #include <string.h>
 #include <vector>
 #include <algorithm>
+#include <thread>
+#include <chrono>
 
 namespace {
 
@@ -65,7 +67,7 @@ enum Phase { PH_NONE = 0, PH_UPLOADED, PH_COUNTED, PH_BLOOM, PH_ENCODED };
 struct leon_ctx {
     leon_opts opts;
     std::string err;
-    cudaStream_t st = nullptr;
+    cudaStream_t st = nullptr, st2 = nullptr;   // st2: the anchor dictionary coder runs beside the per-block work
     LaunchCounter lc;
     KernelTimer kt;
     bool own_stream = true;
@@ -97,9 +99,16 @@ struct leon_ctx {
     uint64_t dict_cap = 0, dict_count = 0;
     DevBuf d_anchors, d_counters;
     // walk + entropy
-    DevBuf d_bif, d_err, d_recs, d_symoff, d_tri, d_nsym, d_descs, d_outall, d_outsize, d_dnaoff, d_dna, d_bs, d_qout;
-    DevBuf d_dict_tri, d_dict_desc, d_dict_out, d_dict_size;
-    uint64_t nblocks = 0, dna_nbytes = 0, dict_nbytes = 0;
+    DevBuf d_bif, d_err, d_recs, d_symoff, d_srec, d_srec_alt, d_segstart, d_chunkoff, d_chist, d_rec, d_sh, d_descs, d_outall,
+        d_outsize, d_dnaoff, d_dna, d_bs, d_qout;
+    DevBuf d_dict_rec, d_dict_sh, d_dict_desc, d_dict_out, d_dict_size, d_scan2;
+    PinBuf h_desc, h_dstage_rec[2], h_dstage_sh[2];
+    cudaEvent_t ev_dstage[2] = {nullptr, nullptr};
+    std::thread dict_thread;             // host side of the anchor dictionary coder (see dict_host_worker)
+    std::vector<uint8_t> dict_host_out;
+    std::string dict_thread_err;
+    double dict_host_ms = 0;
+    uint64_t nblocks = 0, dna_nbytes = 0, dict_nbytes = 0, nsym_total = 0;
     PinBuf h_dna, h_bs, h_dict, h_qual, h_qsizes, h_apos, h_aaddr;
     uint64_t reads_without_anchor = 0;
     int32_t min_len = 0, max_len = 0;
@@ -164,6 +173,26 @@ void do_upload(leon_ctx *c, const leon_reads *rd)
     c->phase = PH_UPLOADED;
 }
 
+// Stable LSD radix sort of n keys on the `passes` 8-bit digits starting at bit `shift0`; keys/alt are swapped so
+// that `keys` ends up pointing at the sorted array.
+template <typename K> void radix_sort(leon_ctx *c, K *&keys, K *&alt, uint64_t n, int shift0, int passes)
+{
+    using namespace lbcount;
+    cudaStream_t st = c->st;
+    uint32_t ntiles = cdiv_u(n, RS_TILE);
+    if (ntiles == 0) ntiles = 1;
+    c->d_tile_hist.reserve((uint64_t)ntiles * 256 * 4);
+    c->d_tile_off.reserve((uint64_t)ntiles * 256 * 8);
+    for (int p = 0; p < passes && n > 1; p++) {
+        int shift = shift0 + 8 * p;
+        LB_TIMED(c->kt, "k_rs_hist", st, LB_LAUNCH(c->lc, (k_rs_hist<K>), ntiles, RS_THREADS, 0, st, keys, n, shift, c->d_tile_hist.as<uint32_t>(), ntiles));
+        lbscan::exclusive_scan<uint64_t>((uint64_t)ntiles * 256, HistIn{c->d_tile_hist.as<uint32_t>()},
+                                         HistOut{c->d_tile_off.as<uint64_t>()}, c->d_scan, st, c->lc);
+        LB_TIMED(c->kt, "k_rs_scatter", st, LB_LAUNCH(c->lc, (k_rs_scatter<K>), ntiles, RS_THREADS, 0, st, keys, alt, n, shift, c->d_tile_off.as<uint64_t>(), ntiles));
+        std::swap(keys, alt);
+    }
+}
+
 template <typename K> void do_count(leon_ctx *c)
 {
     using namespace lbcount;
@@ -191,21 +220,9 @@ template <typename K> void do_count(leon_ctx *c)
     CUDA_TRY(cudaEventRecord(c->ev[3], st));
 
     // LSD radix sort over the ceil(2k/8) low bytes (the sentinel is all ones, so it stays the maximum)
-    uint32_t ntiles = cdiv_u(nk, RS_TILE);
-    if (ntiles == 0) ntiles = 1;
-    c->d_tile_hist.reserve((uint64_t)ntiles * 256 * 4);
-    c->d_tile_off.reserve((uint64_t)ntiles * 256 * 8);
-    int passes = (2 * k + 7) / 8;
-    c->tm.sort_passes = 0;
-    for (int p = 0; p < passes && nk > 1; p++) {
-        int shift = 8 * p;
-        LB_TIMED(c->kt, "k_rs_hist", st, LB_LAUNCH(c->lc, (k_rs_hist<K>), ntiles, RS_THREADS, 0, st, keys, nk, shift, c->d_tile_hist.as<uint32_t>(), ntiles));
-        lbscan::exclusive_scan<uint64_t>((uint64_t)ntiles * 256, HistIn{c->d_tile_hist.as<uint32_t>()},
-                                         HistOut{c->d_tile_off.as<uint64_t>()}, c->d_scan, st, c->lc);
-        LB_TIMED(c->kt, "k_rs_scatter", st, LB_LAUNCH(c->lc, (k_rs_scatter<K>), ntiles, RS_THREADS, 0, st, keys, alt, nk, shift, c->d_tile_off.as<uint64_t>(), ntiles));
-        std::swap(keys, alt);
-        c->tm.sort_passes++;
-    }
+    int passes = nk > 1 ? (2 * k + 7) / 8 : 0;
+    radix_sort<K>(c, keys, alt, nk, 0, passes);
+    c->tm.sort_passes = (uint32_t)passes;
     c->tm.sort_keys = nk;
     c->sorted_keys = keys;
     c->heads = alt;
@@ -274,6 +291,67 @@ template <typename K> void do_bloom(leon_ctx *c)
 }  // namespace
 
 namespace {
+
+// Anchor dictionary dump (C/Leon.cpp:1034-1042,1245-1260): ONE never-reset range coder over all anchors.  The
+// data-parallel part (order-0 model state and the exact reciprocal of `total` for every symbol) is computed on the
+// GPU (DictCountIn/DictRecOut); what is left is the strictly serial low/range recurrence, 3 multiplies per symbol.
+// A GPU thread needs ~110 ns per step of it (measured, profiles/), a host core ~5 ns, and the dump belongs to the
+// orchestrator (Leon::encodeInsertedAnchor), so by default this recurrence runs on a host thread that streams the
+// records out of HBM while the GPU walks and codes the blocks.  opts.dict_on_device = 1 runs it as a kernel instead
+// (k_range_encode on the second stream); both produce the same bytes.
+constexpr uint64_t DICT_STAGE_SYMS = 1ull << 20;
+
+void dict_host_worker(leon_ctx *c, uint64_t nsym)
+{
+    auto t0 = std::chrono::steady_clock::now();
+    try {
+        CUDA_TRY(cudaSetDevice(c->opts.device));
+        const uint4 *d_rec = c->d_dict_rec.as<uint4>();
+        const uint8_t *d_sh = c->d_dict_sh.as<uint8_t>();
+        std::vector<uint8_t> &out = c->dict_host_out;
+        out.clear();
+        out.reserve(nsym / 3 + 64);
+        const uint64_t nch = (nsym + DICT_STAGE_SYMS - 1) / DICT_STAGE_SYMS;
+        auto issue = [&](uint64_t i) {
+            uint64_t off = i * DICT_STAGE_SYMS, n = std::min(DICT_STAGE_SYMS, nsym - off);
+            CUDA_TRY(cudaMemcpyAsync(c->h_dstage_rec[i & 1].p, d_rec + off, n * sizeof(uint4), cudaMemcpyDeviceToHost, c->st2));
+            CUDA_TRY(cudaMemcpyAsync(c->h_dstage_sh[i & 1].p, d_sh + off, n, cudaMemcpyDeviceToHost, c->st2));
+            CUDA_TRY(cudaEventRecord(c->ev_dstage[i & 1], c->st2));
+        };
+        uint64_t low = 0, range = ~0ull;
+        const uint64_t TOP = 1ull << 56, BOTTOM = 1ull << 48;
+        if (nch) issue(0);
+        for (uint64_t i = 0; i < nch; i++) {
+            if (i + 1 < nch) issue(i + 1);
+            CUDA_TRY(cudaEventSynchronize(c->ev_dstage[i & 1]));
+            const uint32_t *rec = c->h_dstage_rec[i & 1].as<uint32_t>();
+            const uint8_t *sh = c->h_dstage_sh[i & 1].as<uint8_t>();
+            uint64_t n = std::min(DICT_STAGE_SYMS, nsym - i * DICT_STAGE_SYMS);
+            for (uint64_t j = 0; j < n; j++) {
+                uint32_t lo = rec[4 * j], w = rec[4 * j + 1];
+                uint64_t m = ((uint64_t)rec[4 * j + 3] << 32) | rec[4 * j + 2];
+                uint32_t s = sh[j];
+                uint64_t num = range + (s >> 7);                    // wraps only for the very first symbol
+                uint64_t q = ((s >> 7) && num == 0) ? m : (uint64_t)(((unsigned __int128)num * m) >> 64);
+                q >>= (s & 63u);                                    // == range / total (RangeCoder.cpp:108)
+                low += (uint64_t)lo * q;
+                range = q * (uint64_t)w;
+                while ((low ^ (low + range)) < TOP || range < BOTTOM) {
+                    if (range < BOTTOM && (low ^ (low + range)) >= TOP) range = (0 - low) & (BOTTOM - 1);
+                    out.push_back((uint8_t)(low >> 56));
+                    range <<= 8;
+                    low <<= 8;
+                }
+            }
+        }
+        for (int x = 0; x < 8; x++) { out.push_back((uint8_t)(low >> 56)); low <<= 8; }   // flush, RangeCoder.cpp:136-145
+    } catch (const LeonError &e) {
+        c->dict_thread_err = e.msg;
+    } catch (const std::exception &e) {
+        c->dict_thread_err = e.what();
+    }
+    c->dict_host_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+}
 
 template <typename K> lbanchor::DictDev<K> dict_view(leon_ctx *c, int which)
 {
@@ -439,6 +517,46 @@ template <typename K> void do_encode(leon_ctx *c)
     int32_t *apos = c->d_apos.as<int32_t>();
     uint32_t *aaddr = c->d_aaddr.as<uint32_t>();
 
+    // anchor dictionary stream: one coder over all anchors, flushed once (C/Leon.cpp:1034-1042,1245-1260).  It is one
+    // serial chain, so it runs on the second stream next to everything below.
+    uint32_t *ovf = c->d_counters.as<uint32_t>() + 2;
+    {
+        cudaStream_t s2 = c->st2;
+        uint64_t A = c->dict_count;
+        uint64_t nsym = A * (uint64_t)k;
+        if (nsym >= 0xffffff00ull) throw LeonError(LEON_E_OVERFLOW, "anchor dictionary stream longer than 2^32 symbols");
+        c->d_dict_rec.reserve((nsym + 1) * sizeof(uint4));
+        c->d_dict_sh.reserve(nsym + 1);
+        c->d_dict_desc.reserve(sizeof(StreamDesc));
+        c->d_dict_out.reserve(2 * nsym + 64);
+        c->d_dict_size.reserve(16);
+        CUDA_TRY(cudaMemsetAsync(c->d_counters.p, 0, 64, st));
+        CUDA_TRY(cudaEventRecord(c->ev[13], st));
+        CUDA_TRY(cudaStreamWaitEvent(s2, c->ev[13], 0));
+        if (A)
+            lbscan::exclusive_scan<lbscan::U32x4>(A, DictCountIn<K>{c->d_anchors.as<K>(), k},
+                                                  DictRecOut<K>{c->d_anchors.as<K>(), k, c->d_dict_rec.as<uint4>(), c->d_dict_sh.as<uint8_t>()},
+                                                  c->d_scan2, s2, c->lc);
+        if (c->opts.dict_on_device) {
+            StreamDesc d{0, nsym, 0, 2 * nsym + 16};
+            c->h_desc.reserve(sizeof d);
+            memcpy(c->h_desc.p, &d, sizeof d);
+            CUDA_TRY(cudaMemcpyAsync(c->d_dict_desc.p, c->h_desc.p, sizeof d, cudaMemcpyHostToDevice, s2));
+            LB_TIMED(c->kt, "k_range_encode_dict", s2, LB_LAUNCH(c->lc, k_range_encode, 1, 32, 0, s2, c->d_dict_rec.as<uint4>(), c->d_dict_sh.as<uint8_t>(),
+                      c->d_dict_desc.as<StreamDesc>(), c->d_dict_out.as<uint8_t>(), c->d_dict_size.as<uint64_t>(), 1, ovf + 1));
+            CUDA_TRY(cudaEventRecord(c->ev[14], s2));
+        } else {
+            for (int i = 0; i < 2; i++) {
+                c->h_dstage_rec[i].reserve(DICT_STAGE_SYMS * sizeof(uint4));
+                c->h_dstage_sh[i].reserve(DICT_STAGE_SYMS);
+                if (!c->ev_dstage[i]) CUDA_TRY(cudaEventCreateWithFlags(&c->ev_dstage[i], cudaEventDisableTiming));
+            }
+            c->dict_thread_err.clear();
+            if (c->dict_thread.joinable()) c->dict_thread.join();
+            c->dict_thread = std::thread(dict_host_worker, c, nsym);
+        }
+    }
+
     c->d_err.reserve((c->nkmers + 1) * 4);
     // qualities first: the smoothing pass borrows the error-position buffer as its prefix-count scratch
     if (c->opts.has_qual) {
@@ -460,31 +578,56 @@ template <typename K> void do_encode(leon_ctx *c)
     // per-block entropy coding
     c->nblocks = R ? (R + rpb - 1) / rpb : 0;
     c->dna_nbytes = 0;
-    c->d_counters.reserve(64);
-    uint32_t *ovf = c->d_counters.as<uint32_t>() + 2;
-    CUDA_TRY(cudaMemsetAsync(c->d_counters.p, 0, 64, st));
     if (c->nblocks) {
-        c->d_symoff.reserve((R + 1) * 8);
-        uint64_t *symtot = lbscan::exclusive_scan<uint64_t>(R, SymBoundIn{offsets, apos, c->d_recs.as<ReadRec>()},
-                                                            SymBoundOut{c->d_symoff.as<uint64_t>()}, c->d_scan, st, c->lc);
-        uint64_t total_bound = fetch_scalar(c, symtot);
-        // the scan scratch is reused below, keep the total in the counters buffer
-        uint64_t *symtot_keep = (uint64_t *)(c->d_counters.as<uint8_t>() + 16);
-        CUDA_TRY(cudaMemcpyAsync(symtot_keep, &total_bound, 8, cudaMemcpyHostToDevice, st));
-        c->d_tri.reserve((total_bound + 1) * sizeof(uint4));
-        c->d_nsym.reserve(c->nblocks * 8);
+        if (c->nblocks >= (1ull << 18)) throw LeonError(LEON_E_OVERFLOW, "more than 2^18 blocks in one read set");
+        ReadRec *recs = c->d_recs.as<ReadRec>();
+        c->d_symoff.reserve((R + 2) * 8);
+        uint64_t *symoff = c->d_symoff.as<uint64_t>();
+        SymCountIn cin{bases, offsets, koff, apos, aaddr, recs, c->d_bif.as<uint8_t>(), c->d_err.as<uint32_t>()};
+        uint64_t *symtot = lbscan::exclusive_scan<uint64_t>(R, cin, SymOffOut{symoff}, c->d_scan, st, c->lc);
+        CUDA_TRY(cudaMemcpyAsync(symoff + R, symtot, 8, cudaMemcpyDeviceToDevice, st));
+        uint64_t nsym = fetch_scalar(c, symtot);
+        if (nsym >= 0xffffff00ull) throw LeonError(LEON_E_OVERFLOW, "more than 2^32 symbols in one read set");
+        c->nsym_total = nsym;
+        c->d_srec.reserve((nsym + 1) * 8);
+        c->d_srec_alt.reserve((nsym + 1) * 8);
+        uint64_t *srec = c->d_srec.as<uint64_t>(), *salt = c->d_srec_alt.as<uint64_t>();
+        LB_TIMED(c->kt, "k_emit_syms", st, LB_LAUNCH(c->lc, k_emit_syms, cdiv_u(R, 256), 256, 0, st, bases, offsets, koff, R, rpb, apos, aaddr, recs,
+                  c->d_bif.as<uint8_t>(), c->d_err.as<uint32_t>(), symoff, srec));
+        // stable sort by (block, model): key bits [40, 46 + bits(nblocks - 1))
+        int keybits = REC_MODEL_BITS;
+        while (keybits < 24 && ((c->nblocks - 1) >> (keybits - REC_MODEL_BITS))) keybits++;
+        radix_sort<uint64_t>(c, srec, salt, nsym, REC_KEY_SHIFT, (keybits + 7) / 8);
+        // segments and chunks
+        c->d_segstart.reserve((c->nblocks * NUM_MODELS + 2) * 8);
+        c->d_chunkoff.reserve((c->nblocks * NUM_MODELS + 2) * 8);
+        uint64_t *segstart = c->d_segstart.as<uint64_t>(), *chunkoff = c->d_chunkoff.as<uint64_t>();
+        uint64_t nseg = 0, nchunks = 0;
+        if (nsym) {
+            uint64_t *segtot = lbscan::exclusive_scan<uint64_t>(nsym, SegHeadIn{srec}, SegHeadOut{segstart}, c->d_scan, st, c->lc);
+            nseg = fetch_scalar(c, segtot);
+            CUDA_TRY(cudaMemcpyAsync(segstart + nseg, symoff + R, 8, cudaMemcpyDeviceToDevice, st));
+            uint64_t *chtot = lbscan::exclusive_scan<uint64_t>(nseg, SegChunksIn{segstart}, SegChunksOut{chunkoff}, c->d_scan, st, c->lc);
+            nchunks = fetch_scalar(c, chtot);
+        }
+        c->d_rec.reserve((nsym + 1) * sizeof(uint4));
+        c->d_sh.reserve(nsym + 1);
+        if (nchunks) {
+            c->d_chist.reserve(nchunks * 256 * 4);
+            uint32_t *H = c->d_chist.as<uint32_t>();
+            LB_TIMED(c->kt, "k_chunk_hist", st, LB_LAUNCH(c->lc, k_chunk_hist, (unsigned)nchunks, 256, 0, st, srec, segstart, chunkoff, nseg, H));
+            LB_TIMED(c->kt, "k_seg_scan", st, LB_LAUNCH(c->lc, k_seg_scan, (unsigned)nseg, 256, 0, st, chunkoff, nseg, nchunks, H));
+            LB_TIMED(c->kt, "k_chunk_ranks", st, LB_LAUNCH(c->lc, k_chunk_ranks, (unsigned)nchunks, CHUNK, 0, st, srec, segstart, chunkoff, nseg, H,
+                      c->d_rec.as<uint4>(), c->d_sh.as<uint8_t>()));
+        }
         c->d_descs.reserve(c->nblocks * sizeof(StreamDesc));
-        c->d_outall.reserve(2 * total_bound + 16 * c->nblocks + 16);
+        c->d_outall.reserve(2 * nsym + 16 * c->nblocks + 16);
         c->d_outsize.reserve(c->nblocks * 8);
         c->d_dnaoff.reserve(c->nblocks * 8);
         c->d_bs.reserve(c->nblocks * 16);
-        LB_TIMED(c->kt, "k_model_scan", st, LB_LAUNCH(c->lc, k_model_scan, (unsigned)c->nblocks, 32, 0, st, bases, offsets, koff, R, rpb, apos, aaddr,
-                  c->d_recs.as<ReadRec>(), c->d_bif.as<uint8_t>(), c->d_err.as<uint32_t>(), c->d_symoff.as<uint64_t>(),
-                  c->d_tri.as<uint4>(), c->d_nsym.as<uint64_t>()));
-        LB_LAUNCH(c->lc, k_block_descs, cdiv_u(c->nblocks, 128), 128, 0, st, c->d_symoff.as<uint64_t>(), symtot_keep,
-                  c->d_nsym.as<uint64_t>(), R, rpb, c->nblocks, c->d_descs.as<StreamDesc>());
-        LB_TIMED(c->kt, "k_range_encode", st, LB_LAUNCH(c->lc, k_range_encode, (unsigned)c->nblocks, 32, 0, st, c->d_tri.as<uint4>(), c->d_descs.as<StreamDesc>(),
-                  c->d_outall.as<uint8_t>(), c->d_outsize.as<uint64_t>(), 0, ovf));
+        LB_LAUNCH(c->lc, k_block_descs, cdiv_u(c->nblocks, 128), 128, 0, st, symoff, R, rpb, c->nblocks, c->d_descs.as<StreamDesc>());
+        LB_TIMED(c->kt, "k_range_encode", st, LB_LAUNCH(c->lc, k_range_encode, (unsigned)c->nblocks, 32, 0, st, c->d_rec.as<uint4>(), c->d_sh.as<uint8_t>(),
+                  c->d_descs.as<StreamDesc>(), c->d_outall.as<uint8_t>(), c->d_outsize.as<uint64_t>(), 0, ovf));
         uint64_t *dtot = lbscan::exclusive_scan<uint64_t>(c->nblocks, SizeIn{c->d_outsize.as<uint64_t>()},
                                                           SizeOut{c->d_dnaoff.as<uint64_t>()}, c->d_scan, st, c->lc);
         c->dna_nbytes = fetch_scalar(c, dtot);
@@ -494,24 +637,17 @@ template <typename K> void do_encode(leon_ctx *c)
         LB_LAUNCH(c->lc, k_blocksizes, cdiv_u(c->nblocks, 128), 128, 0, st, c->d_outsize.as<uint64_t>(), R, rpb, c->nblocks,
                   c->d_bs.as<uint64_t>());
     }
-
-    // anchor dictionary stream: one coder over all anchors, flushed once (C/Leon.cpp:1034-1042,1245-1260)
-    {
-        uint64_t A = c->dict_count;
-        uint64_t nsym = A * (uint64_t)k;
-        if (nsym >= 0xffffff00ull) throw LeonError(LEON_E_OVERFLOW, "anchor dictionary stream longer than 2^32 symbols");
-        c->d_dict_tri.reserve((nsym + 1) * sizeof(uint4));
-        c->d_dict_desc.reserve(sizeof(StreamDesc));
-        c->d_dict_out.reserve(2 * nsym + 64);
-        c->d_dict_size.reserve(8);
-        if (A)
-            lbscan::exclusive_scan<lbscan::U32x4>(A, DictCountIn<K>{c->d_anchors.as<K>(), k},
-                                                  DictTriOut<K>{c->d_anchors.as<K>(), k, c->d_dict_tri.as<uint4>()}, c->d_scan, st, c->lc);
-        StreamDesc d{0, nsym, 0, 2 * nsym + 16};
-        CUDA_TRY(cudaMemcpyAsync(c->d_dict_desc.p, &d, sizeof d, cudaMemcpyHostToDevice, st));
-        LB_TIMED(c->kt, "k_range_encode_dict", st, LB_LAUNCH(c->lc, k_range_encode, 1, 32, 0, st, c->d_dict_tri.as<uint4>(), c->d_dict_desc.as<StreamDesc>(),
-                  c->d_dict_out.as<uint8_t>(), c->d_dict_size.as<uint64_t>(), 1, ovf));
+    // join the dictionary coder
+    if (c->opts.dict_on_device) {
+        CUDA_TRY(cudaStreamWaitEvent(st, c->ev[14], 0));
         c->dict_nbytes = fetch_scalar(c, c->d_dict_size.as<uint64_t>());
+        if (fetch_scalar(c, ovf + 1)) throw LeonError(LEON_E_OVERFLOW, "range coder output of the anchor dictionary exceeded its capacity bound");
+    } else {
+        CUDA_TRY(cudaEventRecord(c->ev[15], st));
+        c->dict_thread.join();
+        CUDA_TRY(cudaEventRecord(c->ev[14], st));      // ev[15]..ev[14]: how long the stream waited for the host coder
+        if (!c->dict_thread_err.empty()) throw LeonError(LEON_E_CUDA, "anchor dictionary coder: " + c->dict_thread_err);
+        c->dict_nbytes = c->dict_host_out.size();
     }
     if (fetch_scalar(c, ovf)) throw LeonError(LEON_E_OVERFLOW, "range coder output exceeded its capacity bound");
     {
@@ -531,7 +667,8 @@ void do_fetch(leon_ctx *c, leon_result *out)
     c->h_bloom.reserve(c->bloom.nbytes + 8);
     CUDA_TRY(cudaMemcpyAsync(c->h_bloom.p, c->bloom.words, c->bloom.nbytes, cudaMemcpyDeviceToHost, st));
     c->h_dict.reserve(c->dict_nbytes + 8);
-    CUDA_TRY(cudaMemcpyAsync(c->h_dict.p, c->d_dict_out.p, c->dict_nbytes, cudaMemcpyDeviceToHost, st));
+    if (c->opts.dict_on_device) CUDA_TRY(cudaMemcpyAsync(c->h_dict.p, c->d_dict_out.p, c->dict_nbytes, cudaMemcpyDeviceToHost, st));
+    else memcpy(c->h_dict.p, c->dict_host_out.data(), c->dict_nbytes);
     c->h_dna.reserve(c->dna_nbytes + 8);
     c->h_bs.reserve(c->nblocks * 16 + 8);
     if (c->nblocks) {
@@ -601,6 +738,8 @@ static void fill_timings(leon_ctx *c)
     c->tm.d2h_ms = el(11, 12);
     c->tm.total_ms = el(2, 10);
     c->tm.kernel_launches = c->lc.n;
+    c->tm.dict_host_ms = c->opts.dict_on_device ? 0.f : (float)c->dict_host_ms;
+    c->tm.dict_wait_ms = c->opts.dict_on_device ? 0.f : el(15, 14);
     c->kt.resolve();
     c->tm.sort_pass_ms = 0;
     for (auto &sl : c->kt.slots)
@@ -633,6 +772,7 @@ int leon_create(const leon_opts *opts, leon_ctx **out)
     try {
         CUDA_TRY(cudaSetDevice(opts->device));
         CUDA_TRY(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
+        CUDA_TRY(cudaStreamCreateWithFlags(&c->st2, cudaStreamNonBlocking));
         for (int i = 0; i < 16; i++) CUDA_TRY(cudaEventCreate(&c->ev[i]));
         for (int i = 0; i < 16; i++) CUDA_TRY(cudaEventRecord(c->ev[i], c->st));
     } catch (const LeonError &er) {
@@ -648,20 +788,24 @@ void leon_destroy(leon_ctx *c)
 {
     if (!c) return;
     cudaSetDevice(c->opts.device);
+    if (c->dict_thread.joinable()) c->dict_thread.join();
     if (c->st) cudaStreamSynchronize(c->st);
     DevBuf *dev[] = {&c->d_bases, &c->d_offsets, &c->d_quals, &c->d_koff, &c->d_keys, &c->d_keys_alt, &c->d_tile_hist, &c->d_tile_off,
                      &c->d_scan, &c->d_histo, &c->d_stats, &c->d_tbl, &c->d_bloom, &c->d_apos, &c->d_aaddr, &c->d_insflag, &c->d_plist,
                      &c->d_cand_pos, &c->d_cand_key, &c->d_cand_slot, &c->d_state, &c->d_ct_proxy, &c->d_ct_keys, &c->d_ct_ins,
                      &c->d_ct_fu, &c->d_dict_keys[0], &c->d_dict_keys[1], &c->d_dict_addr[0], &c->d_dict_addr[1], &c->d_dict_time[0],
-                     &c->d_dict_time[1], &c->d_anchors, &c->d_counters, &c->d_bif, &c->d_err, &c->d_recs, &c->d_symoff, &c->d_tri,
-                     &c->d_nsym, &c->d_descs, &c->d_outall, &c->d_outsize, &c->d_dnaoff, &c->d_dna, &c->d_bs, &c->d_qout,
-                     &c->d_dict_tri, &c->d_dict_desc, &c->d_dict_out, &c->d_dict_size};
+                     &c->d_dict_time[1], &c->d_anchors, &c->d_counters, &c->d_bif, &c->d_err, &c->d_recs, &c->d_symoff, &c->d_srec, &c->d_srec_alt, &c->d_segstart,
+                     &c->d_chunkoff, &c->d_chist, &c->d_rec, &c->d_sh, &c->d_scan2, &c->d_descs, &c->d_outall, &c->d_outsize, &c->d_dnaoff, &c->d_dna, &c->d_bs, &c->d_qout,
+                     &c->d_dict_rec, &c->d_dict_sh, &c->d_dict_desc, &c->d_dict_out, &c->d_dict_size};
     for (DevBuf *b : dev) b->release();
-    PinBuf *pin[] = {&c->h_histo, &c->h_small, &c->h_bloom, &c->h_dna, &c->h_bs, &c->h_dict, &c->h_qual, &c->h_qsizes, &c->h_apos, &c->h_aaddr};
+    PinBuf *pin[] = {&c->h_histo, &c->h_small, &c->h_bloom, &c->h_dna, &c->h_bs, &c->h_dict, &c->h_qual, &c->h_qsizes, &c->h_apos, &c->h_aaddr, &c->h_desc, &c->h_dstage_rec[0], &c->h_dstage_rec[1],
+                     &c->h_dstage_sh[0], &c->h_dstage_sh[1]};
     for (PinBuf *b : pin) b->release();
     for (int i = 0; i < 16; i++) cudaEventDestroy(c->ev[i]);
     c->kt.release();
+    for (int i = 0; i < 2; i++) if (c->ev_dstage[i]) cudaEventDestroy(c->ev_dstage[i]);
     if (c->st && c->own_stream) cudaStreamDestroy(c->st);
+    if (c->st2) { cudaStreamSynchronize(c->st2); cudaStreamDestroy(c->st2); }
     delete c;
 }
 
@@ -867,7 +1011,7 @@ int leon_debug_fetch(leon_ctx *c, const char *name, void *dst, uint64_t cap, uin
     else if (s == "koff") { src = c->d_koff.p; n = (c->nreads + 1) * 8; }
     else if (s == "bif") { src = c->d_bif.p; n = c->nkmers; }
     else if (s == "err") { src = c->d_err.p; n = c->nkmers * 4; }
-    else if (s == "nsym") { src = c->d_nsym.p; n = c->nblocks * 8; }
+    else if (s == "nsym") { src = c->d_symoff.as<uint64_t>() + c->nreads; n = c->nblocks ? 8 : 0; }
     else throw LeonError(LEON_E_ARG, "leon_debug_fetch: unknown buffer name " + s);
     *nbytes = n;
     if (dst && src) {

@@ -120,6 +120,20 @@ def test_bloom_queries_match_oracle():
         eng.close()
 
 
+@pytest.mark.parametrize("name", ["fa_k31_blocks", "fa_k63", "fq_k31_lossy", "fa_k31_edge"])
+def test_dictionary_coder_on_device_and_on_host_agree(name):
+    """The anchor dictionary dump is the same bytes whether its serial recurrence runs as a kernel or on the host thread
+    (the default), and both equal the reference's anchorsDict."""
+    c = load_case(name)
+    for on_device in (True, False):
+        eng = _engine(c, dict_on_device=on_device)
+        r = eng.compress(c["bases"], c["offsets"], c["quals"] if c["has_qual"] else None)
+        eng.close()
+        assert r["anchor_count"] == int(c["anchor_count"])
+        assert np.array_equal(r["anchors_dict"], c["anchors_dict"]), "on_device=%s" % on_device
+        assert np.array_equal(r["dna"], c["dna_concat"])
+
+
 def test_edge_inputs():
     """Empty set, reads shorter than k, all-N reads, a single read: same bytes as the oracle, no faults."""
     from oracle import oracle_py as O
