@@ -215,10 +215,12 @@ def algorithmic_bytes(kernel, st):
         return 1.0 * NK * kb
     if kernel == "k_extract":         # read the bases, write one key per k-mer
         return NB + NK * kb
-    if kernel == "k_model_scan":      # per symbol: read its source byte/word, write a 16-byte triple
-        return st["nsym"] * 17.0
-    if kernel == "k_range_encode":    # read the 16-byte triple of every symbol, write the output bytes
-        return st["nsym"] * 16.0 + st["dna_bytes"]
+    if kernel == "k_chunk_ranks":     # read the 8-byte sorted record, write the 17-byte coder record; histogram row per chunk
+        return st["nsym"] * (8.0 + 17.0 + 2.0)
+    if kernel == "k_emit_syms":
+        return st["nsym"] * 8.0 + NB
+    if kernel == "k_range_encode":    # read the 17-byte record of every symbol, write the output bytes
+        return st["nsym"] * 17.0 + st["dna_bytes"]
     if kernel == "k_run_stats" or kernel == "k_insert_runs":
         return st["nruns"] * (8.0 + kb)
     return None
@@ -281,7 +283,7 @@ def main_b200(args):
             a[0] += ms
             a[1] += n
         for k, v in eng.timings().items():
-            if k.endswith("_ms"):
+            if k.endswith("_ms") or k in ("anchor_batches", "anchor_rounds"):
                 phase[k] = phase.get(k, 0.0) + v
     e1.record(stream)
     barrier()

@@ -571,8 +571,13 @@ template <typename K> void do_encode(leon_ctx *c)
     c->d_bif.reserve(c->nkmers + 1);
     c->d_recs.reserve((R + 1) * sizeof(lbwalk::ReadRec));
     if (R)
-        LB_TIMED(c->kt, "k_walk", st, LB_LAUNCH(c->lc, (lbwalk::k_walk<K>), warp_grid(R), 256, 0, st, bases, offsets, koff, R, c->bloom, c->d_tbl.as<uint64_t>(),
-                  apos, c->d_bif.as<uint8_t>(), c->d_err.as<uint32_t>(), c->d_recs.as<lbwalk::ReadRec>()));
+    {
+        // bases of the 256 reads of a CTA are staged in shared memory when they fit (40 KB), else read from global
+        uint64_t need = ((256ull * (uint64_t)c->max_len + 31) & ~15ull) + 16;
+        uint32_t stage_bytes = need <= 40960 ? (uint32_t)need : 16u;
+        LB_TIMED(c->kt, "k_walk", st, LB_LAUNCH(c->lc, (lbwalk::k_walk<K>), cdiv_u(R, 256), 256, stage_bytes, st, bases, offsets, koff, R, c->bloom,
+                  c->d_tbl.as<uint64_t>(), apos, c->d_bif.as<uint8_t>(), c->d_err.as<uint32_t>(), c->d_recs.as<lbwalk::ReadRec>(), stage_bytes));
+    }
     CUDA_TRY(cudaEventRecord(c->ev[9], st));
 
     // per-block entropy coding

@@ -27,97 +27,161 @@ template <typename K> LB_D K seed_step(K kmer, unsigned nt, bool right, int k)  
     return (kmer >> 2) | ((K)nt << (2 * (k - 1)));
 }
 
-template <typename K> struct WalkState {
-    K kmer;
-    uint32_t nBif, nErr;
-    uint8_t *bif;
-    uint32_t *err;
-};
-
-// one extension step; everything is warp-uniform except the probes inside warp_contains4
+// ---- Bloom neighbourhood query, one thread per query ------------------------------------------------------------
+// contains4 of COL/Bloom.hpp:645-798 for the k-mer `fwd` (with `rc` its reverse complement, kept incrementally by the
+// caller).  The 28 tested bits are racine + cano2(c) + {0, simplehash16(i) & 4095}: for each of the 7 hashes the four
+// candidates sit inside one 14-bit field, so a query is 7 independent 2-word gathers (no early exit: in a walk one of
+// the four neighbours is almost always present and needs all 7).  tbl12 = low 12 bits of the simplehash16 table.
 template <typename K>
-LB_D void walk_step(WalkState<K> &w, uint8_t c, uint32_t pos, bool right, const BloomDev &b, const uint64_t *tbl, int lane)
+LB_D unsigned thread_contains4(const BloomDev &b, K fwd, K rc, bool right, const uint16_t *tbl12)
 {
     const int k = b.k;
-    if (c == 'N') { w.kmer = seed_step(w.kmer, 0u, right, k); return; }   // N was rewritten to A, nothing is emitted
-    unsigned ntb = leon_nt2bin(c);
-    unsigned res4 = lbbloom::warp_contains4<K>(b, w.kmer, right, tbl, lane);
-    int cnt = __popc(res4);
-    unsigned first = res4 ? (unsigned)(__ffs(res4) - 1) : 0u;
-    bool solid = (res4 >> ntb) & 1u;
-    unsigned nt = ntb;
-    int sym = -1;          // symbol to emit: bit 7 = binary model
-    bool err = false;
-    if (solid) {
-        if (cnt == 1) nt = first;
-        else if (cnt == 2) sym = 0x80 | (ntb == first ? 0 : 1);
-        else sym = (int)ntb;
+    const K m2 = kmer_mask(K(0), k - 2);
+    K mid = right ? (fwd & m2) : (fwd >> 4);
+    K rmid = right ? (rc >> 4) : (rc & m2);
+    K hp = rmid < mid ? rmid : mid;
+    uint64_t racine = bloom_racine(hp, b);
+    // cano2 of (first nt, last nt) for the four candidates, 4 bits each
+    unsigned fixed = right ? (unsigned)((fwd >> (2 * (k - 2))) & 3) : (unsigned)((fwd >> 2) & 3);
+    unsigned p0, p1, p2, p3;
+    if (right) {
+        p0 = bloom_cano2((fixed << 2) + 0); p1 = bloom_cano2((fixed << 2) + 1);
+        p2 = bloom_cano2((fixed << 2) + 2); p3 = bloom_cano2((fixed << 2) + 3);
     } else {
-        sym = (int)ntb;
-        if (cnt == 1 || cnt == 2) { err = true; nt = first; }
+        p0 = bloom_cano2(0 + fixed); p1 = bloom_cano2(4 + fixed); p2 = bloom_cano2(8 + fixed); p3 = bloom_cano2(12 + fixed);
     }
-    if (sym >= 0) { if (lane == 0) w.bif[w.nBif] = (uint8_t)sym; w.nBif++; }
-    if (err) { if (lane == 0) w.err[w.nErr] = pos; w.nErr++; }
-    w.kmer = seed_step(w.kmer, nt, right, k);
+    const uint64_t hlow = kmer_low64(hp);
+    const unsigned t0 = sizeof(K) == 8 ? tbl12[hlow & 255] : 0u;     // third table term of the one-word variant
+    uint32_t w0[7], w1[7];
+    unsigned sh[7];
+#pragma unroll
+    for (int i = 0; i < 7; i++) {
+        unsigned off = 0;
+        if (i) off = (tbl12[(hlow >> i) & 255] ^ tbl12[(hlow >> (i + 8)) & 255] ^ t0) & 4095u;
+        uint64_t bit = racine + off;
+        const uint32_t *w = b.words + (bit >> 5);
+        w0[i] = __ldg(w);
+        w1[i] = __ldg(w + 1);
+        sh[i] = (unsigned)bit & 31u;
+    }
+    unsigned alive = 15u;
+#pragma unroll
+    for (int i = 0; i < 7; i++) {
+        uint32_t f = __funnelshift_r(w0[i], w1[i], sh[i]);        // 32 filter bits starting at racine + off
+        alive &= ((f >> p0) & 1u) | (((f >> p1) & 1u) << 1) | (((f >> p2) & 1u) << 2) | (((f >> p3) & 1u) << 3);
+    }
+    return alive;
 }
 
+// Stages the bases of reads [r0, r1) of a CTA in shared memory with one bulk asynchronous copy (TMA, 1-D), so that
+// the per-thread walks read their bases from shared memory.  Returns the shared-memory address of bases[offsets[r0]],
+// or nullptr when the span does not fit (very long reads): callers then read from global memory.
+LB_D const uint8_t *stage_reads(const uint8_t *__restrict__ bases, uint64_t o0, uint64_t o1, uint8_t *smem, uint32_t smem_bytes,
+                                uint64_t *bar)
+{
+    const uint8_t *src = bases + (o0 & ~15ull);
+    uint64_t bytes = ((o1 - (o0 & ~15ull)) + 15ull) & ~15ull;
+    if (bytes > smem_bytes) return nullptr;        // CTA-uniform
+    if (bytes == 0) return smem;
+    uint32_t bar_a = (uint32_t)__cvta_generic_to_shared(bar);
+    uint32_t dst_a = (uint32_t)__cvta_generic_to_shared(smem);
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_a));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"((uint32_t)bytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(dst_a), "l"(src), "r"((uint32_t)bytes), "r"(bar_a) : "memory");
+    }
+    uint32_t done = 0;
+    while (!done) {
+        asm volatile("{\n\t.reg .pred p;\n\t"
+                     "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(bar_a) : "memory");
+    }
+    return smem + (o0 & 15ull);
+}
+
+// One thread per read.  Left walk (positions anchor-1 .. 0) then right walk (anchor+k .. L-1), as one loop of L-k
+// direction-generic steps so that the threads of a warp stay converged whatever their anchor positions.
 template <typename K>
 __global__ void __launch_bounds__(256) k_walk(const uint8_t *__restrict__ bases, const uint64_t *__restrict__ offsets,
                                               const uint64_t *__restrict__ koff, uint64_t nreads, BloomDev b,
                                               const uint64_t *__restrict__ tbl_g, const int32_t *__restrict__ apos,
-                                              uint8_t *__restrict__ bif, uint32_t *__restrict__ err, ReadRec *__restrict__ recs)
+                                              uint8_t *__restrict__ bif, uint32_t *__restrict__ err, ReadRec *__restrict__ recs,
+                                              uint32_t stage_bytes)
 {
-    __shared__ uint64_t tbl[256];
-    tbl[threadIdx.x] = tbl_g[threadIdx.x];
-    __syncthreads();
+    extern __shared__ __align__(128) uint8_t stage[];
+    __shared__ uint16_t tbl12[256];
+    __shared__ __align__(8) uint64_t bar;
+    tbl12[threadIdx.x] = (uint16_t)(tbl_g[threadIdx.x] & 4095u);
     const int k = b.k;
-    const int lane = threadIdx.x & 31;
-    uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
-    for (uint64_t r = warp; r < nreads; r += nwarps) {
-        uint64_t o = offsets[r], L = offsets[r + 1] - o;
-        const uint8_t *s = bases + o;
-        uint32_t nN = 0;
-        for (uint64_t base = 0; base < L; base += 32) {
-            uint64_t i = base + lane;
-            nN += __popc(__ballot_sync(0xffffffffu, i < L && s[i] == 'N'));
-        }
-        ReadRec rec = {nN, 0, 0, 0, 0};
-        int32_t ap = apos[r];
-        if (ap >= 0 && L >= (uint64_t)k) {
-            uint64_t i0 = (uint64_t)ap + lane, i1 = (uint64_t)ap + 32 + lane;
-            uint64_t w0 = pack32(i0 < L ? base_code_n_as_a(s[i0]) : 0u);
-            uint64_t w1 = pack32(i1 < L ? base_code_n_as_a(s[i1]) : 0u);
-            K anchor = window_kmer<K>(w0, w1, 0, 0, k);
-            rec.revcomp = anchor != kmer_canon(anchor, k);
-            WalkState<K> w{anchor, 0, 0, bif + koff[r], err + koff[r]};
-            // left walk: positions ap-1 .. 0
-            for (int64_t i = (int64_t)ap - 1; i >= 0; i -= 32) {
-                int64_t mine = i - lane;
-                uint8_t cb = mine >= 0 ? s[mine] : (uint8_t)0;
-                int steps = i + 1 < 32 ? (int)(i + 1) : 32;
-                for (int t = 0; t < steps; t++) {
-                    uint8_t c = (uint8_t)__shfl_sync(0xffffffffu, (unsigned)cb, t);
-                    walk_step<K>(w, c, (uint32_t)(i - t), false, b, tbl, lane);
+    const uint64_t r0 = (uint64_t)blockIdx.x * 256;
+    const uint64_t r1 = r0 + 256 < nreads ? r0 + 256 : nreads;
+    const uint64_t o0 = offsets[r0];
+    const uint8_t *sbase = stage_reads(bases, o0, offsets[r1], stage, stage_bytes, &bar);
+    __syncthreads();
+    const uint64_t r = r0 + threadIdx.x;
+    if (r >= nreads) return;
+    const uint64_t o = offsets[r], L = offsets[r + 1] - o;
+    const uint8_t *s = sbase ? sbase + (o - o0) : bases + o;
+    uint32_t nN = 0;
+    for (uint64_t i = 0; i < L; i++) nN += s[i] == 'N';
+    ReadRec rec = {nN, 0, 0, 0, 0};
+    const int32_t ap = apos[r];
+    if (ap >= 0 && L >= (uint64_t)k) {
+        K anchor = K(0);
+        for (int i = 0; i < k; i++) anchor = (anchor << 2) | K((uint64_t)base_code_n_as_a(s[ap + i]));
+        const K arc = kmer_revcomp(anchor, k);
+        rec.revcomp = arc < anchor;
+        const K mask = kmer_mask(K(0), k);
+        const int top = 2 * (k - 1);
+        K fwd = anchor, rc = arc;
+        uint8_t *bp = bif + koff[r];
+        uint32_t *ep = err + koff[r];
+        uint32_t nBif = 0, nErr = 0;
+        const uint32_t nsteps = (uint32_t)(L - k), nleft = (uint32_t)ap;
+        for (uint32_t t = 0; t < nsteps; t++) {
+            const bool right = t >= nleft;
+            if (t == nleft) { fwd = anchor; rc = arc; rec.nErrLeft = nErr; }
+            const uint32_t pos = right ? (uint32_t)ap + k + (t - nleft) : nleft - 1 - t;
+            const uint8_t c = s[pos];
+            unsigned nt = 0;
+            if (c != 'N') {   // at an N the walk advances with 'A' and emits nothing (C/DnaCoder.cpp:772-790)
+                const unsigned ntb = leon_nt2bin(c);
+                const unsigned res4 = thread_contains4<K>(b, fwd, rc, right, tbl12);
+                const int cnt = __popc(res4);
+                const unsigned first = res4 ? (unsigned)(__ffs(res4) - 1) : 0u;
+                const bool solid = (res4 >> ntb) & 1u;
+                nt = ntb;
+                int sym = -1;          // symbol to emit: bit 7 = binary model
+                bool e = false;
+                if (solid) {
+                    if (cnt == 2) sym = 0x80 | (ntb == first ? 0 : 1);
+                    else if (cnt > 2) sym = (int)ntb;
+                } else {
+                    sym = (int)ntb;
+                    if (cnt == 1 || cnt == 2) { e = true; nt = first; }
                 }
+                if (sym >= 0) bp[nBif++] = (uint8_t)sym;
+                if (e) ep[nErr++] = pos;
             }
-            rec.nErrLeft = w.nErr;
-            // right walk: positions ap+k .. L-1
-            w.kmer = anchor;
-            for (uint64_t i = (uint64_t)ap + k; i < L; i += 32) {
-                uint64_t mine = i + lane;
-                uint8_t cb = mine < L ? s[mine] : (uint8_t)0;
-                int steps = L - i < 32 ? (int)(L - i) : 32;
-                for (int t = 0; t < steps; t++) {
-                    uint8_t c = (uint8_t)__shfl_sync(0xffffffffu, (unsigned)cb, t);
-                    walk_step<K>(w, c, (uint32_t)(i + t), true, b, tbl, lane);
-                }
+            if (right) {
+                fwd = ((fwd << 2) | K((uint64_t)nt)) & mask;
+                rc = (rc >> 2) | (K((uint64_t)(nt ^ 2u)) << top);
+            } else {
+                fwd = (fwd >> 2) | (K((uint64_t)nt) << top);
+                rc = ((rc << 2) | K((uint64_t)(nt ^ 2u))) & mask;
             }
-            rec.nErr = w.nErr;
-            rec.nBif = w.nBif;
         }
-        if (lane == 0) recs[r] = rec;
+        if (nleft >= nsteps) rec.nErrLeft = nErr;
+        rec.nErr = nErr;
+        rec.nBif = nBif;
     }
+    recs[r] = rec;
 }
 
 // ---- qualities -----------------------------------------------------------------------------------------------
