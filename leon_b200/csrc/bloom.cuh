@@ -6,21 +6,19 @@
 
 namespace lbbloom {
 
+// solid list = (canonical k-mer, abundance) pairs with abundance >= 2, in any order (OR is order-independent)
 template <typename K>
-__global__ void __launch_bounds__(256) k_insert_runs(const K *__restrict__ keys, const uint64_t *__restrict__ heads, uint64_t nruns,
-                                                     uint64_t n, uint32_t min_abundance, BloomDev b, const uint64_t *__restrict__ tbl_g)
+__global__ void __launch_bounds__(256) k_insert_solid(const K *__restrict__ keys, const uint32_t *__restrict__ cnt, uint64_t nsolid,
+                                                      uint32_t min_abundance, BloomDev b, const uint64_t *__restrict__ tbl_g)
 {
     __shared__ uint64_t tbl[256];
     tbl[threadIdx.x] = tbl_g[threadIdx.x];
     __syncthreads();
-    for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < nruns; j += (uint64_t)gridDim.x * blockDim.x) {
-        uint64_t s = heads[j], e = j + 1 < nruns ? heads[j + 1] : n;
-        K key = keys[s];
-        if (key == kmer_sentinel<K>()) continue;
-        uint64_t cnt = e - s;
-        if (cnt < 2) continue;                               // not in the DSK solid list
-        uint64_t c31 = cnt > 0x7fffffffull ? 0x7fffffffull : cnt;
-        if ((int64_t)c31 < (int64_t)min_abundance) continue; // (int)abundance >= _min_abundance
+    for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < nsolid; j += (uint64_t)gridDim.x * blockDim.x) {
+        uint32_t c = cnt[j];
+        uint32_t c31 = c > 0x7fffffffu ? 0x7fffffffu : c;
+        if ((int32_t)c31 < (int32_t)min_abundance) continue;   // (int)abundance >= _min_abundance, K/BloomBuilder.hpp:173-180
+        K key = keys[j];
         K hp = bloom_hashpart(key, b.k);
         uint64_t h0 = bloom_racine(hp, b) + bloom_prefval(key, b.k);
         atomicOr(b.words + (h0 >> 5), 1u << (h0 & 31));

@@ -1,8 +1,17 @@
 // Phase 1 — solid k-mer counting in HBM (replaces DSK as used by Leon, SURVEY.md 8a-1;
-// K/SortingCountAlgorithm.cpp:499-644, K/Model.hpp:725-764,876-883, K/PartitionsCommand.cpp:1206-1460):
-//   extract_kmers : one warp per read, canonical k-mer of every window free of invalid characters
-//   radix sort    : LSD, 8-bit digits, stable (tile histogram -> digit-major scan -> ranked scatter)
-//   run stats     : run heads by scan, abundance histogram (u16 truncation + clamp), solid count
+// K/SortingCountAlgorithm.cpp:499-644, K/Model.hpp:725-764,876-883, K/PartitionsCommand.cpp:1206-1460).
+// Only the multiset of canonical k-mers matters to Leon (histogram, solid list), not their order, so instead of a
+// full sort the keys are PARTITIONED by a mixing hash and each bucket is counted in a shared-memory hash table:
+//   k_extract      : one warp per read, canonical k-mer of every window free of invalid characters
+//   k_part_hist /
+//   k_part_scatter : stable 8-bit partition pass (tile histogram -> digit-major scan -> ranks -> shared-memory
+//                    staging -> coalesced runs); 1-3 passes on hash digits give buckets of ~5 k keys.  The same
+//                    two kernels, with a plain shift digit, are the radix sort of entropy.cuh.
+//   k_bucket_bounds: first key of every bucket
+//   k_bucket_count : one CTA per bucket; open-addressing table in shared memory (CAS on the key, atomicAdd on the
+//                    count); abundance histogram (u16 truncation + clamp, MI/impl/Histogram.hpp:87), solid list
+//                    (abundance >= 2, K/SortingCountAlgorithm.cpp:210).  A bucket whose distinct keys overflow the
+//                    table is split by further hash bits and redone, so any input is handled.
 #pragma once
 #include "common.cuh"
 #include "kmer_math.cuh"
@@ -105,28 +114,45 @@ __global__ void __launch_bounds__(256) k_extract(const uint8_t *__restrict__ bas
     }
 }
 
-// ---- radix sort --------------------------------------------------------------------------------------------
+// ---- partition pass (also the LSD radix sort pass of entropy.cuh) ------------------------------------------------
 constexpr int RS_THREADS = 256;
-constexpr int RS_ITEMS = 16;
-constexpr int RS_TILE = RS_THREADS * RS_ITEMS;     // 4096 keys per CTA
 constexpr int RS_WARPS = RS_THREADS / 32;
-constexpr int RS_WCHUNK = 32 * RS_ITEMS;           // 512 consecutive keys per warp
+template <typename K> struct RsCfg { static constexpr int ITEMS = sizeof(K) == 8 ? 16 : 8; static constexpr int TILE = RS_THREADS * ITEMS; };
 
-template <typename K> LB_D unsigned digit_of(K key, int shift) { return (unsigned)(key >> shift) & 255u; }
+// murmur3 finaliser: every output bit depends on every input bit
+LB_HD uint64_t mix64(uint64_t x)
+{
+    x ^= x >> 33; x *= 0xff51afd7ed558ccdULL;
+    x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL;
+    x ^= x >> 33;
+    return x;
+}
+LB_HD uint64_t key_mix(uint64_t k) { return mix64(k); }
+LB_HD uint64_t key_mix(u128 k) { return mix64(k.lo ^ mix64(k.hi + 0x9E3779B97F4A7C15ULL)); }
+
+template <typename K> struct ShiftDigit {     // radix sort on key bits [shift, shift + 8)
+    int shift;
+    LB_D unsigned operator()(K key) const { return (unsigned)(key >> shift) & 255u; }
+};
+template <typename K> struct HashDigit {      // partition on hash bits [shift, shift + 8) & mask
+    int shift; unsigned mask;
+    LB_D unsigned operator()(K key) const { return (unsigned)(key_mix(key) >> shift) & mask; }
+};
 
 // tile_hist[d * ntiles + tile] = number of keys of the tile whose digit is d
-template <typename K>
-__global__ void __launch_bounds__(RS_THREADS) k_rs_hist(const K *__restrict__ keys, uint64_t n, int shift,
-                                                        uint32_t *__restrict__ tile_hist, uint32_t ntiles)
+template <typename K, typename D>
+__global__ void __launch_bounds__(RS_THREADS) k_part_hist(const K *__restrict__ keys, uint64_t n, D digit,
+                                                          uint32_t *__restrict__ tile_hist, uint32_t ntiles)
 {
+    constexpr int ITEMS = RsCfg<K>::ITEMS, TILE = RsCfg<K>::TILE;
     __shared__ uint32_t h[256];
     h[threadIdx.x] = 0;
     __syncthreads();
-    uint64_t base = (uint64_t)blockIdx.x * RS_TILE;
+    uint64_t base = (uint64_t)blockIdx.x * TILE;
 #pragma unroll
-    for (int j = 0; j < RS_ITEMS; j++) {
+    for (int j = 0; j < ITEMS; j++) {
         uint64_t i = base + (uint64_t)j * RS_THREADS + threadIdx.x;
-        if (i < n) atomicAdd(&h[digit_of(keys[i], shift)], 1u);
+        if (i < n) atomicAdd(&h[digit(keys[i])], 1u);
     }
     __syncthreads();
     tile_hist[(uint64_t)threadIdx.x * ntiles + blockIdx.x] = h[threadIdx.x];
@@ -141,29 +167,35 @@ struct HistOut {
     __device__ void operator()(uint64_t i, uint64_t ex, uint64_t) const { o[i] = ex; }
 };
 
-// stable scatter: rank of a key among equal digits = (tile offset for the digit) + (keys of earlier warps of the
-// tile with that digit) + (earlier keys of this warp with that digit).  Warp w owns keys [w*512, w*512+512) of the
-// tile, visited row by row (32 consecutive keys per row), so ranks follow the input order.
-template <typename K>
-__global__ void __launch_bounds__(RS_THREADS) k_rs_scatter(const K *__restrict__ in, K *__restrict__ out, uint64_t n, int shift,
-                                                           const uint64_t *__restrict__ tile_off, uint32_t ntiles)
+// Stable scatter.  Rank of a key among the keys of its digit = (tile offset of the digit) + (keys of earlier warps of
+// the tile with that digit) + (earlier keys of this warp with that digit); warp w owns keys [w*32*ITEMS, ...) of the
+// tile, row by row, so ranks follow the input order.  Keys are first placed at their tile-local sorted position in
+// shared memory, then written out: consecutive threads write consecutive addresses of a digit's run.
+template <typename K, typename D>
+__global__ void __launch_bounds__(RS_THREADS) k_part_scatter(const K *__restrict__ in, K *__restrict__ out, uint64_t n, D digit,
+                                                             const uint64_t *__restrict__ tile_off, uint32_t ntiles)
 {
+    constexpr int ITEMS = RsCfg<K>::ITEMS, TILE = RsCfg<K>::TILE;
     __shared__ uint32_t whist[RS_WARPS][256];
-    __shared__ uint64_t wbase[RS_WARPS][256];
+    __shared__ uint32_t dstart[256];
+    __shared__ uint64_t gbase[256];
+    __shared__ uint32_t wsum[RS_WARPS];
+    __shared__ K stage[TILE];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int i = threadIdx.x; i < RS_WARPS * 256; i += RS_THREADS) (&whist[0][0])[i] = 0;
     __syncthreads();
 
-    K key[RS_ITEMS];
-    uint32_t rank[RS_ITEMS];
-    uint64_t wstart = (uint64_t)blockIdx.x * RS_TILE + (uint64_t)warp * RS_WCHUNK;
+    K key[ITEMS];
+    uint16_t rank[ITEMS], dig[ITEMS];
+    const uint64_t tbase = (uint64_t)blockIdx.x * TILE;
+    const uint64_t wstart = tbase + (uint64_t)warp * (32 * ITEMS);
     const uint32_t lt_mask = (1u << lane) - 1u;
 #pragma unroll
-    for (int r = 0; r < RS_ITEMS; r++) {
+    for (int r = 0; r < ITEMS; r++) {
         uint64_t i = wstart + (uint64_t)r * 32 + lane;
         bool valid = i < n;
         key[r] = valid ? in[i] : kmer_sentinel<K>();
-        unsigned d = valid ? digit_of(key[r], shift) : 256u;   // 256 groups the out-of-range lanes together
+        unsigned d = valid ? digit(key[r]) : 256u;   // 256 groups the out-of-range lanes together
         uint32_t peers = __match_any_sync(0xffffffffu, d);
         int leader = __ffs(peers) - 1;
         uint32_t old = 0;
@@ -172,82 +204,214 @@ __global__ void __launch_bounds__(RS_THREADS) k_rs_scatter(const K *__restrict__
             whist[warp][d] = old + __popc(peers);
         }
         old = __shfl_sync(0xffffffffu, old, leader);
-        rank[r] = old + __popc(peers & lt_mask);
+        rank[r] = (uint16_t)(old + __popc(peers & lt_mask));
+        dig[r] = (uint16_t)d;
         __syncwarp();
     }
     __syncthreads();
     {
-        // thread d turns the per-warp counts of digit d into per-warp global bases
-        unsigned d = threadIdx.x;
-        uint64_t b = tile_off[(uint64_t)d * ntiles + blockIdx.x];
+        // thread d: per-warp counts of digit d -> exclusive prefix over the warps; digit totals -> tile-local starts
+        const unsigned d = threadIdx.x;
+        uint32_t tot = 0;
 #pragma unroll
         for (int w = 0; w < RS_WARPS; w++) {
-            wbase[w][d] = b;
-            b += whist[w][d];
+            uint32_t c = whist[w][d];
+            whist[w][d] = tot;
+            tot += c;
         }
+        uint32_t incl = tot;
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) {
+            uint32_t o = __shfl_up_sync(0xffffffffu, incl, s);
+            if (lane >= s) incl += o;
+        }
+        if (lane == 31) wsum[warp] = incl;
+        __syncthreads();
+        uint32_t base = 0;
+        for (int w = 0; w < warp; w++) base += wsum[w];
+        dstart[d] = base + incl - tot;
+        gbase[d] = tile_off[(uint64_t)d * ntiles + blockIdx.x];
     }
     __syncthreads();
 #pragma unroll
-    for (int r = 0; r < RS_ITEMS; r++) {
-        uint64_t i = wstart + (uint64_t)r * 32 + lane;
-        if (i < n) out[wbase[warp][digit_of(key[r], shift)] + rank[r]] = key[r];
+    for (int r = 0; r < ITEMS; r++)
+        if (dig[r] < 256) stage[dstart[dig[r]] + whist[warp][dig[r]] + rank[r]] = key[r];
+    __syncthreads();
+    const uint32_t nt = n - tbase < (uint64_t)TILE ? (uint32_t)(n - tbase) : (uint32_t)TILE;
+    for (uint32_t i = threadIdx.x; i < nt; i += RS_THREADS) {
+        K kx = stage[i];
+        unsigned d = digit(kx);
+        out[gbase[d] + (i - dstart[d])] = kx;
     }
 }
 
-// ---- run-length statistics -----------------------------------------------------------------------------------
-template <typename K> struct HeadIn {
-    const K *keys;
-    __device__ uint32_t operator()(uint64_t i) const { return (i == 0 || keys[i] != keys[i - 1]) ? 1u : 0u; }
-};
-struct HeadOut {
-    uint64_t *heads;
-    __device__ void operator()(uint64_t i, uint32_t ex, uint32_t v) const { if (v) heads[ex] = i; }
-};
-// (run count can exceed 2^32 only if n does; the scan type is widened by the caller in that case)
-template <typename K> struct HeadIn64 {
-    const K *keys;
-    __device__ uint64_t operator()(uint64_t i) const { return (i == 0 || keys[i] != keys[i - 1]) ? 1ull : 0ull; }
-};
-struct HeadOut64 {
-    uint64_t *heads;
-    __device__ void operator()(uint64_t i, uint64_t ex, uint64_t v) const { if (v) heads[ex] = i; }
-};
+// ---- buckets ------------------------------------------------------------------------------------------------------
+// After the partition passes the keys are ordered by bucket id = top `bits` bits of key_mix.
+// bstart[b] = index of the first key of bucket b (b = 0 .. nbuckets, bstart[nbuckets] = n).
+template <typename K>
+__global__ void __launch_bounds__(256) k_bucket_bounds(const K *__restrict__ keys, uint64_t n, int bits, uint64_t nbuckets,
+                                                       uint64_t *__restrict__ bstart)
+{
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        uint64_t b = bits ? key_mix(keys[i]) >> (64 - bits) : 0;
+        uint64_t first = i ? (bits ? key_mix(keys[i - 1]) >> (64 - bits) : 0) + 1 : 0;
+        for (uint64_t x = first; x <= b; x++) bstart[x] = i;
+        if (i == n - 1)
+            for (uint64_t x = b + 1; x <= nbuckets; x++) bstart[x] = n;
+    }
+}
 
 struct CountStats { unsigned long long nb_solid_total, nb_distinct, nb_valid; };
 
-// abundance histogram over ALL distinct k-mers: bin = count truncated to u16, clamped to 10000
-// (MI/impl/Histogram.hpp:87); solid = abundance >= 2 (K/SortingCountAlgorithm.cpp:210)
-template <typename K>
-__global__ void __launch_bounds__(256) k_run_stats(const K *__restrict__ keys, const uint64_t *__restrict__ heads, uint64_t nruns,
-                                                   uint64_t n, unsigned long long *__restrict__ histo, CountStats *stats)
+constexpr int BC_THREADS = 256;
+constexpr int BC_STACK = 48;
+template <typename K> struct BcCfg {
+    static constexpr int SLOTS = sizeof(K) == 8 ? 8192 : 4096;     // table slots per CTA (96 KB / 112 KB: 2 CTAs per SM)
+    static constexpr int FILL_MAX = SLOTS * 3 / 4;                 // distinct keys admitted per table
+    static constexpr int TARGET = SLOTS * 3 / 4;                   // keys per bucket the partition aims for
+    static constexpr size_t SMEM = (size_t)SLOTS * (12 + (sizeof(K) == 8 ? 0 : sizeof(K)));
+};
+
+template <typename K> LB_D uint64_t table_tag(K key, uint64_t salt);
+template <> LB_D uint64_t table_tag<uint64_t>(uint64_t key, uint64_t) { return key; }     // never the sentinel ~0
+template <> LB_D uint64_t table_tag<u128>(u128 key, uint64_t salt)
 {
-    extern __shared__ uint32_t sh[];  // 10001 bins
-    for (int i = threadIdx.x; i < 10001; i += blockDim.x) sh[i] = 0;
+    uint64_t t = mix64(key.lo + salt) ^ key.hi;
+    return t == ~0ull ? 0x5bd1e995ull : t;
+}
+
+// One CTA per bucket.  `sel/nsplit`: a table pass admits the keys whose selector bits equal `sel`; it starts with
+// the whole bucket (or ceil(size / BC_TARGET) parts) and halves a part whenever its distinct keys overflow the table.
+// 128-bit keys are claimed through a 64-bit tag (CAS) and verified against the full key after the pass; a tag shared
+// by two different keys (probability ~2^-40 per run) makes the pass repeat with another salt.
+template <typename K>
+__global__ void __launch_bounds__(BC_THREADS) k_bucket_count(const K *__restrict__ keys, const uint64_t *__restrict__ bstart,
+                                                             unsigned long long *__restrict__ histo,
+                                                             CountStats *__restrict__ stats, K *__restrict__ solid_keys,
+                                                             uint32_t *__restrict__ solid_cnt,
+                                                             unsigned long long *__restrict__ nsolid_out)
+{
+    constexpr int BC_SLOTS = BcCfg<K>::SLOTS, BC_FILL_MAX = BcCfg<K>::FILL_MAX, BC_TARGET = BcCfg<K>::TARGET;
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    uint64_t *tags = reinterpret_cast<uint64_t *>(smem_raw);                       // [BC_SLOTS]
+    uint32_t *cnts = reinterpret_cast<uint32_t *>(tags + BC_SLOTS);                 // [BC_SLOTS]
+    K *full = reinterpret_cast<K *>(cnts + BC_SLOTS);                               // [BC_SLOTS], 128-bit keys only
+    __shared__ uint32_t st_sel[BC_STACK], st_ns[BC_STACK];
+    __shared__ int sp;
+    __shared__ uint32_t ndistinct, overflow, collision, nsol;
+    __shared__ unsigned long long sol_base;
+    __shared__ unsigned long long acc[3];
+    __shared__ uint32_t shist[256];
+    const uint64_t b = blockIdx.x;
+    const uint64_t beg = bstart[b], end = bstart[b + 1];
+    const uint64_t size = end - beg;
+    if (size == 0) return;
+    const int tid = threadIdx.x;
+    if (tid == 0) {
+        uint32_t ns = 1;
+        while ((uint64_t)ns * BC_TARGET < size && ns < 32) ns <<= 1;
+        sp = 0;
+        for (uint32_t x = 0; x < ns; x++) { st_sel[sp] = x; st_ns[sp] = ns; sp++; }
+        acc[0] = acc[1] = acc[2] = 0;
+    }
+    shist[tid] = 0;
     __syncthreads();
-    unsigned long long solid = 0, distinct = 0, valid = 0;
-    for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < nruns; j += (uint64_t)gridDim.x * blockDim.x) {
-        uint64_t s = heads[j], e = j + 1 < nruns ? heads[j + 1] : n;
-        if (keys[s] == kmer_sentinel<K>()) continue;
-        uint64_t cnt = e - s;
-        unsigned idx = (unsigned)(cnt & 0xffffu);
-        atomicAdd(&sh[idx >= 10000u ? 10000u : idx], 1u);
-        distinct++;
-        valid += cnt;
-        if (cnt >= 2) solid++;
+    uint64_t salt = 0x1234567;
+    while (true) {
+        __syncthreads();
+        if (sp == 0) break;
+        const uint32_t sel = st_sel[sp - 1], ns = st_ns[sp - 1];
+        __syncthreads();
+        if (tid == 0) { sp--; ndistinct = 0; overflow = 0; collision = 0; nsol = 0; }
+        for (int i = tid; i < BC_SLOTS; i += BC_THREADS) { tags[i] = ~0ull; cnts[i] = 0; }
+        __syncthreads();
+        // insert
+        for (uint64_t i = beg + tid; i < end; i += BC_THREADS) {
+            K key = keys[i];
+            if (key == kmer_sentinel<K>()) continue;
+            uint64_t mx = key_mix(key);
+            if (((uint32_t)(mx >> 20) & (ns - 1)) != sel) continue;
+            uint64_t tag = table_tag<K>(key, salt);
+            uint32_t slot = (uint32_t)(mx ^ (mx >> 37)) & (BC_SLOTS - 1);
+            for (int probe = 0; probe < BC_SLOTS; probe++) {
+                unsigned long long old = atomicCAS((unsigned long long *)&tags[slot], ~0ull, (unsigned long long)tag);
+                if (old == ~0ull) {
+                    if (sizeof(K) > 8) full[slot] = key;
+                    if (atomicAdd(&ndistinct, 1u) >= BC_FILL_MAX) overflow = 1;
+                    atomicAdd(&cnts[slot], 1u);
+                    break;
+                }
+                if (old == tag) { atomicAdd(&cnts[slot], 1u); break; }
+                slot = (slot + 1) & (BC_SLOTS - 1);
+            }
+            if (*(volatile uint32_t *)&overflow) break;
+        }
+        __syncthreads();
+        if (overflow) {   // too many distinct keys for one table: split this part in two and redo
+            if (tid == 0) {
+                if (sp + 2 <= BC_STACK && ns < (1u << 24)) {
+                    st_sel[sp] = sel; st_ns[sp] = ns * 2; sp++;
+                    st_sel[sp] = sel + ns; st_ns[sp] = ns * 2; sp++;
+                } else atomicAdd(&stats->nb_valid, 1ull << 62);   // cannot happen for distinct keys; poisons the result
+            }
+            continue;
+        }
+        if (sizeof(K) > 8) {   // verify the tags of 128-bit keys
+            for (uint64_t i = beg + tid; i < end; i += BC_THREADS) {
+                K key = keys[i];
+                if (key == kmer_sentinel<K>()) continue;
+                uint64_t mx = key_mix(key);
+                if (((uint32_t)(mx >> 20) & (ns - 1)) != sel) continue;
+                uint64_t tag = table_tag<K>(key, salt);
+                uint32_t slot = (uint32_t)(mx ^ (mx >> 37)) & (BC_SLOTS - 1);
+                while (tags[slot] != tag) slot = (slot + 1) & (BC_SLOTS - 1);
+                if (full[slot] != key) collision = 1;
+            }
+            __syncthreads();
+            if (collision) {
+                if (tid == 0) { st_sel[sp] = sel; st_ns[sp] = ns; sp++; }
+                salt = salt * 6364136223846793005ULL + 1442695040888963407ULL;
+                continue;
+            }
+        }
+        // emit: histogram over all distinct keys, solid list for abundance >= 2
+        unsigned long long distinct = 0, valid = 0, solid = 0;
+        for (int i = tid; i < BC_SLOTS; i += BC_THREADS) {
+            uint32_t c = cnts[i];
+            if (!c) continue;
+            distinct++;
+            valid += c;
+            unsigned idx = c & 0xffffu;
+            if (idx < 256u) atomicAdd(&shist[idx], 1u);
+            else atomicAdd(&histo[idx >= 10000u ? 10000u : idx], 1ull);
+            if (c >= 2) { solid++; atomicAdd(&nsol, 1u); }
+        }
+        for (int d = 16; d; d >>= 1) {
+            distinct += __shfl_down_sync(0xffffffffu, distinct, d);
+            valid += __shfl_down_sync(0xffffffffu, valid, d);
+            solid += __shfl_down_sync(0xffffffffu, solid, d);
+        }
+        if ((tid & 31) == 0) { atomicAdd(&acc[0], solid); atomicAdd(&acc[1], distinct); atomicAdd(&acc[2], valid); }
+        __syncthreads();
+        if (tid == 0) { sol_base = nsol ? atomicAdd(nsolid_out, (unsigned long long)nsol) : 0; nsol = 0; }
+        __syncthreads();
+        for (int i = tid; i < BC_SLOTS; i += BC_THREADS) {
+            uint32_t c = cnts[i];
+            if (c < 2) continue;
+            uint64_t o = sol_base + atomicAdd(&nsol, 1u);
+            K key;
+            if (sizeof(K) > 8) key = full[i];
+            else kmer_make(key, tags[i], 0);
+            solid_keys[o] = key;
+            solid_cnt[o] = c;
+        }
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < 10001; i += blockDim.x)
-        if (sh[i]) atomicAdd(&histo[i], (unsigned long long)sh[i]);
-    // block reduction of the three counters through warp shuffles + atomics
-    for (int d = 16; d; d >>= 1) {
-        solid += __shfl_down_sync(0xffffffffu, solid, d);
-        distinct += __shfl_down_sync(0xffffffffu, distinct, d);
-        valid += __shfl_down_sync(0xffffffffu, valid, d);
-    }
-    if ((threadIdx.x & 31) == 0) {
-        if (solid) atomicAdd(&stats->nb_solid_total, solid);
-        if (distinct) atomicAdd(&stats->nb_distinct, distinct);
-        if (valid) atomicAdd(&stats->nb_valid, valid);
+    if (shist[tid]) atomicAdd(&histo[tid], (unsigned long long)shist[tid]);
+    if (tid == 0) {
+        if (acc[0]) atomicAdd(&stats->nb_solid_total, acc[0]);
+        if (acc[1]) atomicAdd(&stats->nb_distinct, acc[1]);
+        if (acc[2]) atomicAdd(&stats->nb_valid, acc[2]);
     }
 }
 

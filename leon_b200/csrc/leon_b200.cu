@@ -81,9 +81,9 @@ struct leon_ctx {
     DevBuf d_bases, d_offsets, d_quals, d_koff;
     // counting
     DevBuf d_keys, d_keys_alt, d_tile_hist, d_tile_off, d_scan, d_histo, d_stats, d_tbl;
-    void *sorted_keys = nullptr;     // points into d_keys or d_keys_alt
-    void *heads = nullptr;           // run heads live in the other one
-    uint64_t nruns = 0;
+    void *solid_keys = nullptr;      // solid list (abundance >= 2): keys in d_keys or d_keys_alt, counts in d_solid_cnt
+    uint64_t nsolid = 0;
+    DevBuf d_bstart, d_solid_cnt;
     PinBuf h_histo, h_small;
     leon_count_result cres;
     int32_t min_abundance = 0;
@@ -173,24 +173,27 @@ void do_upload(leon_ctx *c, const leon_reads *rd)
     c->phase = PH_UPLOADED;
 }
 
-// Stable LSD radix sort of n keys on the `passes` 8-bit digits starting at bit `shift0`; keys/alt are swapped so
-// that `keys` ends up pointing at the sorted array.
-template <typename K> void radix_sort(leon_ctx *c, K *&keys, K *&alt, uint64_t n, int shift0, int passes)
+// One stable 8-bit partition pass (tile histogram -> digit-major scan -> scatter); keys/alt are swapped so that `keys`
+// points at the result.
+template <typename K, typename D> void partition_pass(leon_ctx *c, K *&keys, K *&alt, uint64_t n, D digit)
 {
     using namespace lbcount;
     cudaStream_t st = c->st;
-    uint32_t ntiles = cdiv_u(n, RS_TILE);
+    uint32_t ntiles = cdiv_u(n, RsCfg<K>::TILE);
     if (ntiles == 0) ntiles = 1;
     c->d_tile_hist.reserve((uint64_t)ntiles * 256 * 4);
     c->d_tile_off.reserve((uint64_t)ntiles * 256 * 8);
-    for (int p = 0; p < passes && n > 1; p++) {
-        int shift = shift0 + 8 * p;
-        LB_TIMED(c->kt, "k_rs_hist", st, LB_LAUNCH(c->lc, (k_rs_hist<K>), ntiles, RS_THREADS, 0, st, keys, n, shift, c->d_tile_hist.as<uint32_t>(), ntiles));
-        lbscan::exclusive_scan<uint64_t>((uint64_t)ntiles * 256, HistIn{c->d_tile_hist.as<uint32_t>()},
-                                         HistOut{c->d_tile_off.as<uint64_t>()}, c->d_scan, st, c->lc);
-        LB_TIMED(c->kt, "k_rs_scatter", st, LB_LAUNCH(c->lc, (k_rs_scatter<K>), ntiles, RS_THREADS, 0, st, keys, alt, n, shift, c->d_tile_off.as<uint64_t>(), ntiles));
-        std::swap(keys, alt);
-    }
+    LB_TIMED(c->kt, "k_part_hist", st, LB_LAUNCH(c->lc, (k_part_hist<K, D>), ntiles, RS_THREADS, 0, st, keys, n, digit, c->d_tile_hist.as<uint32_t>(), ntiles));
+    lbscan::exclusive_scan<uint64_t>((uint64_t)ntiles * 256, HistIn{c->d_tile_hist.as<uint32_t>()},
+                                     HistOut{c->d_tile_off.as<uint64_t>()}, c->d_scan, st, c->lc);
+    LB_TIMED(c->kt, "k_part_scatter", st, LB_LAUNCH(c->lc, (k_part_scatter<K, D>), ntiles, RS_THREADS, 0, st, keys, alt, n, digit, c->d_tile_off.as<uint64_t>(), ntiles));
+    std::swap(keys, alt);
+}
+
+// Stable LSD radix sort of n keys on the `passes` 8-bit digits starting at bit `shift0`.
+template <typename K> void radix_sort(leon_ctx *c, K *&keys, K *&alt, uint64_t n, int shift0, int passes)
+{
+    for (int p = 0; p < passes && n > 1; p++) partition_pass(c, keys, alt, n, lbcount::ShiftDigit<K>{shift0 + 8 * p});
 }
 
 template <typename K> void do_count(leon_ctx *c)
@@ -219,30 +222,45 @@ template <typename K> void do_count(leon_ctx *c)
                       c->d_offsets.as<uint64_t>(), koff, c->nreads, k, keys));
     CUDA_TRY(cudaEventRecord(c->ev[3], st));
 
-    // LSD radix sort over the ceil(2k/8) low bytes (the sentinel is all ones, so it stays the maximum)
-    int passes = nk > 1 ? (2 * k + 7) / 8 : 0;
-    radix_sort<K>(c, keys, alt, nk, 0, passes);
-    c->tm.sort_passes = (uint32_t)passes;
+    // partition by hash into buckets of ~BcCfg::TARGET keys: LSD passes over the top `bits` bits of key_mix
+    int bits = 0;
+    while (bits < 24 && (nk >> bits) > (uint64_t)BcCfg<K>::TARGET) bits++;
+    c->tm.sort_passes = 0;
+    {
+        // pass p handles hash bits [64 - bits + off, 64 - bits + off + w)
+        int off = 0;
+        while (off < bits) {
+            int w = bits - off < 8 ? bits - off : 8;
+            partition_pass(c, keys, alt, nk, HashDigit<K>{64 - bits + off, (1u << w) - 1u});
+            off += w;
+            c->tm.sort_passes++;
+        }
+    }
     c->tm.sort_keys = nk;
-    c->sorted_keys = keys;
-    c->heads = alt;
     CUDA_TRY(cudaEventRecord(c->ev[4], st));
 
-    // run heads -> abundance histogram
+    // per-bucket counting in shared-memory tables -> abundance histogram, solid list
     c->d_histo.reserve(10001 * 8);
-    c->d_stats.reserve(sizeof(CountStats));
+    c->d_stats.reserve(sizeof(CountStats) + 8);
     CUDA_TRY(cudaMemsetAsync(c->d_histo.p, 0, 10001 * 8, st));
-    CUDA_TRY(cudaMemsetAsync(c->d_stats.p, 0, sizeof(CountStats), st));
-    c->nruns = 0;
+    CUDA_TRY(cudaMemsetAsync(c->d_stats.p, 0, sizeof(CountStats) + 8, st));
+    c->nsolid = 0;
+    c->solid_keys = alt;
     CountStats stats = {0, 0, 0};
     if (nk) {
-        uint64_t *tot_runs = lbscan::exclusive_scan<uint64_t>(nk, HeadIn64<K>{keys}, HeadOut64{(uint64_t *)alt}, c->d_scan, st, c->lc);
-        c->nruns = fetch_scalar(c, tot_runs);
-        unsigned grid = (unsigned)std::min<uint64_t>((c->nruns + 255) / 256, (uint64_t)NUM_SMS * 8);
-        if (grid == 0) grid = 1;
-        LB_TIMED(c->kt, "k_run_stats", st, LB_LAUNCH(c->lc, (k_run_stats<K>), grid, 256, 10001 * 4, st, keys, (const uint64_t *)alt, c->nruns, nk,
-                  (unsigned long long *)c->d_histo.p, c->d_stats.as<CountStats>()));
+        uint64_t nbuckets = 1ull << bits;
+        c->d_bstart.reserve((nbuckets + 2) * 8);
+        c->d_solid_cnt.reserve((nk / 2 + 2) * 4);
+        unsigned grid = (unsigned)std::min<uint64_t>((nk + 255) / 256, (uint64_t)NUM_SMS * 16);
+        LB_TIMED(c->kt, "k_bucket_bounds", st, LB_LAUNCH(c->lc, (k_bucket_bounds<K>), grid, 256, 0, st, keys, nk, bits, nbuckets, c->d_bstart.as<uint64_t>()));
+        CUDA_TRY(cudaFuncSetAttribute(k_bucket_count<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BcCfg<K>::SMEM));
+        unsigned long long *nsolid_d = (unsigned long long *)(c->d_stats.as<uint8_t>() + sizeof(CountStats));
+        LB_TIMED(c->kt, "k_bucket_count", st, LB_LAUNCH(c->lc, (k_bucket_count<K>), (unsigned)nbuckets, BC_THREADS, BcCfg<K>::SMEM, st, keys,
+                  c->d_bstart.as<uint64_t>(), (unsigned long long *)c->d_histo.p, c->d_stats.as<CountStats>(), alt,
+                  c->d_solid_cnt.as<uint32_t>(), nsolid_d));
         stats = fetch_scalar(c, c->d_stats.as<CountStats>());
+        c->nsolid = fetch_scalar(c, nsolid_d);
+        if (stats.nb_valid >> 62) throw LeonError(LEON_E_OVERFLOW, "k-mer counting: a bucket could not be split any further");
     }
     c->h_histo.reserve(10001 * 8);
     CUDA_TRY(cudaMemcpyAsync(c->h_histo.p, c->d_histo.p, 10001 * 8, cudaMemcpyDeviceToHost, st));
@@ -279,10 +297,10 @@ template <typename K> void do_bloom(leon_ctx *c)
     c->d_bloom.reserve(alloc);
     b.words = c->d_bloom.as<uint32_t>();
     CUDA_TRY(cudaMemsetAsync(b.words, 0, alloc, st));
-    if (c->nruns) {
-        unsigned grid = (unsigned)std::min<uint64_t>((c->nruns + 255) / 256, (uint64_t)NUM_SMS * 8);
-        LB_TIMED(c->kt, "k_insert_runs", st, LB_LAUNCH(c->lc, (lbbloom::k_insert_runs<K>), grid, 256, 0, st, (const K *)c->sorted_keys, (const uint64_t *)c->heads,
-                  c->nruns, c->nkmers, (uint32_t)c->min_abundance, b, c->d_tbl.as<uint64_t>()));
+    if (c->nsolid) {
+        unsigned grid = (unsigned)std::min<uint64_t>((c->nsolid + 255) / 256, (uint64_t)NUM_SMS * 8);
+        LB_TIMED(c->kt, "k_insert_solid", st, LB_LAUNCH(c->lc, (lbbloom::k_insert_solid<K>), grid, 256, 0, st, (const K *)c->solid_keys,
+                  c->d_solid_cnt.as<uint32_t>(), c->nsolid, (uint32_t)c->min_abundance, b, c->d_tbl.as<uint64_t>()));
     }
     CUDA_TRY(cudaEventRecord(c->ev[6], st));
     c->phase = PH_BLOOM;
@@ -796,7 +814,7 @@ void leon_destroy(leon_ctx *c)
     if (c->dict_thread.joinable()) c->dict_thread.join();
     if (c->st) cudaStreamSynchronize(c->st);
     DevBuf *dev[] = {&c->d_bases, &c->d_offsets, &c->d_quals, &c->d_koff, &c->d_keys, &c->d_keys_alt, &c->d_tile_hist, &c->d_tile_off,
-                     &c->d_scan, &c->d_histo, &c->d_stats, &c->d_tbl, &c->d_bloom, &c->d_apos, &c->d_aaddr, &c->d_insflag, &c->d_plist,
+                     &c->d_scan, &c->d_bstart, &c->d_solid_cnt, &c->d_histo, &c->d_stats, &c->d_tbl, &c->d_bloom, &c->d_apos, &c->d_aaddr, &c->d_insflag, &c->d_plist,
                      &c->d_cand_pos, &c->d_cand_key, &c->d_cand_slot, &c->d_state, &c->d_ct_proxy, &c->d_ct_keys, &c->d_ct_ins,
                      &c->d_ct_fu, &c->d_dict_keys[0], &c->d_dict_keys[1], &c->d_dict_addr[0], &c->d_dict_addr[1], &c->d_dict_time[0],
                      &c->d_dict_time[1], &c->d_anchors, &c->d_counters, &c->d_bif, &c->d_err, &c->d_recs, &c->d_symoff, &c->d_srec, &c->d_srec_alt, &c->d_segstart,
@@ -1010,7 +1028,8 @@ int leon_debug_fetch(leon_ctx *c, const char *name, void *dst, uint64_t cap, uin
     uint64_t n = 0;
     std::string s(name);
     size_t ksz = c->opts.kmer_size <= 31 ? 8 : 16;
-    if (s == "sorted_keys") { src = c->sorted_keys; n = c->nkmers * ksz; }
+    if (s == "solid_keys") { src = c->solid_keys; n = c->nsolid * ksz; }
+    else if (s == "solid_cnt") { src = c->d_solid_cnt.p; n = c->nsolid * 4; }
     else if (s == "anchors") { src = c->d_anchors.p; n = c->dict_count * ksz; }
     else if (s == "recs") { src = c->d_recs.p; n = c->nreads * sizeof(lbwalk::ReadRec); }
     else if (s == "koff") { src = c->d_koff.p; n = (c->nreads + 1) * 8; }
