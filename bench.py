@@ -42,6 +42,7 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--reads", type=int, default=0, help="override the number of reads per GPU (debug; marks the line invalid)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--anchor-batch", type=int, default=0, help="reads per anchor-resolution batch (0 = library default)")
     ap.add_argument("--phases", action="store_true", help="print per-phase / per-kernel device times to stderr")
     return ap.parse_args()
 
@@ -253,7 +254,8 @@ def main_b200(args):
     pin_o.array[:] = offs
     offs = pin_o.array
 
-    eng = leon_b200.Leon(kmer_size=KMER, reads_per_block=RPB, has_qual=False, device=local_rank)
+    eng = leon_b200.Leon(kmer_size=KMER, reads_per_block=RPB, has_qual=False, device=local_rank,
+                         anchor_batch=args.anchor_batch)
     stream = torch.cuda.current_stream()
     eng.set_stream(stream.cuda_stream)
     if world > 1:

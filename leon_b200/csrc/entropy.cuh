@@ -334,40 +334,35 @@ __global__ void k_block_descs(const uint64_t *__restrict__ symoff, uint64_t nrea
     StreamDesc d;
     d.rec_base = base;
     d.nsym = end - base;
-    d.out_base = 2 * base + 16 * b;
-    d.out_cap = 2 * (end - base) + 16;
+    d.out_base = 2 * base + 1024 * b;
+    d.out_cap = 2 * (end - base) + 1024;
     descs[b] = d;
 }
 
 // One coding step (RangeEncoder::encode, C/RangeCoder.cpp:106-134) with range / total done as
-// hi64((range + inc) * magic) >> shift (div_magic).  `emit` receives every byte shifted out.
-template <typename Emit>
-LB_D void rc_step(uint64_t &low, uint64_t &range, uint32_t lo, uint32_t w, uint64_t m, uint32_t sh, Emit &emit)
+// hi64((range + inc) * magic) >> shift (div_magic).  Bytes shifted out go to *op (op advances); when `store` is
+// false (output region exhausted, reported as overflow by the caller) they are only counted.
+LB_D void rc_step(uint64_t &low, uint64_t &range, const uint4 t, const uint32_t sh, uint8_t *&op, const bool store)
 {
-    uint64_t q = __umul64hi(range + (sh >> 7), m) >> (sh & 63u);
-    low += (uint64_t)lo * q;
-    range = q * (uint64_t)w;
+    const uint64_t m = ((uint64_t)t.w << 32) | t.z;
+    const uint64_t q = __umul64hi(range + (sh >> 7), m) >> (sh & 63u);
+    low += (uint64_t)t.x * q;
+    range = q * (uint64_t)t.y;
     while (true) {
-        uint32_t xh = (uint32_t)(low >> 32) ^ (uint32_t)((low + range) >> 32);
-        if (xh >= (1u << 24)) {                       // top bytes of low and low + range differ
-            if ((uint32_t)(range >> 32) >= (1u << 16)) break;
+        const uint32_t lh = (uint32_t)(low >> 32);
+        const uint32_t sh32 = (uint32_t)((low + range) >> 32);
+        if ((lh ^ sh32) >= (1u << 24)) {                       // top bytes of low and low + range differ
+            if ((uint32_t)(range >> 32) >= (1u << 16)) break;  // range >= 2^48
             range = (0 - low) & (RC_BOTTOM - 1);
         }
-        emit((uint8_t)(low >> 56));
+        if (store) *op = (uint8_t)(lh >> 24);
+        op++;
         range <<= 8;
         low <<= 8;
     }
 }
 
-struct ByteSink {
-    uint8_t *p;
-    uint32_t n, cap;
-    LB_D void operator()(uint8_t b)
-    {
-        if (n < cap) p[n] = b;
-        n++;
-    }
-};
+constexpr uint32_t RC_MAX_BYTES_PER_SYMBOL = 12;   // <= 4 bytes of information + one clamp and its 7 refill shifts
 
 // RangeEncoder::encode / flush, C/RangeCoder.cpp:106-145.  One warp per stream: the 32 lanes stage the next 32 symbol
 // records in shared memory (coalesced loads, issued one batch ahead), lane 0 runs the low/range recurrence over them
@@ -376,13 +371,15 @@ __global__ void __launch_bounds__(32) k_range_encode(const uint4 *__restrict__ r
                                                      const StreamDesc *__restrict__ descs, uint8_t *__restrict__ out_all,
                                                      uint64_t *__restrict__ out_size, int always_flush, uint32_t *overflow)
 {
-    __shared__ uint4 srec[2][33];
-    __shared__ uint32_t ssh[2][33];
+    __shared__ uint4 srec[2][34];
+    __shared__ uint32_t ssh[2][34];
     const int lane = threadIdx.x;
     const StreamDesc d = descs[blockIdx.x];
     const uint4 *rec = rec_all + d.rec_base;
     const uint8_t *sh = sh_all + d.rec_base;
-    ByteSink sink{out_all + d.out_base, 0u, (uint32_t)(d.out_cap > 0xfffffff0ull ? 0xfffffff0ull : d.out_cap)};
+    uint8_t *const out0 = out_all + d.out_base;
+    uint8_t *op = out0;
+    bool ovf = false;
     uint64_t low = 0, range = ~0ull;
     uint4 nx = make_uint4(0u, 1u, 0xffffffffu, 0xffffffffu);
     uint32_t nsx = 0x80u;
@@ -396,44 +393,55 @@ __global__ void __launch_bounds__(32) k_range_encode(const uint4 *__restrict__ r
         __syncwarp();
         if (lane == 0) {
             const int steps = d.nsym - base < 32 ? (int)(d.nsym - base) : 32;
-            uint4 t = srec[buf][0];
-            uint32_t s = ssh[buf][0];
+            // room for the worst case of this batch, checked once instead of per byte
+            const bool store = (uint64_t)(op - out0) + 32 * RC_MAX_BYTES_PER_SYMBOL + 8 <= d.out_cap;
+            ovf |= !store;
+            const uint4 *sr = srec[buf];
+            const uint32_t *ss = ssh[buf];
             int j = 0;
             if (base == 0) {
                 // first symbol: range is 2^64 - 1, so range + inc may wrap; (2^64 * m) >> 64 == m
+                uint4 t = sr[0];
+                uint32_t s = ss[0];
                 uint64_t m = ((uint64_t)t.w << 32) | t.z;
                 uint64_t q = ((s >> 7) ? m : __umul64hi(range, m)) >> (s & 63u);
                 low = (uint64_t)t.x * q;
                 range = q * (uint64_t)t.y;
                 while ((low ^ (low + range)) < RC_TOP || range < RC_BOTTOM) {
                     if (range < RC_BOTTOM && (low ^ (low + range)) >= RC_TOP) range = (0 - low) & (RC_BOTTOM - 1);
-                    sink((uint8_t)(low >> 56));
+                    if (store) *op = (uint8_t)(low >> 56);
+                    op++;
                     range <<= 8;
                     low <<= 8;
                 }
-                t = srec[buf][1];
-                s = ssh[buf][1];
                 j = 1;
             }
-            for (; j < steps; j++) {
-                uint4 tn = srec[buf][j + 1];          // slot 32 exists: the arrays have 33 entries
-                uint32_t sn = ssh[buf][j + 1];
-                rc_step(low, range, t.x, t.y, ((uint64_t)t.w << 32) | t.z, s, sink);
-                t = tn;
-                s = sn;
+            uint4 ta = sr[j];
+            uint32_t sa = ss[j];
+            for (; j + 1 < steps; j += 2) {          // two symbols per iteration: no register rotation
+                uint4 tb = sr[j + 1];
+                uint32_t sb = ss[j + 1];
+                rc_step(low, range, ta, sa, op, store);
+                ta = sr[j + 2];                       // slots 32, 33 exist: the arrays have 34 entries
+                sa = ss[j + 2];
+                rc_step(low, range, tb, sb, op, store);
             }
+            if (j < steps) rc_step(low, range, ta, sa, op, store);
         }
         __syncwarp();
     }
     if (lane == 0) {
-        if (always_flush || sink.n > 0) {                       // DnaEncoder::writeBlock flushes only a non-empty buffer
+        uint64_t nout = (uint64_t)(op - out0);
+        if (always_flush || nout > 0) {                       // DnaEncoder::writeBlock flushes only a non-empty buffer
             for (int x = 0; x < 8; x++) {
-                sink((uint8_t)(low >> 56));
+                if (nout < d.out_cap) out0[nout] = (uint8_t)(low >> 56);
+                else ovf = true;
+                nout++;
                 low <<= 8;
             }
         }
-        out_size[blockIdx.x] = sink.n;
-        if (sink.n > sink.cap) *overflow = 1;
+        out_size[blockIdx.x] = nout;
+        if (ovf) *overflow = 1;
     }
 }
 

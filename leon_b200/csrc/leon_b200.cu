@@ -433,7 +433,8 @@ template <typename K> void do_anchors(leon_ctx *c)
     c->tm.anchor_batches = 0;
     c->tm.anchor_rounds = 0;
 
-    uint64_t S = c->opts.anchor_batch > 0 ? (uint64_t)c->opts.anchor_batch : 32768;
+    // measured on B200 (4.6 M reads): 32 k -> 30 ms, 256 k -> 12 ms, 1 M -> 11 ms, one batch -> 27 ms
+    uint64_t S = c->opts.anchor_batch > 0 ? (uint64_t)c->opts.anchor_batch : 524288;
     const bool adaptive = c->opts.anchor_batch <= 0;
     for (uint64_t lo = 0; lo < R;) {
         uint64_t hi = std::min(R, lo + S);
@@ -504,7 +505,7 @@ template <typename K> void do_anchors(leon_ctx *c)
                           dict_view<K>(c, c->dict_cur), apos, aaddr, (const uint8_t *)insflag);
         }
         if (adaptive) {
-            if ((uint64_t)nins * 50 < nb && S < (1ull << 20)) S *= 2;
+            if ((uint64_t)nins * 50 < nb && S < (1ull << 21)) S *= 2;
         }
         lo = hi;
     }
@@ -546,7 +547,7 @@ template <typename K> void do_encode(leon_ctx *c)
         c->d_dict_rec.reserve((nsym + 1) * sizeof(uint4));
         c->d_dict_sh.reserve(nsym + 1);
         c->d_dict_desc.reserve(sizeof(StreamDesc));
-        c->d_dict_out.reserve(2 * nsym + 64);
+        c->d_dict_out.reserve(2 * nsym + 1024);
         c->d_dict_size.reserve(16);
         CUDA_TRY(cudaMemsetAsync(c->d_counters.p, 0, 64, st));
         CUDA_TRY(cudaEventRecord(c->ev[13], st));
@@ -556,7 +557,7 @@ template <typename K> void do_encode(leon_ctx *c)
                                                   DictRecOut<K>{c->d_anchors.as<K>(), k, c->d_dict_rec.as<uint4>(), c->d_dict_sh.as<uint8_t>()},
                                                   c->d_scan2, s2, c->lc);
         if (c->opts.dict_on_device) {
-            StreamDesc d{0, nsym, 0, 2 * nsym + 16};
+            StreamDesc d{0, nsym, 0, 2 * nsym + 1024};
             c->h_desc.reserve(sizeof d);
             memcpy(c->h_desc.p, &d, sizeof d);
             CUDA_TRY(cudaMemcpyAsync(c->d_dict_desc.p, c->h_desc.p, sizeof d, cudaMemcpyHostToDevice, s2));
@@ -644,7 +645,7 @@ template <typename K> void do_encode(leon_ctx *c)
                       c->d_rec.as<uint4>(), c->d_sh.as<uint8_t>()));
         }
         c->d_descs.reserve(c->nblocks * sizeof(StreamDesc));
-        c->d_outall.reserve(2 * nsym + 16 * c->nblocks + 16);
+        c->d_outall.reserve(2 * nsym + 1024 * c->nblocks + 1024);
         c->d_outsize.reserve(c->nblocks * 8);
         c->d_dnaoff.reserve(c->nblocks * 8);
         c->d_bs.reserve(c->nblocks * 16);
