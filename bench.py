@@ -42,6 +42,7 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--reads", type=int, default=0, help="override the number of reads per GPU (debug; marks the line invalid)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--fastq", action="store_true", help="configs[2] shape: FASTQ with synthetic qualities, lossy (debug line)")
     ap.add_argument("--anchor-batch", type=int, default=0, help="reads per anchor-resolution batch (0 = library default)")
     ap.add_argument("--phases", action="store_true", help="print per-phase / per-kernel device times to stderr")
     return ap.parse_args()
@@ -249,12 +250,14 @@ def main_b200(args):
     total_reads = args.reads if args.reads else GENOME_LEN * COVERAGE // READ_LEN
     genome = synth.make_genome(GENOME_LEN, 1)
     pin_b = leon_b200.api.PinnedArray(total_reads * READ_LEN)
-    bases, offs, _ = synth.sample_reads(genome, total_reads, READ_LEN, 2, out_bases=pin_b.array)
+    pin_q = leon_b200.api.PinnedArray(total_reads * READ_LEN) if args.fastq else None
+    bases, offs, quals = synth.sample_reads(genome, total_reads, READ_LEN, 2, out_bases=pin_b.array, with_quals=args.fastq,
+                                            out_quals=pin_q.array if args.fastq else None)
     pin_o = leon_b200.api.PinnedArray((total_reads + 1) * 8, np.uint64)
     pin_o.array[:] = offs
     offs = pin_o.array
 
-    eng = leon_b200.Leon(kmer_size=KMER, reads_per_block=RPB, has_qual=False, device=local_rank,
+    eng = leon_b200.Leon(kmer_size=KMER, reads_per_block=RPB, has_qual=args.fastq, device=local_rank,
                          anchor_batch=args.anchor_batch)
     stream = torch.cuda.current_stream()
     eng.set_stream(stream.cuda_stream)
@@ -267,7 +270,7 @@ def main_b200(args):
         torch.cuda.synchronize()
 
     # ---- value: inputs resident in HBM
-    eng.upload(bases, offs)
+    eng.upload(bases, offs, quals)
     for _ in range(args.warmup):
         eng.run_device()
     sampler = ClockSampler(local_rank)
@@ -308,13 +311,13 @@ def main_b200(args):
 
     # ---- e2e: host buffers in, host buffers out, through the C ABI one-shot call
     for _ in range(min(args.warmup, 2)):
-        eng.compress(bases, offs, copy=False)
+        eng.compress(bases, offs, quals, copy=False)
     barrier()
     g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     g0.record(stream)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        r = eng.compress(bases, offs, copy=False)
+        r = eng.compress(bases, offs, quals, copy=False)
     g1.record(stream)
     barrier()
     e2e_wall = (time.perf_counter() - t0) * 1000.0
@@ -323,9 +326,9 @@ def main_b200(args):
         t = torch.tensor([e2e_ms], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item())
-    h2d = int(bases.nbytes + offs.nbytes)
+    h2d = int(bases.nbytes + offs.nbytes + (quals.nbytes if quals is not None else 0))
     d2h = int(len(r["bloom"]) + len(r["anchors_dict"]) + len(r["dna"]) + r["blocksizes"].nbytes +
-              r["anchor_pos"].nbytes + r["anchor_addr"].nbytes)
+              r["anchor_pos"].nbytes + r["anchor_addr"].nbytes + len(r["qual_text"]))
     e2e_value = total_reads / (e2e_ms / 1000.0)
 
     # ---- roofline of the dominant kernel (largest share of the device time of the timed region)
@@ -365,7 +368,7 @@ def main_b200(args):
         "metric": METRIC, "value": value, "unit": "reads/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u64",
         "data": "synthetic",
-        "config": {"workload": WORKLOAD if not args.reads else "DEBUG SIZE (invalid as a bench line): %d reads" % total_reads,
+        "config": {"workload": (WORKLOAD if not args.fastq else "DEBUG (configs[2] shape, FASTQ lossy)") if not args.reads else "DEBUG SIZE (invalid as a bench line): %d reads" % total_reads,
                    "reads": total_reads, "read_len": READ_LEN, "kmer_size": KMER, "reads_per_block": RPB,
                    "l2": "inputs larger than L2 (460 MB of bases, 2.6 GB of keys per step); no flush needed",
                    "parallelism": "1 process per GPU"},
