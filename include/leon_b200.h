@@ -140,6 +140,19 @@ typedef struct leon_kernel_time {
 } leon_kernel_time;
 int leon_get_kernel_times(const leon_ctx *ctx, leon_kernel_time *out, int cap, int *n);
 
+/* Multi-GPU (one process and one context per GPU of a node, NCCL over NVLink).  The reference has no
+ * counterpart (its parallelism is the Dispatcher's threads, DP/impl/Command.cpp:119).  Rank 0 calls
+ * leon_comm_unique_id and hands the 128 bytes to the other ranks (any host channel), every rank then calls
+ * leon_comm_init before leon_upload.  The read set is dealt in rounds of nranks * S consecutive reads, S to each rank
+ * in rank order, S = leon_comm_batch_reads() (a multiple of reads_per_block); every rank uploads its own reads in
+ * file order.  Counting exchanges k-mers by hash owner (all-to-all), the Bloom filter is the OR of the ranks' parts
+ * (all-gather), anchor candidates are all-gathered per batch so that addresses equal the serial reference's.  Each
+ * rank returns its own blocks (block j of round g on rank r is block (g * nranks + r) * S / reads_per_block + j of the
+ * file); the Bloom filter, the counts and (on rank 0) the anchor dictionary are those of the whole set. */
+int leon_comm_unique_id(void *id128);
+int leon_comm_init(leon_ctx *ctx, int rank, int nranks, const void *id128);
+int leon_comm_batch_reads(const leon_ctx *ctx, uint64_t *reads);
+
 /* Makes the context launch on the caller's CUDA stream (a cudaStream_t; e.g. the host framework's current stream)
  * instead of its own, so that the caller's events bracket the work.  The reference has no equivalent: its
  * Dispatcher owns its threads (DP/impl/Command.cpp:119). */

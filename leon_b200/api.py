@@ -10,7 +10,8 @@ LIB_PATH = os.path.join(HERE, "libleon_b200.so")
 ABI_SYMBOLS = [
     "leon_b200_abi_version", "leon_create", "leon_destroy", "leon_last_error", "leon_alloc_pinned", "leon_free_pinned",
     "leon_compress", "leon_upload", "leon_count", "leon_bloom_build", "leon_encode", "leon_run_device", "leon_fetch",
-    "leon_get_timings", "leon_get_kernel_times", "leon_set_stream", "leon_debug_bloom_query", "leon_debug_hashes", "leon_debug_fetch",
+    "leon_get_timings", "leon_get_kernel_times", "leon_set_stream", "leon_comm_unique_id", "leon_comm_init",
+    "leon_comm_batch_reads", "leon_debug_bloom_query", "leon_debug_hashes", "leon_debug_fetch",
 ]
 
 
@@ -90,6 +91,9 @@ def load_library(path=LIB_PATH):
     L.leon_get_timings.argtypes = [C.c_void_p, C.POINTER(Timings)]
     L.leon_get_kernel_times.argtypes = [C.c_void_p, C.POINTER(KernelTime), C.c_int, C.POINTER(C.c_int)]
     L.leon_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+    L.leon_comm_unique_id.argtypes = [C.c_void_p]
+    L.leon_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+    L.leon_comm_batch_reads.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
     L.leon_debug_bloom_query.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.c_void_p]
     L.leon_debug_hashes.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
     L.leon_debug_fetch.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
@@ -233,6 +237,26 @@ class Leon:
         n = C.c_int()
         self._check(self.L.leon_get_kernel_times(self.ctx, arr, 64, C.byref(n)))
         return {arr[i].name.decode(): (float(arr[i].ms_total), int(arr[i].launches)) for i in range(min(n.value, 64))}
+
+    @staticmethod
+    def comm_unique_id():
+        """128 opaque bytes (an ncclUniqueId) created by rank 0 and handed to every rank."""
+        L = load_library()
+        buf = (C.c_uint8 * 128)()
+        rc = L.leon_comm_unique_id(buf)
+        if rc != 0:
+            raise LeonError(rc, L.leon_last_error(None).decode())
+        return bytes(buf)
+
+    def comm_init(self, rank, nranks, unique_id):
+        buf = (C.c_uint8 * 128).from_buffer_copy(unique_id)
+        self._check(self.L.leon_comm_init(self.ctx, rank, nranks, buf))
+        self.rank, self.nranks = rank, nranks
+
+    def comm_batch_reads(self):
+        v = C.c_uint64()
+        self._check(self.L.leon_comm_batch_reads(self.ctx, C.byref(v)))
+        return int(v.value)
 
     def set_stream(self, cuda_stream_ptr):
         self._check(self.L.leon_set_stream(self.ctx, C.c_void_p(cuda_stream_ptr)))

@@ -91,8 +91,8 @@ template <typename K> struct LookupFn {
 // passes A and B.  apos[r] < 0: search all positions; apos[r] >= 0: only positions before it.
 template <typename K>
 __global__ void __launch_bounds__(256) k_anchor_lookup(const uint8_t *__restrict__ bases, const uint64_t *__restrict__ offsets,
-                                                       uint64_t lo, uint64_t hi, int k, DictDev<K> d, int32_t *apos,
-                                                       uint32_t *aaddr, const uint8_t *__restrict__ skip)
+                                                       uint64_t lo, uint64_t hi, uint64_t delta, int k, DictDev<K> d,
+                                                       int32_t *apos, uint32_t *aaddr, const uint8_t *__restrict__ skip)
 {
     const int lane = threadIdx.x & 31;
     uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(256) k_anchor_lookup(const uint8_t *__restrict
         uint64_t n = L - k + 1;
         int32_t cur = apos[r];
         uint64_t lim = cur >= 0 ? (uint64_t)cur : n;
-        LookupFn<K> f{d, k, (uint32_t)r, lim, lane, -1, 0};
+        LookupFn<K> f{d, k, (uint32_t)(r + delta), lim, lane, -1, 0};   // r + delta = index of the read in the whole set
         warp_for_kmers<K>(bases + o, L, k, 0, lim, lane, f);
         if (lane == 0 && f.pos >= 0) { apos[r] = (int32_t)f.pos; aaddr[r] = f.addr; }
     }
@@ -123,6 +123,12 @@ struct POut {
     uint32_t *plist; uint64_t lo;
     __device__ void operator()(uint64_t i, uint32_t ex, uint32_t v) const { if (v) plist[ex] = (uint32_t)(lo + i); }
 };
+// index of the P reads in the whole read set (local index + delta of the batch)
+__global__ void k_fill_gid(const uint32_t *__restrict__ plist, uint32_t m, uint64_t delta, uint32_t *__restrict__ gid)
+{
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < m) gid[j] = (uint32_t)(plist[j] + delta);
+}
 
 template <typename K> struct CandFn {
     const BloomDev &b; const uint64_t *tbl; int k; int lane;
@@ -254,16 +260,18 @@ template <typename K> struct DecideFn {
 
 template <typename K>
 __global__ void __launch_bounds__(256) k_round_decide(const uint8_t *__restrict__ bases, const uint64_t *__restrict__ offsets,
-                                                      const uint32_t *__restrict__ plist, uint32_t m, int k, CandTable<K> t,
-                                                      uint64_t salt, const uint32_t *__restrict__ cand_slot, uint8_t *state,
-                                                      uint32_t *remaining)
+                                                      const uint32_t *__restrict__ plist, uint32_t m, uint32_t joff, int k,
+                                                      CandTable<K> t, uint64_t salt, const uint32_t *__restrict__ cand_slot,
+                                                      uint8_t *state, uint32_t *remaining)
 {
     const int lane = threadIdx.x & 31;
     uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
-    for (uint32_t j = warp; j < m; j += nwarps) {
+    // this rank's P reads are entries [joff, joff + m) of the batch-wide P list; plist holds their local read indices
+    for (uint32_t jl = warp; jl < m; jl += nwarps) {
+        const uint32_t j = joff + jl;
         if (state[j] != ST_UNDECIDED) continue;
-        uint64_t r = plist[j];
+        uint64_t r = plist[jl];
         uint64_t o = offsets[r], L = offsets[r + 1] - o;
         uint64_t n = L - k + 1;
         DecideFn<K> f{t, k, j, salt, false, false};
@@ -276,25 +284,36 @@ __global__ void __launch_bounds__(256) k_round_decide(const uint8_t *__restrict_
     }
 }
 
+// after the states of the other ranks arrived: their new inserters enter the table
+__global__ void k_ins_update(const uint8_t *__restrict__ state, const uint32_t *__restrict__ cand_slot, uint32_t m, uint32_t *ins)
+{
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < m && state[j] == ST_INSERTER) atomicMin(&ins[cand_slot[j]], j);
+}
+
 struct InsIn {
     const uint8_t *state;
     __device__ uint32_t operator()(uint64_t j) const { return state[j] == ST_INSERTER ? 1u : 0u; }
 };
 template <typename K> struct InsOut {
-    const uint32_t *plist; const int32_t *cand_pos; const K *cand_key;
+    const uint32_t *gid; const int32_t *cand_pos; const K *cand_key;
     DictDev<K> d; uint32_t base_addr; K *anchors; int32_t *apos; uint32_t *aaddr; uint8_t *inserter;
+    uint32_t own_lo, own_hi; uint64_t delta;      // entries [own_lo, own_hi) are reads of this rank: local index = gid - delta
     __device__ void operator()(uint64_t j, uint32_t ex, uint32_t v) const
     {
         if (!v) return;
-        uint32_t r = plist[j];
+        uint32_t g = gid[j];
         uint32_t a = base_addr + ex;
         K key = cand_key[j];
         anchors[a] = key;
-        apos[r] = cand_pos[j];
-        aaddr[r] = a;
-        inserter[r] = 1;
+        if (j >= own_lo && j < own_hi) {
+            uint64_t r = g - delta;
+            apos[r] = cand_pos[j];
+            aaddr[r] = a;
+            inserter[r] = 1;
+        }
         uint64_t s = dict_hash(key) & d.mask;
-        while (atomicCAS(&d.time[s], LB_EMPTY32, r) != LB_EMPTY32) s = (s + 1) & d.mask;   // keys are distinct
+        while (atomicCAS(&d.time[s], LB_EMPTY32, g) != LB_EMPTY32) s = (s + 1) & d.mask;   // keys are distinct
         d.keys[s] = key;
         d.addr[s] = a;
     }

@@ -30,6 +30,17 @@ __global__ void __launch_bounds__(256) k_insert_solid(const K *__restrict__ keys
     }
 }
 
+// N GPUs: every rank inserted the solid k-mers it owns into a zeroed array of the full size; the filter is the OR of
+// the N arrays (all-gathered over NVLink into parts[rank][nwords]).
+__global__ void __launch_bounds__(256) k_or_reduce(const uint32_t *__restrict__ parts, int n, uint64_t nwords, uint32_t *__restrict__ out)
+{
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nwords; i += (uint64_t)gridDim.x * blockDim.x) {
+        uint32_t v = 0;
+        for (int r = 0; r < n; r++) v |= parts[(uint64_t)r * nwords + i];
+        out[i] = v;
+    }
+}
+
 // contains4 of COL/Bloom.hpp:645-798 executed by one warp: lane c*7+i tests hash i of candidate nucleotide c, so the
 // 28 probes of a step are ONE warp-wide gather inside the <= 514-byte window [racine, racine+13+4095].
 // All lanes must call it with the same `kmer`; returns the 4-bit mask (bit nt = neighbour nt present).

@@ -263,6 +263,18 @@ __global__ void __launch_bounds__(256) k_bucket_bounds(const K *__restrict__ key
 
 struct CountStats { unsigned long long nb_solid_total, nb_distinct, nb_valid; };
 
+// Where the keys of a bucket are.  One GPU: one source, its own partitioned array.  N GPUs: rank p owns the buckets
+// [lo, lo + gridDim.x) and received, from every rank s, that rank's keys of those buckets as one contiguous chunk
+// (still ordered by bucket): the keys of bucket b that came from s are [base[s] + bstart[s][b], base[s] + bstart[s][b+1])
+// with base[s] = (offset of the chunk in `keys`) - bstart[s][lo]  (unsigned wrap-around arithmetic).
+constexpr int MAX_RANKS = 8;
+struct BucketSrc {
+    int nsrc;
+    uint64_t lo;
+    const uint64_t *bstart[MAX_RANKS];
+    uint64_t base[MAX_RANKS];
+};
+
 constexpr int BC_THREADS = 256;
 constexpr int BC_STACK = 48;
 template <typename K> struct BcCfg {
@@ -285,7 +297,7 @@ template <> LB_D uint64_t table_tag<u128>(u128 key, uint64_t salt)
 // 128-bit keys are claimed through a 64-bit tag (CAS) and verified against the full key after the pass; a tag shared
 // by two different keys (probability ~2^-40 per run) makes the pass repeat with another salt.
 template <typename K>
-__global__ void __launch_bounds__(BC_THREADS) k_bucket_count(const K *__restrict__ keys, const uint64_t *__restrict__ bstart,
+__global__ void __launch_bounds__(BC_THREADS) k_bucket_count(const K *__restrict__ keys, const BucketSrc src,
                                                              unsigned long long *__restrict__ histo,
                                                              CountStats *__restrict__ stats, K *__restrict__ solid_keys,
                                                              uint32_t *__restrict__ solid_cnt,
@@ -302,11 +314,17 @@ __global__ void __launch_bounds__(BC_THREADS) k_bucket_count(const K *__restrict
     __shared__ unsigned long long sol_base;
     __shared__ unsigned long long acc[3];
     __shared__ uint32_t shist[256];
-    const uint64_t b = blockIdx.x;
-    const uint64_t beg = bstart[b], end = bstart[b + 1];
-    const uint64_t size = end - beg;
-    if (size == 0) return;
+    __shared__ uint64_t seg_beg[MAX_RANKS], seg_end[MAX_RANKS];
+    const uint64_t b = src.lo + blockIdx.x;
     const int tid = threadIdx.x;
+    if (tid < src.nsrc) {
+        seg_beg[tid] = src.base[tid] + src.bstart[tid][b];
+        seg_end[tid] = src.base[tid] + src.bstart[tid][b + 1];
+    }
+    __syncthreads();
+    uint64_t size = 0;
+    for (int sx = 0; sx < src.nsrc; sx++) size += seg_end[sx] - seg_beg[sx];
+    if (size == 0) return;
     if (tid == 0) {
         uint32_t ns = 1;
         while ((uint64_t)ns * BC_TARGET < size && ns < 32) ns <<= 1;
@@ -326,7 +344,8 @@ __global__ void __launch_bounds__(BC_THREADS) k_bucket_count(const K *__restrict
         for (int i = tid; i < BC_SLOTS; i += BC_THREADS) { tags[i] = ~0ull; cnts[i] = 0; }
         __syncthreads();
         // insert
-        for (uint64_t i = beg + tid; i < end; i += BC_THREADS) {
+        for (int sx = 0; sx < src.nsrc; sx++)
+        for (uint64_t i = seg_beg[sx] + tid; i < seg_end[sx]; i += BC_THREADS) {
             K key = keys[i];
             if (key == kmer_sentinel<K>()) continue;
             uint64_t mx = key_mix(key);
@@ -357,7 +376,8 @@ __global__ void __launch_bounds__(BC_THREADS) k_bucket_count(const K *__restrict
             continue;
         }
         if (sizeof(K) > 8) {   // verify the tags of 128-bit keys
-            for (uint64_t i = beg + tid; i < end; i += BC_THREADS) {
+            for (int sx = 0; sx < src.nsrc; sx++)
+            for (uint64_t i = seg_beg[sx] + tid; i < seg_end[sx]; i += BC_THREADS) {
                 K key = keys[i];
                 if (key == kmer_sentinel<K>()) continue;
                 uint64_t mx = key_mix(key);

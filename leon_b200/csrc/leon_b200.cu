@@ -11,6 +11,7 @@
 #include "walk.cuh"
 #include "entropy.cuh"
 #include "simplehash_table.h"
+#include "comm.cuh"
 #include <string.h>
 #include <vector>
 #include <algorithm>
@@ -83,7 +84,9 @@ struct leon_ctx {
     DevBuf d_keys, d_keys_alt, d_tile_hist, d_tile_off, d_scan, d_histo, d_stats, d_tbl;
     void *solid_keys = nullptr;      // solid list (abundance >= 2): keys in d_keys or d_keys_alt, counts in d_solid_cnt
     uint64_t nsolid = 0;
-    DevBuf d_bstart, d_solid_cnt;
+    DevBuf d_bstart, d_solid_cnt, d_bstart_all, d_keys_recv, d_solid_keys, d_pick, d_bloom_all, d_xchg;
+    Comm comm;
+    uint64_t nkmers_total = 0;
     PinBuf h_histo, h_small;
     leon_count_result cres;
     int32_t min_abundance = 0;
@@ -92,7 +95,7 @@ struct leon_ctx {
     BloomDev bloom;
     PinBuf h_bloom;
     // anchors
-    DevBuf d_apos, d_aaddr, d_insflag, d_plist, d_cand_pos, d_cand_key, d_cand_slot, d_state;
+    DevBuf d_apos, d_aaddr, d_insflag, d_plist, d_cand_pos, d_cand_key, d_cand_gid, d_cand_slot, d_state;
     DevBuf d_ct_proxy, d_ct_keys, d_ct_ins, d_ct_fu;
     DevBuf d_dict_keys[2], d_dict_addr[2], d_dict_time[2];
     int dict_cur = 0;
@@ -173,6 +176,16 @@ void do_upload(leon_ctx *c, const leon_reads *rd)
     c->phase = PH_UPLOADED;
 }
 
+// out[s * (n + 1) + p] = tables[s * stride + los[p]]: the bucket boundaries the all-to-all needs, N x (N + 1) values
+__global__ void k_pick_bounds(const uint64_t *__restrict__ tables, uint64_t stride, int n, const uint64_t *__restrict__ los,
+                              uint64_t *__restrict__ out)
+{
+    int i = threadIdx.x;
+    if (i >= n * (n + 1)) return;
+    int s = i / (n + 1), p = i % (n + 1);
+    out[i] = tables[(uint64_t)s * stride + los[p]];
+}
+
 // One stable 8-bit partition pass (tile histogram -> digit-major scan -> scatter); keys/alt are swapped so that `keys`
 // points at the result.
 template <typename K, typename D> void partition_pass(leon_ctx *c, K *&keys, K *&alt, uint64_t n, D digit)
@@ -222,14 +235,24 @@ template <typename K> void do_count(leon_ctx *c)
                       c->d_offsets.as<uint64_t>(), koff, c->nreads, k, keys));
     CUDA_TRY(cudaEventRecord(c->ev[3], st));
 
-    // partition by hash into buckets of ~BcCfg::TARGET keys: LSD passes over the top `bits` bits of key_mix
+    // partition by hash into buckets of ~BcCfg::TARGET keys: LSD passes over the top `bits` bits of key_mix.
+    // With N GPUs the buckets are sized on the total number of keys and rank p owns a contiguous range of them.
+    const int N = c->comm.n, me = c->comm.rank;
+    uint64_t nk_total = nk;
+    if (c->comm.active()) {
+        c->d_xchg.reserve(256);
+        CUDA_TRY(cudaMemcpyAsync(c->d_xchg.p, &c->nkmers, 8, cudaMemcpyHostToDevice, st));
+        NCCL_TRY(nccl_api().AllReduce(c->d_xchg.p, c->d_xchg.p, 1, ncclUint64, ncclSum, c->comm.comm, st));
+        nk_total = fetch_scalar(c, c->d_xchg.as<uint64_t>());
+    }
+    c->nkmers_total = nk_total;
     int bits = 0;
-    while (bits < 24 && (nk >> bits) > (uint64_t)BcCfg<K>::TARGET) bits++;
+    while (bits < 24 && ((nk_total >> bits) > (uint64_t)BcCfg<K>::TARGET || (1 << bits) < N)) bits++;
     c->tm.sort_passes = 0;
     {
         // pass p handles hash bits [64 - bits + off, 64 - bits + off + w)
         int off = 0;
-        while (off < bits) {
+        while (off < bits && nk > 0) {
             int w = bits - off < 8 ? bits - off : 8;
             partition_pass(c, keys, alt, nk, HashDigit<K>{64 - bits + off, (1u << w) - 1u});
             off += w;
@@ -247,21 +270,82 @@ template <typename K> void do_count(leon_ctx *c)
     c->nsolid = 0;
     c->solid_keys = alt;
     CountStats stats = {0, 0, 0};
+    const uint64_t nbuckets = 1ull << bits;
+    c->d_bstart.reserve((nbuckets + 2) * 8);
+    uint64_t *bstart = c->d_bstart.as<uint64_t>();
     if (nk) {
-        uint64_t nbuckets = 1ull << bits;
-        c->d_bstart.reserve((nbuckets + 2) * 8);
-        c->d_solid_cnt.reserve((nk / 2 + 2) * 4);
         unsigned grid = (unsigned)std::min<uint64_t>((nk + 255) / 256, (uint64_t)NUM_SMS * 16);
-        LB_TIMED(c->kt, "k_bucket_bounds", st, LB_LAUNCH(c->lc, (k_bucket_bounds<K>), grid, 256, 0, st, keys, nk, bits, nbuckets, c->d_bstart.as<uint64_t>()));
+        LB_TIMED(c->kt, "k_bucket_bounds", st, LB_LAUNCH(c->lc, (k_bucket_bounds<K>), grid, 256, 0, st, keys, nk, bits, nbuckets, bstart));
+    } else {
+        CUDA_TRY(cudaMemsetAsync(bstart, 0, (nbuckets + 1) * 8, st));
+    }
+    BucketSrc src;
+    memset(&src, 0, sizeof src);
+    const K *count_keys = keys;
+    uint64_t count_buckets = nbuckets, count_n = nk;
+    if (!c->comm.active()) {
+        src.nsrc = 1; src.lo = 0; src.bstart[0] = bstart; src.base[0] = 0;
+    } else {
+        // exchange: every rank gets, from every rank, the keys of the buckets it owns (all-to-all over NVLink)
+        auto lo_of = [&](int p) { return ((uint64_t)p * nbuckets + N - 1) / N; };
+        c->d_bstart_all.reserve((uint64_t)N * (nbuckets + 1) * 8);
+        uint64_t *ball = c->d_bstart_all.as<uint64_t>();
+        NCCL_TRY(nccl_api().AllGather(bstart, ball, nbuckets + 1, ncclUint64, c->comm.comm, st));
+        // boundary values bstart_s[lo_p] for all s, p
+        c->d_pick.reserve((uint64_t)N * (N + 1) * 8);
+        std::vector<uint64_t> los(N + 1);
+        for (int p = 0; p <= N; p++) los[p] = lo_of(p);
+        c->h_small.reserve(4096);
+        memcpy(c->h_small.p, los.data(), (N + 1) * 8);
+        CUDA_TRY(cudaMemcpyAsync(c->d_xchg.as<uint8_t>() + 64, c->h_small.p, (N + 1) * 8, cudaMemcpyHostToDevice, st));
+        LB_LAUNCH(c->lc, k_pick_bounds, 1, 128, 0, st, ball, nbuckets + 1, N, (const uint64_t *)(c->d_xchg.as<uint8_t>() + 64),
+                  c->d_pick.as<uint64_t>());
+        std::vector<uint64_t> pick((size_t)N * (N + 1));
+        CUDA_TRY(cudaMemcpyAsync(c->h_small.p, c->d_pick.p, pick.size() * 8, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        memcpy(pick.data(), c->h_small.p, pick.size() * 8);
+        auto B = [&](int s_, int p) { return pick[(size_t)s_ * (N + 1) + p]; };
+        uint64_t recv_total = 0;
+        std::vector<uint64_t> recv_off(N);
+        for (int s_ = 0; s_ < N; s_++) { recv_off[s_] = recv_total; recv_total += B(s_, me + 1) - B(s_, me); }
+        c->d_keys_recv.reserve((recv_total + 1) * sizeof(K));
+        K *recv = c->d_keys_recv.as<K>();
+        const size_t W = sizeof(K) / 8;
+        NCCL_TRY(nccl_api().GroupStart());
+        for (int p = 0; p < N; p++) {
+            uint64_t scnt = B(me, p + 1) - B(me, p), rcnt = B(p, me + 1) - B(p, me);
+            if (p == me) continue;
+            if (scnt) NCCL_TRY(nccl_api().Send(keys + B(me, p), scnt * W, ncclUint64, p, c->comm.comm, st));
+            if (rcnt) NCCL_TRY(nccl_api().Recv(recv + recv_off[p], rcnt * W, ncclUint64, p, c->comm.comm, st));
+        }
+        NCCL_TRY(nccl_api().GroupEnd());
+        {
+            uint64_t cnt = B(me, me + 1) - B(me, me);
+            if (cnt) CUDA_TRY(cudaMemcpyAsync(recv + recv_off[me], keys + B(me, me), cnt * sizeof(K), cudaMemcpyDeviceToDevice, st));
+        }
+        src.nsrc = N; src.lo = lo_of(me);
+        for (int s_ = 0; s_ < N; s_++) { src.bstart[s_] = ball + (uint64_t)s_ * (nbuckets + 1); src.base[s_] = recv_off[s_] - B(s_, me); }
+        count_keys = recv;
+        count_buckets = lo_of(me + 1) - lo_of(me);
+        count_n = recv_total;
+        c->d_solid_keys.reserve((recv_total / 2 + 2) * sizeof(K));
+        c->solid_keys = c->d_solid_keys.p;
+    }
+    if (count_n && count_buckets) {
+        c->d_solid_cnt.reserve((count_n / 2 + 2) * 4);
         CUDA_TRY(cudaFuncSetAttribute(k_bucket_count<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BcCfg<K>::SMEM));
         unsigned long long *nsolid_d = (unsigned long long *)(c->d_stats.as<uint8_t>() + sizeof(CountStats));
-        LB_TIMED(c->kt, "k_bucket_count", st, LB_LAUNCH(c->lc, (k_bucket_count<K>), (unsigned)nbuckets, BC_THREADS, BcCfg<K>::SMEM, st, keys,
-                  c->d_bstart.as<uint64_t>(), (unsigned long long *)c->d_histo.p, c->d_stats.as<CountStats>(), alt,
+        LB_TIMED(c->kt, "k_bucket_count", st, LB_LAUNCH(c->lc, (k_bucket_count<K>), (unsigned)count_buckets, BC_THREADS, BcCfg<K>::SMEM, st, count_keys,
+                  src, (unsigned long long *)c->d_histo.p, c->d_stats.as<CountStats>(), (K *)c->solid_keys,
                   c->d_solid_cnt.as<uint32_t>(), nsolid_d));
-        stats = fetch_scalar(c, c->d_stats.as<CountStats>());
         c->nsolid = fetch_scalar(c, nsolid_d);
-        if (stats.nb_valid >> 62) throw LeonError(LEON_E_OVERFLOW, "k-mer counting: a bucket could not be split any further");
     }
+    if (c->comm.active()) {   // global histogram and counters
+        NCCL_TRY(nccl_api().AllReduce(c->d_histo.p, c->d_histo.p, 10001, ncclUint64, ncclSum, c->comm.comm, st));
+        NCCL_TRY(nccl_api().AllReduce(c->d_stats.p, c->d_stats.p, 3, ncclUint64, ncclSum, c->comm.comm, st));
+    }
+    stats = fetch_scalar(c, c->d_stats.as<CountStats>());
+    if (stats.nb_valid >> 62) throw LeonError(LEON_E_OVERFLOW, "k-mer counting: a bucket could not be split any further");
     c->h_histo.reserve(10001 * 8);
     CUDA_TRY(cudaMemcpyAsync(c->h_histo.p, c->d_histo.p, 10001 * 8, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
@@ -301,6 +385,13 @@ template <typename K> void do_bloom(leon_ctx *c)
         unsigned grid = (unsigned)std::min<uint64_t>((c->nsolid + 255) / 256, (uint64_t)NUM_SMS * 8);
         LB_TIMED(c->kt, "k_insert_solid", st, LB_LAUNCH(c->lc, (lbbloom::k_insert_solid<K>), grid, 256, 0, st, (const K *)c->solid_keys,
                   c->d_solid_cnt.as<uint32_t>(), c->nsolid, (uint32_t)c->min_abundance, b, c->d_tbl.as<uint64_t>()));
+    }
+    if (c->comm.active()) {
+        uint64_t nwords = alloc / 4;
+        c->d_bloom_all.reserve((uint64_t)c->comm.n * alloc);
+        NCCL_TRY(nccl_api().AllGather(b.words, c->d_bloom_all.p, nwords, ncclUint32, c->comm.comm, st));
+        unsigned grid = (unsigned)std::min<uint64_t>((nwords + 255) / 256, (uint64_t)NUM_SMS * 8);
+        LB_TIMED(c->kt, "k_or_reduce", st, LB_LAUNCH(c->lc, lbbloom::k_or_reduce, grid, 256, 0, st, c->d_bloom_all.as<uint32_t>(), c->comm.n, nwords, b.words));
     }
     CUDA_TRY(cudaEventRecord(c->ev[6], st));
     c->phase = PH_BLOOM;
@@ -404,6 +495,28 @@ template <typename K> void dict_ensure(leon_ctx *c, uint64_t want_entries)
     c->dict_cur = other;
 }
 
+// In-place variable-size all-gather: rank p's part is buf[off[p] .. off[p] + cnt[p]) (elements of `esize` bytes).
+void allgather_v(leon_ctx *c, void *buf, const std::vector<uint32_t> &off, const std::vector<uint32_t> &cnt, size_t esize)
+{
+    NCCL_TRY(nccl_api().GroupStart());
+    for (int p = 0; p < c->comm.n; p++) {
+        if (!cnt[p]) continue;
+        uint8_t *part = (uint8_t *)buf + (size_t)off[p] * esize;
+        NCCL_TRY(nccl_api().Broadcast(part, part, (size_t)cnt[p] * esize, ncclUint8, p, c->comm.comm, c->st));
+    }
+    NCCL_TRY(nccl_api().GroupEnd());
+}
+
+// Reads per rank in one anchor batch.  With N ranks the read set is dealt in rounds of N * S consecutive reads, S to
+// each rank in rank order (leon_comm_shard): batch g holds the g-th such round, so batches follow the file order and
+// every rank works in every batch.  S is then a multiple of the block size so that blocks stay whole.
+uint64_t anchor_batch_reads(const leon_ctx *c)
+{
+    if (c->opts.anchor_batch > 0) return (uint64_t)c->opts.anchor_batch;
+    if (c->comm.n > 1) return 10ull * (uint64_t)c->opts.reads_per_block;
+    return 524288;   // measured on B200 (4.6 M reads): 32 k -> 30 ms, 256 k -> 12 ms, 1 M -> 11 ms, one batch -> 27 ms
+}
+
 // Phase 3a: anchors for all reads, in ordered batches (see anchors.cuh)
 template <typename K> void do_anchors(leon_ctx *c)
 {
@@ -411,6 +524,7 @@ template <typename K> void do_anchors(leon_ctx *c)
     cudaStream_t st = c->st;
     const int k = c->opts.kmer_size;
     const uint64_t R = c->nreads;
+    const int N = c->comm.n, me = c->comm.rank;
     const uint8_t *bases = c->d_bases.as<uint8_t>();
     const uint64_t *offsets = c->d_offsets.as<uint64_t>();
 
@@ -423,7 +537,6 @@ template <typename K> void do_anchors(leon_ctx *c)
     int32_t *apos = c->d_apos.as<int32_t>();
     uint32_t *aaddr = c->d_aaddr.as<uint32_t>();
     uint8_t *insflag = c->d_insflag.as<uint8_t>();
-    c->d_anchors.reserve((R + 1) * sizeof(K));
     c->d_counters.reserve(64);
     uint32_t *counters = c->d_counters.as<uint32_t>();   // [0] collision, [1] remaining
     c->dict_cap = 1 << 16;
@@ -433,34 +546,77 @@ template <typename K> void do_anchors(leon_ctx *c)
     c->tm.anchor_batches = 0;
     c->tm.anchor_rounds = 0;
 
-    // measured on B200 (4.6 M reads): 32 k -> 30 ms, 256 k -> 12 ms, 1 M -> 11 ms, one batch -> 27 ms
-    uint64_t S = c->opts.anchor_batch > 0 ? (uint64_t)c->opts.anchor_batch : 524288;
-    const bool adaptive = c->opts.anchor_batch <= 0;
-    for (uint64_t lo = 0; lo < R;) {
-        uint64_t hi = std::min(R, lo + S);
-        uint64_t nb = hi - lo;
+    const uint64_t S = anchor_batch_reads(c);
+    // number of batches: the same on every rank
+    uint64_t nbatches = (R + S - 1) / S;
+    uint64_t R_total = R;
+    if (N > 1) {
+        c->d_xchg.reserve(256);
+        uint64_t v[2] = {nbatches, R};
+        CUDA_TRY(cudaMemcpyAsync(c->d_xchg.p, v, 16, cudaMemcpyHostToDevice, st));
+        NCCL_TRY(nccl_api().AllReduce(c->d_xchg.p, c->d_xchg.p, 1, ncclUint64, ncclMax, c->comm.comm, st));
+        NCCL_TRY(nccl_api().AllReduce(c->d_xchg.as<uint64_t>() + 1, c->d_xchg.as<uint64_t>() + 1, 1, ncclUint64, ncclSum, c->comm.comm, st));
+        nbatches = fetch_scalar(c, c->d_xchg.as<uint64_t>());
+        R_total = fetch_scalar(c, c->d_xchg.as<uint64_t>() + 1);
+    }
+    if (R_total >= 0xfffffff0ull) throw LeonError(LEON_E_ARG, "more than 2^32-16 reads in one read set");
+    c->d_anchors.reserve((std::min<uint64_t>(R_total, 1ull << 22) + 1) * sizeof(K));
+    uint64_t anchors_cap = c->d_anchors.cap / sizeof(K);
+    std::vector<uint32_t> m_all(N, 0), m_off(N, 0);
+
+    for (uint64_t g = 0; g < nbatches; g++) {
+        const uint64_t lo = std::min(R, g * S), hi = std::min(R, (g + 1) * S);
+        const uint64_t nb = hi - lo;
+        const uint64_t delta = g * (uint64_t)(N - 1) * S + (uint64_t)me * S;   // local read index + delta = index in the whole set
         c->tm.anchor_batches++;
         // A: lookup against the dictionary of earlier batches
-        if (c->dict_count)
-            LB_LAUNCH(c->lc, (k_anchor_lookup<K>), warp_grid(nb), 256, 0, st, bases, offsets, lo, hi, k,
+        if (c->dict_count && nb)
+            LB_LAUNCH(c->lc, (k_anchor_lookup<K>), warp_grid(nb), 256, 0, st, bases, offsets, lo, hi, delta, k,
                       dict_view<K>(c, c->dict_cur), apos, aaddr, (const uint8_t *)nullptr);
         // P: no-hit reads in order
-        c->d_plist.reserve(nb * 4);
+        c->d_plist.reserve((nb + 1) * 4);
         uint32_t *plist = c->d_plist.as<uint32_t>();
-        uint32_t *mtot = lbscan::exclusive_scan<uint32_t>(nb, PIn{offsets, apos, lo, k}, POut{plist, lo}, c->d_scan, st, c->lc);
-        uint32_t m = fetch_scalar(c, mtot);
+        uint32_t m_own = 0;
+        if (nb) {
+            uint32_t *mtot = lbscan::exclusive_scan<uint32_t>(nb, PIn{offsets, apos, lo, k}, POut{plist, lo}, c->d_scan, st, c->lc);
+            m_own = fetch_scalar(c, mtot);
+        }
+        uint32_t m = m_own, joff = 0;
+        if (N > 1) {   // sizes of everybody's P list
+            CUDA_TRY(cudaMemcpyAsync(c->d_xchg.as<uint32_t>() + 16 + me, &m_own, 4, cudaMemcpyHostToDevice, st));
+            NCCL_TRY(nccl_api().AllGather(c->d_xchg.as<uint32_t>() + 16 + me, c->d_xchg.as<uint32_t>() + 16, 1, ncclUint32, c->comm.comm, st));
+            c->h_small.reserve(256);
+            CUDA_TRY(cudaMemcpyAsync(c->h_small.p, c->d_xchg.as<uint32_t>() + 16, 4 * N, cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaStreamSynchronize(st));
+            memcpy(m_all.data(), c->h_small.p, 4 * N);
+            uint64_t tot = 0;
+            for (int p = 0; p < N; p++) { m_off[p] = (uint32_t)tot; tot += m_all[p]; }
+            if (tot >= 0xfffffff0ull) throw LeonError(LEON_E_OVERFLOW, "anchor batch with more than 2^32 candidate reads");
+            m = (uint32_t)tot;
+            joff = m_off[me];
+        }
         uint32_t nins = 0;
         if (m) {
             c->d_cand_pos.reserve((uint64_t)m * 4);
             c->d_cand_key.reserve((uint64_t)m * sizeof(K));
+            c->d_cand_gid.reserve((uint64_t)m * 4);
             c->d_cand_slot.reserve((uint64_t)m * 4);
             c->d_state.reserve(m);
             int32_t *cand_pos = c->d_cand_pos.as<int32_t>();
             K *cand_key = c->d_cand_key.as<K>();
+            uint32_t *cand_gid = c->d_cand_gid.as<uint32_t>();
             uint32_t *cand_slot = c->d_cand_slot.as<uint32_t>();
             uint8_t *state = c->d_state.as<uint8_t>();
-            LB_LAUNCH(c->lc, (k_candidates<K>), warp_grid(m), 256, 0, st, bases, offsets, plist, m, k, c->bloom,
-                      c->d_tbl.as<uint64_t>(), cand_pos, cand_key);
+            if (m_own) {
+                LB_LAUNCH(c->lc, k_fill_gid, cdiv_u(m_own, 256), 256, 0, st, plist, m_own, delta, cand_gid + joff);
+                LB_LAUNCH(c->lc, (k_candidates<K>), warp_grid(m_own), 256, 0, st, bases, offsets, plist, m_own, k, c->bloom,
+                          c->d_tbl.as<uint64_t>(), cand_pos + joff, cand_key + joff);
+            }
+            if (N > 1) {   // candidates of all ranks, in the order of the whole read set
+                allgather_v(c, cand_pos, m_off, m_all, 4);
+                allgather_v(c, cand_key, m_off, m_all, sizeof(K));
+                allgather_v(c, cand_gid, m_off, m_all, 4);
+            }
             // table over candidate values
             uint64_t tcap = 1024;
             while (tcap < 2ull * m) tcap <<= 1;
@@ -482,32 +638,45 @@ template <typename K> void do_anchors(leon_ctx *c)
                 if (attempt > 8) throw LeonError(LEON_E_OVERFLOW, "anchor candidate table: repeated proxy collisions");
                 salt = salt * 6364136223846793005ULL + 1442695040888963407ULL;
             }
-            // R: rounds of deterministic reservations
+            // R: rounds of deterministic reservations; every rank decides its own reads, states are shared per round
             while (true) {
                 c->tm.anchor_rounds++;
                 CUDA_TRY(cudaMemsetAsync(t.fu, 0xff, tcap * 4, st));
                 CUDA_TRY(cudaMemsetAsync(counters + 1, 0, 4, st));
                 LB_LAUNCH(c->lc, k_round_fu, cdiv_u(m, 256), 256, 0, st, state, cand_slot, m, t.fu);
-                LB_LAUNCH(c->lc, (k_round_decide<K>), warp_grid(m), 256, 0, st, bases, offsets, plist, m, k, t, salt, cand_slot,
-                          state, counters + 1);
+                if (m_own)
+                    LB_LAUNCH(c->lc, (k_round_decide<K>), warp_grid(m_own), 256, 0, st, bases, offsets, plist, m_own, joff, k, t, salt,
+                              cand_slot, state, counters + 1);
+                if (N > 1) {
+                    allgather_v(c, state, m_off, m_all, 1);
+                    LB_LAUNCH(c->lc, k_ins_update, cdiv_u(m, 256), 256, 0, st, state, cand_slot, m, t.ins);
+                    NCCL_TRY(nccl_api().AllReduce(counters + 1, counters + 1, 1, ncclUint32, ncclSum, c->comm.comm, st));
+                }
                 if (!fetch_scalar(c, counters + 1)) break;
             }
-            // I: addresses in read order, insertion into D
+            // I: addresses in read order, insertion into D (every rank inserts every new anchor)
             dict_ensure<K>(c, c->dict_count + m);
-            InsOut<K> io{plist, cand_pos, cand_key, dict_view<K>(c, c->dict_cur), (uint32_t)c->dict_count,
-                         c->d_anchors.as<K>(), apos, aaddr, insflag};
+            if (c->dict_count + m + 1 > anchors_cap) {
+                // grow the anchor list (keeps its content)
+                uint64_t ncap = std::max<uint64_t>(anchors_cap * 2, c->dict_count + m + 1);
+                DevBuf nbuf;
+                nbuf.reserve(ncap * sizeof(K));
+                CUDA_TRY(cudaMemcpyAsync(nbuf.p, c->d_anchors.p, c->dict_count * sizeof(K), cudaMemcpyDeviceToDevice, st));
+                CUDA_TRY(cudaStreamSynchronize(st));
+                c->d_anchors.release();
+                c->d_anchors = nbuf;
+                anchors_cap = ncap;
+            }
+            InsOut<K> io{cand_gid, cand_pos, cand_key, dict_view<K>(c, c->dict_cur), (uint32_t)c->dict_count,
+                         c->d_anchors.as<K>(), apos, aaddr, insflag, joff, joff + m_own, delta};
             uint32_t *itot = lbscan::exclusive_scan<uint32_t>(m, InsIn{state}, io, c->d_scan, st, c->lc);
             nins = fetch_scalar(c, itot);
             c->dict_count += nins;
             // B: anchors of this batch can pre-empt later reads of the batch at earlier positions
-            if (nins)
-                LB_LAUNCH(c->lc, (k_anchor_lookup<K>), warp_grid(nb), 256, 0, st, bases, offsets, lo, hi, k,
+            if (nins && nb)
+                LB_LAUNCH(c->lc, (k_anchor_lookup<K>), warp_grid(nb), 256, 0, st, bases, offsets, lo, hi, delta, k,
                           dict_view<K>(c, c->dict_cur), apos, aaddr, (const uint8_t *)insflag);
         }
-        if (adaptive) {
-            if ((uint64_t)nins * 50 < nb && S < (1ull << 21)) S *= 2;
-        }
-        lo = hi;
     }
     CUDA_TRY(cudaEventRecord(c->ev[7], st));
 }
@@ -556,7 +725,9 @@ template <typename K> void do_encode(leon_ctx *c)
             lbscan::exclusive_scan<lbscan::U32x4>(A, DictCountIn<K>{c->d_anchors.as<K>(), k},
                                                   DictRecOut<K>{c->d_anchors.as<K>(), k, c->d_dict_rec.as<uint4>(), c->d_dict_sh.as<uint8_t>()},
                                                   c->d_scan2, s2, c->lc);
-        if (c->opts.dict_on_device) {
+        if (c->comm.rank != 0) {
+            // the dump is identical on every rank: rank 0 codes it
+        } else if (c->opts.dict_on_device) {
             StreamDesc d{0, nsym, 0, 2 * nsym + 1024};
             c->h_desc.reserve(sizeof d);
             memcpy(c->h_desc.p, &d, sizeof d);
@@ -662,7 +833,9 @@ template <typename K> void do_encode(leon_ctx *c)
                   c->d_bs.as<uint64_t>());
     }
     // join the dictionary coder
-    if (c->opts.dict_on_device) {
+    if (c->comm.rank != 0) {
+        c->dict_nbytes = 0;
+    } else if (c->opts.dict_on_device) {
         CUDA_TRY(cudaStreamWaitEvent(st, c->ev[14], 0));
         c->dict_nbytes = fetch_scalar(c, c->d_dict_size.as<uint64_t>());
         if (fetch_scalar(c, ovf + 1)) throw LeonError(LEON_E_OVERFLOW, "range coder output of the anchor dictionary exceeded its capacity bound");
@@ -691,7 +864,8 @@ void do_fetch(leon_ctx *c, leon_result *out)
     c->h_bloom.reserve(c->bloom.nbytes + 8);
     CUDA_TRY(cudaMemcpyAsync(c->h_bloom.p, c->bloom.words, c->bloom.nbytes, cudaMemcpyDeviceToHost, st));
     c->h_dict.reserve(c->dict_nbytes + 8);
-    if (c->opts.dict_on_device) CUDA_TRY(cudaMemcpyAsync(c->h_dict.p, c->d_dict_out.p, c->dict_nbytes, cudaMemcpyDeviceToHost, st));
+    if (c->comm.rank != 0) { }
+    else if (c->opts.dict_on_device) CUDA_TRY(cudaMemcpyAsync(c->h_dict.p, c->d_dict_out.p, c->dict_nbytes, cudaMemcpyDeviceToHost, st));
     else memcpy(c->h_dict.p, c->dict_host_out.data(), c->dict_nbytes);
     c->h_dna.reserve(c->dna_nbytes + 8);
     c->h_bs.reserve(c->nblocks * 16 + 8);
@@ -814,8 +988,10 @@ void leon_destroy(leon_ctx *c)
     cudaSetDevice(c->opts.device);
     if (c->dict_thread.joinable()) c->dict_thread.join();
     if (c->st) cudaStreamSynchronize(c->st);
+    if (c->comm.comm) nccl_api().CommDestroy(c->comm.comm);
     DevBuf *dev[] = {&c->d_bases, &c->d_offsets, &c->d_quals, &c->d_koff, &c->d_keys, &c->d_keys_alt, &c->d_tile_hist, &c->d_tile_off,
-                     &c->d_scan, &c->d_bstart, &c->d_solid_cnt, &c->d_histo, &c->d_stats, &c->d_tbl, &c->d_bloom, &c->d_apos, &c->d_aaddr, &c->d_insflag, &c->d_plist,
+                     &c->d_scan, &c->d_bstart, &c->d_solid_cnt, &c->d_bstart_all, &c->d_keys_recv, &c->d_solid_keys, &c->d_pick,
+                     &c->d_bloom_all, &c->d_xchg, &c->d_cand_gid, &c->d_histo, &c->d_stats, &c->d_tbl, &c->d_bloom, &c->d_apos, &c->d_aaddr, &c->d_insflag, &c->d_plist,
                      &c->d_cand_pos, &c->d_cand_key, &c->d_cand_slot, &c->d_state, &c->d_ct_proxy, &c->d_ct_keys, &c->d_ct_ins,
                      &c->d_ct_fu, &c->d_dict_keys[0], &c->d_dict_keys[1], &c->d_dict_addr[0], &c->d_dict_addr[1], &c->d_dict_time[0],
                      &c->d_dict_time[1], &c->d_anchors, &c->d_counters, &c->d_bif, &c->d_err, &c->d_recs, &c->d_symoff, &c->d_srec, &c->d_srec_alt, &c->d_segstart,
@@ -936,6 +1112,45 @@ int leon_get_timings(const leon_ctx *c, leon_timings *out)
 {
     if (!c || !out) return LEON_E_ARG;
     *out = c->tm;
+    return LEON_OK;
+}
+
+int leon_comm_unique_id(void *id128)
+{
+    if (!id128) return LEON_E_ARG;
+    std::string err;
+    if (!nccl_api().load(err)) { g_create_error = err; return LEON_E_CUDA; }
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+    ncclUniqueId id;
+    if (nccl_api().GetUniqueId(&id) != ncclSuccess) { g_create_error = "ncclGetUniqueId failed"; return LEON_E_CUDA; }
+    memcpy(id128, &id, 128);
+    return LEON_OK;
+}
+
+int leon_comm_init(leon_ctx *c, int rank, int nranks, const void *id128)
+{
+    if (!c || !id128) return LEON_E_ARG;
+    LB_API_BEGIN
+    if (nranks < 1 || nranks > lbcount::MAX_RANKS || rank < 0 || rank >= nranks)
+        throw LeonError(LEON_E_ARG, "leon_comm_init: 1 <= nranks <= 8 and 0 <= rank < nranks");
+    if (c->comm.comm) throw LeonError(LEON_E_STATE, "leon_comm_init: communicator already set");
+    if (nranks > 1 && c->opts.anchor_batch > 0 && c->opts.anchor_batch % c->opts.reads_per_block)
+        throw LeonError(LEON_E_ARG, "leon_comm_init: anchor_batch must be a multiple of reads_per_block");
+    std::string err;
+    if (!nccl_api().load(err)) throw LeonError(LEON_E_CUDA, err);
+    CUDA_TRY(cudaSetDevice(c->opts.device));
+    ncclUniqueId id;
+    memcpy(&id, id128, 128);
+    NCCL_TRY(nccl_api().CommInitRank(&c->comm.comm, nranks, id, rank));
+    c->comm.rank = rank;
+    c->comm.n = nranks;
+    LB_API_END(c)
+}
+
+int leon_comm_batch_reads(const leon_ctx *c, uint64_t *reads)
+{
+    if (!c || !reads) return LEON_E_ARG;
+    *reads = anchor_batch_reads(c);
     return LEON_OK;
 }
 
