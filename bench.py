@@ -211,10 +211,12 @@ def algorithmic_bytes(kernel, st):
     kb = 8 if KMER <= 31 else 16
     if kernel == "k_walk":            # one 544-byte Bloom window per extension step: (L - k) steps per read
         return 544.0 * (NB - KMER * R)
-    if kernel == "k_rs_scatter":      # read every key once, write it once
-        return 2.0 * NK * kb
-    if kernel == "k_rs_hist":
+    if kernel == "k_part_scatter":    # read every key once, write it once (launches: hash passes over the k-mer keys and
+        return 2.0 * NK * kb          # shift passes over the symbol records; the k-mer figure is used for the average)
+    if kernel == "k_part_hist":
         return 1.0 * NK * kb
+    if kernel == "k_bucket_count":    # read every key once, write (key, count) of the solid ones
+        return 1.0 * NK * kb + st["nruns"] * (kb + 4.0)
     if kernel == "k_extract":         # read the bases, write one key per k-mer
         return NB + NK * kb
     if kernel == "k_chunk_ranks":     # read the 8-byte sorted record, write the 17-byte coder record; histogram row per chunk
@@ -246,23 +248,45 @@ def main_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    # ---- the workload: every rank generates the same seeded read set and keeps its contiguous share of blocks
+    # ---- the workload: every rank generates the same seeded read set; with N > 1 ranks the set is dealt in rounds of
+    # N * S consecutive reads, S to each rank in rank order (leon_b200.shard; include/leon_b200.h leon_comm_*), so the
+    # total work is fixed as N grows ("strong").
+    from leon_b200 import shard
     total_reads = args.reads if args.reads else GENOME_LEN * COVERAGE // READ_LEN
     genome = synth.make_genome(GENOME_LEN, 1)
-    pin_b = leon_b200.api.PinnedArray(total_reads * READ_LEN)
-    pin_q = leon_b200.api.PinnedArray(total_reads * READ_LEN) if args.fastq else None
-    bases, offs, quals = synth.sample_reads(genome, total_reads, READ_LEN, 2, out_bases=pin_b.array, with_quals=args.fastq,
-                                            out_quals=pin_q.array if args.fastq else None)
-    pin_o = leon_b200.api.PinnedArray((total_reads + 1) * 8, np.uint64)
+    S = 0
+    if world == 1:
+        pin_b = leon_b200.api.PinnedArray(total_reads * READ_LEN)
+        pin_q = leon_b200.api.PinnedArray(total_reads * READ_LEN) if args.fastq else None
+        bases, offs, quals = synth.sample_reads(genome, total_reads, READ_LEN, 2, out_bases=pin_b.array, with_quals=args.fastq,
+                                                out_quals=pin_q.array if args.fastq else None)
+    else:
+        S = args.anchor_batch if args.anchor_batch else shard.choose_batch_reads(total_reads, world, RPB)
+        fb, fo, fq = synth.sample_reads(genome, total_reads, READ_LEN, 2, with_quals=args.fastq)
+        sb, offs, sq = shard.shard_reads(fb, fo, fq, rank, world, S)
+        del fb, fq
+        pin_b = leon_b200.api.PinnedArray(len(sb))
+        pin_b.array[:] = sb
+        bases = pin_b.array
+        quals = None
+        if args.fastq:
+            pin_q = leon_b200.api.PinnedArray(len(sq))
+            pin_q.array[:] = sq
+            quals = pin_q.array
+        del sb, sq
+    local_reads = len(offs) - 1
+    pin_o = leon_b200.api.PinnedArray((local_reads + 1) * 8, np.uint64)
     pin_o.array[:] = offs
     offs = pin_o.array
 
     eng = leon_b200.Leon(kmer_size=KMER, reads_per_block=RPB, has_qual=args.fastq, device=local_rank,
-                         anchor_batch=args.anchor_batch)
+                         anchor_batch=S if world > 1 else args.anchor_batch)
     stream = torch.cuda.current_stream()
     eng.set_stream(stream.cuda_stream)
     if world > 1:
-        raise SystemExit("bench.py: the multi-GPU path is not wired into this bench yet")
+        uid = [leon_b200.Leon.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        eng.comm_init(rank, world, uid[0])
 
     def barrier():
         if world > 1:
@@ -302,7 +326,8 @@ def main_b200(args):
     ms_per_step = dev_ms / args.steps
     value = total_reads / (ms_per_step / 1000.0)
     res = eng.fetch(copy=False)
-    stats = {"nreads": total_reads, "nbases": total_reads * READ_LEN, "nkmers": res["nb_kmers"],
+    # the roofline describes rank 0's launches: its own share of the reads
+    stats = {"nreads": local_reads, "nbases": local_reads * READ_LEN, "nkmers": local_reads * (READ_LEN - KMER + 1),
              "nruns": res["nb_distinct"], "dna_bytes": len(res["dna"])}
     nsym = eng.debug_fetch("nsym", np.uint64)
     stats["nsym"] = float(nsym.sum())
@@ -329,6 +354,10 @@ def main_b200(args):
     h2d = int(bases.nbytes + offs.nbytes + (quals.nbytes if quals is not None else 0))
     d2h = int(len(r["bloom"]) + len(r["anchors_dict"]) + len(r["dna"]) + r["blocksizes"].nbytes +
               r["anchor_pos"].nbytes + r["anchor_addr"].nbytes + len(r["qual_text"]))
+    if world > 1:   # bytes of all ranks
+        t = torch.tensor([h2d, d2h, launches], device="cuda", dtype=torch.int64)
+        dist.all_reduce(t)
+        h2d, d2h, launches = (int(x) for x in t.tolist())
     e2e_value = total_reads / (e2e_ms / 1000.0)
 
     # ---- roofline of the dominant kernel (largest share of the device time of the timed region)
@@ -371,7 +400,9 @@ def main_b200(args):
         "config": {"workload": (WORKLOAD if not args.fastq else "DEBUG (configs[2] shape, FASTQ lossy)") if not args.reads else "DEBUG SIZE (invalid as a bench line): %d reads" % total_reads,
                    "reads": total_reads, "read_len": READ_LEN, "kmer_size": KMER, "reads_per_block": RPB,
                    "l2": "inputs larger than L2 (460 MB of bases, 2.6 GB of keys per step); no flush needed",
-                   "parallelism": "1 process per GPU"},
+                   "parallelism": "1 process per GPU" if world == 1 else
+                   "%d ranks, reads dealt in rounds of %d x %d; NCCL: k-mer all-to-all by hash owner, Bloom all-gather + OR, "
+                   "anchor candidates all-gathered per batch" % (world, world, S)},
         "input_gbs": value * READ_LEN / 1e9,
         "e2e": {"value": e2e_value, "unit": "reads/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_ms, "input_gbs": e2e_value * READ_LEN / 1e9},

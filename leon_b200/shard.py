@@ -93,3 +93,25 @@ def merge_results(results, nreads, nranks, S, reads_per_block):
         reads_without_anchor=sum(r["reads_without_anchor"] for r in results),
     )
     return out
+
+
+def choose_batch_reads(nreads, nranks, reads_per_block, max_blocks=16):
+    """Reads per rank and anchor batch (S, a multiple of reads_per_block) that balances the ranks for a set of known
+    size: the S in [1, max_blocks] blocks minimising (blocks of the busiest rank + number of exchange rounds) -- a round
+    of anchor exchanges costs about as much as coding one block.  Any S gives the same output; this only shortens the run."""
+    nblocks = (nreads + reads_per_block - 1) // reads_per_block
+    best = None
+    for sb in range(1, max_blocks + 1):
+        per = [0] * nranks
+        rounds = 0
+        b = 0
+        while b < nblocks:
+            for r in range(nranks):
+                take = min(sb, max(0, nblocks - b))
+                per[r] += take
+                b += take
+            rounds += 1
+        key = max(per) + rounds
+        if best is None or key <= best[0]:
+            best = (key, sb)
+    return best[1] * reads_per_block
