@@ -228,6 +228,19 @@ __global__ void __launch_bounds__(256) k_seg_scan(const uint64_t *__restrict__ c
     for (; i < n; i++) { uint32_t a = p[0]; p[0] = run; run += a; p += 256; }
 }
 
+// floor(num / d) and the remainder for num < d * 2^32 (32-bit quotient), d < 2^32: quotient estimate in double
+// precision, biased down so that it is the exact quotient or one less, then one correction.
+LB_D uint32_t div_64_32(uint64_t num, uint32_t d, double rcp_d, uint64_t &rem)
+{
+    // |relative error| of double(num) * rcp_d is < 2^-50; the quotient is < 2^32, so after the bias the estimate is
+    // within (q - 1, q]: its floor is q or q - 1
+    uint64_t q = __double2ull_rz(__ull2double_rz(num) * rcp_d * (1.0 - 1.0 / 1125899906842624.0));
+    uint64_t r = num - q * d;
+    if (r >= d) { q++; r -= d; }
+    rem = r;
+    return (uint32_t)q;
+}
+
 // Exact n / d for every 64-bit n by one multiply-add-high and a shift:  n / d == (hi64(n * m + a)) >> s.
 // Round-up magic when it fits in 64 bits, else round-down magic with the numerator incremented (a = m), which also
 // covers powers of two with m = 2^64 - 1.
@@ -236,10 +249,10 @@ LB_D void div_magic(uint32_t d, uint64_t &m, uint32_t &s, uint32_t &inc)
     int L = 31 - __clz(d);
     s = (uint32_t)L;
     if ((d & (d - 1)) == 0) { m = ~0ull; inc = 1; return; }
-    uint64_t t = (1ull << L) << 32;
-    uint64_t q1 = t / d, r1 = t - q1 * d;
-    uint64_t t2 = r1 << 32;
-    uint64_t q0 = t2 / d, r2 = t2 - q0 * d;
+    const double rcp = 1.0 / (double)d;
+    uint64_t r1, r2;
+    uint64_t q1 = div_64_32((1ull << L) << 32, d, rcp, r1);      // in (2^31, 2^32): d is not a power of two
+    uint64_t q0 = div_64_32(r1 << 32, d, rcp, r2);
     uint64_t mdown = (q1 << 32) | q0;            // floor(2^(64+L) / d)
     if ((uint64_t)d - r2 < (1ull << L)) { m = mdown + 1; inc = 0; }
     else { m = mdown; inc = 1; }
@@ -254,13 +267,18 @@ LB_D void store_symrec(uint4 *__restrict__ rec, uint8_t *__restrict__ sh, uint64
     sh[pos] = (uint8_t)(s | (inc << 7));
 }
 
+// Ranks of the symbols of one 512-symbol chunk among the earlier symbols of their (block, model) segment.  The counts of
+// the earlier chunks come from H (k_seg_scan); inside the chunk the 16 warps first count their own values (hw), a pass
+// over the warps turns that into "occurrences of value v before warp w" (T), each warp prefix-sums its row of T over the
+// values (P), and the ranks among the earlier lanes of the own warp come from one ballot per value bit.
 __global__ void __launch_bounds__(CHUNK) k_chunk_ranks(const uint64_t *__restrict__ recs, const uint64_t *__restrict__ seg_start,
                                                        const uint64_t *__restrict__ chunk_off, uint64_t nseg,
                                                        const uint32_t *__restrict__ H, uint4 *__restrict__ rec_out,
                                                        uint8_t *__restrict__ sh_out)
 {
-    __shared__ uint8_t vals[CHUNK];
-    __shared__ uint32_t cnt[256], cum[256], wsum[8];
+    constexpr int NW = CHUNK / 32;
+    __shared__ uint32_t T[NW][256];
+    __shared__ uint32_t P[NW][256];
     __shared__ uint64_t sh_beg, sh_end, sh_ci;
     const uint64_t c = blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -272,45 +290,56 @@ __global__ void __launch_bounds__(CHUNK) k_chunk_ranks(const uint64_t *__restric
         sh_end = end < beg + CHUNK ? end : beg + CHUNK;
         sh_ci = ci;
     }
+#pragma unroll
+    for (int i = 0; i < NW * 256 / CHUNK; i++) (&T[0][0])[tid + i * CHUNK] = 0;
     __syncthreads();
     const uint64_t beg = sh_beg;
     const int n = (int)(sh_end - beg);
+    const bool act = tid < n;
     uint64_t rec = 0;
     unsigned v = 0;
-    if (tid < n) { rec = recs[beg + tid]; v = (unsigned)(rec & 255u); vals[tid] = (uint8_t)v; }
-    // exclusive prefix over the 256 values of the counts of the earlier chunks
-    uint32_t hv = 0, incl = 0;
-    if (tid < 256) {
-        hv = H[c * 256 + tid];
-        cnt[tid] = hv;
-        incl = hv;
+    if (act) { rec = recs[beg + tid]; v = (unsigned)(rec & 255u); atomicAdd(&T[warp][v], 1u); }
+    const unsigned model = (unsigned)(__shfl_sync(0xffffffffu, rec, 0) >> REC_KEY_SHIFT) & ((1u << REC_MODEL_BITS) - 1u);
+    __syncthreads();
+    if (tid < 256) {      // occurrences of value tid before warp w (earlier chunks + earlier warps)
+        uint32_t run = H[c * 256 + tid];
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= d) incl += o;
+        for (int w = 0; w < NW; w++) { uint32_t t = T[w][tid]; T[w][tid] = run; run += t; }
+    }
+    __syncthreads();
+    {   // P[warp][v] = sum over u < v of T[warp][u]
+        uint32_t a[8], sum = 0;
+#pragma unroll
+        for (int i = 0; i < 8; i++) { a[i] = T[warp][lane * 8 + i]; sum += a[i]; }
+        uint32_t incl = sum;
+#pragma unroll
+        for (int dlt = 1; dlt < 32; dlt <<= 1) {
+            uint32_t o = __shfl_up_sync(0xffffffffu, incl, dlt);
+            if (lane >= dlt) incl += o;
         }
-        if (lane == 31) wsum[warp] = incl;
+        uint32_t run = incl - sum;
+#pragma unroll
+        for (int i = 0; i < 8; i++) { P[warp][lane * 8 + i] = run; run += a[i]; }
     }
-    __syncthreads();
-    if (tid < 256) {
-        uint32_t base = 0;
-        for (int w = 0; w < warp; w++) base += wsum[w];
-        cum[tid] = base + incl - hv;
+    __syncwarp();
+    // ranks among the earlier lanes of the warp: lanes that agree with v on the bits above b and have bit b clear while
+    // v has it set are smaller
+    const uint32_t alphabet = model_alphabet(model);        // a chunk holds one (block, model) segment
+    const unsigned amask = __ballot_sync(0xffffffffu, act);
+    const unsigned lt = (1u << lane) - 1u;
+    unsigned same = amask, less = 0;
+#pragma unroll
+    for (int b = 7; b >= 0; b--) {
+        const unsigned bb = __ballot_sync(0xffffffffu, act && ((v >> b) & 1u));
+        if ((v >> b) & 1u) { less += __popc(same & ~bb & lt); same &= bb; }
+        else same &= ~bb;
     }
-    __syncthreads();
-    if (tid >= n) return;
-    // ranks among the earlier symbols of this chunk
-    uint32_t less = 0, eq = 0;
-    const int bound = n - 1 < warp * 32 + 31 ? n - 1 : warp * 32 + 31;   // largest tid of the warp that has a symbol
-    for (int j = 0; j < bound; j++) {
-        unsigned u = vals[j];
-        if (j < tid) { less += u < v; eq += u == v; }
-    }
-    unsigned model = (unsigned)(rec >> REC_KEY_SHIFT) & ((1u << REC_MODEL_BITS) - 1u);
+    const unsigned eq = __popc(same & lt);
+    if (!act) return;
     uint64_t pos = (rec >> 8) & 0xffffffffull;
-    uint32_t lo = v + cum[v] + less;
-    uint32_t w = 1u + cnt[v] + eq;
-    uint32_t tot = model_alphabet(model) + (uint32_t)(sh_ci * CHUNK) + (uint32_t)tid;
+    uint32_t lo = v + P[warp][v] + less;
+    uint32_t w = 1u + T[warp][v] + eq;
+    uint32_t tot = alphabet + (uint32_t)(sh_ci * CHUNK) + (uint32_t)tid;
     store_symrec(rec_out, sh_out, pos, lo, w, tot);
 }
 
@@ -345,7 +374,7 @@ __global__ void k_block_descs(const uint64_t *__restrict__ symoff, uint64_t nrea
 LB_D void rc_step(uint64_t &low, uint64_t &range, const uint4 t, const uint32_t sh, uint8_t *&op, const bool store)
 {
     const uint64_t m = ((uint64_t)t.w << 32) | t.z;
-    const uint64_t q = __umul64hi(range + (sh >> 7), m) >> (sh & 63u);
+    const uint64_t q = (uint64_t)(((unsigned __int128)range * m + ((sh & 0x80u) ? m : 0ull)) >> 64) >> (sh & 63u);
     low += (uint64_t)t.x * q;
     range = q * (uint64_t)t.y;
     while (true) {
@@ -367,7 +396,7 @@ constexpr uint32_t RC_MAX_BYTES_PER_SYMBOL = 12;   // <= 4 bytes of information 
 // RangeEncoder::encode / flush, C/RangeCoder.cpp:106-145.  One warp per stream: the 32 lanes stage the next 32 symbol
 // records in shared memory (coalesced loads, issued one batch ahead), lane 0 runs the low/range recurrence over them
 // with the record of the next symbol already in registers.
-__global__ void __launch_bounds__(32) k_range_encode(const uint4 *__restrict__ rec_all, const uint8_t *__restrict__ sh_all,
+__global__ void __launch_bounds__(32) k_range_encode_v0(const uint4 *__restrict__ rec_all, const uint8_t *__restrict__ sh_all,
                                                      const StreamDesc *__restrict__ descs, uint8_t *__restrict__ out_all,
                                                      uint64_t *__restrict__ out_size, int always_flush, uint32_t *overflow)
 {
@@ -442,6 +471,207 @@ __global__ void __launch_bounds__(32) k_range_encode(const uint4 *__restrict__ r
         }
         out_size[blockIdx.x] = nout;
         if (ovf) *overflow = 1;
+    }
+}
+
+// ---- range coder, current kernel ------------------------------------------------------------------------------
+// A single warp issues at most one instruction every other cycle per pipe, so the serial recurrence is bound by the
+// NUMBER of instructions per symbol as much as by their dependent chain.  Everything that does not depend on
+// (low, range) is therefore done by the 31 other lanes: they unpack the records into shared memory in the form lane 0
+// consumes (LDS.128 + LDS.64 per symbol), pad the last batch with identity symbols so that lane 0 runs fixed groups of
+// four steps without bounds checks, and copy the output bytes, which lane 0 leaves in shared memory, to global memory.
+
+// the two halves of a 64-bit value as separate 32-bit registers (keeps the compiler from re-fusing 32-bit tests on
+// the high word into 64-bit compares)
+LB_D void split64(uint64_t v, uint32_t &lo, uint32_t &hi) { asm("mov.b64 {%0, %1}, %2;" : "=r"(lo), "=r"(hi) : "l"(v)); }
+
+// shared-memory accesses by 32-bit address (plain LDS / STS without generic-address arithmetic)
+LB_D uint4 lds128(uint32_t a)
+{
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+    return v;
+}
+LB_D uint2 lds64(uint32_t a)
+{
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a));
+    return v;
+}
+LB_D void sts8(uint32_t a, uint32_t v) { asm volatile("st.shared.u8 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+
+// One generic coding step (RangeEncoder::encode, C/RangeCoder.cpp:106-134): any symbol, any state.  Bytes go to shared
+// memory at address `on` (advanced).
+LB_D void rc_step_any(uint64_t &low, uint64_t &range, const uint4 t, const uint32_t shift, const uint32_t inc, uint32_t &on)
+{
+    const uint64_t m = ((uint64_t)t.w << 32) | t.z;
+    const uint64_t q = (uint64_t)(((unsigned __int128)range * m + (inc ? m : 0ull)) >> 64) >> shift;
+    low += (uint64_t)t.x * q;
+    range = q * (uint64_t)t.y;
+#pragma unroll 1
+    for (int guard = 0; guard < (int)RC_MAX_BYTES_PER_SYMBOL; guard++) {   // the bound only matters for corrupt records (range 0)
+        const uint32_t lh = (uint32_t)(low >> 32);
+        if ((lh ^ (uint32_t)((low + range) >> 32)) >= (1u << 24)) {     // top bytes of low and low + range differ
+            if ((uint32_t)(range >> 32) >= (1u << 16)) break;           // range >= 2^48
+            range = (0 - low) & (RC_BOTTOM - 1);
+        }
+        sts8(on++, lh >> 24);
+        range <<= 8;
+        low <<= 8;
+    }
+}
+
+// The common case of a coding step as straight-line code.  State: low, and rp = range + inc of THIS symbol (div_magic:
+// range / total == hi64((range + inc) * magic) >> shift; rp fits in 64 bits because range < 2^64 - 1 once a real symbol
+// has been coded; the first symbols of a stream go through rc_step_any).  With x = hi32(low) ^ hi32(low + range) the
+// renormalisation loop exits after 0 byte (x >= 2^24 and range >= 2^48) or after exactly 1 byte (x in [2^16, 2^24): the
+// second byte differs once shifted in; range >= 2^48 already) for all but a few percent of the symbols; for those the
+// step returns false with (lw, rg) = the state before renormalisation.  The byte is stored unconditionally and the
+// output index advances by 0 or 1.
+LB_D bool rc_step_fast(uint64_t &low, uint64_t &rp, const uint4 t, const uint32_t shift, const uint32_t inc_next,
+                       uint32_t &on, uint64_t &lw, uint64_t &rg)
+{
+    const uint64_t m = ((uint64_t)t.w << 32) | t.z;
+    const uint64_t q = __umul64hi(rp, m) >> shift;
+    lw = low + (uint64_t)t.x * q;
+    rg = q * (uint64_t)t.y;
+    uint32_t ll, lh, rl, rh, sl, shi;
+    split64(lw, ll, lh);
+    split64(rg, rl, rh);
+    split64(lw + rg, sl, shi);
+    const uint32_t x = lh ^ shi;
+    if (__builtin_expect(min(x, rh) < (1u << 16), 0)) return false;
+    const bool one = x < (1u << 24);
+    sts8(on, lh >> 24);
+    if (one) on++;
+    low = one ? (lw << 8) : lw;
+    rp = one ? ((rg << 8) | inc_next) : (rg + inc_next);
+    return true;
+}
+
+constexpr int RC_BATCH = 64;       // symbol records staged per round (two per lane)
+constexpr int RC_OBUF = RC_BATCH * RC_MAX_BYTES_PER_SYMBOL + 32;   // + scratch word at the end
+
+// RangeEncoder::encode / flush, C/RangeCoder.cpp:106-145.  One warp per stream.
+__global__ void __launch_bounds__(32) k_range_encode(const uint4 *__restrict__ rec_all, const uint8_t *__restrict__ sh_all,
+                                                     const StreamDesc *__restrict__ descs, uint8_t *__restrict__ out_all,
+                                                     uint64_t *__restrict__ out_size, int always_flush, uint32_t *overflow)
+{
+    __shared__ uint4 srec[2][RC_BATCH + 4];
+    __shared__ uint2 ssh[2][RC_BATCH + 4];       // (shift, inc)
+    __shared__ uint8_t sout[RC_OBUF];
+    const int lane = threadIdx.x;
+    const StreamDesc d = descs[blockIdx.x];
+    const uint4 *rec = rec_all + d.rec_base;
+    const uint8_t *sh = sh_all + d.rec_base;
+    uint8_t *const out0 = out_all + d.out_base;
+    uint64_t opos = 0;                            // bytes produced so far (all lanes)
+    uint64_t low = 0, range = ~0ull;              // lane 0
+    // identity symbol (total 1: magic 2^64 - 1, inc 1, shift 0 gives q = range; low += 0; range = q * 1): pads the last batch
+    const uint4 idle = make_uint4(0u, 1u, 0xffffffffu, 0xffffffffu);
+    uint4 na = idle, nb = idle;
+    uint32_t nsa = 0x80u, nsb = 0x80u;
+    if ((uint64_t)lane < d.nsym) { na = rec[lane]; nsa = sh[lane]; }
+    if ((uint64_t)lane + 32 < d.nsym) { nb = rec[lane + 32]; nsb = sh[lane + 32]; }
+    if (lane < 4) {     // slots past the batch: only their inc (0) is read, as the "next inc" of the last step
+        srec[0][RC_BATCH + lane] = idle; srec[1][RC_BATCH + lane] = idle;
+        ssh[0][RC_BATCH + lane] = make_uint2(0u, 0u); ssh[1][RC_BATCH + lane] = make_uint2(0u, 0u);
+    }
+    for (uint64_t base = 0; base < d.nsym; base += RC_BATCH) {
+        const int buf = (int)((base / RC_BATCH) & 1);
+        srec[buf][lane] = na;
+        srec[buf][lane + 32] = nb;
+        ssh[buf][lane] = make_uint2(nsa & 63u, nsa >> 7);
+        ssh[buf][lane + 32] = make_uint2(nsb & 63u, nsb >> 7);
+        const uint64_t in = base + RC_BATCH + lane;
+        na = idle; nb = idle; nsa = 0x80u; nsb = 0x80u;
+        if (in < d.nsym) { na = rec[in]; nsa = sh[in]; }
+        if (in + 32 < d.nsym) { nb = rec[in + 32]; nsb = sh[in + 32]; }
+        __syncwarp();
+        const uint32_t sout_a = (uint32_t)__cvta_generic_to_shared(sout);
+        uint32_t on = sout_a;
+        if (lane == 0) {
+            const uint32_t sr = (uint32_t)__cvta_generic_to_shared(srec[buf]);     // record j at sr + 16 j
+            const uint32_t ss = (uint32_t)__cvta_generic_to_shared(ssh[buf]);      // (shift, inc) of j at ss + 8 j
+            int j = 0;
+            if (base == 0) {      // range = 2^64 - 1: range + inc does not fit in 64 bits yet
+#pragma unroll 1
+                for (; j < 4; j++) {
+                    const uint2 sx = lds64(ss + 8 * j);
+                    rc_step_any(low, range, lds128(sr + 16 * j), sx.x, sx.y, on);
+                }
+            }
+            uint4 t0 = lds128(sr + 16 * j);
+            uint2 s0 = lds64(ss + 8 * j);
+            uint64_t rp = range + s0.y;
+            while (j < RC_BATCH) {
+                uint64_t lw, rg;
+                int bad = -1;
+                uint32_t keep = 0;
+#pragma unroll 1
+                for (; j < RC_BATCH; j += 4) {
+                    const uint4 t1 = lds128(sr + 16 * j + 16), t2 = lds128(sr + 16 * j + 32), t3 = lds128(sr + 16 * j + 48);
+                    const uint4 t4 = lds128(sr + 16 * j + 64);
+                    const uint2 s1 = lds64(ss + 8 * j + 8), s2 = lds64(ss + 8 * j + 16), s3 = lds64(ss + 8 * j + 24);
+                    const uint2 s4 = lds64(ss + 8 * j + 32);
+                    keep = t1.x ^ t2.x ^ t3.x ^ t4.x ^ s1.x ^ s2.x ^ s3.x ^ s4.x;
+                    if (!rc_step_fast(low, rp, t0, s0.x, s1.y, on, lw, rg)) { bad = 0; break; }
+                    if (!rc_step_fast(low, rp, t1, s1.x, s2.y, on, lw, rg)) { bad = 1; break; }
+                    if (!rc_step_fast(low, rp, t2, s2.x, s3.y, on, lw, rg)) { bad = 2; break; }
+                    if (!rc_step_fast(low, rp, t3, s3.x, s4.y, on, lw, rg)) { bad = 3; break; }
+                    t0 = t4;
+                    s0 = s4;
+                }
+                if (bad >= 0) {
+                    // rare: finish symbol j + bad with the generic loop, code the rest of its group generically, resume.
+                    // (The group's records are consumed here as well so that their loads stay at the top of the group,
+                    // ahead of the dependent chain, instead of being sunk below the steps' exit branches.)
+                    asm volatile("st.shared.u32 [%0], %1;" ::"r"(sout_a + RC_OBUF - 4), "r"(keep) : "memory");
+                    low = lw;
+                    range = rg;
+#pragma unroll 1
+                    for (int guard = 0; guard < (int)RC_MAX_BYTES_PER_SYMBOL; guard++) {
+                        const uint32_t lh = (uint32_t)(low >> 32);
+                        if ((lh ^ (uint32_t)((low + range) >> 32)) >= (1u << 24)) {
+                            if ((uint32_t)(range >> 32) >= (1u << 16)) break;
+                            range = (0 - low) & (RC_BOTTOM - 1);
+                        }
+                        sts8(on++, lh >> 24);
+                        range <<= 8;
+                        low <<= 8;
+                    }
+#pragma unroll 1
+                    for (int i = j + bad + 1; i < j + 4; i++) {
+                        const uint2 sx = lds64(ss + 8 * i);
+                        rc_step_any(low, range, lds128(sr + 16 * i), sx.x, sx.y, on);
+                    }
+                    j += 4;
+                    t0 = lds128(sr + 16 * j);
+                    s0 = lds64(ss + 8 * j);
+                    rp = range + s0.y;
+                }
+            }
+            range = rp;           // the slot past the batch has inc 0
+        }
+        on -= sout_a;
+        // all lanes: copy the bytes of this batch to the stream's output region
+        on = __shfl_sync(0xffffffffu, on, 0);
+        for (uint32_t i = lane; i < on; i += 32)
+            if (opos + i < d.out_cap) out0[opos + i] = sout[i];
+        opos += on;
+        __syncwarp();
+    }
+    if (lane == 0) {
+        uint64_t nout = opos;
+        if (always_flush || nout > 0) {                       // DnaEncoder::writeBlock flushes only a non-empty buffer
+            for (int x = 0; x < 8; x++) {
+                if (nout < d.out_cap) out0[nout] = (uint8_t)(low >> 56);
+                nout++;
+                low <<= 8;
+            }
+        }
+        out_size[blockIdx.x] = nout;
+        if (nout > d.out_cap) *overflow = 1;
     }
 }
 

@@ -1,0 +1,138 @@
+// Micro-benchmark + self-check of the range coder kernels of entropy.cuh on synthetic symbol records shaped like a
+// C2 block (about 10.8 symbols and 3.5-4 output bytes per read).  Development tool, not part of the library:
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -I leon_b200/csrc -o tools/bin/rc_bench tools/rc_bench.cu
+//   ./rc_bench [streams=92] [reads_per_stream=50000]
+// Every variant must reproduce the bytes of a plain host coder that divides (RangeCoder.cpp:106-145).
+#include "entropy.cuh"
+#include <vector>
+#include <random>
+#include <chrono>
+
+struct HostModel {
+    std::vector<uint32_t> cnt; uint32_t total;
+    explicit HostModel(int n) : cnt(n, 1), total(n) {}
+    void get(unsigned v, uint32_t &lo, uint32_t &w, uint32_t &tot) {
+        lo = 0; for (unsigned u = 0; u < v; u++) lo += cnt[u];
+        w = cnt[v]; tot = total; cnt[v]++; total++;
+    }
+};
+static void host_magic(uint32_t d, uint64_t &m, uint32_t &s, uint32_t &inc)
+{
+    int L = 31 - __builtin_clz(d);
+    s = L;
+    if ((d & (d - 1)) == 0) { m = ~0ull; inc = 1; return; }
+    unsigned __int128 t = (unsigned __int128)1 << (64 + L);
+    uint64_t mdown = (uint64_t)(t / d);
+    uint64_t r2 = (uint64_t)(t - (unsigned __int128)mdown * d);
+    if ((uint64_t)d - r2 < (1ull << L)) { m = mdown + 1; inc = 0; } else { m = mdown; inc = 1; }
+}
+struct Sym { uint32_t lo, w, tot; };
+
+static void gen_stream(uint64_t seed, int reads, std::vector<Sym> &out)
+{
+    std::mt19937_64 rng(seed);
+    HostModel type(2), size0(256), pos0(256), a0(256), a1(256), a2(256), rev(2), nn(256), ne(256), ep(256), bif(5), bifb(2);
+    auto put = [&](HostModel &m, unsigned v) { Sym s; m.get(v, s.lo, s.w, s.tot); out.push_back(s); };
+    for (int r = 0; r < reads; r++) {
+        put(type, 0); put(size0, 100); put(pos0, rng() % 70);
+        uint32_t addr = rng() % 258028;
+        put(a0, (addr & 127) | 128); put(a1, ((addr >> 7) & 127) | 128); put(a2, addr >> 14);
+        put(rev, rng() & 1); put(nn, 0);
+        unsigned nerr = (rng() % 100) < 30 ? 1 + (rng() % 100 < 15) : 0;
+        put(ne, nerr);
+        for (unsigned e = 0; e < nerr; e++) put(ep, rng() % 69);
+        for (unsigned e = 0; e < nerr; e++) put(bif, rng() % 4);
+        if (rng() % 100 < 8) put(bifb, rng() & 1);
+    }
+}
+
+static void host_encode(const std::vector<Sym> &syms, std::vector<uint8_t> &out)
+{
+    uint64_t low = 0, range = ~0ull;
+    for (const Sym &s : syms) {
+        range /= s.tot; low += (uint64_t)s.lo * range; range *= s.w;
+        while ((low ^ (low + range)) < RC_TOP || range < RC_BOTTOM) {
+            if (range < RC_BOTTOM && (low ^ (low + range)) >= RC_TOP) range = (0 - low) & (RC_BOTTOM - 1);
+            out.push_back((uint8_t)(low >> 56)); range <<= 8; low <<= 8;
+        }
+    }
+    for (int i = 0; i < 8; i++) { out.push_back((uint8_t)(low >> 56)); low <<= 8; }
+}
+
+__global__ void k_magic_check(uint32_t d0, uint32_t n, uint32_t stride, const uint64_t *want_m, const uint8_t *want_s, uint32_t *bad)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t d = d0 + i * stride;
+    uint64_t m; uint32_t s, inc;
+    lbent::div_magic(d, m, s, inc);
+    if (m != want_m[i] || (uint8_t)(s | (inc << 7)) != want_s[i]) atomicAdd(bad, 1u);
+}
+
+#define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("%s: %s\n", #x, cudaGetErrorString(e)); return 1; } } while (0)
+
+int main(int argc, char **argv)
+{
+    int streams = argc > 1 ? atoi(argv[1]) : 92, reads = argc > 2 ? atoi(argv[2]) : 50000;
+    using namespace lbent;
+    {   // div_magic on the device == exact host arithmetic: every d in [2, 2^22], then a stride through the 32-bit range
+        const uint32_t n = 1u << 22;
+        std::vector<uint64_t> wm(n); std::vector<uint8_t> ws(n);
+        uint64_t *d_m; uint8_t *d_s; uint32_t *d_bad;
+        CK(cudaMalloc(&d_m, n * 8)); CK(cudaMalloc(&d_s, n)); CK(cudaMalloc(&d_bad, 4));
+        for (int pass = 0; pass < 2; pass++) {
+            uint32_t d0 = 2, stride = pass ? 1021 : 1;
+            for (uint32_t i = 0; i < n; i++) { uint32_t sft, inc; host_magic(d0 + i * stride, wm[i], sft, inc); ws[i] = (uint8_t)(sft | (inc << 7)); }
+            CK(cudaMemcpy(d_m, wm.data(), n * 8, cudaMemcpyHostToDevice)); CK(cudaMemcpy(d_s, ws.data(), n, cudaMemcpyHostToDevice));
+            CK(cudaMemset(d_bad, 0, 4));
+            k_magic_check<<<n / 256, 256>>>(d0, n, stride, d_m, d_s, d_bad);
+            uint32_t bad; CK(cudaMemcpy(&bad, d_bad, 4, cudaMemcpyDeviceToHost));
+            printf("div_magic check, stride %u: %u mismatches of %u\n", stride, bad, n);
+        }
+        cudaFree(d_m); cudaFree(d_s); cudaFree(d_bad);
+    }
+    std::vector<uint4> rec; std::vector<uint8_t> sh; std::vector<StreamDesc> descs; std::vector<std::vector<uint8_t>> want(streams);
+    uint64_t base = 0, rare = 0;
+    for (int s = 0; s < streams; s++) {
+        std::vector<Sym> syms; gen_stream(1000 + s, reads, syms);
+        host_encode(syms, want[s]);
+        for (const Sym &y : syms) {
+            uint64_t m; uint32_t sft, inc; host_magic(y.tot, m, sft, inc);
+            rec.push_back(make_uint4(y.lo, y.w, (uint32_t)m, (uint32_t)(m >> 32))); sh.push_back((uint8_t)(sft | (inc << 7)));
+        }
+        StreamDesc d; d.rec_base = base; d.nsym = syms.size(); d.out_base = 2 * base + 1024 * s; d.out_cap = 2 * syms.size() + 1024;
+        descs.push_back(d); base += syms.size();
+    }
+    uint64_t nbytes = 0; for (auto &w : want) nbytes += w.size();
+    printf("%d streams, %llu symbols (%.1f per read), %llu bytes (%.2f per read)\n", streams, (unsigned long long)base,
+           (double)base / streams / reads, (unsigned long long)nbytes, (double)nbytes / streams / reads);
+    (void)rare;
+    uint4 *d_rec; uint8_t *d_sh, *d_out; StreamDesc *d_desc; uint64_t *d_size; uint32_t *d_ovf;
+    uint64_t outcap = 2 * base + 1024ull * streams + 1024;
+    CK(cudaMalloc(&d_rec, (base + 64) * 16)); CK(cudaMalloc(&d_sh, base + 64)); CK(cudaMalloc(&d_out, outcap));
+    CK(cudaMalloc(&d_desc, streams * sizeof(StreamDesc))); CK(cudaMalloc(&d_size, streams * 8)); CK(cudaMalloc(&d_ovf, 4));
+    CK(cudaMemcpy(d_rec, rec.data(), base * 16, cudaMemcpyHostToDevice)); CK(cudaMemcpy(d_sh, sh.data(), base, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(d_desc, descs.data(), streams * sizeof(StreamDesc), cudaMemcpyHostToDevice));
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    std::vector<uint8_t> got(outcap); std::vector<uint64_t> sizes(streams);
+    for (int variant = 0; variant < 2; variant++) {
+        float best = 1e9f;
+        for (int it = 0; it < 4; it++) {
+            CK(cudaMemset(d_out, 0xEE, outcap)); CK(cudaMemset(d_ovf, 0, 4));
+            CK(cudaEventRecord(e0));
+            if (variant == 0) k_range_encode_v0<<<streams, 32>>>(d_rec, d_sh, d_desc, d_out, d_size, 0, d_ovf);
+            else k_range_encode<<<streams, 32>>>(d_rec, d_sh, d_desc, d_out, d_size, 0, d_ovf);
+            CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1)); CK(cudaGetLastError());
+            float ms; cudaEventElapsedTime(&ms, e0, e1); if (ms < best) best = ms;
+        }
+        CK(cudaMemcpy(got.data(), d_out, outcap, cudaMemcpyDeviceToHost)); CK(cudaMemcpy(sizes.data(), d_size, streams * 8, cudaMemcpyDeviceToHost));
+        uint32_t ovf; CK(cudaMemcpy(&ovf, d_ovf, 4, cudaMemcpyDeviceToHost));
+        int bad = 0;
+        for (int s = 0; s < streams; s++) {
+            if (sizes[s] != want[s].size() || memcmp(got.data() + descs[s].out_base, want[s].data(), want[s].size())) bad++;
+        }
+        double nsps = best * 1e6 / ((double)base / streams);
+        printf("variant %d: %.3f ms  %.1f ns/symbol/stream (%.0f cycles @1.965GHz)  mismatching streams %d  overflow %u\n", variant, best, nsps, nsps * 1.965, bad, ovf);
+    }
+    return 0;
+}
