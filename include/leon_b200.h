@@ -101,7 +101,8 @@ typedef struct leon_timings {
     uint64_t sort_keys;           /* keys per pass */
     float dict_host_ms;           /* wall time of the host thread coding the anchor dictionary (0 when on device) */
     float dict_wait_ms;           /* how long the stream's work had been finished before that thread was */
-    float reserved[4];
+    float dict_copy_wait_ms;      /* part of dict_host_ms spent waiting for the records to arrive from the device */
+    float reserved[3];
 } leon_timings;
 
 typedef struct leon_ctx leon_ctx;

@@ -56,7 +56,8 @@ class Timings(C.Structure):
                                          "entropy_ms", "d2h_ms", "total_ms")] + \
                [("kernel_launches", C.c_uint64), ("sort_passes", C.c_uint32), ("anchor_batches", C.c_uint32),
                 ("anchor_rounds", C.c_uint32), ("sort_pass_ms", C.c_float), ("sort_keys", C.c_uint64),
-                ("dict_host_ms", C.c_float), ("dict_wait_ms", C.c_float), ("reserved", C.c_float * 4)]
+                ("dict_host_ms", C.c_float), ("dict_wait_ms", C.c_float), ("dict_copy_wait_ms", C.c_float),
+                ("reserved", C.c_float * 3)]
 
 
 class KernelTime(C.Structure):

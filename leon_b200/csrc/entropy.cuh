@@ -368,111 +368,7 @@ __global__ void k_block_descs(const uint64_t *__restrict__ symoff, uint64_t nrea
     descs[b] = d;
 }
 
-// One coding step (RangeEncoder::encode, C/RangeCoder.cpp:106-134) with range / total done as
-// hi64((range + inc) * magic) >> shift (div_magic).  Bytes shifted out go to *op (op advances); when `store` is
-// false (output region exhausted, reported as overflow by the caller) they are only counted.
-LB_D void rc_step(uint64_t &low, uint64_t &range, const uint4 t, const uint32_t sh, uint8_t *&op, const bool store)
-{
-    const uint64_t m = ((uint64_t)t.w << 32) | t.z;
-    const uint64_t q = (uint64_t)(((unsigned __int128)range * m + ((sh & 0x80u) ? m : 0ull)) >> 64) >> (sh & 63u);
-    low += (uint64_t)t.x * q;
-    range = q * (uint64_t)t.y;
-    while (true) {
-        const uint32_t lh = (uint32_t)(low >> 32);
-        const uint32_t sh32 = (uint32_t)((low + range) >> 32);
-        if ((lh ^ sh32) >= (1u << 24)) {                       // top bytes of low and low + range differ
-            if ((uint32_t)(range >> 32) >= (1u << 16)) break;  // range >= 2^48
-            range = (0 - low) & (RC_BOTTOM - 1);
-        }
-        if (store) *op = (uint8_t)(lh >> 24);
-        op++;
-        range <<= 8;
-        low <<= 8;
-    }
-}
-
 constexpr uint32_t RC_MAX_BYTES_PER_SYMBOL = 12;   // <= 4 bytes of information + one clamp and its 7 refill shifts
-
-// RangeEncoder::encode / flush, C/RangeCoder.cpp:106-145.  One warp per stream: the 32 lanes stage the next 32 symbol
-// records in shared memory (coalesced loads, issued one batch ahead), lane 0 runs the low/range recurrence over them
-// with the record of the next symbol already in registers.
-__global__ void __launch_bounds__(32) k_range_encode_v0(const uint4 *__restrict__ rec_all, const uint8_t *__restrict__ sh_all,
-                                                     const StreamDesc *__restrict__ descs, uint8_t *__restrict__ out_all,
-                                                     uint64_t *__restrict__ out_size, int always_flush, uint32_t *overflow)
-{
-    __shared__ uint4 srec[2][34];
-    __shared__ uint32_t ssh[2][34];
-    const int lane = threadIdx.x;
-    const StreamDesc d = descs[blockIdx.x];
-    const uint4 *rec = rec_all + d.rec_base;
-    const uint8_t *sh = sh_all + d.rec_base;
-    uint8_t *const out0 = out_all + d.out_base;
-    uint8_t *op = out0;
-    bool ovf = false;
-    uint64_t low = 0, range = ~0ull;
-    uint4 nx = make_uint4(0u, 1u, 0xffffffffu, 0xffffffffu);
-    uint32_t nsx = 0x80u;
-    if ((uint64_t)lane < d.nsym) { nx = rec[lane]; nsx = sh[lane]; }
-    for (uint64_t base = 0; base < d.nsym; base += 32) {
-        const int buf = (int)((base >> 5) & 1);
-        srec[buf][lane] = nx;
-        ssh[buf][lane] = nsx;
-        uint64_t in = base + 32 + lane;
-        if (in < d.nsym) { nx = rec[in]; nsx = sh[in]; }
-        __syncwarp();
-        if (lane == 0) {
-            const int steps = d.nsym - base < 32 ? (int)(d.nsym - base) : 32;
-            // room for the worst case of this batch, checked once instead of per byte
-            const bool store = (uint64_t)(op - out0) + 32 * RC_MAX_BYTES_PER_SYMBOL + 8 <= d.out_cap;
-            ovf |= !store;
-            const uint4 *sr = srec[buf];
-            const uint32_t *ss = ssh[buf];
-            int j = 0;
-            if (base == 0) {
-                // first symbol: range is 2^64 - 1, so range + inc may wrap; (2^64 * m) >> 64 == m
-                uint4 t = sr[0];
-                uint32_t s = ss[0];
-                uint64_t m = ((uint64_t)t.w << 32) | t.z;
-                uint64_t q = ((s >> 7) ? m : __umul64hi(range, m)) >> (s & 63u);
-                low = (uint64_t)t.x * q;
-                range = q * (uint64_t)t.y;
-                while ((low ^ (low + range)) < RC_TOP || range < RC_BOTTOM) {
-                    if (range < RC_BOTTOM && (low ^ (low + range)) >= RC_TOP) range = (0 - low) & (RC_BOTTOM - 1);
-                    if (store) *op = (uint8_t)(low >> 56);
-                    op++;
-                    range <<= 8;
-                    low <<= 8;
-                }
-                j = 1;
-            }
-            uint4 ta = sr[j];
-            uint32_t sa = ss[j];
-            for (; j + 1 < steps; j += 2) {          // two symbols per iteration: no register rotation
-                uint4 tb = sr[j + 1];
-                uint32_t sb = ss[j + 1];
-                rc_step(low, range, ta, sa, op, store);
-                ta = sr[j + 2];                       // slots 32, 33 exist: the arrays have 34 entries
-                sa = ss[j + 2];
-                rc_step(low, range, tb, sb, op, store);
-            }
-            if (j < steps) rc_step(low, range, ta, sa, op, store);
-        }
-        __syncwarp();
-    }
-    if (lane == 0) {
-        uint64_t nout = (uint64_t)(op - out0);
-        if (always_flush || nout > 0) {                       // DnaEncoder::writeBlock flushes only a non-empty buffer
-            for (int x = 0; x < 8; x++) {
-                if (nout < d.out_cap) out0[nout] = (uint8_t)(low >> 56);
-                else ovf = true;
-                nout++;
-                low <<= 8;
-            }
-        }
-        out_size[blockIdx.x] = nout;
-        if (ovf) *overflow = 1;
-    }
-}
 
 // ---- range coder, current kernel ------------------------------------------------------------------------------
 // A single warp issues at most one instruction every other cycle per pipe, so the serial recurrence is bound by the
@@ -521,32 +417,48 @@ LB_D void rc_step_any(uint64_t &low, uint64_t &range, const uint4 t, const uint3
     }
 }
 
-// The common case of a coding step as straight-line code.  State: low, and rp = range + inc of THIS symbol (div_magic:
-// range / total == hi64((range + inc) * magic) >> shift; rp fits in 64 bits because range < 2^64 - 1 once a real symbol
-// has been coded; the first symbols of a stream go through rc_step_any).  With x = hi32(low) ^ hi32(low + range) the
-// renormalisation loop exits after 0 byte (x >= 2^24 and range >= 2^48) or after exactly 1 byte (x in [2^16, 2^24): the
-// second byte differs once shifted in; range >= 2^48 already) for all but a few percent of the symbols; for those the
-// step returns false with (lw, rg) = the state before renormalisation.  The byte is stored unconditionally and the
-// output index advances by 0 or 1.
-LB_D bool rc_step_fast(uint64_t &low, uint64_t &rp, const uint4 t, const uint32_t shift, const uint32_t inc_next,
-                       uint32_t &on, uint64_t &lw, uint64_t &rg)
+// The common case of a coding step as straight-line code without any predicate or branch (ISETP -> predicated use and
+// ISETP -> BRA each cost ~13 cycles of a single warp's time, measured with ncu's per-instruction stall samples).
+// State: low, and rp = range + inc of THIS symbol (div_magic: range / total == hi64((range + inc) * magic) >> shift; rp
+// fits in 64 bits because range < 2^64 - 1 once a real symbol has been coded; the first symbols of a stream go through
+// rc_step_any).  With x = hi32(low) ^ hi32(low + range) the renormalisation loop of RangeEncoder::encode exits after
+// 0 byte (x >= 2^24 and range >= 2^48) or after exactly 1 byte (x in [2^16, 2^24): the second byte differs once shifted
+// in; shifted range >= 2^48) for 98.6 % of the symbols.  The "one byte settled" decision is an arithmetic mask that
+// selects between the two candidates of (low, rp); the byte is stored unconditionally and the output index advances by
+// 0 or 1.  Whether the step was one of the rare ones (two bytes or more, or a range clamp) is only accumulated (rmin):
+// the caller tests it once per group of four steps and, if so, recodes the group from its saved start state with
+// rc_step_any.  After a
+// rare symbol the remaining steps of the group run on a meaningless state, which is harmless: pure arithmetic, and the
+// output index advances by at most one per step.
+LB_D void rc_step_spec(uint64_t &low, uint64_t &rp, uint32_t &on, uint32_t &rmin, const uint4 t, const uint32_t shift,
+                       const uint32_t inc_next)
 {
     const uint64_t m = ((uint64_t)t.w << 32) | t.z;
     const uint64_t q = __umul64hi(rp, m) >> shift;
-    lw = low + (uint64_t)t.x * q;
-    rg = q * (uint64_t)t.y;
+    const uint64_t lw = low + (uint64_t)t.x * q;
+    const uint64_t rg = q * (uint64_t)t.y;
+    const uint64_t top = low + (uint64_t)(t.x + t.y) * q;     // == lw + rg, formed beside them instead of after them
     uint32_t ll, lh, rl, rh, sl, shi;
     split64(lw, ll, lh);
     split64(rg, rl, rh);
-    split64(lw + rg, sl, shi);
+    split64(top, sl, shi);
     const uint32_t x = lh ^ shi;
-    if (__builtin_expect(min(x, rh) < (1u << 16), 0)) return false;
-    const bool one = x < (1u << 24);
+    uint32_t mask;                                            // all ones when x < 2^24 (top byte settled), else 0
+    asm("{ .reg .u32 t; shr.u32 t, %1, 24; sub.u32 t, t, 1; shr.s32 %0, t, 31; }" : "=r"(mask) : "r"(x));
     sts8(on, lh >> 24);
-    if (one) on++;
-    low = one ? (lw << 8) : lw;
-    rp = one ? ((rg << 8) | inc_next) : (rg + inc_next);
-    return true;
+    on -= mask;
+    // candidates: no byte -> (lw, rg + inc_next); one byte -> (lw << 8, (rg << 8) | inc_next)
+    const uint32_t l1l = ll << 8, l1h = (lh << 8) | (ll >> 24);
+    const uint64_t c0 = rg + inc_next;
+    uint32_t c0l, c0h;
+    split64(c0, c0l, c0h);
+    const uint32_t c1l = (rl << 8) | inc_next, c1h = (rh << 8) | (rl >> 24);
+    // rare unless the second byte is not settled as well (x >= 2^16) and the range after the 0 or 1 byte is >= 2^48
+    rmin = min(rmin, min(x, rh ^ ((rh ^ ((rh << 8) | (rl >> 24))) & mask)));
+    const uint32_t nl = ll ^ ((ll ^ l1l) & mask), nh = lh ^ ((lh ^ l1h) & mask);
+    const uint32_t pl = c0l ^ ((c0l ^ c1l) & mask), ph = c0h ^ ((c0h ^ c1h) & mask);
+    low = ((uint64_t)nh << 32) | nl;
+    rp = ((uint64_t)ph << 32) | pl;
 }
 
 constexpr int RC_BATCH = 64;       // symbol records staged per round (two per lane)
@@ -604,52 +516,33 @@ __global__ void __launch_bounds__(32) k_range_encode(const uint4 *__restrict__ r
             uint4 t0 = lds128(sr + 16 * j);
             uint2 s0 = lds64(ss + 8 * j);
             uint64_t rp = range + s0.y;
-            while (j < RC_BATCH) {
-                uint64_t lw, rg;
-                int bad = -1;
-                uint32_t keep = 0;
 #pragma unroll 1
-                for (; j < RC_BATCH; j += 4) {
-                    const uint4 t1 = lds128(sr + 16 * j + 16), t2 = lds128(sr + 16 * j + 32), t3 = lds128(sr + 16 * j + 48);
-                    const uint4 t4 = lds128(sr + 16 * j + 64);
-                    const uint2 s1 = lds64(ss + 8 * j + 8), s2 = lds64(ss + 8 * j + 16), s3 = lds64(ss + 8 * j + 24);
-                    const uint2 s4 = lds64(ss + 8 * j + 32);
-                    keep = t1.x ^ t2.x ^ t3.x ^ t4.x ^ s1.x ^ s2.x ^ s3.x ^ s4.x;
-                    if (!rc_step_fast(low, rp, t0, s0.x, s1.y, on, lw, rg)) { bad = 0; break; }
-                    if (!rc_step_fast(low, rp, t1, s1.x, s2.y, on, lw, rg)) { bad = 1; break; }
-                    if (!rc_step_fast(low, rp, t2, s2.x, s3.y, on, lw, rg)) { bad = 2; break; }
-                    if (!rc_step_fast(low, rp, t3, s3.x, s4.y, on, lw, rg)) { bad = 3; break; }
-                    t0 = t4;
-                    s0 = s4;
-                }
-                if (bad >= 0) {
-                    // rare: finish symbol j + bad with the generic loop, code the rest of its group generically, resume.
-                    // (The group's records are consumed here as well so that their loads stay at the top of the group,
-                    // ahead of the dependent chain, instead of being sunk below the steps' exit branches.)
-                    asm volatile("st.shared.u32 [%0], %1;" ::"r"(sout_a + RC_OBUF - 4), "r"(keep) : "memory");
-                    low = lw;
-                    range = rg;
+            for (; j < RC_BATCH; j += 4) {
+                const uint4 t1 = lds128(sr + 16 * j + 16), t2 = lds128(sr + 16 * j + 32), t3 = lds128(sr + 16 * j + 48);
+                const uint4 t4 = lds128(sr + 16 * j + 64);
+                const uint2 s1 = lds64(ss + 8 * j + 8), s2 = lds64(ss + 8 * j + 16), s3 = lds64(ss + 8 * j + 24);
+                const uint2 s4 = lds64(ss + 8 * j + 32);
+                const uint64_t low_g = low, rp_g = rp;          // state at the start of the group
+                const uint32_t on_g = on;
+                uint32_t rmin = 0xffffffffu;
+                rc_step_spec(low, rp, on, rmin, t0, s0.x, s1.y);
+                rc_step_spec(low, rp, on, rmin, t1, s1.x, s2.y);
+                rc_step_spec(low, rp, on, rmin, t2, s2.x, s3.y);
+                rc_step_spec(low, rp, on, rmin, t3, s3.x, s4.y);
+                if (__builtin_expect(rmin < (1u << 16), 0)) {
+                    // a step needed more than one byte or a range clamp: recode the group with the generic step
+                    low = low_g;
+                    range = rp_g - s0.y;
+                    on = on_g;
 #pragma unroll 1
-                    for (int guard = 0; guard < (int)RC_MAX_BYTES_PER_SYMBOL; guard++) {
-                        const uint32_t lh = (uint32_t)(low >> 32);
-                        if ((lh ^ (uint32_t)((low + range) >> 32)) >= (1u << 24)) {
-                            if ((uint32_t)(range >> 32) >= (1u << 16)) break;
-                            range = (0 - low) & (RC_BOTTOM - 1);
-                        }
-                        sts8(on++, lh >> 24);
-                        range <<= 8;
-                        low <<= 8;
-                    }
-#pragma unroll 1
-                    for (int i = j + bad + 1; i < j + 4; i++) {
+                    for (int i = j; i < j + 4; i++) {
                         const uint2 sx = lds64(ss + 8 * i);
                         rc_step_any(low, range, lds128(sr + 16 * i), sx.x, sx.y, on);
                     }
-                    j += 4;
-                    t0 = lds128(sr + 16 * j);
-                    s0 = lds64(ss + 8 * j);
-                    rp = range + s0.y;
+                    rp = range + s4.y;
                 }
+                t0 = t4;
+                s0 = s4;
             }
             range = rp;           // the slot past the batch has inc 0
         }
@@ -707,8 +600,10 @@ __global__ void k_blocksizes(const uint64_t *__restrict__ sizes, uint64_t nreads
 }
 
 // ---- anchor dictionary stream ----------------------------------------------------------------------------------
+// The dictionary grows batch by batch; slices [a0, a0 + n) of it are turned into records as soon as they exist, `base`
+// = nucleotide counts of the anchors before the slice (the total of the previous slices' scans).
 template <typename K> struct DictCountIn {
-    const K *anchors; int k;
+    const K *anchors; int k;       // anchors: first anchor of the slice
     __device__ lbscan::U32x4 operator()(uint64_t a) const
     {
         K x = anchors[a];
@@ -719,12 +614,12 @@ template <typename K> struct DictCountIn {
 };
 // k symbols per anchor, most significant nucleotide first (toString order, C/Leon.cpp:1245-1253), Order0Model(5)
 template <typename K> struct DictRecOut {
-    const K *anchors; int k; uint4 *rec; uint8_t *sh;
+    const K *anchors; int k; uint4 *rec; uint8_t *sh; lbscan::U32x4 base;
     __device__ void operator()(uint64_t a, lbscan::U32x4 ex, lbscan::U32x4) const
     {
         K x = anchors[a];
-        uint32_t c[4] = {ex.a, ex.b, ex.c, ex.d};
-        uint32_t tot = 5u + ex.a + ex.b + ex.c + ex.d;
+        uint32_t c[4] = {base.a + ex.a, base.b + ex.b, base.c + ex.c, base.d + ex.d};
+        uint32_t tot = 5u + c[0] + c[1] + c[2] + c[3];
         uint64_t o = a * (uint64_t)k;
         for (int i = k - 1; i >= 0; i--) {
             unsigned v = (unsigned)(x >> (2 * i)) & 3u;

@@ -16,6 +16,7 @@
 #include <vector>
 #include <algorithm>
 #include <thread>
+#include <atomic>
 #include <chrono>
 
 namespace {
@@ -105,12 +106,16 @@ struct leon_ctx {
     DevBuf d_bif, d_err, d_recs, d_symoff, d_srec, d_srec_alt, d_segstart, d_chunkoff, d_chist, d_rec, d_sh, d_descs, d_outall,
         d_outsize, d_dnaoff, d_dna, d_bs, d_qout;
     DevBuf d_dict_rec, d_dict_sh, d_dict_desc, d_dict_out, d_dict_size, d_scan2;
-    PinBuf h_desc, h_dstage_rec[2], h_dstage_sh[2];
-    cudaEvent_t ev_dstage[2] = {nullptr, nullptr};
+    PinBuf h_desc, h_dstage_rec[2], h_dstage_sh[2], h_dict_tot;
+    DevBuf d_dict_rec2[2], d_dict_sh2[2];
+    cudaEvent_t ev_dstage[2] = {nullptr, nullptr}, ev_dtot = nullptr;
+    std::atomic<uint64_t> dict_pub{0};     // anchors inserted so far (published by the main thread after every batch)
+    std::atomic<bool> dict_fin{false}, dict_abort{false};
+    LaunchCounter lc2;                     // launches of the dictionary thread
     std::thread dict_thread;             // host side of the anchor dictionary coder (see dict_host_worker)
     std::vector<uint8_t> dict_host_out;
     std::string dict_thread_err;
-    double dict_host_ms = 0;
+    double dict_host_ms = 0, dict_copy_wait_ms = 0;
     uint64_t nblocks = 0, dna_nbytes = 0, dict_nbytes = 0, nsym_total = 0;
     PinBuf h_dna, h_bs, h_dict, h_qual, h_qsizes, h_apos, h_aaddr;
     uint64_t reads_without_anchor = 0;
@@ -404,54 +409,139 @@ namespace {
 // Anchor dictionary dump (C/Leon.cpp:1034-1042,1245-1260): ONE never-reset range coder over all anchors.  The
 // data-parallel part (order-0 model state and the exact reciprocal of `total` for every symbol) is computed on the
 // GPU (DictCountIn/DictRecOut); what is left is the strictly serial low/range recurrence, 3 multiplies per symbol.
-// A GPU thread needs ~110 ns per step of it (measured, profiles/), a host core ~5 ns, and the dump belongs to the
+// A GPU thread needs ~70 ns per step of it (measured, profiles/), a host core ~6 ns, and the dump belongs to the
 // orchestrator (Leon::encodeInsertedAnchor), so by default this recurrence runs on a host thread that streams the
-// records out of HBM while the GPU walks and codes the blocks.  opts.dict_on_device = 1 runs it as a kernel instead
-// (k_range_encode on the second stream); both produce the same bytes.
-constexpr uint64_t DICT_STAGE_SYMS = 1ull << 20;
+// records out of HBM while the GPU resolves the later anchor batches, walks and codes the blocks: the dictionary is
+// append-only, so the thread starts with the first batch and follows the published anchor count.
+// opts.dict_on_device = 1 runs it as a kernel instead (k_range_encode on the second stream); both produce the same bytes.
+constexpr uint64_t DICT_STAGE_SYMS = 1ull << 19;
 
-void dict_host_worker(leon_ctx *c, uint64_t nsym)
+// One slice of records through the recurrence; same step as rc_step_spec (entropy.cuh): 0 or 1 output byte without a
+// data-dependent branch, the rare rest through the generic loop of RangeEncoder::encode.
+void dict_code_slice(const uint32_t *rec, const uint8_t *sh, uint64_t n, bool first, uint64_t &low, uint64_t &range,
+                     std::vector<uint8_t> &out)
+{
+    const uint64_t TOP = 1ull << 56, BOTTOM = 1ull << 48;
+    const size_t pos0 = out.size();
+    out.resize(pos0 + n * 2 + 64);          // the common step writes <= 1 byte per symbol; the rare path re-checks
+    uint8_t *op = out.data() + pos0;
+    const uint8_t *op_end = out.data() + out.size();
+    uint64_t j = 0;
+    if (first && n) {                       // first symbol: range = 2^64 - 1, range + inc needs 65 bits
+        const uint64_t m = ((uint64_t)rec[3] << 32) | rec[2];
+        const uint32_t s = sh[0];
+        const uint64_t q = (uint64_t)(((unsigned __int128)range * m + ((s & 0x80u) ? m : 0ull)) >> 64) >> (s & 63u);
+        low += (uint64_t)rec[0] * q;
+        range = q * (uint64_t)rec[1];
+        while ((low ^ (low + range)) < TOP || range < BOTTOM) {
+            if (range < BOTTOM && (low ^ (low + range)) >= TOP) range = (0 - low) & (BOTTOM - 1);
+            *op++ = (uint8_t)(low >> 56);
+            range <<= 8;
+            low <<= 8;
+        }
+        j = 1;
+    }
+    uint64_t rp = range + (j < n ? (sh[j] >> 7) : 0u);      // range + inc of symbol j
+    for (; j < n; j++) {
+        const uint32_t lo = rec[4 * j], w = rec[4 * j + 1];
+        const uint64_t m = ((uint64_t)rec[4 * j + 3] << 32) | rec[4 * j + 2];
+        const uint32_t inc_next = j + 1 < n ? (sh[j + 1] >> 7) : 0u;
+        const uint64_t q = (uint64_t)(((unsigned __int128)rp * m) >> 64) >> (sh[j] & 63u);   // == range / total
+        low += (uint64_t)lo * q;
+        range = q * (uint64_t)w;
+        const uint32_t x = (uint32_t)((low ^ (low + range)) >> 32), rh = (uint32_t)(range >> 32);
+        if (__builtin_expect((x < rh ? x : rh) < 65536u, 0)) {
+            while ((low ^ (low + range)) < TOP || range < BOTTOM) {
+                if (range < BOTTOM && (low ^ (low + range)) >= TOP) range = (0 - low) & (BOTTOM - 1);
+                *op++ = (uint8_t)(low >> 56);
+                range <<= 8;
+                low <<= 8;
+            }
+            if (op + (n - j) + 32 > op_end) {      // keep one byte per remaining symbol plus a rare step in reserve
+                const size_t used = op - out.data();
+                out.resize(out.size() * 2 + 64);
+                op = out.data() + used;
+                op_end = out.data() + out.size();
+            }
+            rp = range + inc_next;
+            continue;
+        }
+        const unsigned one = x < (1u << 24);
+        *op = (uint8_t)(low >> 56);
+        op += one;
+        low <<= 8 * one;
+        range <<= 8 * one;
+        rp = range + inc_next;
+    }
+    out.resize(op - out.data());
+}
+
+template <typename K> void dict_host_worker(leon_ctx *c)
 {
     auto t0 = std::chrono::steady_clock::now();
+    double copy_wait = 0, idle = 0;
     try {
         CUDA_TRY(cudaSetDevice(c->opts.device));
-        const uint4 *d_rec = c->d_dict_rec.as<uint4>();
-        const uint8_t *d_sh = c->d_dict_sh.as<uint8_t>();
+        const int k = c->opts.kmer_size;
+        const uint64_t slice_anchors = std::max<uint64_t>(1, DICT_STAGE_SYMS / (uint64_t)k);
+        const uint64_t slice_syms = slice_anchors * (uint64_t)k;
+        cudaStream_t s2 = c->st2;
+        for (int i = 0; i < 2; i++) {
+            c->d_dict_rec2[i].reserve((slice_syms + 1) * sizeof(uint4));
+            c->d_dict_sh2[i].reserve(slice_syms + 1);
+            c->h_dstage_rec[i].reserve(slice_syms * sizeof(uint4));
+            c->h_dstage_sh[i].reserve(slice_syms);
+            if (!c->ev_dstage[i]) CUDA_TRY(cudaEventCreateWithFlags(&c->ev_dstage[i], cudaEventDisableTiming));
+        }
+        if (!c->ev_dtot) CUDA_TRY(cudaEventCreateWithFlags(&c->ev_dtot, cudaEventDisableTiming));
+        c->h_dict_tot.reserve(64);
         std::vector<uint8_t> &out = c->dict_host_out;
         out.clear();
-        out.reserve(nsym / 3 + 64);
-        const uint64_t nch = (nsym + DICT_STAGE_SYMS - 1) / DICT_STAGE_SYMS;
-        auto issue = [&](uint64_t i) {
-            uint64_t off = i * DICT_STAGE_SYMS, n = std::min(DICT_STAGE_SYMS, nsym - off);
-            CUDA_TRY(cudaMemcpyAsync(c->h_dstage_rec[i & 1].p, d_rec + off, n * sizeof(uint4), cudaMemcpyDeviceToHost, c->st2));
-            CUDA_TRY(cudaMemcpyAsync(c->h_dstage_sh[i & 1].p, d_sh + off, n, cudaMemcpyDeviceToHost, c->st2));
-            CUDA_TRY(cudaEventRecord(c->ev_dstage[i & 1], c->st2));
-        };
         uint64_t low = 0, range = ~0ull;
-        const uint64_t TOP = 1ull << 56, BOTTOM = 1ull << 48;
-        if (nch) issue(0);
-        for (uint64_t i = 0; i < nch; i++) {
-            if (i + 1 < nch) issue(i + 1);
-            CUDA_TRY(cudaEventSynchronize(c->ev_dstage[i & 1]));
-            const uint32_t *rec = c->h_dstage_rec[i & 1].as<uint32_t>();
-            const uint8_t *sh = c->h_dstage_sh[i & 1].as<uint8_t>();
-            uint64_t n = std::min(DICT_STAGE_SYMS, nsym - i * DICT_STAGE_SYMS);
-            for (uint64_t j = 0; j < n; j++) {
-                uint32_t lo = rec[4 * j], w = rec[4 * j + 1];
-                uint64_t m = ((uint64_t)rec[4 * j + 3] << 32) | rec[4 * j + 2];
-                uint32_t s = sh[j];
-                uint64_t num = range + (s >> 7);                    // wraps only for the very first symbol
-                uint64_t q = ((s >> 7) && num == 0) ? m : (uint64_t)(((unsigned __int128)num * m) >> 64);
-                q >>= (s & 63u);                                    // == range / total (RangeCoder.cpp:108)
-                low += (uint64_t)lo * q;
-                range = q * (uint64_t)w;
-                while ((low ^ (low + range)) < TOP || range < BOTTOM) {
-                    if (range < BOTTOM && (low ^ (low + range)) >= TOP) range = (0 - low) & (BOTTOM - 1);
-                    out.push_back((uint8_t)(low >> 56));
-                    range <<= 8;
-                    low <<= 8;
-                }
+        lbscan::U32x4 base{0, 0, 0, 0};
+        uint64_t launched = 0;                 // anchors handed to the GPU so far
+        struct Pending { uint64_t n; int slot; } pend[2];
+        int npend = 0, next_slot = 0;
+        bool first = true;
+        while (true) {
+            if (c->dict_abort.load()) break;
+            const bool fin = c->dict_fin.load(std::memory_order_acquire);
+            const uint64_t avail = c->dict_pub.load(std::memory_order_acquire);
+            while (npend < 2 && launched < avail) {     // records of the next slice: scan + D2H on the second stream
+                const uint64_t n = std::min(slice_anchors, avail - launched);
+                const int slot = next_slot;
+                next_slot ^= 1;
+                const K *an = c->d_anchors.as<K>() + launched;
+                lbscan::U32x4 *tot = lbscan::exclusive_scan<lbscan::U32x4>(
+                    n, lbent::DictCountIn<K>{an, k},
+                    lbent::DictRecOut<K>{an, k, c->d_dict_rec2[slot].as<uint4>(), c->d_dict_sh2[slot].as<uint8_t>(), base},
+                    c->d_scan2, s2, c->lc2);
+                CUDA_TRY(cudaMemcpyAsync(c->h_dict_tot.p, tot, sizeof(lbscan::U32x4), cudaMemcpyDeviceToHost, s2));
+                CUDA_TRY(cudaEventRecord(c->ev_dtot, s2));
+                CUDA_TRY(cudaMemcpyAsync(c->h_dstage_rec[slot].p, c->d_dict_rec2[slot].p, n * k * sizeof(uint4), cudaMemcpyDeviceToHost, s2));
+                CUDA_TRY(cudaMemcpyAsync(c->h_dstage_sh[slot].p, c->d_dict_sh2[slot].p, n * k, cudaMemcpyDeviceToHost, s2));
+                CUDA_TRY(cudaEventRecord(c->ev_dstage[slot], s2));
+                CUDA_TRY(cudaEventSynchronize(c->ev_dtot));      // counts of this slice: base of the next one
+                base = base + *c->h_dict_tot.as<lbscan::U32x4>();
+                pend[npend++] = Pending{n, slot};
+                launched += n;
             }
+            if (npend == 0) {
+                if (fin) break;             // fin is set after the last publication, and everything published is coded
+                auto w0 = std::chrono::steady_clock::now();
+                std::this_thread::sleep_for(std::chrono::microseconds(20));
+                idle += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - w0).count();
+                continue;
+            }
+            const Pending p = pend[0];
+            pend[0] = pend[1];
+            npend--;
+            auto w0 = std::chrono::steady_clock::now();
+            CUDA_TRY(cudaEventSynchronize(c->ev_dstage[p.slot]));
+            copy_wait += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - w0).count();
+            dict_code_slice(c->h_dstage_rec[p.slot].as<uint32_t>(), c->h_dstage_sh[p.slot].as<uint8_t>(), p.n * (uint64_t)k, first,
+                            low, range, out);
+            first = false;
         }
         for (int x = 0; x < 8; x++) { out.push_back((uint8_t)(low >> 56)); low <<= 8; }   // flush, RangeCoder.cpp:136-145
     } catch (const LeonError &e) {
@@ -459,7 +549,8 @@ void dict_host_worker(leon_ctx *c, uint64_t nsym)
     } catch (const std::exception &e) {
         c->dict_thread_err = e.what();
     }
-    c->dict_host_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    c->dict_copy_wait_ms = copy_wait;
+    c->dict_host_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count() - idle;
 }
 
 template <typename K> lbanchor::DictDev<K> dict_view(leon_ctx *c, int which)
@@ -560,8 +651,19 @@ template <typename K> void do_anchors(leon_ctx *c)
         R_total = fetch_scalar(c, c->d_xchg.as<uint64_t>() + 1);
     }
     if (R_total >= 0xfffffff0ull) throw LeonError(LEON_E_ARG, "more than 2^32-16 reads in one read set");
-    c->d_anchors.reserve((std::min<uint64_t>(R_total, 1ull << 22) + 1) * sizeof(K));
+    if ((uint64_t)k * R_total >= 0xffffff00ull) throw LeonError(LEON_E_OVERFLOW, "anchor dictionary stream could exceed 2^32 symbols");
+    // every read inserts at most one anchor: sized once, so that the dictionary thread can read the list while it grows
+    c->d_anchors.reserve((R_total + 1) * sizeof(K));
     uint64_t anchors_cap = c->d_anchors.cap / sizeof(K);
+    const bool dict_thread_on = c->comm.rank == 0 && !c->opts.dict_on_device;
+    if (dict_thread_on) {
+        if (c->dict_thread.joinable()) c->dict_thread.join();
+        c->dict_thread_err.clear();
+        c->dict_pub.store(0);
+        c->dict_fin.store(false);
+        c->dict_abort.store(false);
+        c->dict_thread = std::thread(dict_host_worker<K>, c);
+    }
     std::vector<uint32_t> m_all(N, 0), m_off(N, 0);
 
     for (uint64_t g = 0; g < nbatches; g++) {
@@ -656,28 +758,20 @@ template <typename K> void do_anchors(leon_ctx *c)
             }
             // I: addresses in read order, insertion into D (every rank inserts every new anchor)
             dict_ensure<K>(c, c->dict_count + m);
-            if (c->dict_count + m + 1 > anchors_cap) {
-                // grow the anchor list (keeps its content)
-                uint64_t ncap = std::max<uint64_t>(anchors_cap * 2, c->dict_count + m + 1);
-                DevBuf nbuf;
-                nbuf.reserve(ncap * sizeof(K));
-                CUDA_TRY(cudaMemcpyAsync(nbuf.p, c->d_anchors.p, c->dict_count * sizeof(K), cudaMemcpyDeviceToDevice, st));
-                CUDA_TRY(cudaStreamSynchronize(st));
-                c->d_anchors.release();
-                c->d_anchors = nbuf;
-                anchors_cap = ncap;
-            }
+            if (c->dict_count + m + 1 > anchors_cap) throw LeonError(LEON_E_OVERFLOW, "anchor list: more anchors than reads");
             InsOut<K> io{cand_gid, cand_pos, cand_key, dict_view<K>(c, c->dict_cur), (uint32_t)c->dict_count,
                          c->d_anchors.as<K>(), apos, aaddr, insflag, joff, joff + m_own, delta};
             uint32_t *itot = lbscan::exclusive_scan<uint32_t>(m, InsIn{state}, io, c->d_scan, st, c->lc);
             nins = fetch_scalar(c, itot);
             c->dict_count += nins;
+            if (dict_thread_on) c->dict_pub.store(c->dict_count, std::memory_order_release);   // the stream is idle: the new anchors are in HBM
             // B: anchors of this batch can pre-empt later reads of the batch at earlier positions
             if (nins && nb)
                 LB_LAUNCH(c->lc, (k_anchor_lookup<K>), warp_grid(nb), 256, 0, st, bases, offsets, lo, hi, delta, k,
                           dict_view<K>(c, c->dict_cur), apos, aaddr, (const uint8_t *)insflag);
         }
     }
+    if (dict_thread_on) c->dict_fin.store(true, std::memory_order_release);
     CUDA_TRY(cudaEventRecord(c->ev[7], st));
 }
 
@@ -690,7 +784,7 @@ __global__ void k_count_noanchor(const int32_t *__restrict__ apos, uint64_t n, u
     if ((threadIdx.x & 31) == 0 && v) atomicAdd(out, v);
 }
 
-template <typename K> void do_encode(leon_ctx *c)
+template <typename K> void do_encode_body(leon_ctx *c)
 {
     using namespace lbent;
     cudaStream_t st = c->st;
@@ -705,46 +799,34 @@ template <typename K> void do_encode(leon_ctx *c)
     int32_t *apos = c->d_apos.as<int32_t>();
     uint32_t *aaddr = c->d_aaddr.as<uint32_t>();
 
-    // anchor dictionary stream: one coder over all anchors, flushed once (C/Leon.cpp:1034-1042,1245-1260).  It is one
-    // serial chain, so it runs on the second stream next to everything below.
+    // anchor dictionary stream: one coder over all anchors, flushed once (C/Leon.cpp:1034-1042,1245-1260).  By default
+    // the host thread started by do_anchors is already coding it; dict_on_device runs it as one more stream of
+    // k_range_encode on the second stream next to everything below.
     uint32_t *ovf = c->d_counters.as<uint32_t>() + 2;
-    {
+    CUDA_TRY(cudaMemsetAsync(c->d_counters.p, 0, 64, st));
+    if (c->comm.rank == 0 && c->opts.dict_on_device) {
         cudaStream_t s2 = c->st2;
         uint64_t A = c->dict_count;
         uint64_t nsym = A * (uint64_t)k;
-        if (nsym >= 0xffffff00ull) throw LeonError(LEON_E_OVERFLOW, "anchor dictionary stream longer than 2^32 symbols");
         c->d_dict_rec.reserve((nsym + 1) * sizeof(uint4));
         c->d_dict_sh.reserve(nsym + 1);
         c->d_dict_desc.reserve(sizeof(StreamDesc));
         c->d_dict_out.reserve(2 * nsym + 1024);
         c->d_dict_size.reserve(16);
-        CUDA_TRY(cudaMemsetAsync(c->d_counters.p, 0, 64, st));
         CUDA_TRY(cudaEventRecord(c->ev[13], st));
         CUDA_TRY(cudaStreamWaitEvent(s2, c->ev[13], 0));
         if (A)
             lbscan::exclusive_scan<lbscan::U32x4>(A, DictCountIn<K>{c->d_anchors.as<K>(), k},
-                                                  DictRecOut<K>{c->d_anchors.as<K>(), k, c->d_dict_rec.as<uint4>(), c->d_dict_sh.as<uint8_t>()},
+                                                  DictRecOut<K>{c->d_anchors.as<K>(), k, c->d_dict_rec.as<uint4>(), c->d_dict_sh.as<uint8_t>(),
+                                                                lbscan::U32x4{0, 0, 0, 0}},
                                                   c->d_scan2, s2, c->lc);
-        if (c->comm.rank != 0) {
-            // the dump is identical on every rank: rank 0 codes it
-        } else if (c->opts.dict_on_device) {
-            StreamDesc d{0, nsym, 0, 2 * nsym + 1024};
-            c->h_desc.reserve(sizeof d);
-            memcpy(c->h_desc.p, &d, sizeof d);
-            CUDA_TRY(cudaMemcpyAsync(c->d_dict_desc.p, c->h_desc.p, sizeof d, cudaMemcpyHostToDevice, s2));
-            LB_TIMED(c->kt, "k_range_encode_dict", s2, LB_LAUNCH(c->lc, k_range_encode, 1, 32, 0, s2, c->d_dict_rec.as<uint4>(), c->d_dict_sh.as<uint8_t>(),
-                      c->d_dict_desc.as<StreamDesc>(), c->d_dict_out.as<uint8_t>(), c->d_dict_size.as<uint64_t>(), 1, ovf + 1));
-            CUDA_TRY(cudaEventRecord(c->ev[14], s2));
-        } else {
-            for (int i = 0; i < 2; i++) {
-                c->h_dstage_rec[i].reserve(DICT_STAGE_SYMS * sizeof(uint4));
-                c->h_dstage_sh[i].reserve(DICT_STAGE_SYMS);
-                if (!c->ev_dstage[i]) CUDA_TRY(cudaEventCreateWithFlags(&c->ev_dstage[i], cudaEventDisableTiming));
-            }
-            c->dict_thread_err.clear();
-            if (c->dict_thread.joinable()) c->dict_thread.join();
-            c->dict_thread = std::thread(dict_host_worker, c, nsym);
-        }
+        StreamDesc d{0, nsym, 0, 2 * nsym + 1024};
+        c->h_desc.reserve(sizeof d);
+        memcpy(c->h_desc.p, &d, sizeof d);
+        CUDA_TRY(cudaMemcpyAsync(c->d_dict_desc.p, c->h_desc.p, sizeof d, cudaMemcpyHostToDevice, s2));
+        LB_TIMED(c->kt, "k_range_encode_dict", s2, LB_LAUNCH(c->lc, k_range_encode, 1, 32, 0, s2, c->d_dict_rec.as<uint4>(), c->d_dict_sh.as<uint8_t>(),
+                  c->d_dict_desc.as<StreamDesc>(), c->d_dict_out.as<uint8_t>(), c->d_dict_size.as<uint64_t>(), 1, ovf + 1));
+        CUDA_TRY(cudaEventRecord(c->ev[14], s2));
     }
 
     c->d_err.reserve((c->nkmers + 1) * 4);
@@ -856,6 +938,18 @@ template <typename K> void do_encode(leon_ctx *c)
     c->phase = PH_ENCODED;
 }
 
+// do_encode_body with the dictionary thread stopped on every error path
+template <typename K> void do_encode(leon_ctx *c)
+{
+    try {
+        do_encode_body<K>(c);
+    } catch (...) {
+        c->dict_abort.store(true);
+        if (c->dict_thread.joinable()) c->dict_thread.join();
+        throw;
+    }
+}
+
 void do_fetch(leon_ctx *c, leon_result *out)
 {
     cudaStream_t st = c->st;
@@ -935,8 +1029,9 @@ static void fill_timings(leon_ctx *c)
     c->tm.entropy_ms = el(9, 10);
     c->tm.d2h_ms = el(11, 12);
     c->tm.total_ms = el(2, 10);
-    c->tm.kernel_launches = c->lc.n;
+    c->tm.kernel_launches = c->lc.n + c->lc2.n;
     c->tm.dict_host_ms = c->opts.dict_on_device ? 0.f : (float)c->dict_host_ms;
+    c->tm.dict_copy_wait_ms = c->opts.dict_on_device ? 0.f : (float)c->dict_copy_wait_ms;
     c->tm.dict_wait_ms = c->opts.dict_on_device ? 0.f : el(15, 14);
     c->kt.resolve();
     c->tm.sort_pass_ms = 0;
@@ -986,6 +1081,7 @@ void leon_destroy(leon_ctx *c)
 {
     if (!c) return;
     cudaSetDevice(c->opts.device);
+    c->dict_abort.store(true);
     if (c->dict_thread.joinable()) c->dict_thread.join();
     if (c->st) cudaStreamSynchronize(c->st);
     if (c->comm.comm) nccl_api().CommDestroy(c->comm.comm);
@@ -996,14 +1092,16 @@ void leon_destroy(leon_ctx *c)
                      &c->d_ct_fu, &c->d_dict_keys[0], &c->d_dict_keys[1], &c->d_dict_addr[0], &c->d_dict_addr[1], &c->d_dict_time[0],
                      &c->d_dict_time[1], &c->d_anchors, &c->d_counters, &c->d_bif, &c->d_err, &c->d_recs, &c->d_symoff, &c->d_srec, &c->d_srec_alt, &c->d_segstart,
                      &c->d_chunkoff, &c->d_chist, &c->d_rec, &c->d_sh, &c->d_scan2, &c->d_descs, &c->d_outall, &c->d_outsize, &c->d_dnaoff, &c->d_dna, &c->d_bs, &c->d_qout,
-                     &c->d_dict_rec, &c->d_dict_sh, &c->d_dict_desc, &c->d_dict_out, &c->d_dict_size};
+                     &c->d_dict_rec, &c->d_dict_sh, &c->d_dict_desc, &c->d_dict_out, &c->d_dict_size,
+                     &c->d_dict_rec2[0], &c->d_dict_rec2[1], &c->d_dict_sh2[0], &c->d_dict_sh2[1]};
     for (DevBuf *b : dev) b->release();
     PinBuf *pin[] = {&c->h_histo, &c->h_small, &c->h_bloom, &c->h_dna, &c->h_bs, &c->h_dict, &c->h_qual, &c->h_qsizes, &c->h_apos, &c->h_aaddr, &c->h_desc, &c->h_dstage_rec[0], &c->h_dstage_rec[1],
-                     &c->h_dstage_sh[0], &c->h_dstage_sh[1]};
+                     &c->h_dstage_sh[0], &c->h_dstage_sh[1], &c->h_dict_tot};
     for (PinBuf *b : pin) b->release();
     for (int i = 0; i < 16; i++) cudaEventDestroy(c->ev[i]);
     c->kt.release();
     for (int i = 0; i < 2; i++) if (c->ev_dstage[i]) cudaEventDestroy(c->ev_dstage[i]);
+    if (c->ev_dtot) cudaEventDestroy(c->ev_dtot);
     if (c->st && c->own_stream) cudaStreamDestroy(c->st);
     if (c->st2) { cudaStreamSynchronize(c->st2); cudaStreamDestroy(c->st2); }
     delete c;
