@@ -68,50 +68,81 @@ struct NkOut {
 };
 
 // ---- extraction ------------------------------------------------------------------------------------------
-// keys[koff[r] + p] = canonical k-mer at position p of read r, or the sentinel when the window holds an invalid
-// character ((c>>3)&1, MI/api/Data.hpp:176).  One warp per read, 32 positions per step.
+// Stages the bases of reads [r0, r1) of a CTA in shared memory with one bulk asynchronous copy (TMA, 1-D), so that
+// the per-thread walks read their bases from shared memory.  Returns the shared-memory address of bases[offsets[r0]],
+// or nullptr when the span does not fit (very long reads): callers then read from global memory.
+LB_D const uint8_t *stage_reads(const uint8_t *__restrict__ bases, uint64_t o0, uint64_t o1, uint8_t *smem, uint32_t smem_bytes,
+                                uint64_t *bar)
+{
+    const uint8_t *src = bases + (o0 & ~15ull);
+    uint64_t bytes = ((o1 - (o0 & ~15ull)) + 15ull) & ~15ull;
+    if (bytes > smem_bytes) return nullptr;        // CTA-uniform
+    if (bytes == 0) return smem;
+    uint32_t bar_a = (uint32_t)__cvta_generic_to_shared(bar);
+    uint32_t dst_a = (uint32_t)__cvta_generic_to_shared(smem);
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_a));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"((uint32_t)bytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(dst_a), "l"(src), "r"((uint32_t)bytes), "r"(bar_a) : "memory");
+    }
+    uint32_t done = 0;
+    while (!done) {
+        asm volatile("{\n\t.reg .pred p;\n\t"
+                     "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(bar_a) : "memory");
+    }
+    return smem + (o0 & 15ull);
+}
+
+// Canonical k-mer of every window of every read; the sentinel when the window holds an invalid character ((c>>3)&1,
+// MI/api/Data.hpp:176).  One THREAD per read: the bases of the 256 reads of a CTA are staged in shared memory by one
+// bulk copy, the forward k-mer and its reverse complement are rolled base by base (4 operations each, K/Model.hpp:725-764)
+// and the canonical one is their minimum (:876-883).  Only the multiset of keys matters downstream, so when all reads
+// of the CTA have the same length the keys of the tile are written position-major (key of read t, window p at
+// tile_base + p * reads + t: every store instruction of a warp is one contiguous run); otherwise at koff[r] + p.
 template <typename K>
 __global__ void __launch_bounds__(256) k_extract(const uint8_t *__restrict__ bases, const uint64_t *__restrict__ offsets,
-                                                 const uint64_t *__restrict__ koff, uint64_t nreads, int k, K *__restrict__ keys)
+                                                 const uint64_t *__restrict__ koff, uint64_t nreads, int k, K *__restrict__ keys,
+                                                 uint32_t stage_bytes)
 {
-    const int lane = threadIdx.x & 31;
-    uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
-    for (uint64_t r = warp; r < nreads; r += nwarps) {
-        uint64_t o = offsets[r], L = offsets[r + 1] - o;
-        if (L < (uint64_t)k) continue;
-        uint64_t n = L - k + 1;
-        const uint8_t *s = bases + o;
-        K *out = keys + koff[r];
-        uint64_t w0, w1 = 0, w2 = 0;
-        uint32_t n0, n1 = 0, n2 = 0;
-        // prime the window with chunks 0 and 1
-        {
-            uint8_t c = (uint64_t)lane < L ? s[lane] : (uint8_t)'A';
-            w0 = pack32(base_code(c));
-            n0 = __ballot_sync(0xffffffffu, base_invalid(c));
-            uint64_t i1 = 32 + lane;
-            c = i1 < L ? s[i1] : (uint8_t)'A';
-            w1 = pack32(base_code(c));
-            n1 = __ballot_sync(0xffffffffu, base_invalid(c));
-        }
-        for (uint64_t base = 0; base < n; base += 32) {
-            uint64_t i2 = base + 64 + lane;
-            uint8_t c = i2 < L ? s[i2] : (uint8_t)'A';
-            w2 = pack32(base_code(c));
-            n2 = __ballot_sync(0xffffffffu, base_invalid(c));
-            uint64_t p = base + lane;
-            if (p < n) {
-                K fwd = window_kmer<K>(w0, w1, w2, lane, k);
-                // invalid characters in [lane, lane+k) of the 96-bit mask n0 | n1<<32 | n2<<64 (k <= 63)
-                uint64_t nlo = (uint64_t)n0 | ((uint64_t)n1 << 32);
-                uint64_t win = lane ? ((nlo >> lane) | ((uint64_t)n2 << (64 - lane))) : nlo;
-                win &= (1ULL << k) - 1;
-                out[p] = win ? kmer_sentinel<K>() : kmer_canon(fwd, k);
-            }
-            w0 = w1; w1 = w2; n0 = n1; n1 = n2;
+    extern __shared__ __align__(128) uint8_t stage[];
+    __shared__ __align__(8) uint64_t bar;
+    const uint64_t r0 = (uint64_t)blockIdx.x * 256;
+    const uint64_t r1 = r0 + 256 < nreads ? r0 + 256 : nreads;
+    const uint64_t o0 = offsets[r0];
+    const uint8_t *sbase = stage_reads(bases, o0, offsets[r1], stage, stage_bytes, &bar);
+    const uint64_t r = r0 + threadIdx.x;
+    const bool have = r < nreads;
+    const uint64_t o = have ? offsets[r] : 0, L = have ? offsets[r + 1] - o : 0;
+    const uint64_t L0 = offsets[r0 + 1] - o0;
+    const int uniform = __syncthreads_and(!have || L == L0);      // also orders the staged bytes before their use
+    if (!have || L < (uint64_t)k) return;
+    const uint8_t *s = sbase ? sbase + (o - o0) : bases + o;
+    const uint64_t n = L - k + 1;
+    const uint64_t stride = uniform ? (r1 - r0) : 1;
+    K *out = uniform ? keys + koff[r0] + threadIdx.x : keys + koff[r];
+    const K mask = kmer_mask(K(0), k);
+    const int top = 2 * (k - 1);
+    K fwd = K(0), rc = K(0);
+    uint32_t clean = 0;                    // valid characters since the last invalid one (saturates at k)
+    for (uint64_t i = 0; i < L; i++) {
+        const uint8_t c = s[i];
+        const unsigned code = base_code(c);
+        fwd = ((fwd << 2) | K((uint64_t)code)) & mask;
+        rc = (rc >> 2) | (K((uint64_t)(code ^ 2u)) << top);
+        clean = base_invalid(c) ? 0u : (clean < (uint32_t)k ? clean + 1 : clean);
+        if (i + 1 >= (uint64_t)k) {
+            const uint64_t p = i + 1 - k;
+            out[p * stride] = clean >= (uint32_t)k ? (rc < fwd ? rc : fwd) : kmer_sentinel<K>();
         }
     }
+    (void)n;
 }
 
 // ---- partition pass (also the LSD radix sort pass of entropy.cuh) ------------------------------------------------

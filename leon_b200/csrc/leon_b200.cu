@@ -236,8 +236,13 @@ template <typename K> void do_count(leon_ctx *c)
     c->d_keys.reserve((nk + 1) * sizeof(K));
     c->d_keys_alt.reserve((nk + 1) * (sizeof(K) > 8 ? sizeof(K) : 8));
     K *keys = c->d_keys.as<K>(), *alt = c->d_keys_alt.as<K>();
-    if (nk) LB_TIMED(c->kt, "k_extract", st, LB_LAUNCH(c->lc, (k_extract<K>), warp_grid(c->nreads), 256, 0, st, c->d_bases.as<uint8_t>(),
-                      c->d_offsets.as<uint64_t>(), koff, c->nreads, k, keys));
+    if (nk) {
+        // bases of the 256 reads of a CTA are staged in shared memory when they fit (40 KB), else read from global
+        uint64_t need = ((256ull * (uint64_t)c->max_len + 31) & ~15ull) + 16;
+        uint32_t stage_bytes = need <= 40960 ? (uint32_t)need : 16u;
+        LB_TIMED(c->kt, "k_extract", st, LB_LAUNCH(c->lc, (k_extract<K>), cdiv_u(c->nreads, 256), 256, stage_bytes, st, c->d_bases.as<uint8_t>(),
+                  c->d_offsets.as<uint64_t>(), koff, c->nreads, k, keys, stage_bytes));
+    }
     CUDA_TRY(cudaEventRecord(c->ev[3], st));
 
     // partition by hash into buckets of ~BcCfg::TARGET keys: LSD passes over the top `bits` bits of key_mix.
@@ -466,13 +471,17 @@ void dict_code_slice(const uint32_t *rec, const uint8_t *sh, uint64_t n, bool fi
             rp = range + inc_next;
             continue;
         }
-        const unsigned one = x < (1u << 24);
+        // both candidates of (low, rp) beside the test, selected by conditional moves: the dependent chain of a step is
+        // multiply-high, shift, multiply, add, xor, compare, select
+        const bool one = x < (1u << 24);
+        const uint64_t rp0 = range + inc_next, rp1 = (range << 8) | inc_next;
+        const uint64_t low1 = low << 8;
         *op = (uint8_t)(low >> 56);
         op += one;
-        low <<= 8 * one;
-        range <<= 8 * one;
-        rp = range + inc_next;
+        rp = one ? rp1 : rp0;
+        low = one ? low1 : low;
     }
+    range = rp;      // inc_next of the last symbol is 0
     out.resize(op - out.data());
 }
 
@@ -521,7 +530,9 @@ template <typename K> void dict_host_worker(leon_ctx *c)
                 CUDA_TRY(cudaMemcpyAsync(c->h_dstage_rec[slot].p, c->d_dict_rec2[slot].p, n * k * sizeof(uint4), cudaMemcpyDeviceToHost, s2));
                 CUDA_TRY(cudaMemcpyAsync(c->h_dstage_sh[slot].p, c->d_dict_sh2[slot].p, n * k, cudaMemcpyDeviceToHost, s2));
                 CUDA_TRY(cudaEventRecord(c->ev_dstage[slot], s2));
+                auto w1 = std::chrono::steady_clock::now();
                 CUDA_TRY(cudaEventSynchronize(c->ev_dtot));      // counts of this slice: base of the next one
+                copy_wait += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - w1).count();
                 base = base + *c->h_dict_tot.as<lbscan::U32x4>();
                 pend[npend++] = Pending{n, slot};
                 launched += n;
@@ -1065,7 +1076,12 @@ int leon_create(const leon_opts *opts, leon_ctx **out)
     try {
         CUDA_TRY(cudaSetDevice(opts->device));
         CUDA_TRY(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
-        CUDA_TRY(cudaStreamCreateWithFlags(&c->st2, cudaStreamNonBlocking));
+        {   // the second stream carries the small record kernels and copies of the dictionary thread: highest priority,
+            // so that they slot in between the thread blocks of the big kernels instead of queueing behind them
+            int lo_pri = 0, hi_pri = 0;
+            CUDA_TRY(cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri));
+            CUDA_TRY(cudaStreamCreateWithPriority(&c->st2, cudaStreamNonBlocking, hi_pri));
+        }
         for (int i = 0; i < 16; i++) CUDA_TRY(cudaEventCreate(&c->ev[i]));
         for (int i = 0; i < 16; i++) CUDA_TRY(cudaEventRecord(c->ev[i], c->st));
     } catch (const LeonError &er) {

@@ -10,6 +10,7 @@
 namespace lbwalk {
 
 using lbcount::pack32;
+using lbcount::stage_reads;
 using lbcount::window_kmer;
 
 // what the walk leaves per read for the entropy stage
@@ -71,38 +72,6 @@ LB_D unsigned thread_contains4(const BloomDev &b, K fwd, K rc, bool right, const
         alive &= ((f >> p0) & 1u) | (((f >> p1) & 1u) << 1) | (((f >> p2) & 1u) << 2) | (((f >> p3) & 1u) << 3);
     }
     return alive;
-}
-
-// Stages the bases of reads [r0, r1) of a CTA in shared memory with one bulk asynchronous copy (TMA, 1-D), so that
-// the per-thread walks read their bases from shared memory.  Returns the shared-memory address of bases[offsets[r0]],
-// or nullptr when the span does not fit (very long reads): callers then read from global memory.
-LB_D const uint8_t *stage_reads(const uint8_t *__restrict__ bases, uint64_t o0, uint64_t o1, uint8_t *smem, uint32_t smem_bytes,
-                                uint64_t *bar)
-{
-    const uint8_t *src = bases + (o0 & ~15ull);
-    uint64_t bytes = ((o1 - (o0 & ~15ull)) + 15ull) & ~15ull;
-    if (bytes > smem_bytes) return nullptr;        // CTA-uniform
-    if (bytes == 0) return smem;
-    uint32_t bar_a = (uint32_t)__cvta_generic_to_shared(bar);
-    uint32_t dst_a = (uint32_t)__cvta_generic_to_shared(smem);
-    if (threadIdx.x == 0) {
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_a));
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"((uint32_t)bytes) : "memory");
-        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                     ::"r"(dst_a), "l"(src), "r"((uint32_t)bytes), "r"(bar_a) : "memory");
-    }
-    uint32_t done = 0;
-    while (!done) {
-        asm volatile("{\n\t.reg .pred p;\n\t"
-                     "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\t"
-                     "selp.u32 %0, 1, 0, p;\n\t}"
-                     : "=r"(done) : "r"(bar_a) : "memory");
-    }
-    return smem + (o0 & 15ull);
 }
 
 // One thread per read.  Left walk (positions anchor-1 .. 0) then right walk (anchor+k .. L-1), as one loop of L-k
