@@ -310,9 +310,11 @@ constexpr int BC_THREADS = 256;
 constexpr int BC_STACK = 48;
 template <typename K> struct BcCfg {
     static constexpr int SLOTS = sizeof(K) == 8 ? 8192 : 4096;     // table slots per CTA (96 KB / 112 KB: 2 CTAs per SM)
-    static constexpr int FILL_MAX = SLOTS * 3 / 4;                 // distinct keys admitted per table
+    static constexpr int SLOTS_SMALL = SLOTS / 4;                  // first attempt: 24 / 28 KB, 8 CTAs per SM
     static constexpr int TARGET = SLOTS * 3 / 4;                   // keys per bucket the partition aims for
-    static constexpr size_t SMEM = (size_t)SLOTS * (12 + (sizeof(K) == 8 ? 0 : sizeof(K)));
+    static constexpr size_t slot_bytes = 12 + (sizeof(K) == 8 ? 0 : sizeof(K));
+    static constexpr size_t SMEM = (size_t)SLOTS * slot_bytes;
+    static constexpr size_t SMEM_SMALL = (size_t)SLOTS_SMALL * slot_bytes;
 };
 
 template <typename K> LB_D uint64_t table_tag(K key, uint64_t salt);
@@ -325,6 +327,10 @@ template <> LB_D uint64_t table_tag<u128>(u128 key, uint64_t salt)
 
 // One CTA per bucket.  `sel/nsplit`: a table pass admits the keys whose selector bits equal `sel`; it starts with
 // the whole bucket (or ceil(size / BC_TARGET) parts) and halves a part whenever its distinct keys overflow the table.
+// Two launches: at sequencing coverage a bucket of ~5 k keys holds a few hundred distinct ones, so the first launch
+// gives every bucket a small table (slots = SLOTS_SMALL: a quarter of the clearing and scanning, four times the
+// resident CTAs) and only lists the buckets whose distinct keys do not fit (retry != nullptr); the second launch
+// (retry_list != nullptr, one CTA per listed bucket) redoes those with the full-size table and the splitting logic.
 // 128-bit keys are claimed through a 64-bit tag (CAS) and verified against the full key after the pass; a tag shared
 // by two different keys (probability ~2^-40 per run) makes the pass repeat with another salt.
 template <typename K>
@@ -332,9 +338,12 @@ __global__ void __launch_bounds__(BC_THREADS) k_bucket_count(const K *__restrict
                                                              unsigned long long *__restrict__ histo,
                                                              CountStats *__restrict__ stats, K *__restrict__ solid_keys,
                                                              uint32_t *__restrict__ solid_cnt,
-                                                             unsigned long long *__restrict__ nsolid_out)
+                                                             unsigned long long *__restrict__ nsolid_out, const int BC_SLOTS,
+                                                             uint32_t *__restrict__ retry, uint32_t *__restrict__ retry_count,
+                                                             const uint32_t *__restrict__ retry_list)
 {
-    constexpr int BC_SLOTS = BcCfg<K>::SLOTS, BC_FILL_MAX = BcCfg<K>::FILL_MAX, BC_TARGET = BcCfg<K>::TARGET;
+    constexpr int BC_TARGET = BcCfg<K>::TARGET;
+    const int BC_FILL_MAX = BC_SLOTS * 3 / 4;                      // distinct keys admitted per table
     extern __shared__ __align__(16) uint8_t smem_raw[];
     uint64_t *tags = reinterpret_cast<uint64_t *>(smem_raw);                       // [BC_SLOTS]
     uint32_t *cnts = reinterpret_cast<uint32_t *>(tags + BC_SLOTS);                 // [BC_SLOTS]
@@ -346,7 +355,7 @@ __global__ void __launch_bounds__(BC_THREADS) k_bucket_count(const K *__restrict
     __shared__ unsigned long long acc[3];
     __shared__ uint32_t shist[256];
     __shared__ uint64_t seg_beg[MAX_RANKS], seg_end[MAX_RANKS];
-    const uint64_t b = src.lo + blockIdx.x;
+    const uint64_t b = src.lo + (retry_list ? retry_list[blockIdx.x] : blockIdx.x);
     const int tid = threadIdx.x;
     if (tid < src.nsrc) {
         seg_beg[tid] = src.base[tid] + src.bstart[tid][b];
@@ -356,6 +365,10 @@ __global__ void __launch_bounds__(BC_THREADS) k_bucket_count(const K *__restrict
     uint64_t size = 0;
     for (int sx = 0; sx < src.nsrc; sx++) size += seg_end[sx] - seg_beg[sx];
     if (size == 0) return;
+    if (retry && size > (uint64_t)BC_TARGET) {      // would need several parts: straight to the full-size launch
+        if (tid == 0) retry[atomicAdd(retry_count, 1u)] = (uint32_t)(b - src.lo);
+        return;
+    }
     if (tid == 0) {
         uint32_t ns = 1;
         while ((uint64_t)ns * BC_TARGET < size && ns < 32) ns <<= 1;
@@ -397,6 +410,10 @@ __global__ void __launch_bounds__(BC_THREADS) k_bucket_count(const K *__restrict
             if (*(volatile uint32_t *)&overflow) break;
         }
         __syncthreads();
+        if (overflow && retry) {   // first launch: leave this bucket to the launch with full-size tables (nothing emitted yet)
+            if (tid == 0) retry[atomicAdd(retry_count, 1u)] = (uint32_t)(b - src.lo);
+            return;
+        }
         if (overflow) {   // too many distinct keys for one table: split this part in two and redo
             if (tid == 0) {
                 if (sp + 2 <= BC_STACK && ns < (1u << 24)) {

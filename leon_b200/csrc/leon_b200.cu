@@ -85,7 +85,7 @@ struct leon_ctx {
     DevBuf d_keys, d_keys_alt, d_tile_hist, d_tile_off, d_scan, d_histo, d_stats, d_tbl;
     void *solid_keys = nullptr;      // solid list (abundance >= 2): keys in d_keys or d_keys_alt, counts in d_solid_cnt
     uint64_t nsolid = 0;
-    DevBuf d_bstart, d_solid_cnt, d_bstart_all, d_keys_recv, d_solid_keys, d_pick, d_bloom_all, d_xchg;
+    DevBuf d_retry, d_bstart, d_solid_cnt, d_bstart_all, d_keys_recv, d_solid_keys, d_pick, d_bloom_all, d_xchg;
     Comm comm;
     uint64_t nkmers_total = 0;
     PinBuf h_histo, h_small;
@@ -345,9 +345,19 @@ template <typename K> void do_count(leon_ctx *c)
         c->d_solid_cnt.reserve((count_n / 2 + 2) * 4);
         CUDA_TRY(cudaFuncSetAttribute(k_bucket_count<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BcCfg<K>::SMEM));
         unsigned long long *nsolid_d = (unsigned long long *)(c->d_stats.as<uint8_t>() + sizeof(CountStats));
-        LB_TIMED(c->kt, "k_bucket_count", st, LB_LAUNCH(c->lc, (k_bucket_count<K>), (unsigned)count_buckets, BC_THREADS, BcCfg<K>::SMEM, st, count_keys,
+        // first launch: small tables; buckets whose distinct keys do not fit are listed and redone with full-size tables
+        c->d_retry.reserve((count_buckets + 2) * 4);
+        uint32_t *retry_cnt = c->d_retry.as<uint32_t>(), *retry_list = retry_cnt + 1;
+        CUDA_TRY(cudaMemsetAsync(retry_cnt, 0, 4, st));
+        LB_TIMED(c->kt, "k_bucket_count", st, LB_LAUNCH(c->lc, (k_bucket_count<K>), (unsigned)count_buckets, BC_THREADS, BcCfg<K>::SMEM_SMALL, st, count_keys,
                   src, (unsigned long long *)c->d_histo.p, c->d_stats.as<CountStats>(), (K *)c->solid_keys,
-                  c->d_solid_cnt.as<uint32_t>(), nsolid_d));
+                  c->d_solid_cnt.as<uint32_t>(), nsolid_d, BcCfg<K>::SLOTS_SMALL, retry_list, retry_cnt, (const uint32_t *)nullptr));
+        const uint32_t nretry = fetch_scalar(c, retry_cnt);
+        if (nretry)
+            LB_TIMED(c->kt, "k_bucket_count", st, LB_LAUNCH(c->lc, (k_bucket_count<K>), nretry, BC_THREADS, BcCfg<K>::SMEM, st, count_keys,
+                      src, (unsigned long long *)c->d_histo.p, c->d_stats.as<CountStats>(), (K *)c->solid_keys,
+                      c->d_solid_cnt.as<uint32_t>(), nsolid_d, BcCfg<K>::SLOTS, (uint32_t *)nullptr, (uint32_t *)nullptr,
+                      (const uint32_t *)retry_list));
         c->nsolid = fetch_scalar(c, nsolid_d);
     }
     if (c->comm.active()) {   // global histogram and counters
@@ -1101,7 +1111,7 @@ void leon_destroy(leon_ctx *c)
     if (c->dict_thread.joinable()) c->dict_thread.join();
     if (c->st) cudaStreamSynchronize(c->st);
     if (c->comm.comm) nccl_api().CommDestroy(c->comm.comm);
-    DevBuf *dev[] = {&c->d_bases, &c->d_offsets, &c->d_quals, &c->d_koff, &c->d_keys, &c->d_keys_alt, &c->d_tile_hist, &c->d_tile_off,
+    DevBuf *dev[] = {&c->d_retry, &c->d_bases, &c->d_offsets, &c->d_quals, &c->d_koff, &c->d_keys, &c->d_keys_alt, &c->d_tile_hist, &c->d_tile_off,
                      &c->d_scan, &c->d_bstart, &c->d_solid_cnt, &c->d_bstart_all, &c->d_keys_recv, &c->d_solid_keys, &c->d_pick,
                      &c->d_bloom_all, &c->d_xchg, &c->d_cand_gid, &c->d_histo, &c->d_stats, &c->d_tbl, &c->d_bloom, &c->d_apos, &c->d_aaddr, &c->d_insflag, &c->d_plist,
                      &c->d_cand_pos, &c->d_cand_key, &c->d_cand_slot, &c->d_state, &c->d_ct_proxy, &c->d_ct_keys, &c->d_ct_ins,
