@@ -89,24 +89,47 @@ template <typename K> struct LookupFn {
 };
 
 // passes A and B.  apos[r] < 0: search all positions; apos[r] >= 0: only positions before it.
+// One thread per read (the bases of the CTA's 256 reads staged in shared memory by one bulk copy): the forward k-mer
+// and its reverse complement are rolled base by base, N read as A (C/DnaCoder.cpp:519-535), and every canonical k-mer is
+// probed until the first hit -- a few tens of instructions per position instead of a warp-wide pack / shift / reverse.
 template <typename K>
 __global__ void __launch_bounds__(256) k_anchor_lookup(const uint8_t *__restrict__ bases, const uint64_t *__restrict__ offsets,
                                                        uint64_t lo, uint64_t hi, uint64_t delta, int k, DictDev<K> d,
-                                                       int32_t *apos, uint32_t *aaddr, const uint8_t *__restrict__ skip)
+                                                       int32_t *apos, uint32_t *aaddr, const uint8_t *__restrict__ skip,
+                                                       uint32_t stage_bytes)
 {
-    const int lane = threadIdx.x & 31;
-    uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
-    for (uint64_t r = lo + warp; r < hi; r += nwarps) {
-        if (skip && skip[r]) continue;
-        uint64_t o = offsets[r], L = offsets[r + 1] - o;
-        if (L < (uint64_t)k) continue;
-        uint64_t n = L - k + 1;
-        int32_t cur = apos[r];
-        uint64_t lim = cur >= 0 ? (uint64_t)cur : n;
-        LookupFn<K> f{d, k, (uint32_t)(r + delta), lim, lane, -1, 0};   // r + delta = index of the read in the whole set
-        warp_for_kmers<K>(bases + o, L, k, 0, lim, lane, f);
-        if (lane == 0 && f.pos >= 0) { apos[r] = (int32_t)f.pos; aaddr[r] = f.addr; }
+    extern __shared__ __align__(128) uint8_t stage[];
+    __shared__ __align__(8) uint64_t bar;
+    const uint64_t r0 = lo + (uint64_t)blockIdx.x * 256;
+    const uint64_t r1 = r0 + 256 < hi ? r0 + 256 : hi;
+    const uint64_t o0 = offsets[r0];
+    const uint8_t *sbase = lbcount::stage_reads(bases, o0, offsets[r1], stage, stage_bytes, &bar);
+    __syncthreads();
+    const uint64_t r = r0 + threadIdx.x;
+    if (r >= hi) return;
+    if (skip && skip[r]) return;
+    const uint64_t o = offsets[r], L = offsets[r + 1] - o;
+    if (L < (uint64_t)k) return;
+    const int32_t cur = apos[r];
+    const uint64_t lim = cur >= 0 ? (uint64_t)cur : L - k + 1;
+    if (lim == 0) return;
+    const uint8_t *s = sbase ? sbase + (o - o0) : bases + o;
+    const K mask = kmer_mask(K(0), k);
+    const int top = 2 * (k - 1);
+    const uint32_t before = (uint32_t)(r + delta);      // index of the read in the whole set
+    K fwd = K(0), rc = K(0);
+    for (uint64_t i = 0; i < lim + k - 1; i++) {
+        const unsigned code = base_code_n_as_a(s[i]);
+        fwd = ((fwd << 2) | K((uint64_t)code)) & mask;
+        rc = (rc >> 2) | (K((uint64_t)(code ^ 2u)) << top);
+        if (i + 1 >= (uint64_t)k) {
+            uint32_t a = 0;
+            if (dict_find(d, rc < fwd ? rc : fwd, before, &a)) {
+                apos[r] = (int32_t)(i + 1 - k);
+                aaddr[r] = a;
+                return;
+            }
+        }
     }
 }
 

@@ -658,6 +658,9 @@ template <typename K> void do_anchors(leon_ctx *c)
     c->tm.anchor_batches = 0;
     c->tm.anchor_rounds = 0;
 
+    // the lookups stage the bases of the 256 reads of a CTA in shared memory when they fit (40 KB)
+    const uint64_t look_need = ((256ull * (uint64_t)c->max_len + 31) & ~15ull) + 16;
+    const uint32_t look_stage = look_need <= 40960 ? (uint32_t)look_need : 16u;
     const uint64_t S = anchor_batch_reads(c);
     // number of batches: the same on every rank
     uint64_t nbatches = (R + S - 1) / S;
@@ -694,8 +697,8 @@ template <typename K> void do_anchors(leon_ctx *c)
         c->tm.anchor_batches++;
         // A: lookup against the dictionary of earlier batches
         if (c->dict_count && nb)
-            LB_LAUNCH(c->lc, (k_anchor_lookup<K>), warp_grid(nb), 256, 0, st, bases, offsets, lo, hi, delta, k,
-                      dict_view<K>(c, c->dict_cur), apos, aaddr, (const uint8_t *)nullptr);
+            LB_LAUNCH(c->lc, (k_anchor_lookup<K>), cdiv_u(nb, 256), 256, look_stage, st, bases, offsets, lo, hi, delta, k,
+                      dict_view<K>(c, c->dict_cur), apos, aaddr, (const uint8_t *)nullptr, look_stage);
         // P: no-hit reads in order
         c->d_plist.reserve((nb + 1) * 4);
         uint32_t *plist = c->d_plist.as<uint32_t>();
@@ -788,8 +791,8 @@ template <typename K> void do_anchors(leon_ctx *c)
             if (dict_thread_on) c->dict_pub.store(c->dict_count, std::memory_order_release);   // the stream is idle: the new anchors are in HBM
             // B: anchors of this batch can pre-empt later reads of the batch at earlier positions
             if (nins && nb)
-                LB_LAUNCH(c->lc, (k_anchor_lookup<K>), warp_grid(nb), 256, 0, st, bases, offsets, lo, hi, delta, k,
-                          dict_view<K>(c, c->dict_cur), apos, aaddr, (const uint8_t *)insflag);
+                LB_LAUNCH(c->lc, (k_anchor_lookup<K>), cdiv_u(nb, 256), 256, look_stage, st, bases, offsets, lo, hi, delta, k,
+                          dict_view<K>(c, c->dict_cur), apos, aaddr, (const uint8_t *)insflag, look_stage);
         }
     }
     if (dict_thread_on) c->dict_fin.store(true, std::memory_order_release);

@@ -2,13 +2,13 @@
 # One GPU-box visit: parity tests, bench line, ncu launch list, ncu --set full of the main kernels.
 set -u
 mkdir -p gpurun_out
-python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" 
+python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"
 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"
-python bench.py --steps 3 --warmup 3 --phases > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
+python bench.py --steps 5 --warmup 3 --phases > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
 python bench.py --impl reference --steps 1 --warmup 0 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"
-ncu --metrics gpu__time_duration.sum --clock-control none -c 1200 --csv --log-file gpurun_out/launches.csv \
+ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file gpurun_out/launches.csv \
     python bench.py --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_launches.log 2>&1; echo "ncu launches rc=$?"
 ncu --set full --clock-control none --import-source on \
-    -k 'regex:k_range_encode|k_walk|k_part_scatter|k_bucket_count|k_chunk_ranks|k_extract' -c 9 -f -o gpurun_out/full \
+    -k 'regex:k_range_encode|k_walk|k_part_scatter|k_part_hist|k_bucket_count|k_bucket_bounds|k_chunk_ranks|k_extract|k_anchor_lookup|k_round_decide|k_candidates' -c 24 -f -o gpurun_out/full \
     python bench.py --steps 1 --warmup 0 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1; echo "ncu full rc=$?"
-tail -3 gpurun_out/pytest_gpu.log; cat gpurun_out/bench.json | cut -c1-600
+tail -3 gpurun_out/pytest_gpu.log; cat gpurun_out/bench.json | cut -c1-400
