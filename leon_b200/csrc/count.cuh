@@ -276,6 +276,152 @@ __global__ void __launch_bounds__(RS_THREADS) k_part_scatter(const K *__restrict
     }
 }
 
+// ---- hash partition of the k-mer keys (MSD, not stable) ---------------------------------------------------------------
+// Counting only needs every bucket's MULTISET of keys, so the partition on the top `bits` bits of key_mix does not have
+// to be stable: most significant digit first, one level per 8 bits.  A level subdivides each of the P partitions of
+// the previous one; tiles are aligned to partition starts (tstart[p] = first tile of partition p), a CTA finds its
+// partition by binary search.  k_msd_hist counts (partition, digit) pairs (shared-memory histogram, then one global
+// atomicAdd per non-empty digit); their exclusive scan is both the partition table of the next level and, after the
+// last level, the bucket boundaries bstart.  k_msd_scatter ranks the keys of a tile inside their digit with
+// shared-memory atomics (the returned old value is the rank), reserves the tile's run of every digit with one global
+// atomicAdd on that digit's cursor, orders the tile by digit in shared memory and writes the runs out coalesced.
+struct MsdLevel {
+    const uint64_t *pstart;   // [P + 1] key index of the first key of every partition
+    const uint64_t *tstart;   // [P + 1] first tile of every partition
+    uint64_t P;
+    int shift;                // digit = (key_mix >> shift) & mask
+    unsigned mask;
+    int wbits;
+};
+
+// partition of tile c (the last p with tstart[p] <= c); false when c is past the last tile
+LB_D bool msd_locate(const MsdLevel &lv, uint64_t c, uint64_t tile, uint64_t &p, uint64_t &beg, uint64_t &end)
+{
+    if (c >= lv.tstart[lv.P]) return false;
+    uint64_t lo = 0, hi = lv.P;      // invariant: tstart[lo] <= c < tstart[hi]
+    while (hi - lo > 1) {
+        uint64_t mid = (lo + hi) >> 1;
+        if (lv.tstart[mid] <= c) lo = mid; else hi = mid;
+    }
+    p = lo;
+    beg = lv.pstart[lo] + (c - lv.tstart[lo]) * tile;
+    end = lv.pstart[lo + 1];
+    if (end > beg + tile) end = beg + tile;
+    return true;
+}
+
+struct MsdTilesIn {
+    const uint64_t *pstart; uint64_t tile;
+    __device__ uint64_t operator()(uint64_t i) const { return (pstart[i + 1] - pstart[i] + tile - 1) / tile; }
+};
+struct MsdTilesOut {
+    uint64_t *tstart;
+    __device__ void operator()(uint64_t i, uint64_t ex, uint64_t) const { tstart[i] = ex; }
+};
+struct MsdCntIn {
+    const unsigned long long *cnt;
+    __device__ uint64_t operator()(uint64_t i) const { return cnt[i]; }
+};
+struct MsdCntOut {
+    uint64_t *pstart; unsigned long long *cursor;
+    __device__ void operator()(uint64_t i, uint64_t ex, uint64_t) const { pstart[i] = ex; cursor[i] = ex; }
+};
+
+template <typename K>
+__global__ void __launch_bounds__(RS_THREADS) k_msd_hist(const K *__restrict__ keys, const MsdLevel lv,
+                                                         unsigned long long *__restrict__ cnt)
+{
+    constexpr int ITEMS = RsCfg<K>::ITEMS, TILE = RsCfg<K>::TILE;
+    __shared__ uint32_t h[256];
+    __shared__ uint64_t sp, sbeg, send;
+    __shared__ int live;
+    if (threadIdx.x == 0) {
+        uint64_t p = 0, b = 0, e = 0;
+        live = msd_locate(lv, blockIdx.x, TILE, p, b, e);
+        sp = p; sbeg = b; send = e;
+    }
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    if (!live) return;
+    const uint64_t beg = sbeg, end = send;
+#pragma unroll
+    for (int j = 0; j < ITEMS; j++) {
+        uint64_t i = beg + (uint64_t)j * RS_THREADS + threadIdx.x;
+        if (i < end) atomicAdd(&h[(unsigned)(key_mix(keys[i]) >> lv.shift) & lv.mask], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x <= lv.mask && h[threadIdx.x]) atomicAdd(&cnt[(sp << lv.wbits) + threadIdx.x], (unsigned long long)h[threadIdx.x]);
+}
+
+template <typename K>
+__global__ void __launch_bounds__(RS_THREADS) k_msd_scatter(const K *__restrict__ in, K *__restrict__ out, const MsdLevel lv,
+                                                            unsigned long long *__restrict__ cursor)
+{
+    constexpr int ITEMS = RsCfg<K>::ITEMS, TILE = RsCfg<K>::TILE;
+    __shared__ uint32_t h[256], dstart[256], wsum[RS_WARPS];
+    __shared__ uint64_t gbase[256];
+    __shared__ K stage[TILE];
+    __shared__ uint8_t sdig[TILE];
+    __shared__ uint64_t sp, sbeg, send;
+    __shared__ int live;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) {
+        uint64_t p = 0, b = 0, e = 0;
+        live = msd_locate(lv, blockIdx.x, TILE, p, b, e);
+        sp = p; sbeg = b; send = e;
+    }
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    if (!live) return;
+    const uint64_t beg = sbeg, end = send;
+    K key[ITEMS];
+    uint16_t rank[ITEMS];
+    uint8_t dig[ITEMS];
+#pragma unroll
+    for (int j = 0; j < ITEMS; j++) {
+        uint64_t i = beg + (uint64_t)j * RS_THREADS + threadIdx.x;
+        if (i < end) {
+            key[j] = in[i];
+            unsigned d = (unsigned)(key_mix(key[j]) >> lv.shift) & lv.mask;
+            dig[j] = (uint8_t)d;
+            rank[j] = (uint16_t)atomicAdd(&h[d], 1u);
+        }
+    }
+    __syncthreads();
+    {
+        const unsigned d = threadIdx.x;
+        const uint32_t tot = h[d];
+        uint32_t incl = tot;
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) {
+            uint32_t o = __shfl_up_sync(0xffffffffu, incl, s);
+            if (lane >= s) incl += o;
+        }
+        if (lane == 31) wsum[warp] = incl;
+        __syncthreads();
+        uint32_t base = 0;
+        for (int w = 0; w < warp; w++) base += wsum[w];
+        dstart[d] = base + incl - tot;
+        gbase[d] = tot ? atomicAdd(&cursor[(sp << lv.wbits) + d], (unsigned long long)tot) : 0ull;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < ITEMS; j++) {
+        uint64_t i = beg + (uint64_t)j * RS_THREADS + threadIdx.x;
+        if (i < end) {
+            uint32_t pos = dstart[dig[j]] + rank[j];
+            stage[pos] = key[j];
+            sdig[pos] = dig[j];
+        }
+    }
+    __syncthreads();
+    const uint32_t nt = (uint32_t)(end - beg);
+    for (uint32_t i = threadIdx.x; i < nt; i += RS_THREADS) {
+        unsigned d = sdig[i];
+        out[gbase[d] + (i - dstart[d])] = stage[i];
+    }
+}
+
 // ---- buckets ------------------------------------------------------------------------------------------------------
 // After the partition passes the keys are ordered by bucket id = top `bits` bits of key_mix.
 // bstart[b] = index of the first key of bucket b (b = 0 .. nbuckets, bstart[nbuckets] = n).

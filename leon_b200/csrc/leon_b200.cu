@@ -85,7 +85,7 @@ struct leon_ctx {
     DevBuf d_keys, d_keys_alt, d_tile_hist, d_tile_off, d_scan, d_histo, d_stats, d_tbl;
     void *solid_keys = nullptr;      // solid list (abundance >= 2): keys in d_keys or d_keys_alt, counts in d_solid_cnt
     uint64_t nsolid = 0;
-    DevBuf d_retry, d_bstart, d_solid_cnt, d_bstart_all, d_keys_recv, d_solid_keys, d_pick, d_bloom_all, d_xchg;
+    DevBuf d_retry, d_pstart_alt, d_tstart, d_mcnt, d_mcur, d_bstart, d_solid_cnt, d_bstart_all, d_keys_recv, d_solid_keys, d_pick, d_bloom_all, d_xchg;
     Comm comm;
     uint64_t nkmers_total = 0;
     PinBuf h_histo, h_small;
@@ -259,12 +259,45 @@ template <typename K> void do_count(leon_ctx *c)
     int bits = 0;
     while (bits < 24 && ((nk_total >> bits) > (uint64_t)BcCfg<K>::TARGET || (1 << bits) < N)) bits++;
     c->tm.sort_passes = 0;
+    const uint64_t nbuckets = 1ull << bits;
+    // two tables of partition starts (ping-pong over the levels); the last one is the bucket table bstart
+    c->d_bstart.reserve((nbuckets + 2) * 8);
+    c->d_pstart_alt.reserve((nbuckets + 2) * 8);
+    c->d_tstart.reserve((nbuckets + 2) * 8);
+    c->d_mcnt.reserve((nbuckets + 2) * 8);
+    c->d_mcur.reserve((nbuckets + 2) * 8);
+    uint64_t *bstart = c->d_bstart.as<uint64_t>();
     {
-        // pass p handles hash bits [64 - bits + off, 64 - bits + off + w)
+        // level l handles hash bits [64 - off - w, 64 - off): most significant digit first
+        int nlevels = (bits + 7) / 8;
+        // the table written by the last level must be d_bstart: start so that the ping-pong ends there
+        uint64_t *pcur = (nlevels & 1) ? c->d_pstart_alt.as<uint64_t>() : c->d_bstart.as<uint64_t>();
+        uint64_t *pnext = (nlevels & 1) ? c->d_bstart.as<uint64_t>() : c->d_pstart_alt.as<uint64_t>();
+        if (bits == 0 || nk == 0) pcur = bstart;
+        c->h_small.reserve(256);
+        uint64_t init[2] = {0, nk};
+        memcpy(c->h_small.p, init, 16);
+        CUDA_TRY(cudaMemcpyAsync(pcur, c->h_small.p, 16, cudaMemcpyHostToDevice, st));
+        if (nk == 0 && bits) CUDA_TRY(cudaMemsetAsync(bstart, 0, (nbuckets + 1) * 8, st));
+        uint64_t P = 1;
         int off = 0;
+        const uint64_t TILE = RsCfg<K>::TILE;
         while (off < bits && nk > 0) {
-            int w = bits - off < 8 ? bits - off : 8;
-            partition_pass(c, keys, alt, nk, HashDigit<K>{64 - bits + off, (1u << w) - 1u});
+            const int w = bits - off < 8 ? bits - off : 8;
+            uint64_t *tstart = c->d_tstart.as<uint64_t>();
+            uint64_t *ttot = lbscan::exclusive_scan<uint64_t>(P, MsdTilesIn{pcur, TILE}, MsdTilesOut{tstart}, c->d_scan, st, c->lc);
+            CUDA_TRY(cudaMemcpyAsync(tstart + P, ttot, 8, cudaMemcpyDeviceToDevice, st));
+            MsdLevel lv{pcur, tstart, P, 64 - off - w, (1u << w) - 1u, w};
+            const unsigned grid = (unsigned)(nk / TILE + P + 1);      // >= number of tiles; the surplus CTAs exit at once
+            unsigned long long *cnt = c->d_mcnt.as<unsigned long long>(), *cur = c->d_mcur.as<unsigned long long>();
+            CUDA_TRY(cudaMemsetAsync(cnt, 0, (P << w) * 8, st));
+            LB_TIMED(c->kt, "k_msd_hist", st, LB_LAUNCH(c->lc, (k_msd_hist<K>), grid, RS_THREADS, 0, st, keys, lv, cnt));
+            uint64_t *ptot = lbscan::exclusive_scan<uint64_t>(P << w, MsdCntIn{cnt}, MsdCntOut{pnext, cur}, c->d_scan, st, c->lc);
+            CUDA_TRY(cudaMemcpyAsync(pnext + (P << w), ptot, 8, cudaMemcpyDeviceToDevice, st));
+            LB_TIMED(c->kt, "k_msd_scatter", st, LB_LAUNCH(c->lc, (k_msd_scatter<K>), grid, RS_THREADS, 0, st, keys, alt, lv, cur));
+            std::swap(keys, alt);
+            std::swap(pcur, pnext);
+            P <<= w;
             off += w;
             c->tm.sort_passes++;
         }
@@ -280,15 +313,6 @@ template <typename K> void do_count(leon_ctx *c)
     c->nsolid = 0;
     c->solid_keys = alt;
     CountStats stats = {0, 0, 0};
-    const uint64_t nbuckets = 1ull << bits;
-    c->d_bstart.reserve((nbuckets + 2) * 8);
-    uint64_t *bstart = c->d_bstart.as<uint64_t>();
-    if (nk) {
-        unsigned grid = (unsigned)std::min<uint64_t>((nk + 255) / 256, (uint64_t)NUM_SMS * 16);
-        LB_TIMED(c->kt, "k_bucket_bounds", st, LB_LAUNCH(c->lc, (k_bucket_bounds<K>), grid, 256, 0, st, keys, nk, bits, nbuckets, bstart));
-    } else {
-        CUDA_TRY(cudaMemsetAsync(bstart, 0, (nbuckets + 1) * 8, st));
-    }
     BucketSrc src;
     memset(&src, 0, sizeof src);
     const K *count_keys = keys;
@@ -1114,7 +1138,7 @@ void leon_destroy(leon_ctx *c)
     if (c->dict_thread.joinable()) c->dict_thread.join();
     if (c->st) cudaStreamSynchronize(c->st);
     if (c->comm.comm) nccl_api().CommDestroy(c->comm.comm);
-    DevBuf *dev[] = {&c->d_retry, &c->d_bases, &c->d_offsets, &c->d_quals, &c->d_koff, &c->d_keys, &c->d_keys_alt, &c->d_tile_hist, &c->d_tile_off,
+    DevBuf *dev[] = {&c->d_retry, &c->d_pstart_alt, &c->d_tstart, &c->d_mcnt, &c->d_mcur, &c->d_bases, &c->d_offsets, &c->d_quals, &c->d_koff, &c->d_keys, &c->d_keys_alt, &c->d_tile_hist, &c->d_tile_off,
                      &c->d_scan, &c->d_bstart, &c->d_solid_cnt, &c->d_bstart_all, &c->d_keys_recv, &c->d_solid_keys, &c->d_pick,
                      &c->d_bloom_all, &c->d_xchg, &c->d_cand_gid, &c->d_histo, &c->d_stats, &c->d_tbl, &c->d_bloom, &c->d_apos, &c->d_aaddr, &c->d_insflag, &c->d_plist,
                      &c->d_cand_pos, &c->d_cand_key, &c->d_cand_slot, &c->d_state, &c->d_ct_proxy, &c->d_ct_keys, &c->d_ct_ins,
