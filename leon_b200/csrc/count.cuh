@@ -354,7 +354,7 @@ __global__ void __launch_bounds__(RS_THREADS) k_msd_hist(const K *__restrict__ k
 }
 
 template <typename K>
-__global__ void __launch_bounds__(RS_THREADS) k_msd_scatter(const K *__restrict__ in, K *__restrict__ out, const MsdLevel lv,
+__global__ void __launch_bounds__(RS_THREADS, 4) k_msd_scatter(const K *__restrict__ in, K *__restrict__ out, const MsdLevel lv,
                                                             unsigned long long *__restrict__ cursor)
 {
     constexpr int ITEMS = RsCfg<K>::ITEMS, TILE = RsCfg<K>::TILE;
