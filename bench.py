@@ -211,12 +211,16 @@ def algorithmic_bytes(kernel, st):
     kb = 8 if KMER <= 31 else 16
     if kernel == "k_walk":            # one 544-byte Bloom window per extension step: (L - k) steps per read
         return 544.0 * (NB - KMER * R)
-    if kernel == "k_part_scatter":    # read every key once, write it once (launches: hash passes over the k-mer keys and
-        return 2.0 * NK * kb          # shift passes over the symbol records; the k-mer figure is used for the average)
-    if kernel == "k_part_hist":
+    if kernel == "k_msd_scatter":     # read every key once, write it once (one launch per 8-bit level of the hash partition)
+        return 2.0 * NK * kb
+    if kernel == "k_msd_hist":
         return 1.0 * NK * kb
-    if kernel == "k_bucket_count":    # read every key once, write (key, count) of the solid ones
-        return 1.0 * NK * kb + st["nruns"] * (kb + 4.0)
+    if kernel == "k_part_scatter":    # stable radix pass over the 8-byte symbol records
+        return 2.0 * st["nsym"] * 8.0
+    if kernel == "k_part_hist":
+        return 1.0 * st["nsym"] * 8.0
+    if kernel == "k_bucket_count":    # read every key once, write (key, count) of the solid ones; averaged over its two launches
+        return (1.0 * NK * kb + st["nruns"] * (kb + 4.0)) / 2.0
     if kernel == "k_extract":         # read the bases, write one key per k-mer
         return NB + NK * kb
     if kernel == "k_chunk_ranks":     # read the 8-byte sorted record, write the 17-byte coder record; histogram row per chunk
@@ -373,12 +377,28 @@ def main_b200(args):
                     "frac": (ach / peak) if ach else None, "traffic": None, "peak_source": peak_src,
                     "launch_ms": per_launch_ms, "launches_per_step": n / args.steps,
                     "share_of_step": ms_tot / dev_ms, "algorithmic_bytes_per_launch": ab}
+        if dom == "k_range_encode":
+            # one warp per block stream runs the serial low/range recurrence: bound by single-warp issue latency, not by
+            # bytes -- the figure that describes it is cycles per symbol of the longest stream
+            nblk = max(1, -(-local_reads // RPB))
+            sym_per_block = stats["nsym"] / nblk
+            roofline["note"] = "latency-bound serial recurrence (one warp per 50000-read block); HBM fraction is not its limit"
+            roofline["ns_per_symbol"] = per_launch_ms * 1e6 / sym_per_block
+            if clocks.get("sm_mhz"):
+                roofline["cycles_per_symbol"] = roofline["ns_per_symbol"] * clocks["sm_mhz"] / 1e3
         tr = os.path.join(ROOT, "profiles", "traffic.json")   # dram bytes per launch from the committed ncu --set full capture
         if os.path.exists(tr):
             try:
                 roofline["traffic"] = json.load(open(tr)).get(dom)
             except Exception:
                 pass
+    kernel_rooflines = {}
+    for kname, (ms_tot_k, n_k) in ktimes.items():
+        ab_k = algorithmic_bytes(kname, stats)
+        if ab_k and n_k:
+            gbs = (ab_k / 1e9) / ((ms_tot_k / n_k) / 1e3)
+            kernel_rooflines[kname] = {"ms_per_launch": ms_tot_k / n_k, "launches_per_step": n_k / args.steps,
+                                       "achieved_gbs": gbs, "frac_of_hbm_peak": gbs / peak}
     if args.phases and rank == 0:
         print("phases (ms/step):", {k: round(v / args.steps, 3) for k, v in phase.items()}, file=sys.stderr)
         print("kernels (ms/step, launches/step):",
@@ -409,6 +429,7 @@ def main_b200(args):
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": roofline,
+        "kernel_rooflines": kernel_rooflines,
         "cpu_baseline": cpu,
         "phases_ms_per_step": {k: v / args.steps for k, v in phase.items()},
         "kernels_ms_per_step": {k: v[0] / args.steps for k, v in ktimes.items()},
