@@ -69,7 +69,8 @@ enum Phase { PH_NONE = 0, PH_UPLOADED, PH_COUNTED, PH_BLOOM, PH_ENCODED };
 struct leon_ctx {
     leon_opts opts;
     std::string err;
-    cudaStream_t st = nullptr, st2 = nullptr;   // st2: the anchor dictionary coder runs beside the per-block work
+    cudaStream_t st = nullptr, st2 = nullptr, st3 = nullptr;   // st3: quality smoothing beside the anchor resolution
+    cudaEvent_t ev_q[2] = {nullptr, nullptr};   // st2: the anchor dictionary coder runs beside the per-block work
     LaunchCounter lc;
     KernelTimer kt;
     bool own_stream = true;
@@ -843,6 +844,20 @@ template <typename K> void do_encode_body(leon_ctx *c)
     const uint64_t *offsets = c->d_offsets.as<uint64_t>();
     const uint64_t *koff = c->d_koff.as<uint64_t>();
 
+    // Quality smoothing only needs the Bloom filter: it runs on a third stream beside the anchor resolution, whose many
+    // small kernels and host round trips leave most of the GPU idle.  It borrows the error-position buffer as its
+    // prefix-count scratch, so the walk waits for it.
+    c->d_err.reserve((c->nkmers + 1) * 4);
+    if (c->opts.has_qual) {
+        c->d_qout.reserve(c->nbases + R + 16);
+        if (R) {
+            CUDA_TRY(cudaEventRecord(c->ev_q[0], st));
+            CUDA_TRY(cudaStreamWaitEvent(c->st3, c->ev_q[0], 0));
+            LB_TIMED(c->kt, "k_quals", c->st3, LB_LAUNCH(c->lc, (lbwalk::k_quals<K>), warp_grid(R), 256, 0, c->st3, bases, c->d_quals.as<uint8_t>(), offsets, koff, R,
+                      c->bloom, c->d_tbl.as<uint64_t>(), c->opts.lossless, c->d_err.as<uint32_t>(), c->d_qout.as<uint8_t>()));
+            CUDA_TRY(cudaEventRecord(c->ev_q[1], c->st3));
+        }
+    }
     do_anchors<K>(c);
     int32_t *apos = c->d_apos.as<int32_t>();
     uint32_t *aaddr = c->d_aaddr.as<uint32_t>();
@@ -877,14 +892,7 @@ template <typename K> void do_encode_body(leon_ctx *c)
         CUDA_TRY(cudaEventRecord(c->ev[14], s2));
     }
 
-    c->d_err.reserve((c->nkmers + 1) * 4);
-    // qualities first: the smoothing pass borrows the error-position buffer as its prefix-count scratch
-    if (c->opts.has_qual) {
-        c->d_qout.reserve(c->nbases + R + 16);
-        if (R)
-            LB_TIMED(c->kt, "k_quals", st, LB_LAUNCH(c->lc, (lbwalk::k_quals<K>), warp_grid(R), 256, 0, st, bases, c->d_quals.as<uint8_t>(), offsets, koff, R,
-                      c->bloom, c->d_tbl.as<uint64_t>(), c->opts.lossless, c->d_err.as<uint32_t>(), c->d_qout.as<uint8_t>()));
-    }
+    if (c->opts.has_qual && R) CUDA_TRY(cudaStreamWaitEvent(st, c->ev_q[1], 0));
     CUDA_TRY(cudaEventRecord(c->ev[8], st));
 
     // walk
@@ -1119,6 +1127,8 @@ int leon_create(const leon_opts *opts, leon_ctx **out)
             CUDA_TRY(cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri));
             CUDA_TRY(cudaStreamCreateWithPriority(&c->st2, cudaStreamNonBlocking, hi_pri));
         }
+        CUDA_TRY(cudaStreamCreateWithFlags(&c->st3, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; i++) CUDA_TRY(cudaEventCreateWithFlags(&c->ev_q[i], cudaEventDisableTiming));
         for (int i = 0; i < 16; i++) CUDA_TRY(cudaEventCreate(&c->ev[i]));
         for (int i = 0; i < 16; i++) CUDA_TRY(cudaEventRecord(c->ev[i], c->st));
     } catch (const LeonError &er) {
@@ -1157,6 +1167,8 @@ void leon_destroy(leon_ctx *c)
     if (c->ev_dtot) cudaEventDestroy(c->ev_dtot);
     if (c->st && c->own_stream) cudaStreamDestroy(c->st);
     if (c->st2) { cudaStreamSynchronize(c->st2); cudaStreamDestroy(c->st2); }
+    if (c->st3) { cudaStreamSynchronize(c->st3); cudaStreamDestroy(c->st3); }
+    for (int i = 0; i < 2; i++) if (c->ev_q[i]) cudaEventDestroy(c->ev_q[i]);
     delete c;
 }
 

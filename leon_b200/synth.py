@@ -69,3 +69,43 @@ def write_fasta(path, bases, offsets, quals=None):
                 else:
                     parts.append(b"@r%d\n%s\n+\n%s\n" % (i, s, quals[int(offsets[i]):int(offsets[i + 1])].tobytes()))
             f.write(b"".join(parts))
+
+
+def add_indels_and_n_runs(bases, offsets, quals, seed, indel_rate=0.0005, n_read_rate=0.005):
+    """BASELINE configs[3] shape: per-base insertions / deletions of 1-3 bases (so read lengths vary) and, in a fraction
+    of the reads, one run of 5-30 N.  Returns new (bases, offsets, quals)."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    n = len(offsets) - 1
+    out_b, out_q, lens = [], [], np.zeros(n, np.int64)
+    for i in range(n):
+        lo, hi = int(offsets[i]), int(offsets[i + 1])
+        r = bases[lo:hi].copy()
+        q = quals[lo:hi].copy() if quals is not None else None
+        L = len(r)
+        nev = rng.binomial(L, indel_rate) if L else 0
+        for _ in range(nev):
+            p = int(rng.integers(0, max(1, len(r))))
+            m = int(rng.integers(1, 4))
+            if rng.random() < 0.5:                       # deletion
+                r = np.concatenate([r[:p], r[p + m:]])
+                if q is not None:
+                    q = np.concatenate([q[:p], q[p + m:]])
+            else:                                        # insertion
+                ins = ACGT[rng.integers(0, 4, m)]
+                r = np.concatenate([r[:p], ins, r[p:]])
+                if q is not None:
+                    q = np.concatenate([q[:p], np.full(m, 33 + 20, np.uint8), q[p:]])
+        if len(r) and rng.random() < n_read_rate:
+            m = int(rng.integers(5, 31))
+            p = int(rng.integers(0, max(1, len(r) - m)))
+            r[p:p + m] = ord("N")
+            if q is not None:
+                q[p:p + m] = 33 + 2
+        out_b.append(r)
+        if q is not None:
+            out_q.append(q)
+        lens[i] = len(r)
+    offs = np.zeros(n + 1, np.uint64)
+    np.cumsum(lens, out=offs[1:])
+    return (np.concatenate(out_b) if out_b else np.zeros(0, np.uint8), offs,
+            np.concatenate(out_q) if quals is not None else None)

@@ -174,3 +174,20 @@ def test_properties_full_shape_reduced_count():
     np.minimum.at(first_use, r1["anchor_addr"][am], idx)
     assert np.all(np.diff(first_use) > 0)
     eng.close()
+
+
+@pytest.mark.parametrize("k,fastq,lossless,seed", [(31, True, False, 11), (63, True, True, 12), (31, False, False, 13)])
+def test_indels_n_runs_variable_lengths(k, fastq, lossless, seed):
+    """BASELINE configs[3]/[4] shape at reduced scale: 150 bp reads with indels (variable lengths), N runs, FASTQ lossy
+    (k = 31) and lossless (k = 63), several blocks, vs the oracle."""
+    from oracle import oracle_py as O
+    from leon_b200 import synth
+    g = synth.make_genome(50000, seed)
+    bases, offs, quals = synth.sample_reads(g, 15000, 150, seed + 100, n_rate=0.001, with_quals=fastq)
+    bases, offs, quals = synth.add_indels_and_n_runs(bases, offs, quals, seed + 200, indel_rate=0.002, n_read_rate=0.02)
+    assert len(np.unique(np.diff(offs.astype(np.int64)))) > 3
+    ref = O.compress(bases, offs, quals, kmer_size=k, reads_per_block=4000, lossless=lossless)
+    eng = _engine(kmer_size=k, reads_per_block=4000, has_qual=fastq, lossless=lossless)
+    r = eng.compress(bases, offs, quals)
+    eng.close()
+    _same(r, ref, fastq)
