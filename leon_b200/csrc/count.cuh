@@ -100,7 +100,7 @@ LB_D const uint8_t *stage_reads(const uint8_t *__restrict__ bases, uint64_t o0, 
     return smem + (o0 & 15ull);
 }
 
-// Canonical k-mer of every window of every read; the sentinel when the window holds an invalid character ((c>>3)&1,
+// Canonical k-mer of every window of every read; an INVALID key when the window holds an invalid character ((c>>3)&1,
 // MI/api/Data.hpp:176).  One THREAD per read: the bases of the 256 reads of a CTA are staged in shared memory by one
 // bulk copy, the forward k-mer and its reverse complement are rolled base by base (4 operations each, K/Model.hpp:725-764)
 // and the canonical one is their minimum (:876-883).  Only the multiset of keys matters downstream, so when all reads
@@ -139,7 +139,10 @@ __global__ void __launch_bounds__(256) k_extract(const uint8_t *__restrict__ bas
         clean = base_invalid(c) ? 0u : (clean < (uint32_t)k ? clean + 1 : clean);
         if (i + 1 >= (uint64_t)k) {
             const uint64_t p = i + 1 - k;
-            out[p * stride] = clean >= (uint32_t)k ? (rc < fwd ? rc : fwd) : kmer_sentinel<K>();
+            K key;
+            if (clean >= (uint32_t)k) key = rc < fwd ? rc : fwd;
+            else kmer_make_invalid(key, (r << 24) ^ p);
+            out[p * stride] = key;
         }
     }
     (void)n;
@@ -537,7 +540,7 @@ __global__ void __launch_bounds__(BC_THREADS) k_bucket_count(const K *__restrict
         for (int sx = 0; sx < src.nsrc; sx++)
         for (uint64_t i = seg_beg[sx] + tid; i < seg_end[sx]; i += BC_THREADS) {
             K key = keys[i];
-            if (key == kmer_sentinel<K>()) continue;
+            if (kmer_invalid(key)) continue;
             uint64_t mx = key_mix(key);
             if (((uint32_t)(mx >> 20) & (ns - 1)) != sel) continue;
             uint64_t tag = table_tag<K>(key, salt);
@@ -573,7 +576,7 @@ __global__ void __launch_bounds__(BC_THREADS) k_bucket_count(const K *__restrict
             for (int sx = 0; sx < src.nsrc; sx++)
             for (uint64_t i = seg_beg[sx] + tid; i < seg_end[sx]; i += BC_THREADS) {
                 K key = keys[i];
-                if (key == kmer_sentinel<K>()) continue;
+                if (kmer_invalid(key)) continue;
                 uint64_t mx = key_mix(key);
                 if (((uint32_t)(mx >> 20) & (ns - 1)) != sel) continue;
                 uint64_t tag = table_tag<K>(key, salt);

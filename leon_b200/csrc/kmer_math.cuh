@@ -84,6 +84,13 @@ LB_HD void kmer_make(u128 &out, uint64_t lo, uint64_t hi) { out = u128(lo, hi); 
 
 // "no k-mer here" marker: never a canonical k-mer (a canonical k-mer has at least its top two bits below 0b11).
 template <typename K> LB_HD K kmer_sentinel() { return ~(K)0; }
+// Windows with an invalid character are written as INVALID keys: top bit set (a k-mer of k <= 31 / k <= 63 bases stays
+// below 2^62 / 2^126) over pseudo-random low bits, so that the hash partition spreads them over all buckets instead of
+// piling every one of them into the sentinel's bucket (at 0.1 % N bases that bucket held 3.5 % of all keys).
+LB_HD bool kmer_invalid(uint64_t x) { return (x >> 63) != 0; }
+LB_HD bool kmer_invalid(const u128 &x) { return (x.hi >> 63) != 0; }
+LB_HD void kmer_make_invalid(uint64_t &out, uint64_t salt) { out = (1ull << 63) | (salt * 0x9E3779B97F4A7C15ULL >> 1); }
+LB_HD void kmer_make_invalid(u128 &out, uint64_t salt) { out = u128(salt * 0x9E3779B97F4A7C15ULL, (1ull << 63) | (salt >> 1)); }
 
 LB_HD uint64_t hash64(uint64_t key, uint64_t seed)  // M/LargeInt1.pri:157-170
 {
