@@ -399,6 +399,22 @@ def main_b200(args):
             gbs = (ab_k / 1e9) / ((ms_tot_k / n_k) / 1e3)
             kernel_rooflines[kname] = {"ms_per_launch": ms_tot_k / n_k, "launches_per_step": n_k / args.steps,
                                        "achieved_gbs": gbs, "frac_of_hbm_peak": gbs / peak}
+    # Bloom-probe roofline of k_walk (north_star): extension steps (= contains4 windows) per second against what the
+    # memory system delivers for that access pattern on a filter of this size (tools/probe_roofline.cu, measured on B200)
+    probe = None
+    if "k_walk" in ktimes and ktimes["k_walk"][1]:
+        wms = ktimes["k_walk"][0] / ktimes["k_walk"][1]
+        steps = float(stats["nbases"] - KMER * stats["nreads"])
+        wps = steps / (wms / 1e3)
+        probe = {"kernel": "k_walk", "windows_per_s": wps, "filter_bytes": int(len(res["bloom"])), "peak_windows_per_s": None,
+                 "frac": None, "regime": None}
+        try:
+            pr = json.load(open(os.path.join(ROOT, "profiles", "probe_roofline.json")))["windows_per_s"]
+            fb = len(res["bloom"])
+            key = "l2_resident_6.9MB" if fb <= 64e6 else ("150MB" if fb <= 300e6 else ("dram_1GB" if fb <= 2e9 else "dram_4.5GB"))
+            probe.update(peak_windows_per_s=pr[key], frac=wps / pr[key], regime=key)
+        except Exception:
+            pass
     if args.phases and rank == 0:
         print("phases (ms/step):", {k: round(v / args.steps, 3) for k, v in phase.items()}, file=sys.stderr)
         print("kernels (ms/step, launches/step):",
@@ -430,6 +446,7 @@ def main_b200(args):
         "clocks": clocks,
         "roofline": roofline,
         "kernel_rooflines": kernel_rooflines,
+        "probe_roofline": probe,
         "cpu_baseline": cpu,
         "phases_ms_per_step": {k: v / args.steps for k, v in phase.items()},
         "kernels_ms_per_step": {k: v[0] / args.steps for k, v in ktimes.items()},
