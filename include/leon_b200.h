@@ -29,7 +29,8 @@ enum {
     LEON_E_CUDA = -2,     /* CUDA runtime error (message has the CUDA string) */
     LEON_E_NOMEM = -3,    /* host or device allocation failed */
     LEON_E_STATE = -4,    /* phase called out of order */
-    LEON_E_OVERFLOW = -5  /* an internal capacity bound was exceeded (message says which) */
+    LEON_E_OVERFLOW = -5, /* an internal capacity bound was exceeded (message says which) */
+    LEON_E_IO = -6        /* the container file could not be written */
 };
 
 /* Option subset of the `leon -c` command line that reaches the hot path (C/Leon.cpp:102-140, 342-431). */
@@ -158,6 +159,28 @@ int leon_comm_batch_reads(const leon_ctx *ctx, uint64_t *reads);
  * instead of its own, so that the caller's events bracket the work.  The reference has no equivalent: its
  * Dispatcher owns its threads (DP/impl/Command.cpp:119). */
 int leon_set_stream(leon_ctx *ctx, void *stream);
+
+/* `.leon` container.  Writes the outputs of leon_compress()/leon_fetch() as the HDF5 file the reference's
+ * `leon -d` opens: groups /metadata, /leon/{anchors,dna,qual,header} and dataset /leon/bloom with the datasets, byte
+ * layouts and string attributes of C/Leon.cpp:485-531 (infobyte, kmerSize), :581-651 (qual_<id>: zlib stream of the
+ * block's quality text, level 9), :653-710 (dna_<id>, header_<id>, attribute "size"), :965-1081 (bloom via
+ * storage/impl/StorageTools.hpp:93-123, anchorsDict/size/anchorAdress, nb_blocks, blocksizes, read statistics).
+ * Host only (no device work, usable without a GPU); the HDF5 1.8 file format is emitted directly (superblock v0,
+ * symbol-table groups, contiguous u8 datasets, variable-length string attributes), the HDF5 library is not needed.
+ * The header stream comes from the host header coder (C/HeaderCoder.cpp); with has_header = 0 the container is what
+ * `-noheader` / `-seq-only` produce and the decoder numbers the reads.  Errors: leon_last_error(NULL). */
+typedef struct leon_container_info {
+    int32_t kmer_size;          /* metadata/kmerSize and the Bloom filter's kmer_size attribute */
+    int32_t is_fasta;           /* 1: decompresses to FASTA, no leon/qual group (FASTA input, -noqual, -seq-only) */
+    int32_t has_header;         /* 0: -noheader / -seq-only */
+    int32_t reserved0;
+    const uint8_t  *first_header;       uint64_t first_header_nbytes;   /* leon/header/firstheader */
+    uint64_t        header_nblocks;
+    const uint64_t *header_blocksizes;  /* [2 * header_nblocks]: bytes, reads (leon/header/blocksizes) */
+    const uint8_t  *header_data;        /* header_<id> blocks, concatenated */
+    uint64_t reserved[4];
+} leon_container_info;
+int leon_write_container(const char *path, const leon_result *result, const leon_container_info *info);
 
 /* Test hooks (parity tests only): Bloom queries on the device filter for host-provided forward k-mers.
  * kmers: n x (lo, hi) u64 pairs.  out4[i] = BloomNeighborCoherent::contains4 mask (COL Bloom.hpp:645-798),

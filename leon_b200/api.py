@@ -11,7 +11,7 @@ ABI_SYMBOLS = [
     "leon_b200_abi_version", "leon_create", "leon_destroy", "leon_last_error", "leon_alloc_pinned", "leon_free_pinned",
     "leon_compress", "leon_upload", "leon_count", "leon_bloom_build", "leon_encode", "leon_run_device", "leon_fetch",
     "leon_get_timings", "leon_get_kernel_times", "leon_set_stream", "leon_comm_unique_id", "leon_comm_init",
-    "leon_comm_batch_reads", "leon_debug_bloom_query", "leon_debug_hashes", "leon_debug_fetch",
+    "leon_comm_batch_reads", "leon_debug_bloom_query", "leon_debug_hashes", "leon_debug_fetch", "leon_write_container",
 ]
 
 
@@ -60,6 +60,12 @@ class Timings(C.Structure):
                 ("reserved", C.c_float * 3)]
 
 
+class ContainerInfo(C.Structure):
+    _fields_ = [("kmer_size", C.c_int32), ("is_fasta", C.c_int32), ("has_header", C.c_int32), ("reserved0", C.c_int32),
+                ("first_header", C.c_void_p), ("first_header_nbytes", C.c_uint64), ("header_nblocks", C.c_uint64),
+                ("header_blocksizes", C.c_void_p), ("header_data", C.c_void_p), ("reserved", C.c_uint64 * 4)]
+
+
 class KernelTime(C.Structure):
     _fields_ = [("name", C.c_char * 32), ("ms_total", C.c_float), ("launches", C.c_uint32)]
 
@@ -98,6 +104,7 @@ def load_library(path=LIB_PATH):
     L.leon_debug_bloom_query.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.c_void_p]
     L.leon_debug_hashes.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
     L.leon_debug_fetch.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
+    L.leon_write_container.argtypes = [C.c_char_p, C.POINTER(Result), C.POINTER(ContainerInfo)]
     _lib = L
     return L
 
@@ -107,6 +114,43 @@ def _arr(ptr, n, dtype, copy=True):
         return np.zeros(0, dtype)
     a = np.ctypeslib.as_array(ptr, shape=(int(n),))
     return a.astype(dtype, copy=True) if copy else a
+
+
+def write_container(path, result, kmer_size, is_fasta, header=None):
+    """Writes a result of Leon.compress()/fetch() (or any dict with the same keys) as the `.leon` HDF5 container the
+    reference's `leon -d` decodes (C/Leon.cpp:485-531, 581-710, 965-1081).  `header` = None for -noheader/-seq-only,
+    else a dict(first_header=bytes, blocksizes=uint64[2n], data=uint8[]) from the host header coder."""
+    L = load_library()
+    keep = []
+
+    def ptr(a, dtype, ctype):
+        a = np.ascontiguousarray(a, dtype)
+        keep.append(a)
+        return a.ctypes.data_as(C.POINTER(ctype))
+
+    r = Result()
+    r.bloom, r.bloom_nbytes, r.bloom_bits = ptr(result["bloom"], np.uint8, C.c_uint8), len(result["bloom"]), int(result["bloom_bits"])
+    r.anchors_dict, r.anchors_dict_nbytes = ptr(result["anchors_dict"], np.uint8, C.c_uint8), len(result["anchors_dict"])
+    r.anchor_count = int(result["anchor_count"])
+    r.nblocks = len(result["blocksizes"]) // 2
+    r.blocksizes = ptr(result["blocksizes"], np.uint64, C.c_uint64)
+    r.dna, r.dna_nbytes = ptr(result["dna"], np.uint8, C.c_uint8), len(result["dna"])
+    if not is_fasta:
+        r.qual_text, r.qual_nbytes = ptr(result["qual_text"], np.uint8, C.c_uint8), len(result["qual_text"])
+        r.qual_block_sizes = ptr(result["qual_block_sizes"], np.uint64, C.c_uint64)
+    r.read_count, r.total_dna_size = int(result["read_count"]), int(result["total_dna_size"])
+    r.min_read_size, r.max_read_size = int(result["min_read_size"]), int(result["max_read_size"])
+    info = ContainerInfo(int(kmer_size), int(bool(is_fasta)), int(header is not None))
+    if header is not None:
+        fh = np.frombuffer(bytes(header["first_header"]), np.uint8)
+        bs = np.ascontiguousarray(header["blocksizes"], np.uint64)
+        hd = np.ascontiguousarray(header["data"], np.uint8)
+        keep += [fh, bs, hd]
+        info.first_header, info.first_header_nbytes = fh.ctypes.data, len(fh)
+        info.header_nblocks, info.header_blocksizes, info.header_data = len(bs) // 2, bs.ctypes.data, hd.ctypes.data
+    rc = L.leon_write_container(os.fsencode(path), C.byref(r), C.byref(info))
+    if rc != 0:
+        raise LeonError(rc, L.leon_last_error(None).decode())
 
 
 class PinnedArray:

@@ -26,7 +26,7 @@ def build(force=False, verbose=False):
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
-        ["-I", SRC_DIR, "-o", LIB, os.path.join(SRC_DIR, "leon_b200.cu")]
+        ["-I", SRC_DIR, "-o", LIB, os.path.join(SRC_DIR, "leon_b200.cu"), os.path.join(SRC_DIR, "container.cpp"), "-lz"]
     subprocess.run(cmd, check=True)
     return LIB
 

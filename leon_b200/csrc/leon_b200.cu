@@ -1173,6 +1173,7 @@ void leon_destroy(leon_ctx *c)
 }
 
 const char *leon_last_error(const leon_ctx *c) { return c ? c->err.c_str() : g_create_error.c_str(); }
+void leon_internal_set_error(const char *msg) { g_create_error = msg ? msg : ""; }   // used by container.cpp
 
 void *leon_alloc_pinned(size_t nbytes)
 {
