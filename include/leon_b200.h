@@ -160,6 +160,24 @@ int leon_comm_batch_reads(const leon_ctx *ctx, uint64_t *reads);
  * Dispatcher owns its threads (DP/impl/Command.cpp:119). */
 int leon_set_stream(leon_ctx *ctx, void *stream);
 
+/* Header stream, host only.  Codes the read names (FASTA/FASTQ header lines without the leading
+ * '>' / '@'; text = concatenated, nreads + 1 offsets) exactly like C/HeaderCoder.cpp:257-524 driven by C/Leon.cpp:786-899
+ * with -nb-cores 1: field-wise comparison with the previous header, per-column adaptive models, one range-coded
+ * stream per block of reads_per_block headers.  Blocks are coded by nthreads host threads (0 = all cores); the bytes
+ * do not depend on nthreads (see leon_b200/csrc/headers.cpp on the reference's left-over state).  The result is
+ * owned by the returned object until leon_headers_free(). */
+typedef struct leon_header_stream {
+    const uint8_t  *first_header;  uint64_t first_header_nbytes;  /* leon/header/firstheader: first name minus its first character */
+    uint64_t        nblocks;
+    const uint64_t *blocksizes;    /* [2 * nblocks]: bytes, headers (leon/header/blocksizes) */
+    const uint8_t  *data;          uint64_t data_nbytes;          /* header_<id> streams, concatenated */
+    int32_t         coded_serially;  /* 1: left-over state of the reference was consulted, the file was coded by one serial coder */
+    int32_t         reserved;
+} leon_header_stream;
+int  leon_headers_encode(const uint8_t *text, const uint64_t *offsets, uint64_t nreads, int32_t reads_per_block,
+                         int32_t nthreads, leon_header_stream **out);
+void leon_headers_free(leon_header_stream *stream);
+
 /* `.leon` container.  Writes the outputs of leon_compress()/leon_fetch() as the HDF5 file the reference's
  * `leon -d` opens: groups /metadata, /leon/{anchors,dna,qual,header} and dataset /leon/bloom with the datasets, byte
  * layouts and string attributes of C/Leon.cpp:485-531 (infobyte, kmerSize), :581-651 (qual_<id>: zlib stream of the

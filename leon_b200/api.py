@@ -12,6 +12,7 @@ ABI_SYMBOLS = [
     "leon_compress", "leon_upload", "leon_count", "leon_bloom_build", "leon_encode", "leon_run_device", "leon_fetch",
     "leon_get_timings", "leon_get_kernel_times", "leon_set_stream", "leon_comm_unique_id", "leon_comm_init",
     "leon_comm_batch_reads", "leon_debug_bloom_query", "leon_debug_hashes", "leon_debug_fetch", "leon_write_container",
+    "leon_headers_encode", "leon_headers_free",
 ]
 
 
@@ -66,6 +67,12 @@ class ContainerInfo(C.Structure):
                 ("header_blocksizes", C.c_void_p), ("header_data", C.c_void_p), ("reserved", C.c_uint64 * 4)]
 
 
+class HeaderStream(C.Structure):
+    _fields_ = [("first_header", C.POINTER(C.c_uint8)), ("first_header_nbytes", C.c_uint64), ("nblocks", C.c_uint64),
+                ("blocksizes", C.POINTER(C.c_uint64)), ("data", C.POINTER(C.c_uint8)), ("data_nbytes", C.c_uint64),
+                ("coded_serially", C.c_int32), ("reserved", C.c_int32)]
+
+
 class KernelTime(C.Structure):
     _fields_ = [("name", C.c_char * 32), ("ms_total", C.c_float), ("launches", C.c_uint32)]
 
@@ -105,6 +112,9 @@ def load_library(path=LIB_PATH):
     L.leon_debug_hashes.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
     L.leon_debug_fetch.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
     L.leon_write_container.argtypes = [C.c_char_p, C.POINTER(Result), C.POINTER(ContainerInfo)]
+    L.leon_headers_encode.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int32, C.c_int32, C.POINTER(C.POINTER(HeaderStream))]
+    L.leon_headers_free.argtypes = [C.POINTER(HeaderStream)]
+    L.leon_headers_free.restype = None
     _lib = L
     return L
 
@@ -114,6 +124,26 @@ def _arr(ptr, n, dtype, copy=True):
         return np.zeros(0, dtype)
     a = np.ctypeslib.as_array(ptr, shape=(int(n),))
     return a.astype(dtype, copy=True) if copy else a
+
+
+def encode_headers(text, offsets, reads_per_block=50000, nthreads=0):
+    """Host header coder (C/HeaderCoder.cpp:257-524 as driven by C/Leon.cpp:786-899): text = the read names without the
+    leading '>' / '@', concatenated; offsets = nreads + 1 positions.  Returns dict(first_header, blocksizes, data,
+    coded_serially), the `header` argument of write_container."""
+    L = load_library()
+    text = np.ascontiguousarray(text, np.uint8)
+    offsets = np.ascontiguousarray(offsets, np.uint64)
+    hs = C.POINTER(HeaderStream)()
+    rc = L.leon_headers_encode(text.ctypes.data, offsets.ctypes.data, len(offsets) - 1, int(reads_per_block), int(nthreads), C.byref(hs))
+    if rc != 0:
+        raise LeonError(rc, L.leon_last_error(None).decode())
+    try:
+        h = hs.contents
+        return dict(first_header=_arr(h.first_header, h.first_header_nbytes, np.uint8).tobytes(),
+                    blocksizes=_arr(h.blocksizes, 2 * h.nblocks, np.uint64), data=_arr(h.data, h.data_nbytes, np.uint8),
+                    coded_serially=bool(h.coded_serially))
+    finally:
+        L.leon_headers_free(hs)
 
 
 def write_container(path, result, kmer_size, is_fasta, header=None):

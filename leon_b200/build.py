@@ -26,7 +26,8 @@ def build(force=False, verbose=False):
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
-        ["-I", SRC_DIR, "-o", LIB, os.path.join(SRC_DIR, "leon_b200.cu"), os.path.join(SRC_DIR, "container.cpp"), "-lz"]
+        ["-I", SRC_DIR, "-o", LIB, os.path.join(SRC_DIR, "leon_b200.cu"), os.path.join(SRC_DIR, "container.cpp"),
+         os.path.join(SRC_DIR, "headers.cpp"), "-lz"]
     subprocess.run(cmd, check=True)
     return LIB
 
