@@ -200,6 +200,44 @@ typedef struct leon_container_info {
 } leon_container_info;
 int leon_write_container(const char *path, const leon_result *result, const leon_container_info *info);
 
+/* File level: `leon -file X -c` end to end (C/Leon.cpp:342-470 executeCompression).  Reads the FASTA/FASTQ file like the
+ * reference's bank (bank/impl/BankFasta.cpp:484-570; format from the file name as C/Leon.cpp:392-416), codes the header
+ * stream on host threads while the GPU codes the sequence stream, writes `out_path` (NULL: in_path + ".leon").
+ * Option names are the reference's command line (C/Leon.cpp:102-140). */
+typedef struct leon_file_opts {
+    int32_t kmer_size;        /* -kmer-size (0 = 31) */
+    int32_t reads_per_block;  /* -reads (0 = 50000) */
+    int32_t lossless;         /* -lossless */
+    int32_t abundance_set;    /* -abundance given */
+    int32_t noheader;         /* -noheader */
+    int32_t noqual;           /* -noqual */
+    int32_t seq_only;         /* -seq-only = -noheader -noqual */
+    int32_t device;           /* CUDA device */
+    int32_t nthreads;         /* -nb-cores: host threads of the header coder and of zlib (0 = all) */
+    int32_t reserved[7];
+} leon_file_opts;
+typedef struct leon_file_stats {
+    uint64_t nreads, total_bases, nblocks, input_bytes, output_bytes;
+    uint64_t header_bytes_in, header_bytes_out, dna_bytes_out;
+    int32_t  is_fasta, has_header, headers_coded_serially, reserved0;
+    float    parse_ms, compress_ms, header_ms, write_ms, total_ms;   /* host wall clock; compress_ms covers the GPU path and, in parallel, the header coder */
+    float    reserved1[3];
+    leon_timings gpu;
+} leon_file_stats;
+int leon_compress_file(const char *in_path, const char *out_path, const leon_file_opts *opts, leon_file_stats *stats);
+
+/* The record reader of leon_compress_file on its own (bank/impl/BankFasta.cpp:484-570): reads a FASTA/FASTQ file (multi-line
+ * sequences, blank lines and CR LF accepted) into the layout leon_compress takes.  Bases and qualities are in pinned
+ * host memory when a CUDA device is present.  headers = the name lines without '>' / '@', concatenated. */
+typedef struct leon_file_reads {
+    leon_reads      reads;
+    const uint8_t  *headers;          /* NULL unless want_headers */
+    const uint64_t *header_offsets;   /* [nreads + 1] */
+    int32_t is_fastq, pinned;
+} leon_file_reads;
+int  leon_read_file(const char *path, int want_quals, int want_headers, leon_file_reads **out);
+void leon_file_reads_free(leon_file_reads *reads);
+
 /* Test hooks (parity tests only): Bloom queries on the device filter for host-provided forward k-mers.
  * kmers: n x (lo, hi) u64 pairs.  out4[i] = BloomNeighborCoherent::contains4 mask (COL Bloom.hpp:645-798),
  * out1[i] = contains() of the canonical form (Bloom.hpp:597-642). */

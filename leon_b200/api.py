@@ -12,7 +12,7 @@ ABI_SYMBOLS = [
     "leon_compress", "leon_upload", "leon_count", "leon_bloom_build", "leon_encode", "leon_run_device", "leon_fetch",
     "leon_get_timings", "leon_get_kernel_times", "leon_set_stream", "leon_comm_unique_id", "leon_comm_init",
     "leon_comm_batch_reads", "leon_debug_bloom_query", "leon_debug_hashes", "leon_debug_fetch", "leon_write_container",
-    "leon_headers_encode", "leon_headers_free",
+    "leon_headers_encode", "leon_headers_free", "leon_compress_file", "leon_read_file", "leon_file_reads_free",
 ]
 
 
@@ -73,6 +73,24 @@ class HeaderStream(C.Structure):
                 ("coded_serially", C.c_int32), ("reserved", C.c_int32)]
 
 
+class FileOpts(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("kmer_size", "reads_per_block", "lossless", "abundance_set", "noheader", "noqual",
+                                         "seq_only", "device", "nthreads")] + [("reserved", C.c_int32 * 7)]
+
+
+class FileStats(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in ("nreads", "total_bases", "nblocks", "input_bytes", "output_bytes",
+                                          "header_bytes_in", "header_bytes_out", "dna_bytes_out")] + \
+               [(n, C.c_int32) for n in ("is_fasta", "has_header", "headers_coded_serially", "reserved0")] + \
+               [(n, C.c_float) for n in ("parse_ms", "compress_ms", "header_ms", "write_ms", "total_ms")] + \
+               [("reserved1", C.c_float * 3), ("gpu", Timings)]
+
+
+class FileReads(C.Structure):
+    _fields_ = [("reads", Reads), ("headers", C.POINTER(C.c_uint8)), ("header_offsets", C.POINTER(C.c_uint64)),
+                ("is_fastq", C.c_int32), ("pinned", C.c_int32)]
+
+
 class KernelTime(C.Structure):
     _fields_ = [("name", C.c_char * 32), ("ms_total", C.c_float), ("launches", C.c_uint32)]
 
@@ -115,6 +133,10 @@ def load_library(path=LIB_PATH):
     L.leon_headers_encode.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int32, C.c_int32, C.POINTER(C.POINTER(HeaderStream))]
     L.leon_headers_free.argtypes = [C.POINTER(HeaderStream)]
     L.leon_headers_free.restype = None
+    L.leon_compress_file.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(FileOpts), C.POINTER(FileStats)]
+    L.leon_read_file.argtypes = [C.c_char_p, C.c_int, C.c_int, C.POINTER(C.POINTER(FileReads))]
+    L.leon_file_reads_free.argtypes = [C.POINTER(FileReads)]
+    L.leon_file_reads_free.restype = None
     _lib = L
     return L
 
@@ -124,6 +146,46 @@ def _arr(ptr, n, dtype, copy=True):
         return np.zeros(0, dtype)
     a = np.ctypeslib.as_array(ptr, shape=(int(n),))
     return a.astype(dtype, copy=True) if copy else a
+
+
+def read_file(path, want_quals=True, want_headers=True):
+    """FASTA/FASTQ reader of the file-level path (bank/impl/BankFasta.cpp:484-570): returns dict(bases, offsets, quals,
+    headers, header_offsets, is_fastq) as numpy copies."""
+    L = load_library()
+    fr = C.POINTER(FileReads)()
+    rc = L.leon_read_file(os.fsencode(path), int(want_quals), int(want_headers), C.byref(fr))
+    if rc != 0:
+        raise LeonError(rc, L.leon_last_error(None).decode())
+    try:
+        f = fr.contents
+        n = int(f.reads.nreads)
+        offs = np.ctypeslib.as_array(C.cast(f.reads.offsets, C.POINTER(C.c_uint64)), shape=(n + 1,)).copy()
+        tot = int(offs[-1])
+        u8 = C.POINTER(C.c_uint8)
+        out = dict(offsets=offs, bases=_arr(C.cast(f.reads.bases, u8), tot, np.uint8),
+                   quals=_arr(C.cast(f.reads.quals, u8), tot, np.uint8) if f.reads.quals else None,
+                   is_fastq=bool(f.is_fastq), headers=None, header_offsets=None)
+        if want_headers:
+            ho = np.ctypeslib.as_array(f.header_offsets, shape=(n + 1,)).copy()
+            out.update(header_offsets=ho, headers=_arr(f.headers, int(ho[-1]), np.uint8))
+        return out
+    finally:
+        L.leon_file_reads_free(fr)
+
+
+def compress_file(in_path, out_path=None, kmer_size=31, reads_per_block=50000, lossless=False, abundance=None, noheader=False,
+                  noqual=False, seq_only=False, device=0, nthreads=0):
+    """`leon -file in_path -c` end to end on the B200 path (C/Leon.cpp:342-470); returns the statistics as a dict."""
+    L = load_library()
+    o = FileOpts(kmer_size, reads_per_block, int(lossless), int(abundance is not None), int(noheader), int(noqual),
+                 int(seq_only), device, nthreads)
+    st = FileStats()
+    rc = L.leon_compress_file(os.fsencode(in_path), os.fsencode(out_path) if out_path else None, C.byref(o), C.byref(st))
+    if rc != 0:
+        raise LeonError(rc, L.leon_last_error(None).decode())
+    d = {n: getattr(st, n) for n, _ in FileStats._fields_ if not n.startswith("reserved") and n != "gpu"}
+    d["gpu"] = {n: getattr(st.gpu, n) for n, _ in Timings._fields_ if n != "reserved"}
+    return d
 
 
 def encode_headers(text, offsets, reads_per_block=50000, nthreads=0):

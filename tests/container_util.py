@@ -173,3 +173,23 @@ class H5Mini:
         assert d["n"] == d["size"]
         d["data"] = np.frombuffer(b, np.uint8, d["n"], d["addr"]) if d["n"] else np.zeros(0, np.uint8)
         return d
+
+
+def ref_h5dump():
+    p = os.path.join(REF_DIR, "gatb-h5dump")
+    return p if os.path.exists(p) else None
+
+
+def ref_dataset(leon_file, dset, scratch):
+    """Bytes of one dataset of an HDF5 file, read by the reference's own gatb-h5dump."""
+    out = os.path.join(scratch, "dump.bin")
+    if os.path.exists(out):
+        os.remove(out)
+    subprocess.run([ref_h5dump(), "-d", dset, "-b", "LE", "-o", out, leon_file], check=True,
+                   stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    return np.fromfile(out, dtype=np.uint8)
+
+
+def ref_attr(leon_file, attr):
+    txt = subprocess.run([ref_h5dump(), "-a", attr, leon_file], check=True, capture_output=True, text=True).stdout
+    return re.search(r'\(0\): "(.*)"', txt).group(1)

@@ -1,0 +1,54 @@
+"""FASTA/FASTQ record reader of the file-level path (leon_read_file) on CPU: layouts the reference's bank accepts
+(bank/impl/BankFasta.cpp:484-570): multi-line sequences, blank lines, CR LF, text before the first record, '@' inside
+qualities, multi-line FASTQ, a missing final newline."""
+import numpy as np
+import pytest
+
+
+def _read(tmp_path, name, text, **kw):
+    import leon_b200
+    p = tmp_path / name
+    p.write_bytes(text)
+    return leon_b200.read_file(str(p), **kw)
+
+
+def _split(a, offs):
+    o = offs.astype(np.int64)
+    return [a[o[i]:o[i + 1]].tobytes() for i in range(len(o) - 1)]
+
+
+def test_fasta_layouts(tmp_path):
+    r = _read(tmp_path, "a.fa", b"junk line\n>r1 first read\nACGT\nNNAC\n\n>r2\r\nGG\r\nTT\r\n>\n>r4\nA", want_quals=False)
+    assert _split(r["bases"], r["offsets"]) == [b"ACGTNNAC", b"GGTT", b"", b"A"]
+    assert _split(r["headers"], r["header_offsets"]) == [b"r1 first read", b"r2", b"", b"r4"]
+    assert not r["is_fastq"] and r["quals"] is None
+
+
+def test_fastq_layouts(tmp_path):
+    txt = b"@r1 x\nACGT\n+\n@II>\n@r2\nAC\nGT\n+r2\n!!\n+@\n@r3\n\n+\n\n@r4\nT\n+\n#"
+    r = _read(tmp_path, "a.fq", txt)
+    assert _split(r["bases"], r["offsets"]) == [b"ACGT", b"ACGT", b"", b"T"]
+    assert _split(r["quals"], r["offsets"]) == [b"@II>", b"!!+@", b"", b"#"]
+    assert _split(r["headers"], r["header_offsets"]) == [b"r1 x", b"r2", b"r3", b"r4"]
+    assert r["is_fastq"]
+    r = _read(tmp_path, "a.fq", txt, want_quals=False, want_headers=False)
+    assert _split(r["bases"], r["offsets"]) == [b"ACGT", b"ACGT", b"", b"T"] and r["headers"] is None
+
+
+def test_reader_errors(tmp_path):
+    import leon_b200
+    from leon_b200.api import LeonError
+    with pytest.raises(LeonError) as e:
+        leon_b200.read_file(str(tmp_path / "missing.fa"))
+    assert e.value.code == -6
+    with pytest.raises(LeonError):
+        _read(tmp_path, "b.fq", b"@r1\nACGT\n+\nIIIIII\n")          # quality longer than the sequence
+    with pytest.raises(LeonError):
+        _read(tmp_path, "c.fq", b"@r1\nACGT\n+\nII\n")              # quality shorter than the sequence
+    with pytest.raises(LeonError):
+        _read(tmp_path, "d.fq", b">r1\nACGT\n")                      # qualities wanted, FASTA given
+    r = _read(tmp_path, "e.fa", b"")
+    assert len(r["offsets"]) == 1
+    with pytest.raises(LeonError) as e:
+        leon_b200.compress_file(str(tmp_path / "reads.txt"))
+    assert e.value.code == -1 and "extension" in str(e.value)

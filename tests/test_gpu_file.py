@@ -1,0 +1,113 @@
+"""File level on the GPU box: `leon_b200 -file X -c` (the command line tool over leon_compress_file) against the compiled
+reference on the same file: (1) every dataset and attribute of our `.leon` equals the one in the container the
+reference writes with -nb-cores 1 (quality blocks compared after inflating), (2) the reference decodes our file back to
+the input names, reads and (lossless) qualities."""
+import os
+import subprocess
+import zlib
+
+import numpy as np
+import pytest
+
+from container_util import H5Mini, ref_attr, ref_dataset, ref_h5dump, ref_leon, REF_DIR, ROOT
+
+pytestmark = pytest.mark.gpu
+CLI = os.path.join(ROOT, "leon_b200", "bin", "leon_b200")
+
+
+def _names(n, rng):
+    x, y, out = 1200, 2000, []
+    for i in range(n):
+        y += int(rng.integers(1, 90))
+        if y > 99000:
+            x, y = x + int(rng.integers(1, 40)), 2000
+        out.append("SRR1870605.%d HWI-ST1136:227:HS059ADXX:1:%d:%d:%d length=100" % (i + 1, 1101 + i // 7000, x, y))
+    return out
+
+
+def _write_file(path, fastq, nreads, seed, line_width=0):
+    from leon_b200 import synth
+    rng = np.random.Generator(np.random.PCG64(seed))
+    g = synth.make_genome(60000, seed)
+    bases, offs, quals = synth.sample_reads(g, nreads, 100, seed + 1, n_rate=0.0005, with_quals=fastq)
+    names = _names(nreads, rng)
+    o = offs.astype(np.int64)
+    reads = [bases[o[i]:o[i + 1]].tobytes() for i in range(nreads)]
+    qs = [quals[o[i]:o[i + 1]].tobytes() for i in range(nreads)] if fastq else None
+    with open(path, "wb") as f:
+        for i in range(nreads):
+            if fastq:
+                f.write(b"@" + names[i].encode() + b"\n" + reads[i] + b"\n+\n" + qs[i] + b"\n")
+            elif line_width:
+                r = reads[i]
+                f.write(b">" + names[i].encode() + b"\n" + b"\n".join(r[j:j + line_width] for j in range(0, len(r), line_width)) + b"\n")
+            else:
+                f.write(b">" + names[i].encode() + b"\n" + reads[i] + b"\n")
+    return [n.encode() for n in names], reads, qs
+
+
+def _decode(leon_file, ext, wd):
+    res = subprocess.run([ref_leon(31), "-file", leon_file, "-d", "-nb-cores", "1"], cwd=wd, capture_output=True, text=True, timeout=900)
+    assert res.returncode == 0, res.stdout[-1500:] + res.stderr[-1500:]
+    return [l.rstrip(b"\n") for l in open(leon_file[:-5] + ".d", "rb")]
+
+
+@pytest.mark.parametrize("ext,flags", [("fastq", ["-lossless"]), ("fastq", []), ("fasta", []), ("fastq", ["-seq-only"]),
+                                       ("fastq", ["-noheader"]), ("fastq", ["-noqual"])])
+def test_cli_file_equals_reference_container(tmp_path, ext, flags):
+    if ref_leon(31) is None or ref_h5dump() is None:
+        pytest.skip("oracle/_ref not built")
+    fastq = ext == "fastq"
+    ours_dir, ref_dir = tmp_path / "ours", tmp_path / "ref"
+    ours_dir.mkdir(); ref_dir.mkdir()
+    names, reads, quals = _write_file(str(ours_dir / ("in." + ext)), fastq, 23000, 5, line_width=0 if fastq else 60)
+    os.link(str(ours_dir / ("in." + ext)), str(ref_dir / ("in." + ext)))
+    common = ["-c", "-kmer-size", "31", "-reads", "5000"] + flags
+    res = subprocess.run([CLI, "-file", str(ours_dir / ("in." + ext))] + common, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stdout + res.stderr
+    res = subprocess.run([ref_leon(31), "-file", str(ref_dir / ("in." + ext)), "-nb-cores", "1"] + common, cwd=str(ref_dir),
+                         capture_output=True, text=True, timeout=900)
+    assert res.returncode == 0 and "EXCEPTION" not in res.stdout + res.stderr, res.stdout[-1500:] + res.stderr[-1500:]
+    mine, theirs = str(ours_dir / ("in.%s.leon" % ext)), str(ref_dir / ("in.%s.leon" % ext))
+
+    h = H5Mini(mine).root
+    compared = 0
+
+    def walk(node, path):
+        nonlocal compared
+        for name, child in node.items():
+            if name.startswith("_"):
+                continue
+            if "attrs" in child:        # dataset
+                d = ref_dataset(theirs, path + "/" + name, str(tmp_path))
+                if name.startswith("qual_"):
+                    assert zlib.decompress(child["data"].tobytes()) == zlib.decompress(d.tobytes()), path + "/" + name
+                else:
+                    assert np.array_equal(child["data"], d), path + "/" + name
+                for a, v in child["attrs"].items():
+                    if not (name.startswith("qual_") and a == "size"):
+                        assert ref_attr(theirs, path + "/" + name + "/" + a) == v, (path, name, a)
+                compared += 1
+            else:
+                walk(child, path + "/" + name)
+
+    walk(h, "")
+    nblocks = 5
+    seq_only, noheader, noqual = "-seq-only" in flags, "-noheader" in flags or "-seq-only" in flags, "-noqual" in flags or "-seq-only" in flags
+    expect = 6 + 1 + 3 + (nblocks + 2) + (0 if noheader else nblocks + 4) + (nblocks if fastq and not noqual else 0)
+    assert compared == expect, (compared, expect)
+
+    out_fastq = fastq and not noqual
+    lines = _decode(mine, ext, str(ours_dir))
+    if noheader:
+        import re
+        hdr = re.compile(rb"^[>@] \d+$")
+        lines = [l for l in lines if not hdr.match(l)]
+        got_reads = lines[0::3] if out_fastq else lines
+    else:
+        step = 4 if out_fastq else 2
+        assert [l[1:] for l in lines[0::step]] == names
+        got_reads = lines[1::step]
+        if "-lossless" in flags:
+            assert lines[3::4] == quals
+    assert got_reads == reads
