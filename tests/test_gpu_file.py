@@ -46,10 +46,11 @@ def _write_file(path, fastq, nreads, seed, line_width=0):
     return [n.encode() for n in names], reads, qs
 
 
-def _decode(leon_file, ext, wd):
+def _decode(leon_file, out_fastq, wd):
     res = subprocess.run([ref_leon(31), "-file", leon_file, "-d", "-nb-cores", "1"], cwd=wd, capture_output=True, text=True, timeout=900)
     assert res.returncode == 0, res.stdout[-1500:] + res.stderr[-1500:]
-    return [l.rstrip(b"\n") for l in open(leon_file[:-5] + ".d", "rb")]
+    # the decoder names its output after the stored type: <prefix>.fastq.d or <prefix>.fasta.d (C/Leon.cpp:1437-1448)
+    return [l.rstrip(b"\n") for l in open(os.path.join(wd, "in.%s.d" % ("fastq" if out_fastq else "fasta")), "rb")]
 
 
 @pytest.mark.parametrize("ext,flags", [("fastq", ["-lossless"]), ("fastq", []), ("fasta", []), ("fastq", ["-seq-only"]),
@@ -98,7 +99,7 @@ def test_cli_file_equals_reference_container(tmp_path, ext, flags):
     assert compared == expect, (compared, expect)
 
     out_fastq = fastq and not noqual
-    lines = _decode(mine, ext, str(ours_dir))
+    lines = _decode(mine, out_fastq, str(ours_dir))
     if noheader:
         import re
         hdr = re.compile(rb"^[>@] \d+$")
