@@ -227,13 +227,15 @@ typedef struct leon_file_stats {
 int leon_compress_file(const char *in_path, const char *out_path, const leon_file_opts *opts, leon_file_stats *stats);
 
 /* The record reader of leon_compress_file on its own (bank/impl/BankFasta.cpp:484-570): reads a FASTA/FASTQ file (multi-line
- * sequences, blank lines and CR LF accepted) into the layout leon_compress takes.  Bases and qualities are in pinned
- * host memory when a CUDA device is present.  headers = the name lines without '>' / '@', concatenated. */
+ * sequences, blank lines and CR LF accepted) into the layout leon_compress takes (exactly sized pageable host memory).
+ * Regular files (FASTA without quality sections, 4-line FASTQ) are read by several host threads over ranges cut at
+ * record starts; anything else by one thread, record by record like the reference.  headers = the name lines
+ * without '>' / '@', concatenated. */
 typedef struct leon_file_reads {
     leon_reads      reads;
     const uint8_t  *headers;          /* NULL unless want_headers */
     const uint64_t *header_offsets;   /* [nreads + 1] */
-    int32_t is_fastq, pinned;
+    int32_t is_fastq, threads_used;
 } leon_file_reads;
 int  leon_read_file(const char *path, int want_quals, int want_headers, leon_file_reads **out);
 void leon_file_reads_free(leon_file_reads *reads);

@@ -88,7 +88,7 @@ class FileStats(C.Structure):
 
 class FileReads(C.Structure):
     _fields_ = [("reads", Reads), ("headers", C.POINTER(C.c_uint8)), ("header_offsets", C.POINTER(C.c_uint64)),
-                ("is_fastq", C.c_int32), ("pinned", C.c_int32)]
+                ("is_fastq", C.c_int32), ("threads_used", C.c_int32)]
 
 
 class KernelTime(C.Structure):
@@ -164,7 +164,7 @@ def read_file(path, want_quals=True, want_headers=True):
         u8 = C.POINTER(C.c_uint8)
         out = dict(offsets=offs, bases=_arr(C.cast(f.reads.bases, u8), tot, np.uint8),
                    quals=_arr(C.cast(f.reads.quals, u8), tot, np.uint8) if f.reads.quals else None,
-                   is_fastq=bool(f.is_fastq), headers=None, header_offsets=None)
+                   is_fastq=bool(f.is_fastq), threads_used=int(f.threads_used), headers=None, header_offsets=None)
         if want_headers:
             ho = np.ctypeslib.as_array(f.header_offsets, shape=(n + 1,)).copy()
             out.update(header_offsets=ho, headers=_arr(f.headers, int(ho[-1]), np.uint8))

@@ -8,6 +8,7 @@
 #include <sys/stat.h>
 #include <unistd.h>
 
+#include <algorithm>
 #include <chrono>
 #include <cstdlib>
 #include <cstring>
@@ -32,20 +33,6 @@ struct Mapped {
     }
 };
 
-// Host buffer for bases / qualities: pinned when a CUDA device is there (true DMA uploads), plain memory otherwise
-// (reading a file is not compute; leon_compress still fails without a device).
-struct Pinned {
-    uint8_t *p = nullptr;
-    bool pinned = false;
-    bool alloc(size_t n) {
-        p = (uint8_t *)leon_alloc_pinned(n);
-        pinned = p != nullptr;
-        if (!p) p = (uint8_t *)malloc(n);
-        return p != nullptr;
-    }
-    ~Pinned() { if (p) { if (pinned) leon_free_pinned(p); else free(p); } }
-};
-
 double now_ms() {
     return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
@@ -55,63 +42,184 @@ inline const uint8_t *line_end(const uint8_t *p, const uint8_t *end) {
     return e ? e : end;
 }
 inline size_t trimmed(const uint8_t *p, const uint8_t *e) { return (size_t)((e > p && e[-1] == '\r' ? e - 1 : e) - p); }
+inline const uint8_t *next_line(const uint8_t *e, const uint8_t *end) { return e < end ? e + 1 : end; }
 
-struct ReadSet {
-    Pinned bases, quals;
-    std::vector<uint64_t> offsets{0}, header_offsets{0};
-    std::vector<uint8_t> headers;
-    bool any_qual = false;
-};
-
-// Returns 0 or a LEON_E_* code; err gets the message.
-int parse_reads(const Mapped &m, bool want_quals, bool want_headers, ReadSet &rs, std::string &err) {
-    if (!rs.bases.alloc(m.n + 1) || (want_quals && !rs.quals.alloc(m.n + 1))) { err = "cannot allocate host memory for the reads"; return LEON_E_NOMEM; }
-    const uint8_t *p = m.p, *end = m.p + m.n;
-    uint64_t nb = 0;
-    rs.offsets.reserve(m.n / 200 + 16);
-    while (p < end && *p != '>' && *p != '@') p++;
-    while (p < end) {
+// Walks the records of [p, end) with the reference's grammar (bank/impl/BankFasta.cpp:484-570), p at a record marker, and
+// stops at the first record that starts at or after `stop`.  The sink sees every name line, sequence line and quality
+// line.  `strict` comes back false when the range holds anything but one-line sequences, one-line qualities and
+// back-to-back records (FASTQ) or holds a quality section at all (FASTA): the conditions under which ranges cut at
+// guessed record starts are guaranteed to parse like the whole file does.
+template <class Sink>
+int walk_records(const uint8_t *p, const uint8_t *end, const uint8_t *stop, bool fastq_mode, Sink &s, const uint8_t **stopped,
+                 bool *strict, std::string &err) {
+    *strict = true;
+    while (p < end && p < stop) {
         const uint8_t *e = line_end(p, end);                 // name line, marker excluded
-        if (want_headers) {
-            rs.headers.insert(rs.headers.end(), p + 1, p + 1 + trimmed(p + 1, e));
-            rs.header_offsets.push_back(rs.headers.size());
-        }
-        p = e < end ? e + 1 : end;
-        const uint64_t start = nb;
+        s.header(p + 1, trimmed(p + 1, e));
+        p = next_line(e, end);
+        uint64_t len = 0;
+        int seq_lines = 0;
         while (p < end && *p != '>' && *p != '@' && *p != '+') {
             e = line_end(p, end);
             size_t n = trimmed(p, e);
-            memcpy(rs.bases.p + nb, p, n);
-            nb += n;
-            p = e < end ? e + 1 : end;
+            s.seq(p, n);
+            len += n;
+            seq_lines++;
+            p = next_line(e, end);
         }
-        const uint64_t len = nb - start;
-        rs.offsets.push_back(nb);
+        s.end_seq();
         if (p < end && *p == '+') {
-            rs.any_qual = true;
+            if (!fastq_mode) *strict = false;
             e = line_end(p, end);
-            p = e < end ? e + 1 : end;
+            p = next_line(e, end);
             uint64_t got = 0;
+            int qual_lines = 0;
             do {                                             // at least one line, then until as long as the sequence
                 if (p >= end) break;
                 e = line_end(p, end);
                 size_t n = trimmed(p, e);
-                if (want_quals) {
-                    // a quality longer than its sequence cannot be laid out at the sequence's offsets
-                    if (got + n > len) { err = "record " + std::to_string(rs.offsets.size() - 1) + ": quality longer than sequence"; return LEON_E_ARG; }
-                    memcpy(rs.quals.p + start + got, p, n);
-                }
+                if (!s.qual(p, n, got, len)) { err = "record " + std::to_string(s.record()) + ": quality longer than sequence"; return LEON_E_ARG; }
                 got += n;
-                p = e < end ? e + 1 : end;
+                qual_lines++;
+                p = next_line(e, end);
             } while (got < len);
-            if (want_quals && got < len) { err = "record " + std::to_string(rs.offsets.size() - 1) + ": quality shorter than sequence"; return LEON_E_ARG; }
+            if (s.wants_quals() && got < len) { err = "record " + std::to_string(s.record()) + ": quality shorter than sequence"; return LEON_E_ARG; }
+            if (seq_lines != 1 || qual_lines != 1 || (p < end && *p != '@' && *p != '>')) *strict = false;
             while (p < end && *p != '>' && *p != '@') p++;   // the reference scans for the next marker character
-        } else if (want_quals) {
-            err = "record " + std::to_string(rs.offsets.size() - 1) + " has no quality line (FASTQ expected)";
-            return LEON_E_ARG;
+        } else {
+            if (fastq_mode) *strict = false;
+            if (s.wants_quals()) { err = "record " + std::to_string(s.record()) + " has no quality line (FASTQ expected)"; return LEON_E_ARG; }
         }
+        s.end_record();
     }
+    *stopped = p;
     return LEON_OK;
+}
+
+struct CountSink {
+    uint64_t records = 0, bases = 0, header_bytes = 0, first_record = 0;
+    bool any_qual = false, quals = false;
+    void header(const uint8_t *, size_t n) { header_bytes += n; }
+    void seq(const uint8_t *, size_t n) { bases += n; }
+    void end_seq() {}
+    bool qual(const uint8_t *, size_t n, uint64_t got, uint64_t len) { any_qual = true; return !quals || got + n <= len; }
+    void end_record() { records++; }
+    bool wants_quals() const { return quals; }
+    uint64_t record() const { return first_record + records; }
+};
+
+struct WriteSink {
+    uint8_t *bases, *quals, *headers;                      // bases of the whole set; quals / headers may be null
+    uint64_t *offsets, *header_offsets;
+    uint64_t rec, nb, nh, start = 0;
+    void header(const uint8_t *p, size_t n) { if (headers) { memcpy(headers + nh, p, n); nh += n; header_offsets[rec + 1] = nh; } }
+    void seq(const uint8_t *p, size_t n) { memcpy(bases + nb, p, n); nb += n; }
+    void end_seq() { offsets[rec + 1] = nb; }
+    bool qual(const uint8_t *p, size_t n, uint64_t got, uint64_t len) {
+        if (!quals) return true;
+        if (got + n > len) return false;
+        memcpy(quals + (nb - len) + got, p, n);
+        return true;
+    }
+    void end_record() { rec++; }
+    bool wants_quals() const { return quals != nullptr; }
+    uint64_t record() const { return rec; }
+};
+
+struct HostBuf {
+    uint8_t *p = nullptr;
+    bool alloc(size_t n) { p = (uint8_t *)malloc(n ? n : 1); return p != nullptr; }
+    ~HostBuf() { free(p); }
+};
+
+struct ReadSet {
+    HostBuf bases, quals, headers;
+    std::vector<uint64_t> offsets, header_offsets;
+    uint64_t nreads = 0, header_bytes = 0;
+    bool any_qual = false;
+    unsigned threads_used = 1;
+};
+
+// Record start at line start c?  FASTA: '>'.  FASTQ: '@' whose line after next starts with '+' (a quality line that
+// begins with '@' is followed, two lines on, by a sequence line, which cannot begin with '+').
+bool record_start(const uint8_t *c, const uint8_t *end, bool fastq_mode) {
+    if (c >= end) return true;
+    if (!fastq_mode) return *c == '>';
+    if (*c != '@') return false;
+    const uint8_t *l2 = next_line(line_end(next_line(line_end(c, end), end), end), end);
+    return l2 < end && *l2 == '+';
+}
+
+// Two passes (count, then write into exactly sized buffers) over up to nthreads ranges cut at record starts; when any
+// range is not strictly regular the file is parsed as one range, i.e. serially like the reference.
+int parse_reads(const Mapped &m, bool want_quals, bool want_headers, unsigned nthreads, ReadSet &rs, std::string &err) {
+    const uint8_t *p = m.p, *end = m.p + m.n;
+    while (p < end && *p != '>' && *p != '@') p++;
+    const bool fastq_mode = p < end && *p == '@';
+    unsigned T = nthreads ? nthreads : std::max(1u, std::thread::hardware_concurrency());
+    T = std::min<unsigned>(T, 64);
+    if ((size_t)(end - p) < (4u << 20)) T = 1;
+    for (;;) {
+        std::vector<const uint8_t *> cut(T + 1, end);
+        cut[0] = p;
+        for (unsigned i = 1; i < T; i++) {
+            const uint8_t *c = p + (size_t)(end - p) / T * i;
+            c = next_line(line_end(c, end), end);
+            while (c < end && !record_start(c, end, fastq_mode)) c = next_line(line_end(c, end), end);
+            cut[i] = std::max(c, cut[i - 1]);
+        }
+        std::vector<CountSink> cnt(T);
+        std::vector<int> rcs(T, LEON_OK);
+        std::vector<std::string> errs(T);
+        std::vector<uint8_t> ok(T, 1);
+        auto run = [&](auto &&fn) {
+            std::vector<std::thread> pool;
+            for (unsigned i = 1; i < T; i++) pool.emplace_back(fn, i);
+            fn(0u);
+            for (auto &t : pool) t.join();
+        };
+        run([&](unsigned i) {
+            const uint8_t *stopped = cut[i];
+            bool strict = true;
+            cnt[i].quals = want_quals;
+            if (cut[i] < cut[i + 1]) rcs[i] = walk_records(cut[i], end, cut[i + 1], fastq_mode, cnt[i], &stopped, &strict, errs[i]);
+            ok[i] = (strict && stopped == cut[i + 1]) ? 1 : 0;
+        });
+        bool regular = true;
+        for (unsigned i = 0; i < T; i++) regular = regular && ok[i];
+        if (T > 1 && !regular) { T = 1; continue; }          // irregular layout: one serial range
+        for (unsigned i = 0; i < T; i++) if (rcs[i]) {       // (record numbers inside a message are range-relative when T > 1)
+            if (T > 1) { T = 1; break; }
+            err = errs[i];
+            return rcs[i];
+        }
+        if (T == 1 && rcs[0]) continue;
+        std::vector<uint64_t> rec0(T + 1, 0), nb0(T + 1, 0), nh0(T + 1, 0);
+        for (unsigned i = 0; i < T; i++) {
+            rec0[i + 1] = rec0[i] + cnt[i].records;
+            nb0[i + 1] = nb0[i] + cnt[i].bases;
+            nh0[i + 1] = nh0[i] + cnt[i].header_bytes;
+            rs.any_qual = rs.any_qual || cnt[i].any_qual;
+        }
+        rs.nreads = rec0[T];
+        rs.header_bytes = nh0[T];
+        rs.threads_used = T;
+        rs.offsets.assign(rs.nreads + 1, 0);
+        if (want_headers) rs.header_offsets.assign(rs.nreads + 1, 0);
+        if (!rs.bases.alloc(nb0[T]) || (want_quals && !rs.quals.alloc(nb0[T])) || (want_headers && !rs.headers.alloc(nh0[T]))) {
+            err = "cannot allocate host memory for the reads";
+            return LEON_E_NOMEM;
+        }
+        run([&](unsigned i) {
+            WriteSink w{rs.bases.p, want_quals ? rs.quals.p : nullptr, want_headers ? rs.headers.p : nullptr, rs.offsets.data(),
+                        want_headers ? rs.header_offsets.data() : nullptr, rec0[i], nb0[i], nh0[i]};
+            const uint8_t *stopped;
+            bool strict;
+            if (cut[i] < cut[i + 1]) rcs[i] = walk_records(cut[i], end, cut[i + 1], fastq_mode, w, &stopped, &strict, errs[i]);
+        });
+        for (unsigned i = 0; i < T; i++) if (rcs[i]) { err = errs[i]; return rcs[i]; }
+        return LEON_OK;
+    }
 }
 
 int map_file(const char *path, Mapped &m, std::string &err) {
@@ -133,6 +241,11 @@ struct FileReads {
     ReadSet rs;
 };
 
+struct Joiner {                                          // joins on every exit path, exceptions included
+    std::thread &t;
+    ~Joiner() { if (t.joinable()) t.join(); }
+};
+
 bool has_any(const std::string &s, const char *a, const char *b) { return s.find(a) != std::string::npos || s.find(b) != std::string::npos; }
 
 }  // namespace
@@ -145,17 +258,17 @@ extern "C" int leon_read_file(const char *path, int want_quals, int want_headers
         int rc = map_file(path, m, err);
         if (rc) { leon_internal_set_error(err.c_str()); return rc; }
         std::unique_ptr<FileReads> f(new FileReads());
-        rc = parse_reads(m, want_quals != 0, want_headers != 0, f->rs, err);
+        rc = parse_reads(m, want_quals != 0, want_headers != 0, 0, f->rs, err);
         if (rc) { leon_internal_set_error(("leon_read_file: " + err).c_str()); return rc; }
         memset(&f->pub, 0, sizeof f->pub);
         f->pub.reads.bases = f->rs.bases.p;
         f->pub.reads.offsets = f->rs.offsets.data();
         f->pub.reads.quals = want_quals ? f->rs.quals.p : nullptr;
-        f->pub.reads.nreads = f->rs.offsets.size() - 1;
-        f->pub.headers = want_headers ? f->rs.headers.data() : nullptr;
+        f->pub.reads.nreads = f->rs.nreads;
+        f->pub.headers = want_headers ? f->rs.headers.p : nullptr;
         f->pub.header_offsets = want_headers ? f->rs.header_offsets.data() : nullptr;
         f->pub.is_fastq = f->rs.any_qual ? 1 : 0;
-        f->pub.pinned = f->rs.bases.pinned ? 1 : 0;
+        f->pub.threads_used = (int32_t)f->rs.threads_used;
         *out = &f.release()->pub;
         return LEON_OK;
     } catch (const std::bad_alloc &) {
@@ -185,15 +298,6 @@ extern "C" int leon_compress_file(const char *in_path, const char *out_path, con
         const bool noheader = o->noheader || o->seq_only;
         const bool is_fasta = !fastq_input || o->noqual || o->seq_only;     // container "type": decompresses to FASTA
 
-        Mapped m;
-        rc = map_file(in_path, m, err);
-        if (rc) { leon_internal_set_error(err.c_str()); return rc; }
-        ReadSet rs;
-        rc = parse_reads(m, !is_fasta, !noheader, rs, err);
-        if (rc) { leon_internal_set_error(("leon_compress_file: " + err).c_str()); return rc; }
-        const uint64_t nreads = rs.offsets.size() - 1;
-        const double t1 = now_ms();
-
         leon_opts lo;
         memset(&lo, 0, sizeof lo);
         lo.kmer_size = o->kmer_size ? o->kmer_size : 31;
@@ -202,18 +306,34 @@ extern "C" int leon_compress_file(const char *in_path, const char *out_path, con
         lo.lossless = o->lossless;
         lo.abundance_set = o->abundance_set;
         lo.device = o->device;
-        rc = leon_create(&lo, &ctx);
-        if (rc) return rc;                                    // message already set by leon_create
+        // the CUDA context comes up (a few hundred ms) while the host threads read the file
+        int crc = LEON_OK;
+        std::string cerr_msg;
+        std::thread create_thread([&]() {
+            crc = leon_create(&lo, &ctx);
+            if (crc) cerr_msg = leon_last_error(nullptr);
+        });
+        Joiner join_create{create_thread};
+        Mapped m;
+        ReadSet rs;
+        rc = map_file(in_path, m, err);
+        if (!rc) rc = parse_reads(m, !is_fasta, !noheader, (unsigned)std::max(0, o->nthreads), rs, err);
+        create_thread.join();
+        if (rc) { if (ctx) leon_destroy(ctx); leon_internal_set_error(("leon_compress_file: " + err).c_str()); return rc; }
+        if (crc) { leon_internal_set_error(cerr_msg.c_str()); return crc; }
+        const uint64_t nreads = rs.nreads;
+        const double t1 = now_ms();
 
         // header stream on host threads while the GPU works on the sequence stream
         int hrc = LEON_OK;
         std::string herr;
         double header_ms = 0;
         std::thread header_thread;
+        Joiner join_header{header_thread};
         if (!noheader) {
             header_thread = std::thread([&]() {
                 const double a = now_ms();
-                hrc = leon_headers_encode(rs.headers.data(), rs.header_offsets.data(), nreads, lo.reads_per_block, o->nthreads, &hs);
+                hrc = leon_headers_encode(rs.headers.p, rs.header_offsets.data(), nreads, lo.reads_per_block, o->nthreads, &hs);
                 if (hrc) herr = leon_last_error(nullptr);
                 header_ms = now_ms() - a;
             });
@@ -250,7 +370,7 @@ extern "C" int leon_compress_file(const char *in_path, const char *out_path, con
             stats->input_bytes = m.n;
             struct stat so;
             if (stat(out.c_str(), &so) == 0) stats->output_bytes = (uint64_t)so.st_size;
-            stats->header_bytes_in = rs.headers.size();
+            stats->header_bytes_in = rs.header_bytes;
             stats->header_bytes_out = hs ? hs->data_nbytes : 0;
             stats->dna_bytes_out = res.dna_nbytes + res.bloom_nbytes + res.anchors_dict_nbytes;
             stats->nblocks = res.nblocks;

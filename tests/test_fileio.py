@@ -52,3 +52,57 @@ def test_reader_errors(tmp_path):
     with pytest.raises(LeonError) as e:
         leon_b200.compress_file(str(tmp_path / "reads.txt"))
     assert e.value.code == -1 and "extension" in str(e.value)
+
+
+def _big_records(n, seed, fastq):
+    rng = np.random.Generator(np.random.PCG64(seed))
+    acgt = np.frombuffer(b"ACGTN", np.uint8)
+    names, reads, quals = [], [], []
+    for i in range(n):
+        L = int(rng.integers(60, 140))
+        reads.append(acgt[rng.integers(0, 5, L)].tobytes())
+        names.append(b"read.%d lane:%d" % (i, i % 7))
+        # qualities over the whole printable range: lines that begin with '@', '+' or '>' are common
+        quals.append(rng.integers(33, 75, L).astype(np.uint8).tobytes() if fastq else None)
+    return names, reads, quals
+
+
+@pytest.mark.parametrize("fastq", [True, False])
+def test_parallel_reader_equals_serial(tmp_path, fastq):
+    """Files above the 4 MB threshold are cut at record starts and read by several threads."""
+    import leon_b200
+    names, reads, quals = _big_records(45000, 3, fastq)
+    assert sum(q[:1] in (b"@", b"+", b">") for q in quals if q) > 1000 or not fastq
+    p = tmp_path / ("big.fq" if fastq else "big.fa")
+    with open(p, "wb") as f:
+        for i in range(len(reads)):
+            if fastq:
+                f.write(b"@" + names[i] + b"\n" + reads[i] + b"\n+\n" + quals[i] + b"\n")
+            else:
+                r = reads[i]
+                f.write(b">" + names[i] + b"\n" + b"\n".join(r[j:j + 50] for j in range(0, len(r), 50)) + b"\n")
+    r = leon_b200.read_file(str(p), want_quals=fastq)
+    assert r["threads_used"] > 1
+    assert _split(r["bases"], r["offsets"]) == reads
+    assert _split(r["headers"], r["header_offsets"]) == names
+    if fastq:
+        assert _split(r["quals"], r["offsets"]) == quals
+
+
+def test_irregular_big_fastq_falls_back_to_one_thread(tmp_path):
+    """Multi-line FASTQ cannot be cut safely: the reader must notice and parse it serially, with the same result."""
+    import leon_b200
+    names, reads, quals = _big_records(45000, 4, True)
+    p = tmp_path / "multi.fastq"
+    with open(p, "wb") as f:
+        for i in range(len(reads)):
+            r, q = reads[i], quals[i]
+            if i % 1000 == 999:      # now and then a record with 2-line sequence and quality
+                h = len(r) // 2
+                f.write(b"@" + names[i] + b"\n" + r[:h] + b"\n" + r[h:] + b"\n+\n" + q[:h] + b"\n" + q[h:] + b"\n")
+            else:
+                f.write(b"@" + names[i] + b"\n" + r + b"\n+\n" + q + b"\n")
+    r = leon_b200.read_file(str(p))
+    assert r["threads_used"] == 1
+    assert _split(r["bases"], r["offsets"]) == reads and _split(r["quals"], r["offsets"]) == quals
+    assert _split(r["headers"], r["header_offsets"]) == names
