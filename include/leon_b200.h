@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define LEON_B200_ABI_VERSION 1
+#define LEON_B200_ABI_VERSION 2
 
 enum {
     LEON_OK = 0,
@@ -44,7 +44,10 @@ typedef struct leon_opts {
     int32_t anchor_batch;     /* reads per anchor-resolution batch (0 = default); any value gives identical output */
     int32_t dict_on_device;   /* 1: run the serial low/range recurrence of the anchor dictionary dump (C/Leon.cpp:1245-1260) as a
                                  single-warp kernel instead of on the host thread (same bytes, ~20x slower per step) */
-    int32_t reserved[8];
+    int32_t qual_zlib_on_device; /* 1: the GPU also writes the zlib streams of the quality blocks (leon_result.qual_z, what
+                                 C/Leon.cpp:581-607 makes with host zlib; run matches + dynamic Huffman, leon_b200/csrc/deflate.cuh) */
+    int32_t skip_qual_text;   /* 1: do not copy the quality text to the host (qual_text stays NULL; needs qual_zlib_on_device) */
+    int32_t reserved[6];
 } leon_opts;
 
 /* A set of reads: concatenated ASCII bases (upper-case ACGTN for reference parity) + R+1 offsets
@@ -90,6 +93,9 @@ typedef struct leon_result {
     const int32_t  *anchor_pos;
     const uint32_t *anchor_addr;
     uint64_t reads_without_anchor;
+    /* leon/qual/qual_<id> as stored: one zlib stream per block, concatenated (only with opts.qual_zlib_on_device) */
+    const uint8_t *qual_z;         uint64_t qual_z_nbytes;
+    const uint64_t *qual_z_block_sizes;
 } leon_result;
 
 /* Device-side phase timings of the last leon_compress()/phase calls, CUDA events on the context's stream. */

@@ -25,7 +25,7 @@ class LeonError(RuntimeError):
 class Opts(C.Structure):
     _fields_ = [("kmer_size", C.c_int32), ("reads_per_block", C.c_int32), ("has_qual", C.c_int32), ("lossless", C.c_int32),
                 ("abundance_set", C.c_int32), ("device", C.c_int32), ("anchor_batch", C.c_int32), ("dict_on_device", C.c_int32),
-                ("reserved", C.c_int32 * 8)]
+                ("qual_zlib_on_device", C.c_int32), ("skip_qual_text", C.c_int32), ("reserved", C.c_int32 * 6)]
 
 
 class Reads(C.Structure):
@@ -49,6 +49,7 @@ class Result(C.Structure):
         ("min_read_size", C.c_int32), ("max_read_size", C.c_int32),
         ("anchor_pos", C.POINTER(C.c_int32)), ("anchor_addr", C.POINTER(C.c_uint32)),
         ("reads_without_anchor", C.c_uint64),
+        ("qual_z", C.POINTER(C.c_uint8)), ("qual_z_nbytes", C.c_uint64), ("qual_z_block_sizes", C.POINTER(C.c_uint64)),
     ]
 
 
@@ -228,8 +229,12 @@ def write_container(path, result, kmer_size, is_fasta, header=None):
     r.blocksizes = ptr(result["blocksizes"], np.uint64, C.c_uint64)
     r.dna, r.dna_nbytes = ptr(result["dna"], np.uint8, C.c_uint8), len(result["dna"])
     if not is_fasta:
-        r.qual_text, r.qual_nbytes = ptr(result["qual_text"], np.uint8, C.c_uint8), len(result["qual_text"])
-        r.qual_block_sizes = ptr(result["qual_block_sizes"], np.uint64, C.c_uint64)
+        if result.get("qual_z") is not None and len(result["qual_z"]):
+            r.qual_z, r.qual_z_nbytes = ptr(result["qual_z"], np.uint8, C.c_uint8), len(result["qual_z"])
+            r.qual_z_block_sizes = ptr(result["qual_z_block_sizes"], np.uint64, C.c_uint64)
+        else:
+            r.qual_text, r.qual_nbytes = ptr(result["qual_text"], np.uint8, C.c_uint8), len(result["qual_text"])
+            r.qual_block_sizes = ptr(result["qual_block_sizes"], np.uint64, C.c_uint64)
     r.read_count, r.total_dna_size = int(result["read_count"]), int(result["total_dna_size"])
     r.min_read_size, r.max_read_size = int(result["min_read_size"]), int(result["max_read_size"])
     info = ContainerInfo(int(kmer_size), int(bool(is_fasta)), int(header is not None))
@@ -274,10 +279,10 @@ class Leon:
     """
 
     def __init__(self, kmer_size=31, reads_per_block=50000, lossless=False, abundance=None, has_qual=False, device=0,
-                 anchor_batch=0, dict_on_device=False):
+                 anchor_batch=0, dict_on_device=False, qual_zlib_on_device=False, skip_qual_text=False):
         self.L = load_library()
         self.opts = Opts(kmer_size, reads_per_block, int(has_qual), int(lossless), int(abundance is not None), device,
-                         anchor_batch, int(dict_on_device))
+                         anchor_batch, int(dict_on_device), int(qual_zlib_on_device), int(skip_qual_text))
         self.ctx = C.c_void_p()
         rc = self.L.leon_create(C.byref(self.opts), C.byref(self.ctx))
         if rc != 0:
@@ -308,8 +313,10 @@ class Leon:
 
     @staticmethod
     def _result(r, copy=True):
-        hq = r.qual_nbytes > 0
+        hq = r.qual_nbytes > 0 or r.qual_z_nbytes > 0
         return dict(
+            qual_z=_arr(r.qual_z, r.qual_z_nbytes, np.uint8, copy),
+            qual_z_block_sizes=_arr(r.qual_z_block_sizes, r.nblocks if r.qual_z_nbytes else 0, np.uint64, copy),
             cutoff=int(r.count.cutoff), nb_solids_cutoff=int(r.count.nb_solids_cutoff),
             nb_solid_total=int(r.count.nb_solid_total), nb_distinct=int(r.count.nb_distinct), nb_kmers=int(r.count.nb_kmers),
             histogram=_arr(r.count.histogram, 10001, np.uint64, copy),

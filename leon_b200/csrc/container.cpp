@@ -395,8 +395,9 @@ extern "C" int leon_write_container(const char *path, const leon_result *r, cons
         if (!path || !r || !info) { leon_internal_set_error("leon_write_container: null argument"); return LEON_E_ARG; }
         if (info->kmer_size < 2 || info->kmer_size > 63) { leon_internal_set_error("leon_write_container: bad kmer_size"); return LEON_E_ARG; }
         const bool fasta = info->is_fasta != 0, has_header = info->has_header != 0;
-        if (!fasta && r->nblocks && (!r->qual_text || !r->qual_block_sizes)) {
-            leon_internal_set_error("leon_write_container: FASTQ container needs the quality text of the result");
+        const bool have_z = r->qual_z && r->qual_z_block_sizes;
+        if (!fasta && r->nblocks && !have_z && (!r->qual_text || !r->qual_block_sizes)) {
+            leon_internal_set_error("leon_write_container: FASTQ container needs the quality text or the zlib streams of the result");
             return LEON_E_ARG;
         }
         if (has_header && (!info->first_header || (info->header_nblocks && (!info->header_blocksizes || !info->header_data)))) {
@@ -456,11 +457,22 @@ extern "C" int leon_write_container(const char *path, const leon_result *r, cons
         std::vector<std::vector<uint8_t>> zq;
         if (!fasta) {
             Group *qual = leon->group("qual");
-            int rc = deflate_blocks(r->qual_text, r->qual_block_sizes, r->nblocks, zq, err);
-            if (rc) { leon_internal_set_error(err.c_str()); return rc; }
-            for (uint64_t b = 0; b < r->nblocks; b++) {
-                Dataset &d = qual->dataset("qual_" + dec(b), zq[b].data(), zq[b].size());
-                d.attrs.push_back({"size", dec(zq[b].size())});
+            if (have_z) {                                   // streams written by the GPU (deflate.cuh)
+                uint64_t zat = 0;
+                for (uint64_t b = 0; b < r->nblocks; b++) {
+                    const uint64_t n = r->qual_z_block_sizes[b];
+                    if (zat + n > r->qual_z_nbytes) { leon_internal_set_error("leon_write_container: qual_z_block_sizes exceed qual_z_nbytes"); return LEON_E_ARG; }
+                    Dataset &d = qual->dataset("qual_" + dec(b), r->qual_z + zat, n);
+                    d.attrs.push_back({"size", dec(n)});
+                    zat += n;
+                }
+            } else {
+                int rc = deflate_blocks(r->qual_text, r->qual_block_sizes, r->nblocks, zq, err);
+                if (rc) { leon_internal_set_error(err.c_str()); return rc; }
+                for (uint64_t b = 0; b < r->nblocks; b++) {
+                    Dataset &d = qual->dataset("qual_" + dec(b), zq[b].data(), zq[b].size());
+                    d.attrs.push_back({"size", dec(zq[b].size())});
+                }
             }
         }
 

@@ -306,6 +306,8 @@ extern "C" int leon_compress_file(const char *in_path, const char *out_path, con
         lo.lossless = o->lossless;
         lo.abundance_set = o->abundance_set;
         lo.device = o->device;
+        lo.qual_zlib_on_device = lo.has_qual;                 // quality blocks leave the GPU as zlib streams
+        lo.skip_qual_text = lo.has_qual;
         // the CUDA context comes up (a few hundred ms) while the host threads read the file
         int crc = LEON_OK;
         std::string cerr_msg;

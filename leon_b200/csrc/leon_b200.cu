@@ -9,6 +9,7 @@
 #include "bloom.cuh"
 #include "anchors.cuh"
 #include "walk.cuh"
+#include "deflate.cuh"
 #include "entropy.cuh"
 #include "simplehash_table.h"
 #include "comm.cuh"
@@ -119,6 +120,12 @@ struct leon_ctx {
     double dict_host_ms = 0, dict_copy_wait_ms = 0;
     uint64_t nblocks = 0, dna_nbytes = 0, dict_nbytes = 0, nsym_total = 0;
     PinBuf h_dna, h_bs, h_dict, h_qual, h_qsizes, h_apos, h_aaddr;
+    // zlib streams of the quality blocks written on the device (deflate.cuh)
+    DevBuf d_qz_blkoff, d_qz_first, d_qz_cblock, d_qz_slots, d_qz_meta, d_qz_coff, d_qz_bsize, d_qz_boff, d_qz_adler, d_qz_out;
+    PinBuf h_qz_tables, h_qz_boff, h_qz_out, h_qz_sizes;
+    cudaEvent_t ev_qz = nullptr;
+    uint32_t qz_nchunks = 0;
+    bool qz_done = false;
     uint64_t reads_without_anchor = 0;
     int32_t min_len = 0, max_len = 0;
 };
@@ -833,6 +840,59 @@ __global__ void k_count_noanchor(const int32_t *__restrict__ apos, uint64_t n, u
     if ((threadIdx.x & 31) == 0 && v) atomicAdd(out, v);
 }
 
+// Quality blocks -> zlib streams on the third stream, right behind k_quals (deflate.cuh).  The chunk tables are built on
+// the host from the block sizes known since leon_upload.
+void deflate_quals(leon_ctx *c)
+{
+    using namespace lbdeflate;
+    const uint64_t nb = c->qsizes.size();
+    uint64_t nchunks = 0;
+    for (uint64_t b = 0; b < nb; b++) nchunks += (c->qsizes[b] + DF_CHUNK - 1) / DF_CHUNK;
+    if (nchunks >= 0xffffffffull) throw LeonError(LEON_E_OVERFLOW, "deflate_quals: too many chunks");
+    c->qz_nchunks = (uint32_t)nchunks;
+    // one pinned table: blk_off[nb + 1] (u64) | chunk_first[nb + 1] (u32) | chunk_block[nchunks] (u32)
+    const size_t off_first = (nb + 1) * 8, off_cblock = off_first + (nb + 1) * 4, tbytes = off_cblock + nchunks * 4;
+    c->h_qz_tables.reserve(tbytes + 16);
+    uint64_t *blk_off = (uint64_t *)c->h_qz_tables.p;
+    uint32_t *first = (uint32_t *)((char *)c->h_qz_tables.p + off_first), *cblock = (uint32_t *)((char *)c->h_qz_tables.p + off_cblock);
+    uint64_t at = 0, ch = 0;
+    for (uint64_t b = 0; b < nb; b++) {
+        blk_off[b] = at; first[b] = (uint32_t)ch;
+        const uint64_t k = (c->qsizes[b] + DF_CHUNK - 1) / DF_CHUNK;
+        for (uint64_t i = 0; i < k; i++) cblock[ch++] = (uint32_t)b;
+        at += c->qsizes[b];
+    }
+    blk_off[nb] = at; first[nb] = (uint32_t)ch;
+    cudaStream_t s3 = c->st3;
+    c->d_qz_blkoff.reserve(tbytes + 16);
+    CUDA_TRY(cudaMemcpyAsync(c->d_qz_blkoff.p, c->h_qz_tables.p, tbytes, cudaMemcpyHostToDevice, s3));
+    const uint64_t *d_blk_off = c->d_qz_blkoff.as<uint64_t>();
+    const uint32_t *d_first = (const uint32_t *)((const char *)c->d_qz_blkoff.p + off_first);
+    const uint32_t *d_cblock = (const uint32_t *)((const char *)c->d_qz_blkoff.p + off_cblock);
+    c->d_qz_slots.reserve(nchunks * (uint64_t)DF_SLOT + 16);
+    c->d_qz_meta.reserve(nchunks * sizeof(ChunkMeta) + 16);
+    c->d_qz_coff.reserve(nchunks * 4 + 16);
+    c->d_qz_bsize.reserve(nb * 8 + 16);
+    c->d_qz_boff.reserve((nb + 1) * 8 + 16);
+    c->d_qz_adler.reserve(nb * 4 + 16);
+    c->d_qz_out.reserve(at + nchunks * 16 + nb * 8 + 64);       // every chunk is at worst stored: text + 5 bytes
+    CUDA_TRY(cudaFuncSetAttribute(k_deflate_chunks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ChunkState)));
+    if (nchunks) {
+        LB_TIMED(c->kt, "k_deflate_chunks", s3, LB_LAUNCH(c->lc, k_deflate_chunks, (unsigned)nchunks, DF_THREADS, sizeof(ChunkState), s3,
+                 c->d_qout.as<uint8_t>(), d_blk_off, d_first, d_cblock, c->d_qz_slots.as<uint8_t>(), c->d_qz_meta.as<ChunkMeta>()));
+        LB_LAUNCH(c->lc, k_deflate_layout, 1, 1024, 0, s3, c->d_qz_meta.as<ChunkMeta>(), d_first, (uint32_t)nb, c->d_qz_coff.as<uint32_t>(),
+                  c->d_qz_bsize.as<uint64_t>(), c->d_qz_boff.as<uint64_t>(), c->d_qz_adler.as<uint32_t>());
+        LB_TIMED(c->kt, "k_deflate_gather", s3, LB_LAUNCH(c->lc, k_deflate_gather, (unsigned)nchunks, 256, 0, s3, c->d_qz_slots.as<uint8_t>(),
+                 c->d_qz_meta.as<ChunkMeta>(), d_first, d_cblock, c->d_qz_coff.as<uint32_t>(), c->d_qz_boff.as<uint64_t>(),
+                 c->d_qz_adler.as<uint32_t>(), c->d_qz_out.as<uint8_t>()));
+        // the layout goes to the host at once so that leon_fetch knows how many bytes to copy
+        c->h_qz_boff.reserve((nb + 1) * 8 + 16);
+        CUDA_TRY(cudaMemcpyAsync(c->h_qz_boff.p, c->d_qz_boff.p, (nb + 1) * 8, cudaMemcpyDeviceToHost, s3));
+    }
+    CUDA_TRY(cudaEventRecord(c->ev_qz, s3));
+    c->qz_done = true;
+}
+
 template <typename K> void do_encode_body(leon_ctx *c)
 {
     using namespace lbent;
@@ -848,6 +908,7 @@ template <typename K> void do_encode_body(leon_ctx *c)
     // small kernels and host round trips leave most of the GPU idle.  It borrows the error-position buffer as its
     // prefix-count scratch, so the walk waits for it.
     c->d_err.reserve((c->nkmers + 1) * 4);
+    c->qz_done = false;
     if (c->opts.has_qual) {
         c->d_qout.reserve(c->nbases + R + 16);
         if (R) {
@@ -856,6 +917,7 @@ template <typename K> void do_encode_body(leon_ctx *c)
             LB_TIMED(c->kt, "k_quals", c->st3, LB_LAUNCH(c->lc, (lbwalk::k_quals<K>), warp_grid(R), 256, 0, c->st3, bases, c->d_quals.as<uint8_t>(), offsets, koff, R,
                       c->bloom, c->d_tbl.as<uint64_t>(), c->opts.lossless, c->d_err.as<uint32_t>(), c->d_qout.as<uint8_t>()));
             CUDA_TRY(cudaEventRecord(c->ev_q[1], c->st3));
+            if (c->opts.qual_zlib_on_device) deflate_quals(c);
         }
     }
     do_anchors<K>(c);
@@ -990,6 +1052,7 @@ template <typename K> void do_encode_body(leon_ctx *c)
         if (R) LB_LAUNCH(c->lc, k_count_noanchor, (unsigned)std::min<uint64_t>((R + 255) / 256, 1024), 256, 0, st, apos, R, cnt);
         c->reads_without_anchor = fetch_scalar(c, cnt);
     }
+    if (c->qz_done) CUDA_TRY(cudaStreamWaitEvent(st, c->ev_qz, 0));   // the run ends when the quality streams are written too
     CUDA_TRY(cudaEventRecord(c->ev[10], st));
     c->phase = PH_ENCODED;
 }
@@ -1031,10 +1094,21 @@ void do_fetch(leon_ctx *c, leon_result *out)
     }
     uint64_t qbytes = 0;
     c->h_qsizes.reserve(c->nblocks * 8 + 8);
-    if (c->opts.has_qual && R) {
+    const bool want_text = !(c->opts.skip_qual_text && c->opts.qual_zlib_on_device);
+    if (c->opts.has_qual && R && want_text) {
         qbytes = c->nbases + R;
         c->h_qual.reserve(qbytes + 8);
         CUDA_TRY(cudaMemcpyAsync(c->h_qual.p, c->d_qout.p, qbytes, cudaMemcpyDeviceToHost, st));
+    }
+    uint64_t zbytes = 0;
+    if (c->opts.has_qual && R && c->opts.qual_zlib_on_device && c->qz_done) {
+        CUDA_TRY(cudaEventSynchronize(c->ev_qz));               // layout table is on the host now
+        const uint64_t *boff = c->h_qz_boff.as<uint64_t>();
+        zbytes = boff[c->nblocks];
+        c->h_qz_out.reserve(zbytes + 8);
+        c->h_qz_sizes.reserve(c->nblocks * 8 + 8);
+        for (uint64_t b = 0; b < c->nblocks; b++) c->h_qz_sizes.as<uint64_t>()[b] = boff[b + 1] - boff[b];
+        CUDA_TRY(cudaMemcpyAsync(c->h_qz_out.p, c->d_qz_out.p, zbytes, cudaMemcpyDeviceToHost, st));
     }
     CUDA_TRY(cudaStreamSynchronize(st));
     memset(out, 0, sizeof *out);
@@ -1043,7 +1117,8 @@ void do_fetch(leon_ctx *c, leon_result *out)
     out->anchors_dict = c->h_dict.as<uint8_t>(); out->anchors_dict_nbytes = c->dict_nbytes; out->anchor_count = c->dict_count;
     out->nblocks = c->nblocks; out->blocksizes = c->h_bs.as<uint64_t>();
     out->dna = c->h_dna.as<uint8_t>(); out->dna_nbytes = c->dna_nbytes;
-    out->qual_text = c->h_qual.as<uint8_t>(); out->qual_nbytes = qbytes; out->qual_block_sizes = c->h_qsizes.as<uint64_t>();
+    out->qual_text = qbytes ? c->h_qual.as<uint8_t>() : nullptr; out->qual_nbytes = qbytes; out->qual_block_sizes = c->h_qsizes.as<uint64_t>();
+    if (zbytes) { out->qual_z = c->h_qz_out.as<uint8_t>(); out->qual_z_nbytes = zbytes; out->qual_z_block_sizes = c->h_qz_sizes.as<uint64_t>(); }
     out->read_count = R; out->total_dna_size = c->nbases;
     out->min_read_size = c->min_len; out->max_read_size = c->max_len;
     out->anchor_pos = c->h_apos.as<int32_t>(); out->anchor_addr = c->h_aaddr.as<uint32_t>();
@@ -1105,6 +1180,7 @@ int leon_create(const leon_opts *opts, leon_ctx **out)
     *out = nullptr;
     if (opts->kmer_size < 2 || opts->kmer_size > 63) { g_create_error = "leon_create: kmer_size must be in [2,63]"; return LEON_E_ARG; }
     if (opts->reads_per_block <= 0) { g_create_error = "leon_create: reads_per_block must be positive"; return LEON_E_ARG; }
+    if (opts->skip_qual_text && !opts->qual_zlib_on_device) { g_create_error = "leon_create: skip_qual_text needs qual_zlib_on_device"; return LEON_E_ARG; }
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0) {
@@ -1129,6 +1205,7 @@ int leon_create(const leon_opts *opts, leon_ctx **out)
         }
         CUDA_TRY(cudaStreamCreateWithFlags(&c->st3, cudaStreamNonBlocking));
         for (int i = 0; i < 2; i++) CUDA_TRY(cudaEventCreateWithFlags(&c->ev_q[i], cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&c->ev_qz, cudaEventDisableTiming));
         for (int i = 0; i < 16; i++) CUDA_TRY(cudaEventCreate(&c->ev[i]));
         for (int i = 0; i < 16; i++) CUDA_TRY(cudaEventRecord(c->ev[i], c->st));
     } catch (const LeonError &er) {
@@ -1169,6 +1246,7 @@ void leon_destroy(leon_ctx *c)
     if (c->st2) { cudaStreamSynchronize(c->st2); cudaStreamDestroy(c->st2); }
     if (c->st3) { cudaStreamSynchronize(c->st3); cudaStreamDestroy(c->st3); }
     for (int i = 0; i < 2; i++) if (c->ev_q[i]) cudaEventDestroy(c->ev_q[i]);
+    if (c->ev_qz) cudaEventDestroy(c->ev_qz);
     delete c;
 }
 

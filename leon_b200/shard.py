@@ -58,13 +58,16 @@ def merge_results(results, nreads, nranks, S, reads_per_block):
     q_parts = [None] * nblocks
     bs = np.zeros(2 * nblocks, np.uint64)
     qs = np.zeros(nblocks, np.uint64)
-    has_q = len(results[0]["qual_block_sizes"]) > 0 or any(len(r["qual_block_sizes"]) for r in results)
+    has_q = any(len(r["qual_text"]) for r in results)
+    has_z = any(len(r.get("qual_z", ())) for r in results)
+    z_parts = [None] * nblocks
+    zs = np.zeros(nblocks, np.uint64)
     apos = np.zeros(nreads, np.int32)
     aaddr = np.zeros(nreads, np.uint32)
     for rank, r in enumerate(results):
         ids = global_block_ids(nreads, rank, nranks, S, reads_per_block)
         assert len(ids) == r["nblocks"], (rank, len(ids), r["nblocks"])
-        off = qoff = 0
+        off = qoff = zoff = 0
         for j, b in enumerate(ids):
             nb = int(r["blocksizes"][2 * j])
             dna_parts[b] = r["dna"][off:off + nb]
@@ -75,6 +78,11 @@ def merge_results(results, nreads, nranks, S, reads_per_block):
                 q_parts[b] = r["qual_text"][qoff:qoff + nq]
                 qoff += nq
                 qs[b] = nq
+            if has_z:
+                nz = int(r["qual_z_block_sizes"][j])
+                z_parts[b] = r["qual_z"][zoff:zoff + nz]
+                zoff += nz
+                zs[b] = nz
         loc = 0
         for lo, hi in rank_read_ranges(nreads, rank, nranks, S):
             apos[lo:hi] = r["anchor_pos"][loc:loc + hi - lo]
@@ -86,6 +94,8 @@ def merge_results(results, nreads, nranks, S, reads_per_block):
         dna=np.concatenate(dna_parts) if nblocks else np.zeros(0, np.uint8),
         qual_text=np.concatenate(q_parts) if (has_q and nblocks) else np.zeros(0, np.uint8),
         qual_block_sizes=qs if has_q else np.zeros(0, np.uint64),
+        qual_z=np.concatenate(z_parts) if (has_z and nblocks) else np.zeros(0, np.uint8),
+        qual_z_block_sizes=zs if has_z else np.zeros(0, np.uint64),
         anchor_pos=apos, anchor_addr=aaddr,
         read_count=sum(r["read_count"] for r in results), total_dna_size=sum(r["total_dna_size"] for r in results),
         min_read_size=min(r["min_read_size"] for r in results if r["read_count"]) if nreads else results[0]["min_read_size"],
