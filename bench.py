@@ -43,6 +43,7 @@ def parse_args():
     ap.add_argument("--reads", type=int, default=0, help="override the number of reads per GPU (debug; marks the line invalid)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--fastq", action="store_true", help="configs[2] shape: FASTQ with synthetic qualities, lossy (debug line)")
+    ap.add_argument("--host-zlib", action="store_true", help="with --fastq: return the quality text instead of zlib streams written by the GPU")
     ap.add_argument("--anchor-batch", type=int, default=0, help="reads per anchor-resolution batch (0 = library default)")
     ap.add_argument("--phases", action="store_true", help="print per-phase / per-kernel device times to stderr")
     return ap.parse_args()
@@ -229,6 +230,12 @@ def algorithmic_bytes(kernel, st):
         return st["nsym"] * 8.0 + NB
     if kernel == "k_range_encode":    # read the 17-byte record of every symbol, write the output bytes
         return st["nsym"] * 17.0 + st["dna_bytes"]
+    if kernel == "k_deflate_chunks":  # read the quality text once, write the compressed chunk once
+        return st["qual_bytes"] + st.get("qual_z_bytes", 0.0)
+    if kernel == "k_deflate_gather":  # move the compressed chunks to their place
+        return 2.0 * st.get("qual_z_bytes", 0.0)
+    if kernel == "k_quals":           # read bases + qualities, write the smoothed text (Bloom lookups not counted)
+        return 2.0 * NB + st["qual_bytes"]
     if kernel == "k_run_stats" or kernel == "k_insert_runs":
         return st["nruns"] * (8.0 + kb)
     return None
@@ -283,8 +290,9 @@ def main_b200(args):
     pin_o.array[:] = offs
     offs = pin_o.array
 
+    dev_zlib = args.fastq and not args.host_zlib
     eng = leon_b200.Leon(kmer_size=KMER, reads_per_block=RPB, has_qual=args.fastq, device=local_rank,
-                         anchor_batch=S if world > 1 else args.anchor_batch)
+                         anchor_batch=S if world > 1 else args.anchor_batch, qual_zlib_on_device=dev_zlib, skip_qual_text=dev_zlib)
     stream = torch.cuda.current_stream()
     eng.set_stream(stream.cuda_stream)
     if world > 1:
@@ -332,7 +340,8 @@ def main_b200(args):
     res = eng.fetch(copy=False)
     # the roofline describes rank 0's launches: its own share of the reads
     stats = {"nreads": local_reads, "nbases": local_reads * READ_LEN, "nkmers": local_reads * (READ_LEN - KMER + 1),
-             "nruns": res["nb_distinct"], "dna_bytes": len(res["dna"])}
+             "nruns": res["nb_distinct"], "dna_bytes": len(res["dna"]),
+             "qual_bytes": float(local_reads * (READ_LEN + 1)) if args.fastq else 0.0, "qual_z_bytes": float(len(res["qual_z"]))}
     nsym = eng.debug_fetch("nsym", np.uint64)
     stats["nsym"] = float(nsym.sum())
     anchors = res["anchor_count"]
@@ -357,7 +366,7 @@ def main_b200(args):
         e2e_ms = float(t.item())
     h2d = int(bases.nbytes + offs.nbytes + (quals.nbytes if quals is not None else 0))
     d2h = int(len(r["bloom"]) + len(r["anchors_dict"]) + len(r["dna"]) + r["blocksizes"].nbytes +
-              r["anchor_pos"].nbytes + r["anchor_addr"].nbytes + len(r["qual_text"]))
+              r["anchor_pos"].nbytes + r["anchor_addr"].nbytes + len(r["qual_text"]) + len(r["qual_z"]))
     if world > 1:   # bytes of all ranks
         t = torch.tensor([h2d, d2h, launches], device="cuda", dtype=torch.int64)
         dist.all_reduce(t)

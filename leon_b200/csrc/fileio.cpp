@@ -10,6 +10,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <memory>
@@ -126,10 +127,20 @@ struct WriteSink {
     uint64_t record() const { return rec; }
 };
 
+// Exactly sized anonymous mapping, transparent huge pages requested: the first touch of a fresh gigabyte by the writer
+// threads is page-fault bound with 4 KiB pages.
 struct HostBuf {
     uint8_t *p = nullptr;
-    bool alloc(size_t n) { p = (uint8_t *)malloc(n ? n : 1); return p != nullptr; }
-    ~HostBuf() { free(p); }
+    size_t cap = 0;
+    bool alloc(size_t n) {
+        cap = ((n ? n : 1) + (2u << 20) - 1) & ~(size_t)((2u << 20) - 1);
+        void *q = mmap(nullptr, cap, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS, -1, 0);
+        if (q == MAP_FAILED) { cap = 0; return false; }
+        madvise(q, cap, MADV_HUGEPAGE);
+        p = (uint8_t *)q;
+        return true;
+    }
+    ~HostBuf() { if (p) munmap(p, cap); }
 };
 
 struct ReadSet {
@@ -159,7 +170,9 @@ int parse_reads(const Mapped &m, bool want_quals, bool want_headers, unsigned nt
     unsigned T = nthreads ? nthreads : std::max(1u, std::thread::hardware_concurrency());
     T = std::min<unsigned>(T, 64);
     if ((size_t)(end - p) < (4u << 20)) T = 1;
+    const bool trace = getenv("LEON_B200_TRACE") != nullptr;
     for (;;) {
+        const double ta = now_ms();
         std::vector<const uint8_t *> cut(T + 1, end);
         cut[0] = p;
         for (unsigned i = 1; i < T; i++) {
@@ -185,6 +198,7 @@ int parse_reads(const Mapped &m, bool want_quals, bool want_headers, unsigned nt
             if (cut[i] < cut[i + 1]) rcs[i] = walk_records(cut[i], end, cut[i + 1], fastq_mode, cnt[i], &stopped, &strict, errs[i]);
             ok[i] = (strict && stopped == cut[i + 1]) ? 1 : 0;
         });
+        const double tb = now_ms();
         bool regular = true;
         for (unsigned i = 0; i < T; i++) regular = regular && ok[i];
         if (T > 1 && !regular) { T = 1; continue; }          // irregular layout: one serial range
@@ -210,6 +224,7 @@ int parse_reads(const Mapped &m, bool want_quals, bool want_headers, unsigned nt
             err = "cannot allocate host memory for the reads";
             return LEON_E_NOMEM;
         }
+        const double tc = now_ms();
         run([&](unsigned i) {
             WriteSink w{rs.bases.p, want_quals ? rs.quals.p : nullptr, want_headers ? rs.headers.p : nullptr, rs.offsets.data(),
                         want_headers ? rs.header_offsets.data() : nullptr, rec0[i], nb0[i], nh0[i]};
@@ -218,6 +233,7 @@ int parse_reads(const Mapped &m, bool want_quals, bool want_headers, unsigned nt
             if (cut[i] < cut[i + 1]) rcs[i] = walk_records(cut[i], end, cut[i + 1], fastq_mode, w, &stopped, &strict, errs[i]);
         });
         for (unsigned i = 0; i < T; i++) if (rcs[i]) { err = errs[i]; return rcs[i]; }
+        if (trace) fprintf(stderr, "[leon_b200] read: %u threads, count pass %.1f ms, alloc %.1f ms, write pass %.1f ms\n", T, tb - ta, tc - tb, now_ms() - tc);
         return LEON_OK;
     }
 }
@@ -320,7 +336,9 @@ extern "C" int leon_compress_file(const char *in_path, const char *out_path, con
         ReadSet rs;
         rc = map_file(in_path, m, err);
         if (!rc) rc = parse_reads(m, !is_fasta, !noheader, (unsigned)std::max(0, o->nthreads), rs, err);
+        const double t_parsed = now_ms();
         create_thread.join();
+        if (getenv("LEON_B200_TRACE")) fprintf(stderr, "[leon_b200] file read %.1f ms, then waited %.1f ms for the CUDA context\n", t_parsed - t0, now_ms() - t_parsed);
         if (rc) { if (ctx) leon_destroy(ctx); leon_internal_set_error(("leon_compress_file: " + err).c_str()); return rc; }
         if (crc) { leon_internal_set_error(cerr_msg.c_str()); return crc; }
         const uint64_t nreads = rs.nreads;

@@ -79,7 +79,7 @@ def main():
             dt = time.time() - t
             assert p.returncode == 0, p.stdout + p.stderr
             runs.append(dt)
-            print("ours run %d: %.3f s\n%s" % (r, dt, p.stdout.strip()), flush=True)
+            print("ours run %d: %.3f s\n%s\n%s" % (r, dt, p.stdout.strip(), p.stderr.strip()), flush=True)
         res["ours_wall_s"] = runs
         res["ours_stdout"] = p.stdout.strip().splitlines()
         res["ours_output_bytes"] = os.path.getsize(inp + ".leon")
