@@ -27,7 +27,6 @@ constexpr int DF_THREADS = 256;
 constexpr int DF_SLICE = 252;                       // bytes per thread: 63 words, an odd stride (no bank conflicts)
 constexpr int DF_CHUNK = DF_THREADS * DF_SLICE;     // 64512 <= 65535, so a chunk also fits one stored block
 constexpr int DF_SLOT = DF_CHUNK + 64;              // bytes reserved per chunk in the scratch buffer
-constexpr int DF_OUT_WORDS = DF_SLOT / 4;
 constexpr int DF_NLIT = 286, DF_NCL = 19;
 constexpr uint32_t DF_ADLER = 65521u;
 
@@ -37,11 +36,16 @@ struct ChunkMeta {            // per chunk, written by k_deflate_chunks
     uint32_t n;               // text bytes
 };
 
+constexpr int DF_HDR_WORDS = 160;                   // dynamic block header: <= 14 + 19 * 3 + 287 * 14 bits
+constexpr int DF_EQ_WORDS = 8;                      // 252 "equals its predecessor" bits per slice
+
 struct ChunkState {
     uint32_t in_w[DF_CHUNK / 4];
-    uint32_t out_w[DF_OUT_WORDS];
+    uint32_t hdr_w[DF_HDR_WORDS];
+    uint32_t eqm[DF_EQ_WORDS * DF_THREADS];    // [word][thread]
     uint32_t freq[DF_NLIT + 2];
     uint32_t nmatch;
+    uint32_t lc[DF_NLIT];                      // code | length << 16
     uint16_t lcode[DF_NLIT];   uint8_t llen[DF_NLIT];
     uint16_t clcode[DF_NCL];   uint8_t cllen[DF_NCL];
     uint8_t  first[DF_THREADS], last[DF_THREADS];
@@ -59,13 +63,51 @@ struct ChunkState {
 DF_HD int df_min(int a, int b) { return a < b ? a : b; }
 DF_HD uint32_t df_byte(const ChunkState &S, int i) { return (S.in_w[i >> 2] >> (8 * (i & 3))) & 255u; }
 
+// byte-wise helpers: device intrinsics, plain C on the host (tools/deflate_sim.cpp)
+DF_HD uint32_t df_cmpeq4(uint32_t a, uint32_t b) {          // 0xff in every byte where a and b agree
+#ifdef __CUDA_ARCH__
+    return __vcmpeq4(a, b);
+#else
+    uint32_t r = 0;
+    for (int i = 0; i < 4; i++) if (((a >> (8 * i)) & 255u) == ((b >> (8 * i)) & 255u)) r |= 255u << (8 * i);
+    return r;
+#endif
+}
+DF_HD uint32_t df_bytesum(uint32_t w) {
+#ifdef __CUDA_ARCH__
+    return __vsadu4(w, 0u);
+#else
+    return (w & 255u) + ((w >> 8) & 255u) + ((w >> 16) & 255u) + (w >> 24);
+#endif
+}
+DF_HD uint32_t df_dot0123(uint32_t w) {                     // 0 * b0 + 1 * b1 + 2 * b2 + 3 * b3
+#ifdef __CUDA_ARCH__
+    return __dp4a(w, 0x03020100u, 0u);
+#else
+    return ((w >> 8) & 255u) + 2u * ((w >> 16) & 255u) + 3u * (w >> 24);
+#endif
+}
+DF_HD int df_ffs(uint32_t w) {                              // 1-based position of the lowest set bit, w != 0
+#ifdef __CUDA_ARCH__
+    return __ffs((int)w);
+#else
+    return __builtin_ffs((int)w);
+#endif
+}
+DF_HD int df_clz(uint32_t w) {
+#ifdef __CUDA_ARCH__
+    return __clz((int)w);
+#else
+    return w ? __builtin_clz(w) : 32;
+#endif
+}
+
 // RFC 1951 3.2.5: length 3..258 -> symbol 257..285, extra bits
 DF_HD void df_len_code(int len, int *sym, int *ebits, int *eval) {
     if (len == 258) { *sym = 285; *ebits = 0; *eval = 0; return; }
     int l = len - 3;
     if (l < 8) { *sym = 257 + l; *ebits = 0; *eval = 0; return; }
-    int e = 0, t = l >> 3;                      // e = floor(log2(l)) - 2
-    while (t) { e++; t >>= 1; }
+    const int e = 29 - df_clz((uint32_t)l);                 // floor(log2(l)) - 2
     *ebits = e;
     *sym = 257 + 4 * e + 4 + ((l >> e) & 3);
     *eval = l & ((1 << e) - 1);
@@ -77,21 +119,45 @@ DF_HD uint32_t df_reverse(uint32_t code, int len) {
     return r;
 }
 
-// ---- phase 1: every thread summarises its slice -----------------------------------------------------------------
+DF_HD uint32_t &df_eq(ChunkState &S, int t, int w) { return S.eqm[w * DF_THREADS + t]; }
+DF_HD uint32_t df_eq(const ChunkState &S, int t, int w) { return S.eqm[w * DF_THREADS + t]; }
+
+// ---- phase 1: every thread summarises its slice, a word at a time ---------------------------------------------------
+// eq bit i (i >= 1) = byte i of the slice equals byte i - 1; sums for the Adler-32; first / last byte and the lengths of
+// the first and last run, through which runs are followed across slices.
 DF_HD void df_summary(ChunkState &S, int t, int n) {
     const int base = t * DF_SLICE;
-    const int len = df_min(DF_SLICE, n - base) > 0 ? df_min(DF_SLICE, n - base) : 0;
+    int len = n - base;
+    len = len > DF_SLICE ? DF_SLICE : (len < 0 ? 0 : len);
     S.slen[t] = (uint16_t)len;
-    uint32_t a = 0, b = 0;
-    if (len) {
-        const uint32_t f = df_byte(S, base), l = df_byte(S, base + len - 1);
-        int lead = 1, trail = 1;
-        while (lead < len && df_byte(S, base + lead) == f) lead++;
-        while (trail < len && df_byte(S, base + len - 1 - trail) == l) trail++;
-        S.first[t] = (uint8_t)f; S.last[t] = (uint8_t)l; S.lead[t] = (uint16_t)lead; S.trail[t] = (uint16_t)trail;
-        for (int i = 0; i < len; i++) { uint32_t d = df_byte(S, base + i); a += d; b += (uint32_t)(len - i) * d; }
+    uint32_t eq[DF_EQ_WORDS];
+    for (int k = 0; k < DF_EQ_WORDS; k++) eq[k] = 0;
+    uint32_t a = 0, b = 0, prevb = 0;
+    const int nw = (len + 3) >> 2, bw = base >> 2;
+    for (int k = 0; k < nw; k++) {
+        uint32_t w = S.in_w[bw + k];
+        const int rem = len - 4 * k;
+        if (rem < 4) w &= (1u << (8 * rem)) - 1u;
+        const uint32_t m = df_cmpeq4(w, (w << 8) | prevb);
+        uint32_t nib = (((m & 0x01010101u) * 0x01020408u) >> 24) & 15u;
+        if (k == 0) nib &= ~1u;
+        if (rem < 4) nib &= (1u << rem) - 1u;
+        eq[k >> 3] |= nib << (4 * (k & 7));
+        prevb = w >> 24;
+        const uint32_t sum = df_bytesum(w);
+        a += sum;
+        b += (uint32_t)(len - 4 * k) * sum - df_dot0123(w);
     }
+    for (int k = 0; k < DF_EQ_WORDS; k++) df_eq(S, t, k) = eq[k];
     S.sa[t] = a; S.sb[t] = b;
+    if (len) {
+        S.first[t] = (uint8_t)df_byte(S, base);
+        S.last[t] = (uint8_t)df_byte(S, base + len - 1);
+        int lead = 1, trail = 1;
+        while (lead < len && ((eq[lead >> 5] >> (lead & 31)) & 1u)) lead++;
+        while (trail < len && ((eq[(len - trail) >> 5] >> ((len - trail) & 31)) & 1u)) trail++;
+        S.lead[t] = (uint16_t)lead; S.trail[t] = (uint16_t)trail;
+    }
 }
 
 // Tokens of the part [j0, j0 + cnt) of a run of L equal bytes: position 0 is a literal, the rest is cut into matches of
@@ -114,6 +180,16 @@ DF_HD void df_run_tokens(int j0, int cnt, int L, uint32_t v, Sink &sink) {
     }
 }
 
+// First position >= pos whose eq bit is clear (a run start), or len.
+DF_HD int df_next_start(const ChunkState &S, int t, int pos, int len) {
+    while (pos < len) {
+        const uint32_t w = ~df_eq(S, t, pos >> 5) >> (pos & 31);
+        if (w) { pos += df_ffs(w) - 1; return pos < len ? pos : len; }
+        pos = (pos | 31) + 1;
+    }
+    return len;
+}
+
 // Walks the runs of slice t (extended into the neighbouring slices through the summaries) and feeds the sink.
 template <class Sink>
 DF_HD void df_slice_tokens(const ChunkState &S, int t, int nact, Sink &sink) {
@@ -133,11 +209,11 @@ DF_HD void df_slice_tokens(const ChunkState &S, int t, int nact, Sink &sink) {
     int i = 0;
     while (i < len) {
         const uint32_t v = df_byte(S, base + i);
-        int e = i + 1;
-        while (e < len && df_byte(S, base + e) == v) e++;
+        const int e = df_next_start(S, t, i + 1, len);
         const int j0 = i == 0 ? back : 0;
         const int L = (e - i) + j0 + (e == len ? fwd : 0);
-        df_run_tokens(j0, e - i, L, v, sink);
+        if (L == 1) sink.literal(v);
+        else df_run_tokens(j0, e - i, L, v, sink);
         i = e;
     }
 }
@@ -164,24 +240,31 @@ struct CountSink {            // phase 2: symbol frequencies
 struct BitCountSink {         // phase 4: bits of a thread's tokens
     const ChunkState &S;
     uint32_t bits;
-    DF_HD void literal(uint32_t v) { bits += S.llen[v]; }
+    DF_HD void literal(uint32_t v) { bits += S.lc[v] >> 16; }
     DF_HD void match(int len) {
         int sym, eb, ev;
         df_len_code(len, &sym, &eb, &ev);
-        bits += S.llen[sym] + eb + 1;          // + the 1-bit distance code
+        bits += (S.lc[sym] >> 16) + eb + 1;     // + the 1-bit distance code
     }
 };
 
-struct BitWriter {            // LSB-first bit packing into zero-initialised words; every bit is written once
+// LSB-first bit packing into zero-initialised words.  A thread owns the bits [start, end) of the stream: the words in
+// the middle are its own (plain stores), the first and the last one are shared with its neighbours (atomic OR).
+struct BitWriter {
     uint32_t *w;
     uint64_t acc;
     int nbits;
     uint32_t word;
-    DF_HD void start(uint32_t *out, uint32_t bitpos) { w = out; acc = 0; nbits = (int)(bitpos & 31u); word = bitpos >> 5; }
+    bool shared;
+    DF_HD void start(uint32_t *out, uint32_t bitpos) { w = out; acc = 0; nbits = (int)(bitpos & 31u); word = bitpos >> 5; shared = true; }
     DF_HD void put(uint32_t v, int n) {
         acc |= (uint64_t)v << nbits;
         nbits += n;
-        if (nbits >= 32) { DF_ATOMIC_OR(&w[word], (uint32_t)acc); word++; acc >>= 32; nbits -= 32; }
+        if (nbits >= 32) {
+            if (shared) { DF_ATOMIC_OR(&w[word], (uint32_t)acc); shared = false; }
+            else w[word] = (uint32_t)acc;
+            word++; acc >>= 32; nbits -= 32;
+        }
     }
     DF_HD void finish() { if (nbits > 0) DF_ATOMIC_OR(&w[word], (uint32_t)acc); }
     DF_HD uint32_t bitpos() const { return word * 32u + (uint32_t)nbits; }
@@ -190,13 +273,13 @@ struct BitWriter {            // LSB-first bit packing into zero-initialised wor
 struct EmitSink {             // phase 5: the codes themselves
     const ChunkState &S;
     BitWriter bw;
-    DF_HD void literal(uint32_t v) { bw.put(S.lcode[v], S.llen[v]); }
+    DF_HD void literal(uint32_t v) { const uint32_t c = S.lc[v]; bw.put(c & 0xffffu, (int)(c >> 16)); }
     DF_HD void match(int len) {
         int sym, eb, ev;
         df_len_code(len, &sym, &eb, &ev);
-        bw.put(S.lcode[sym], S.llen[sym]);
-        if (eb) bw.put((uint32_t)ev, eb);
-        bw.put(0u, 1);                          // distance code 0 (distance 1), a 1-bit code
+        const uint32_t c = S.lc[sym];
+        // code, extra bits and the 1-bit distance code 0 (distance 1) in one go: at most 15 + 5 + 1 bits
+        bw.put((c & 0xffffu) | ((uint32_t)ev << (c >> 16)), (int)(c >> 16) + eb + 1);
     }
 };
 
@@ -272,11 +355,12 @@ DF_HD void df_canonical(const uint8_t *len, int n, int maxbits, uint16_t *code) 
     for (int s = 0; s < n; s++) code[s] = len[s] ? (uint16_t)df_reverse(next[len[s]]++, len[s]) : 0;
 }
 
-// Thread 0: codes from the frequencies, then the dynamic-block header into out_w (RFC 1951 3.2.7).
+// Thread 0: codes from the frequencies, then the dynamic-block header into hdr_w (RFC 1951 3.2.7).
 DF_HD void df_build_block_header(ChunkState &S) {
     S.freq[256] = 1;                                           // end of block
     df_code_lengths(S, S.freq, DF_NLIT, 15, S.llen);
     df_canonical(S.llen, DF_NLIT, 15, S.lcode);
+    for (int k = 0; k < DF_NLIT; k++) S.lc[k] = (uint32_t)S.lcode[k] | ((uint32_t)S.llen[k] << 16);
     int hlit = DF_NLIT;
     while (hlit > 257 && S.llen[hlit - 1] == 0) hlit--;
     const int dlen0 = S.nmatch ? 1 : 0;                        // one distance code; 0 bits = "no distances at all"
@@ -312,8 +396,9 @@ DF_HD void df_build_block_header(ChunkState &S) {
     const uint8_t order[DF_NCL] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
     int hclen = DF_NCL;
     while (hclen > 4 && S.cllen[order[hclen - 1]] == 0) hclen--;
+    for (int k = 0; k < DF_HDR_WORDS; k++) S.hdr_w[k] = 0;
     BitWriter bw;
-    bw.start(S.out_w, 0);
+    bw.start(S.hdr_w, 0);
     bw.put(0u, 1);                                             // BFINAL = 0: the stream is closed by the stored block
     bw.put(2u, 2);                                             // BTYPE = 10, dynamic Huffman
     bw.put((uint32_t)(hlit - 257), 5);
@@ -339,9 +424,9 @@ DF_HD void df_plan(ChunkState &S, int n, uint32_t token_bits) {
 }
 
 // Thread 0, last: the empty stored block that byte-aligns the chunk (BFINAL on the last chunk of a text block).
-DF_HD uint32_t df_close(ChunkState &S, int is_last) {
+DF_HD uint32_t df_close(const ChunkState &S, uint32_t *out, int is_last) {
     BitWriter bw;
-    bw.start(S.out_w, S.end_bits);
+    bw.start(out, S.end_bits);
     bw.put(is_last ? 1u : 0u, 1);
     bw.put(0u, 2);
     uint32_t pos = bw.bitpos();
@@ -349,42 +434,42 @@ DF_HD uint32_t df_close(ChunkState &S, int is_last) {
     if (pad) bw.put(0u, pad);
     bw.put(0x0000u, 16);
     bw.put(0xFFFFu, 16);
-    bw.finish();
+    if (bw.nbits > 0) DF_ATOMIC_OR(&bw.w[bw.word], (uint32_t)bw.acc);
     return bw.bitpos() / 8;
 }
 
 // Thread 0: Adler-32 pieces of the chunk from the slices' sums.
 DF_HD void df_chunk_sums(const ChunkState &S, int n, int nact, uint32_t *sum_a, uint32_t *sum_b) {
-    uint64_t a = 0, b = 0;
+    uint64_t a = 0, b = 0;                                     // <= 256 * 2^32 each: no overflow, one reduction at the end
     for (int t = 0; t < nact; t++) {
         const uint64_t after = (uint64_t)(n - t * DF_SLICE - S.slen[t]);
         a += S.sa[t];
-        b = (b + S.sb[t] + after * S.sa[t]) % DF_ADLER;
+        b += S.sb[t] + after * S.sa[t];
     }
     *sum_a = (uint32_t)(a % DF_ADLER);
-    *sum_b = (uint32_t)b;
+    *sum_b = (uint32_t)(b % DF_ADLER);
 }
 
-// Stored block (BTYPE 00) for a chunk that does not compress: 5 bytes + the text.
-DF_HD void df_stored_header(ChunkState &S, int n, int is_last) {
-    uint8_t *o = (uint8_t *)S.out_w;
+// Stored block (BTYPE 00) for a chunk that does not compress: 5 bytes + the text, straight into the slot.
+DF_HD void df_stored_header(uint8_t *o, int n, int is_last) {
     o[0] = is_last ? 1 : 0;
     o[1] = (uint8_t)(n & 255); o[2] = (uint8_t)(n >> 8);
     o[3] = (uint8_t)(~n & 255); o[4] = (uint8_t)((~n >> 8) & 255);
 }
-DF_HD void df_stored_copy(ChunkState &S, int t) {
-    uint8_t *o = (uint8_t *)S.out_w + 5;
+DF_HD void df_stored_copy(const ChunkState &S, uint8_t *o, int t) {
     const int base = t * DF_SLICE;
-    for (int i = 0; i < S.slen[t]; i++) o[base + i] = (uint8_t)df_byte(S, base + i);
+    for (int i = 0; i < S.slen[t]; i++) o[5 + base + i] = (uint8_t)df_byte(S, base + i);
 }
 
 #ifdef __CUDACC__
 // One CTA per chunk.  text: the quality text of all blocks; blk_off[nblocks + 1]: byte offsets of the blocks in it;
 // chunk_first[nblocks + 1]: first chunk of every block; chunk_block[nchunks]; slots: nchunks x DF_SLOT bytes.
-__global__ void __launch_bounds__(DF_THREADS) k_deflate_chunks(const uint8_t *__restrict__ text, const uint64_t *__restrict__ blk_off,
-                                                                const uint32_t *__restrict__ chunk_first,
-                                                                const uint32_t *__restrict__ chunk_block, uint8_t *__restrict__ slots,
-                                                                ChunkMeta *__restrict__ meta) {
+// Shared memory holds the text of the chunk and the small tables only (2 CTAs per SM); the bits go straight to the
+// chunk's slot in global memory, whose used part is zeroed first.
+__global__ void __launch_bounds__(DF_THREADS, 2) k_deflate_chunks(const uint8_t *__restrict__ text, const uint64_t *__restrict__ blk_off,
+                                                                   const uint32_t *__restrict__ chunk_first,
+                                                                   const uint32_t *__restrict__ chunk_block, uint8_t *__restrict__ slots,
+                                                                   ChunkMeta *__restrict__ meta) {
     extern __shared__ __align__(16) unsigned char df_smem[];
     ChunkState &S = *reinterpret_cast<ChunkState *>(df_smem);
     const int t = threadIdx.x;
@@ -393,6 +478,7 @@ __global__ void __launch_bounds__(DF_THREADS) k_deflate_chunks(const uint8_t *__
     const int n = (int)min((uint64_t)DF_CHUNK, blk_off[b + 1] - start);
     const int is_last = (c + 1 == chunk_first[b + 1]);
     const int nact = (n + DF_SLICE - 1) / DF_SLICE;
+    uint32_t *slot = (uint32_t *)(slots + (uint64_t)c * DF_SLOT);
 
     // text -> shared memory, realigned to words with funnel shifts (block starts are not aligned)
     {
@@ -403,7 +489,6 @@ __global__ void __launch_bounds__(DF_THREADS) k_deflate_chunks(const uint8_t *__
             uint32_t lo = g[w], hi = sh ? g[w + 1] : 0u;       // hi stays inside the allocation: callers pad the text by 8 bytes
             S.in_w[w] = __funnelshift_r(lo, hi, sh);
         }
-        for (int w = t; w < DF_OUT_WORDS; w += DF_THREADS) S.out_w[w] = 0;
         for (int w = t; w < DF_NLIT + 2; w += DF_THREADS) S.freq[w] = 0;
         if (t == 0) S.nmatch = 0;
     }
@@ -431,29 +516,26 @@ __global__ void __launch_bounds__(DF_THREADS) k_deflate_chunks(const uint8_t *__
     if (t == 0) df_plan(S, n, total);
     __syncthreads();
     if (!S.stored) {
+        const int nw = (int)((S.end_bits + 3 + 7 + 32) / 32 + 1);          // tokens + closing stored block
+        for (int w = t; w < nw; w += DF_THREADS) slot[w] = 0;
+        __syncthreads();
+        for (int w = t; w < (int)((S.hdr_bits + 31) / 32); w += DF_THREADS) atomicOr(&slot[w], S.hdr_w[w]);
         EmitSink sink{S};
-        sink.bw.start(S.out_w, S.hdr_bits + excl);
+        sink.bw.start(slot, S.hdr_bits + excl);
         df_slice_tokens(S, t, nact, sink);
         if (t == nact - 1) sink.bw.put(S.lcode[256], S.llen[256]);
         sink.bw.finish();
     } else {
-        if (t == 0) df_stored_header(S, n, is_last);
-        df_stored_copy(S, t);
+        if (t == 0) df_stored_header((uint8_t *)slot, n, is_last);
+        df_stored_copy(S, (uint8_t *)slot, t);
     }
     __syncthreads();
     if (t == 0) {
         ChunkMeta m;
-        m.nbytes = S.stored ? (uint32_t)n + 5u : df_close(S, is_last);
+        m.nbytes = S.stored ? (uint32_t)n + 5u : df_close(S, slot, is_last);
         m.n = (uint32_t)n;
         df_chunk_sums(S, n, nact, &m.sum_a, &m.sum_b);
         meta[c] = m;
-        S.end_bits = m.nbytes;                                  // reused: bytes to copy out
-    }
-    __syncthreads();
-    {
-        uint32_t *dst = (uint32_t *)(slots + (uint64_t)c * DF_SLOT);
-        const int nw = (int)(S.end_bits + 3) / 4;
-        for (int w = t; w < nw; w += DF_THREADS) dst[w] = S.out_w[w];
     }
 }
 

@@ -31,6 +31,8 @@ int main(int argc, char **argv) {
         const int is_last = c + 1 == nchunks, nact = (n + DF_SLICE - 1) / DF_SLICE;
         memset(&S, 0, sizeof S);
         memcpy(S.in_w, text.data() + c * DF_CHUNK, (size_t)n);
+        std::vector<uint32_t> slotv(DF_SLOT / 4, 0xdeadbeefu);         // like the device slot: garbage until zeroed
+        uint32_t *slot = slotv.data();
         for (int t = 0; t < DF_THREADS; t++) df_summary(S, t, n);
         for (int t = 0; t < DF_THREADS; t++) { CountSink sink{S}; df_slice_tokens(S, t, nact, sink); }
         df_build_block_header(S);
@@ -44,24 +46,27 @@ int main(int argc, char **argv) {
         }
         df_plan(S, n, total);
         if (!S.stored) {
+            const int nw = (int)((S.end_bits + 3 + 7 + 32) / 32 + 1);
+            for (int w = 0; w < nw; w++) slot[w] = 0;
+            for (int w = 0; w < (int)((S.hdr_bits + 31) / 32); w++) slot[w] |= S.hdr_w[w];
             for (int t = 0; t < DF_THREADS; t++) {
                 EmitSink sink{S};
-                sink.bw.start(S.out_w, S.hdr_bits + S.bits[t]);
+                sink.bw.start(slot, S.hdr_bits + S.bits[t]);
                 df_slice_tokens(S, t, nact, sink);
                 if (t == nact - 1) sink.bw.put(S.lcode[256], S.llen[256]);
                 sink.bw.finish();
             }
         } else {
-            df_stored_header(S, n, is_last);
-            for (int t = 0; t < DF_THREADS; t++) df_stored_copy(S, t);
+            df_stored_header((uint8_t *)slot, n, is_last);
+            for (int t = 0; t < DF_THREADS; t++) df_stored_copy(S, (uint8_t *)slot, t);
             stored_chunks++;
         }
-        const uint32_t nbytes = S.stored ? (uint32_t)n + 5u : df_close(S, is_last);
+        const uint32_t nbytes = S.stored ? (uint32_t)n + 5u : df_close(S, slot, is_last);
         uint32_t sa, sb;
         df_chunk_sums(S, n, nact, &sa, &sb);
         B = (B + (uint64_t)n % DF_ADLER * A + sb) % DF_ADLER;
         A = (A + sa) % DF_ADLER;
-        out.insert(out.end(), (uint8_t *)S.out_w, (uint8_t *)S.out_w + nbytes);
+        out.insert(out.end(), (uint8_t *)slot, (uint8_t *)slot + nbytes);
     }
     if (nchunks == 0) { const uint8_t e[5] = {1, 0, 0, 0xff, 0xff}; out.insert(out.end(), e, e + 5); }
     const uint32_t ad = (uint32_t)((B << 16) | A);
