@@ -230,7 +230,9 @@ def algorithmic_bytes(kernel, st):
         return st["nsym"] * 8.0 + NB
     if kernel == "k_range_encode":    # read the 17-byte record of every symbol, write the output bytes
         return st["nsym"] * 17.0 + st["dna_bytes"]
-    if kernel == "k_deflate_chunks":  # read the quality text once, write the compressed chunk once
+    if kernel == "k_deflate_count":   # read the quality text once (frequencies and Adler sums are small)
+        return st["qual_bytes"]
+    if kernel == "k_deflate_emit":    # read the quality text once, write the compressed chunk once
         return st["qual_bytes"] + st.get("qual_z_bytes", 0.0)
     if kernel == "k_deflate_gather":  # move the compressed chunks to their place
         return 2.0 * st.get("qual_z_bytes", 0.0)

@@ -10,10 +10,18 @@
 // byte-aligns the stream so that chunks can be concatenated; a second kernel lays the chunks of a block end to end
 // between the 2-byte zlib header and the Adler-32 of the text.
 //
-// The per-thread phases are plain functions over a ChunkState so that tools/deflate_sim.cpp can run the very same code
-// on the host, thread by thread, as a development check; the library only ever runs them inside k_deflate_chunks.
+// Three kernels per run, so that the serial part of a chunk (Huffman construction, ~10^4 dependent instructions) is
+// done by ONE THREAD PER CHUNK, thousands of chunks at once, instead of stalling a CTA:
+//   k_deflate_count  CTA per chunk: run structure of the text, symbol frequencies, Adler-32 pieces
+//   k_deflate_codes  thread per chunk: code lengths, canonical codes, dynamic-block header
+//   k_deflate_emit   CTA per chunk: bits of every thread's tokens, prefix sum, bits into the chunk's slot
+// then k_deflate_layout / k_deflate_gather lay the chunks of a block end to end behind the zlib header.
+//
+// The per-thread phases are plain functions over small state structs so that tools/deflate_sim.cpp can run the very
+// same code on the host, thread by thread, as a development check; the library only ever runs them in the kernels.
 #pragma once
 #include <stdint.h>
+#include <string.h>
 
 #ifdef __CUDACC__
 #define DF_HD __host__ __device__ __forceinline__
@@ -24,44 +32,67 @@
 namespace lbdeflate {
 
 constexpr int DF_THREADS = 256;
-constexpr int DF_SLICE = 252;                       // bytes per thread: 63 words, an odd stride (no bank conflicts)
+constexpr int DF_SLICE = 252;                       // bytes per thread (63 words)
 constexpr int DF_CHUNK = DF_THREADS * DF_SLICE;     // 64512 <= 65535, so a chunk also fits one stored block
 constexpr int DF_SLOT = DF_CHUNK + 64;              // bytes reserved per chunk in the scratch buffer
 constexpr int DF_NLIT = 286, DF_NCL = 19;
 constexpr uint32_t DF_ADLER = 65521u;
+constexpr int DF_HDR_WORDS = 160;                   // dynamic block header: <= 14 + 19 * 3 + 287 * 14 bits
+constexpr int DF_EQ_WORDS = 8;                      // 252 "equals its predecessor" bits per slice
+constexpr int DF_CODES_THREADS = 32;                // k_deflate_codes: chunks per CTA
 
-struct ChunkMeta {            // per chunk, written by k_deflate_chunks
+struct ChunkMeta {            // per chunk
     uint32_t nbytes;          // compressed bytes in the slot
     uint32_t sum_a, sum_b;    // byte sum and position-weighted sum of the chunk's text (Adler-32 pieces), mod 65521
     uint32_t n;               // text bytes
 };
 
-constexpr int DF_HDR_WORDS = 160;                   // dynamic block header: <= 14 + 19 * 3 + 287 * 14 bits
-constexpr int DF_EQ_WORDS = 8;                      // 252 "equals its predecessor" bits per slice
-
-struct ChunkState {
-    uint32_t in_w[DF_CHUNK / 4];
-    uint32_t hdr_w[DF_HDR_WORDS];
-    uint32_t eqm[DF_EQ_WORDS * DF_THREADS];    // [word][thread]
+// Per chunk, in global memory: what k_deflate_count hands to k_deflate_codes and that one to k_deflate_emit.
+struct HuffState {
     uint32_t freq[DF_NLIT + 2];
     uint32_t nmatch;
     uint32_t lc[DF_NLIT];                      // code | length << 16
+    uint32_t hdr_w[DF_HDR_WORDS];
+    uint32_t hdr_bits;
     uint16_t lcode[DF_NLIT];   uint8_t llen[DF_NLIT];
     uint16_t clcode[DF_NCL];   uint8_t cllen[DF_NCL];
-    uint8_t  first[DF_THREADS], last[DF_THREADS];
-    uint16_t slen[DF_THREADS], lead[DF_THREADS], trail[DF_THREADS];
-    uint32_t bits[DF_THREADS];                 // per thread: bits of its tokens, then their exclusive prefix
-    uint32_t sa[DF_THREADS], sb[DF_THREADS];
-    uint32_t hdr_bits, end_bits, stored;
-    // scratch of the Huffman construction (thread 0)
+    // scratch of the Huffman construction
     uint32_t node_w[2 * DF_NLIT];
     uint16_t node_parent[2 * DF_NLIT], order[DF_NLIT];
     uint8_t  node_depth[2 * DF_NLIT];
     uint8_t  cl_sym[DF_NLIT + 34], cl_extra[DF_NLIT + 34];
 };
 
+// Per CTA, in shared memory: the run structure of the chunk's 256 slices.
+struct ChunkState {
+    const uint8_t *text;                       // the chunk's text (global memory)
+    uint32_t eqm[DF_EQ_WORDS * DF_THREADS];    // [word][thread]
+    uint32_t freq[DF_NLIT + 2];
+    uint32_t nmatch;
+    uint32_t lc[DF_NLIT];
+    uint8_t  first[DF_THREADS], last[DF_THREADS];
+    uint16_t slen[DF_THREADS], lead[DF_THREADS], trail[DF_THREADS];
+    uint32_t bits[DF_THREADS];
+    uint32_t sa[DF_THREADS], sb[DF_THREADS];
+    uint32_t hdr_bits, end_bits, stored;
+};
+
 DF_HD int df_min(int a, int b) { return a < b ? a : b; }
-DF_HD uint32_t df_byte(const ChunkState &S, int i) { return (S.in_w[i >> 2] >> (8 * (i & 3))) & 255u; }
+DF_HD uint32_t df_byte(const ChunkState &S, int i) { return S.text[i]; }
+
+// Word k of the bytes at p (any alignment).  The device reads two aligned words (the text is padded by 8 bytes).
+DF_HD uint32_t df_word(const uint8_t *p, int k) {
+#ifdef __CUDA_ARCH__
+    const uintptr_t a = (uintptr_t)p;
+    const uint32_t *g = (const uint32_t *)(a & ~(uintptr_t)3) + k;
+    const int sh = (int)(a & 3) * 8;
+    return sh ? __funnelshift_r(g[0], g[1], sh) : g[0];
+#else
+    uint32_t w;
+    memcpy(&w, p + 4 * k, 4);
+    return w;
+#endif
+}
 
 // byte-wise helpers: device intrinsics, plain C on the host (tools/deflate_sim.cpp)
 DF_HD uint32_t df_cmpeq4(uint32_t a, uint32_t b) {          // 0xff in every byte where a and b agree
@@ -122,6 +153,16 @@ DF_HD uint32_t df_reverse(uint32_t code, int len) {
 DF_HD uint32_t &df_eq(ChunkState &S, int t, int w) { return S.eqm[w * DF_THREADS + t]; }
 DF_HD uint32_t df_eq(const ChunkState &S, int t, int w) { return S.eqm[w * DF_THREADS + t]; }
 
+// First position >= pos whose eq bit is clear (a run start), or len.
+DF_HD int df_next_start(const ChunkState &S, int t, int pos, int len) {
+    while (pos < len) {
+        const uint32_t w = ~df_eq(S, t, pos >> 5) >> (pos & 31);
+        if (w) { pos += df_ffs(w) - 1; return pos < len ? pos : len; }
+        pos = (pos | 31) + 1;
+    }
+    return len;
+}
+
 // ---- phase 1: every thread summarises its slice, a word at a time ---------------------------------------------------
 // eq bit i (i >= 1) = byte i of the slice equals byte i - 1; sums for the Adler-32; first / last byte and the lengths of
 // the first and last run, through which runs are followed across slices.
@@ -130,32 +171,36 @@ DF_HD void df_summary(ChunkState &S, int t, int n) {
     int len = n - base;
     len = len > DF_SLICE ? DF_SLICE : (len < 0 ? 0 : len);
     S.slen[t] = (uint16_t)len;
-    uint32_t eq[DF_EQ_WORDS];
-    for (int k = 0; k < DF_EQ_WORDS; k++) eq[k] = 0;
     uint32_t a = 0, b = 0, prevb = 0;
-    const int nw = (len + 3) >> 2, bw = base >> 2;
-    for (int k = 0; k < nw; k++) {
-        uint32_t w = S.in_w[bw + k];
-        const int rem = len - 4 * k;
-        if (rem < 4) w &= (1u << (8 * rem)) - 1u;
-        const uint32_t m = df_cmpeq4(w, (w << 8) | prevb);
-        uint32_t nib = (((m & 0x01010101u) * 0x01020408u) >> 24) & 15u;
-        if (k == 0) nib &= ~1u;
-        if (rem < 4) nib &= (1u << rem) - 1u;
-        eq[k >> 3] |= nib << (4 * (k & 7));
-        prevb = w >> 24;
-        const uint32_t sum = df_bytesum(w);
-        a += sum;
-        b += (uint32_t)(len - 4 * k) * sum - df_dot0123(w);
+    const int nw = (len + 3) >> 2;
+    const uint8_t *p = S.text + base;
+    for (int q = 0; q < DF_EQ_WORDS; q++) {                 // 8 words of text -> one word of eq bits
+        uint32_t cur = 0;
+        for (int kk = 0; kk < 8; kk++) {
+            const int k = 8 * q + kk;
+            if (k >= nw) break;
+            uint32_t w = df_word(p, k);
+            const int rem = len - 4 * k;
+            if (rem < 4) w &= (1u << (8 * rem)) - 1u;
+            const uint32_t m = df_cmpeq4(w, (w << 8) | prevb);
+            uint32_t nib = (((m & 0x01010101u) * 0x01020408u) >> 24) & 15u;
+            if (k == 0) nib &= ~1u;
+            if (rem < 4) nib &= (1u << rem) - 1u;
+            cur |= nib << (4 * kk);
+            prevb = w >> 24;
+            const uint32_t sum = df_bytesum(w);
+            a += sum;
+            b += (uint32_t)(len - 4 * k) * sum - df_dot0123(w);
+        }
+        df_eq(S, t, q) = cur;
     }
-    for (int k = 0; k < DF_EQ_WORDS; k++) df_eq(S, t, k) = eq[k];
     S.sa[t] = a; S.sb[t] = b;
     if (len) {
         S.first[t] = (uint8_t)df_byte(S, base);
         S.last[t] = (uint8_t)df_byte(S, base + len - 1);
-        int lead = 1, trail = 1;
-        while (lead < len && ((eq[lead >> 5] >> (lead & 31)) & 1u)) lead++;
-        while (trail < len && ((eq[(len - trail) >> 5] >> ((len - trail) & 31)) & 1u)) trail++;
+        const int lead = df_next_start(S, t, 1, len);        // bytes equal to the first one
+        int trail = 1;
+        while (trail < len && ((df_eq(S, t, (len - trail) >> 5) >> ((len - trail) & 31)) & 1u)) trail++;
         S.lead[t] = (uint16_t)lead; S.trail[t] = (uint16_t)trail;
     }
 }
@@ -178,16 +223,6 @@ DF_HD void df_run_tokens(int j0, int cnt, int L, uint32_t v, Sink &sink) {
             j++;
         }
     }
-}
-
-// First position >= pos whose eq bit is clear (a run start), or len.
-DF_HD int df_next_start(const ChunkState &S, int t, int pos, int len) {
-    while (pos < len) {
-        const uint32_t w = ~df_eq(S, t, pos >> 5) >> (pos & 31);
-        if (w) { pos += df_ffs(w) - 1; return pos < len ? pos : len; }
-        pos = (pos | 31) + 1;
-    }
-    return len;
 }
 
 // Walks the runs of slice t (extended into the neighbouring slices through the summaries) and feeds the sink.
@@ -286,7 +321,7 @@ struct EmitSink {             // phase 5: the codes themselves
 // ---- phase 3 (one thread): Huffman code lengths, canonical codes, block header ------------------------------------
 // Lengths of an optimal prefix code limited to maxbits: Huffman by two queues over the sorted leaves, depths clipped
 // to maxbits, then the Kraft sum repaired by lengthening the deepest leaves that are still shorter than maxbits.
-DF_HD void df_code_lengths(ChunkState &S, const uint32_t *freq, int n, int maxbits, uint8_t *len) {
+DF_HD void df_code_lengths(HuffState &S, const uint32_t *freq, int n, int maxbits, uint8_t *len) {
     int m = 0;
     for (int s = 0; s < n; s++) {
         len[s] = 0;
@@ -355,8 +390,8 @@ DF_HD void df_canonical(const uint8_t *len, int n, int maxbits, uint16_t *code) 
     for (int s = 0; s < n; s++) code[s] = len[s] ? (uint16_t)df_reverse(next[len[s]]++, len[s]) : 0;
 }
 
-// Thread 0: codes from the frequencies, then the dynamic-block header into hdr_w (RFC 1951 3.2.7).
-DF_HD void df_build_block_header(ChunkState &S) {
+// One thread per chunk: codes from the frequencies, then the dynamic-block header into hdr_w (RFC 1951 3.2.7).
+DF_HD void df_build_block_header(HuffState &S) {
     S.freq[256] = 1;                                           // end of block
     df_code_lengths(S, S.freq, DF_NLIT, 15, S.llen);
     df_canonical(S.llen, DF_NLIT, 15, S.lcode);
@@ -462,81 +497,100 @@ DF_HD void df_stored_copy(const ChunkState &S, uint8_t *o, int t) {
 }
 
 #ifdef __CUDACC__
-// One CTA per chunk.  text: the quality text of all blocks; blk_off[nblocks + 1]: byte offsets of the blocks in it;
-// chunk_first[nblocks + 1]: first chunk of every block; chunk_block[nchunks]; slots: nchunks x DF_SLOT bytes.
-// Shared memory holds the text of the chunk and the small tables only (2 CTAs per SM); the bits go straight to the
-// chunk's slot in global memory, whose used part is zeroed first.
-__global__ void __launch_bounds__(DF_THREADS, 2) k_deflate_chunks(const uint8_t *__restrict__ text, const uint64_t *__restrict__ blk_off,
-                                                                   const uint32_t *__restrict__ chunk_first,
-                                                                   const uint32_t *__restrict__ chunk_block, uint8_t *__restrict__ slots,
-                                                                   ChunkMeta *__restrict__ meta) {
-    extern __shared__ __align__(16) unsigned char df_smem[];
-    ChunkState &S = *reinterpret_cast<ChunkState *>(df_smem);
-    const int t = threadIdx.x;
-    const uint32_t c = blockIdx.x, b = chunk_block[c], k = c - chunk_first[b];
+struct ChunkGeom { const uint8_t *text; int n, is_last, nact; };
+__device__ __forceinline__ ChunkGeom df_geom(const uint8_t *text, const uint64_t *blk_off, const uint32_t *chunk_first,
+                                             const uint32_t *chunk_block, uint32_t c) {
+    const uint32_t b = chunk_block[c], k = c - chunk_first[b];
     const uint64_t start = blk_off[b] + (uint64_t)k * DF_CHUNK;
-    const int n = (int)min((uint64_t)DF_CHUNK, blk_off[b + 1] - start);
-    const int is_last = (c + 1 == chunk_first[b + 1]);
-    const int nact = (n + DF_SLICE - 1) / DF_SLICE;
-    uint32_t *slot = (uint32_t *)(slots + (uint64_t)c * DF_SLOT);
+    ChunkGeom g;
+    g.text = text + start;
+    g.n = (int)min((uint64_t)DF_CHUNK, blk_off[b + 1] - start);
+    g.is_last = (c + 1 == chunk_first[b + 1]);
+    g.nact = (g.n + DF_SLICE - 1) / DF_SLICE;
+    return g;
+}
 
-    // text -> shared memory, realigned to words with funnel shifts (block starts are not aligned)
-    {
-        const uintptr_t addr = (uintptr_t)(text + start);
-        const uint32_t *g = (const uint32_t *)(addr & ~(uintptr_t)3);
-        const int sh = (int)(addr & 3) * 8, nw = (n + 3) / 4;
-        for (int w = t; w < nw; w += DF_THREADS) {
-            uint32_t lo = g[w], hi = sh ? g[w + 1] : 0u;       // hi stays inside the allocation: callers pad the text by 8 bytes
-            S.in_w[w] = __funnelshift_r(lo, hi, sh);
-        }
-        for (int w = t; w < DF_NLIT + 2; w += DF_THREADS) S.freq[w] = 0;
-        if (t == 0) S.nmatch = 0;
+// text: the quality text of all blocks (padded by 8 bytes); blk_off[nblocks + 1]: byte offsets of the blocks in it;
+// chunk_first[nblocks + 1]: first chunk of every block; chunk_block[nchunks].
+__global__ void __launch_bounds__(DF_THREADS) k_deflate_count(const uint8_t *__restrict__ text, const uint64_t *__restrict__ blk_off,
+                                                               const uint32_t *__restrict__ chunk_first,
+                                                               const uint32_t *__restrict__ chunk_block, HuffState *__restrict__ huff,
+                                                               ChunkMeta *__restrict__ meta) {
+    __shared__ ChunkState S;
+    const int t = threadIdx.x;
+    const uint32_t c = blockIdx.x;
+    const ChunkGeom g = df_geom(text, blk_off, chunk_first, chunk_block, c);
+    if (t == 0) { S.text = g.text; S.nmatch = 0; }
+    for (int w = t; w < DF_NLIT + 2; w += DF_THREADS) S.freq[w] = 0;
+    __syncthreads();
+    df_summary(S, t, g.n);
+    __syncthreads();
+    { CountSink sink{S}; df_slice_tokens(S, t, g.nact, sink); }
+    __syncthreads();
+    HuffState &H = huff[c];
+    for (int w = t; w < DF_NLIT + 2; w += DF_THREADS) H.freq[w] = S.freq[w];
+    if (t == 0) {
+        H.nmatch = S.nmatch;
+        ChunkMeta m;
+        m.nbytes = 0;
+        m.n = (uint32_t)g.n;
+        df_chunk_sums(S, g.n, g.nact, &m.sum_a, &m.sum_b);
+        meta[c] = m;
     }
+}
+
+__global__ void __launch_bounds__(DF_CODES_THREADS) k_deflate_codes(HuffState *__restrict__ huff, uint32_t nchunks) {
+    const uint32_t c = blockIdx.x * DF_CODES_THREADS + threadIdx.x;
+    if (c < nchunks) df_build_block_header(huff[c]);
+}
+
+// slots: nchunks x DF_SLOT bytes.  The bits go straight to the chunk's slot, whose used part is zeroed first.
+__global__ void __launch_bounds__(DF_THREADS) k_deflate_emit(const uint8_t *__restrict__ text, const uint64_t *__restrict__ blk_off,
+                                                              const uint32_t *__restrict__ chunk_first,
+                                                              const uint32_t *__restrict__ chunk_block, const HuffState *__restrict__ huff,
+                                                              uint8_t *__restrict__ slots, ChunkMeta *__restrict__ meta) {
+    __shared__ ChunkState S;
+    const int t = threadIdx.x;
+    const uint32_t c = blockIdx.x;
+    const ChunkGeom g = df_geom(text, blk_off, chunk_first, chunk_block, c);
+    const HuffState &H = huff[c];
+    uint32_t *slot = (uint32_t *)(slots + (uint64_t)c * DF_SLOT);
+    if (t == 0) { S.text = g.text; S.hdr_bits = H.hdr_bits; }
+    for (int w = t; w < DF_NLIT; w += DF_THREADS) S.lc[w] = H.lc[w];
     __syncthreads();
-    df_summary(S, t, n);
-    __syncthreads();
-    { CountSink sink{S}; df_slice_tokens(S, t, nact, sink); }
-    __syncthreads();
-    if (t == 0) df_build_block_header(S);
+    df_summary(S, t, g.n);
     __syncthreads();
     uint32_t mybits;
     {
         BitCountSink sink{S, 0u};
-        df_slice_tokens(S, t, nact, sink);
-        mybits = sink.bits + (t == nact - 1 ? S.llen[256] : 0u);
+        df_slice_tokens(S, t, g.nact, sink);
+        mybits = sink.bits + (t == g.nact - 1 ? (S.lc[256] >> 16) : 0u);
     }
-    // exclusive prefix of the per-thread bit counts
-    uint32_t incl = mybits;
+    uint32_t incl = mybits;                                    // exclusive prefix of the per-thread bit counts
     for (int d = 1; d < 32; d <<= 1) { uint32_t v = __shfl_up_sync(0xffffffffu, incl, d); if ((t & 31) >= d) incl += v; }
     if ((t & 31) == 31) S.bits[t >> 5] = incl;
     __syncthreads();
     uint32_t warp_base = 0, total = 0;
     for (int w = 0; w < DF_THREADS / 32; w++) { uint32_t v = S.bits[w]; if (w < (t >> 5)) warp_base += v; total += v; }
     const uint32_t excl = warp_base + incl - mybits;
-    if (t == 0) df_plan(S, n, total);
+    if (t == 0) df_plan(S, g.n, total);
     __syncthreads();
     if (!S.stored) {
         const int nw = (int)((S.end_bits + 3 + 7 + 32) / 32 + 1);          // tokens + closing stored block
         for (int w = t; w < nw; w += DF_THREADS) slot[w] = 0;
         __syncthreads();
-        for (int w = t; w < (int)((S.hdr_bits + 31) / 32); w += DF_THREADS) atomicOr(&slot[w], S.hdr_w[w]);
+        for (int w = t; w < (int)((S.hdr_bits + 31) / 32); w += DF_THREADS) atomicOr(&slot[w], H.hdr_w[w]);
         EmitSink sink{S};
         sink.bw.start(slot, S.hdr_bits + excl);
-        df_slice_tokens(S, t, nact, sink);
-        if (t == nact - 1) sink.bw.put(S.lcode[256], S.llen[256]);
+        df_slice_tokens(S, t, g.nact, sink);
+        if (t == g.nact - 1) sink.bw.put(S.lc[256] & 0xffffu, (int)(S.lc[256] >> 16));
         sink.bw.finish();
     } else {
-        if (t == 0) df_stored_header((uint8_t *)slot, n, is_last);
+        if (t == 0) df_stored_header((uint8_t *)slot, g.n, g.is_last);
         df_stored_copy(S, (uint8_t *)slot, t);
     }
     __syncthreads();
-    if (t == 0) {
-        ChunkMeta m;
-        m.nbytes = S.stored ? (uint32_t)n + 5u : df_close(S, slot, is_last);
-        m.n = (uint32_t)n;
-        df_chunk_sums(S, n, nact, &m.sum_a, &m.sum_b);
-        meta[c] = m;
-    }
+    if (t == 0) meta[c].nbytes = S.stored ? (uint32_t)g.n + 5u : df_close(S, slot, g.is_last);
 }
 
 // Layout of the zlib streams: per block the offsets of its chunks, its size (2 + chunks + 4) and its Adler-32; then

@@ -121,7 +121,7 @@ struct leon_ctx {
     uint64_t nblocks = 0, dna_nbytes = 0, dict_nbytes = 0, nsym_total = 0;
     PinBuf h_dna, h_bs, h_dict, h_qual, h_qsizes, h_apos, h_aaddr;
     // zlib streams of the quality blocks written on the device (deflate.cuh)
-    DevBuf d_qz_blkoff, d_qz_first, d_qz_cblock, d_qz_slots, d_qz_meta, d_qz_coff, d_qz_bsize, d_qz_boff, d_qz_adler, d_qz_out;
+    DevBuf d_qz_huff, d_qz_blkoff, d_qz_first, d_qz_cblock, d_qz_slots, d_qz_meta, d_qz_coff, d_qz_bsize, d_qz_boff, d_qz_adler, d_qz_out;
     PinBuf h_qz_tables, h_qz_boff, h_qz_out, h_qz_sizes;
     cudaEvent_t ev_qz = nullptr;
     uint32_t qz_nchunks = 0;
@@ -876,10 +876,15 @@ void deflate_quals(leon_ctx *c)
     c->d_qz_boff.reserve((nb + 1) * 8 + 16);
     c->d_qz_adler.reserve(nb * 4 + 16);
     c->d_qz_out.reserve(at + nchunks * 16 + nb * 8 + 64);       // every chunk is at worst stored: text + 5 bytes
-    CUDA_TRY(cudaFuncSetAttribute(k_deflate_chunks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ChunkState)));
+    c->d_qz_huff.reserve(nchunks * sizeof(HuffState) + 16);
     if (nchunks) {
-        LB_TIMED(c->kt, "k_deflate_chunks", s3, LB_LAUNCH(c->lc, k_deflate_chunks, (unsigned)nchunks, DF_THREADS, sizeof(ChunkState), s3,
-                 c->d_qout.as<uint8_t>(), d_blk_off, d_first, d_cblock, c->d_qz_slots.as<uint8_t>(), c->d_qz_meta.as<ChunkMeta>()));
+        LB_TIMED(c->kt, "k_deflate_count", s3, LB_LAUNCH(c->lc, k_deflate_count, (unsigned)nchunks, DF_THREADS, 0, s3,
+                 c->d_qout.as<uint8_t>(), d_blk_off, d_first, d_cblock, c->d_qz_huff.as<HuffState>(), c->d_qz_meta.as<ChunkMeta>()));
+        LB_TIMED(c->kt, "k_deflate_codes", s3, LB_LAUNCH(c->lc, k_deflate_codes, (unsigned)((nchunks + DF_CODES_THREADS - 1) / DF_CODES_THREADS),
+                 DF_CODES_THREADS, 0, s3, c->d_qz_huff.as<HuffState>(), (uint32_t)nchunks));
+        LB_TIMED(c->kt, "k_deflate_emit", s3, LB_LAUNCH(c->lc, k_deflate_emit, (unsigned)nchunks, DF_THREADS, 0, s3,
+                 c->d_qout.as<uint8_t>(), d_blk_off, d_first, d_cblock, c->d_qz_huff.as<HuffState>(), c->d_qz_slots.as<uint8_t>(),
+                 c->d_qz_meta.as<ChunkMeta>()));
         LB_LAUNCH(c->lc, k_deflate_layout, 1, 1024, 0, s3, c->d_qz_meta.as<ChunkMeta>(), d_first, (uint32_t)nb, c->d_qz_coff.as<uint32_t>(),
                   c->d_qz_bsize.as<uint64_t>(), c->d_qz_boff.as<uint64_t>(), c->d_qz_adler.as<uint32_t>());
         LB_TIMED(c->kt, "k_deflate_gather", s3, LB_LAUNCH(c->lc, k_deflate_gather, (unsigned)nchunks, 256, 0, s3, c->d_qz_slots.as<uint8_t>(),
