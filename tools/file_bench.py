@@ -51,6 +51,7 @@ def main():
     ap.add_argument("--fastq", action="store_true")
     ap.add_argument("--flags", default="")
     ap.add_argument("--runs", type=int, default=3)
+    ap.add_argument("--inproc", type=int, default=0, help="also call leon_compress_file N times inside this process (CUDA context already up)")
     ap.add_argument("--no-reference", action="store_true")
     ap.add_argument("--no-decode", action="store_true")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "file_bench.json"))
@@ -81,6 +82,19 @@ def main():
             runs.append(dt)
             print("ours run %d: %.3f s\n%s\n%s" % (r, dt, p.stdout.strip(), p.stderr.strip()), flush=True)
         res["ours_wall_s"] = runs
+        if a.inproc:
+            import leon_b200
+            kw = dict(lossless="-lossless" in flags, noheader="-noheader" in flags, noqual="-noqual" in flags, seq_only="-seq-only" in flags)
+            res["inproc"] = []
+            for r in range(a.inproc):
+                t = time.time()
+                st = leon_b200.compress_file(inp, inp + ".inproc.leon", **kw)
+                dt = time.time() - t
+                res["inproc"].append({"wall_s": dt, "parse_ms": st["parse_ms"], "compress_ms": st["compress_ms"], "header_ms": st["header_ms"],
+                                      "write_ms": st["write_ms"], "gpu_total_ms": st["gpu"]["total_ms"]})
+                print("in-process call %d: %.3f s  (read %.0f ms, compress %.0f ms [GPU path %.0f ms, headers %.0f ms], write %.0f ms)" % (
+                    r, dt, st["parse_ms"], st["compress_ms"], st["gpu"]["total_ms"], st["header_ms"], st["write_ms"]), flush=True)
+            assert open(inp + ".inproc.leon", "rb").read() == open(inp + ".leon", "rb").read()
         res["ours_stdout"] = p.stdout.strip().splitlines()
         res["ours_output_bytes"] = os.path.getsize(inp + ".leon")
         if not a.no_reference and os.path.exists(REF):
