@@ -880,8 +880,9 @@ void deflate_quals(leon_ctx *c)
     if (nchunks) {
         LB_TIMED(c->kt, "k_deflate_count", s3, LB_LAUNCH(c->lc, k_deflate_count, (unsigned)nchunks, DF_THREADS, 0, s3,
                  c->d_qout.as<uint8_t>(), d_blk_off, d_first, d_cblock, c->d_qz_huff.as<HuffState>(), c->d_qz_meta.as<ChunkMeta>()));
-        LB_TIMED(c->kt, "k_deflate_codes", s3, LB_LAUNCH(c->lc, k_deflate_codes, (unsigned)((nchunks + DF_CODES_THREADS - 1) / DF_CODES_THREADS),
-                 DF_CODES_THREADS, 0, s3, c->d_qz_huff.as<HuffState>(), (uint32_t)nchunks));
+        CUDA_TRY(cudaFuncSetAttribute(k_deflate_codes, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(DF_CODES_CHUNKS * sizeof(HuffState))));
+        LB_TIMED(c->kt, "k_deflate_codes", s3, LB_LAUNCH(c->lc, k_deflate_codes, (unsigned)((nchunks + DF_CODES_CHUNKS - 1) / DF_CODES_CHUNKS),
+                 DF_CODES_CHUNKS * 32, DF_CODES_CHUNKS * sizeof(HuffState), s3, c->d_qz_huff.as<HuffState>(), (uint32_t)nchunks));
         LB_TIMED(c->kt, "k_deflate_emit", s3, LB_LAUNCH(c->lc, k_deflate_emit, (unsigned)nchunks, DF_THREADS, 0, s3,
                  c->d_qout.as<uint8_t>(), d_blk_off, d_first, d_cblock, c->d_qz_huff.as<HuffState>(), c->d_qz_slots.as<uint8_t>(),
                  c->d_qz_meta.as<ChunkMeta>()));
