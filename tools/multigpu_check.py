@@ -28,7 +28,7 @@ def run_case(rank, world, k, L, nreads, rpb, fastq, seed, genome):
     from oracle import oracle_py as O
     g = synth.make_genome(genome, seed)
     bases, offs, quals = synth.sample_reads(g, nreads, L, seed + 100, n_rate=0.0005, with_quals=fastq)
-    eng = leon_b200.Leon(kmer_size=k, reads_per_block=rpb, has_qual=fastq, device=rank)
+    eng = leon_b200.Leon(kmer_size=k, reads_per_block=rpb, has_qual=fastq, device=rank, qual_zlib_on_device=fastq)
     uid = [leon_b200.Leon.comm_unique_id() if rank == 0 else None]
     dist.broadcast_object_list(uid, src=0)
     eng.comm_init(rank, world, uid[0])
@@ -51,6 +51,15 @@ def run_case(rank, world, k, L, nreads, rpb, fastq, seed, genome):
                 ok = False
                 d = np.nonzero(m[key][:min(len(m[key]), len(ref[key]))] != ref[key][:min(len(m[key]), len(ref[key]))])[0]
                 print("  MISMATCH %s: len %d/%d first diff %s" % (key, len(m[key]), len(ref[key]), d[:1]))
+        if fastq:       # quality blocks deflated on each rank's GPU: merged streams must inflate to the reference's text
+            import zlib
+            at, parts = 0, []
+            for nz in m["qual_z_block_sizes"]:
+                parts.append(zlib.decompress(m["qual_z"][at:at + int(nz)].tobytes()))
+                at += int(nz)
+            if b"".join(parts) != ref["qual_text"].tobytes() or [len(x) for x in parts] != [int(x) for x in ref["qual_block_sizes"]]:
+                ok = False
+                print("  MISMATCH inflated qual_z")
         am = ref["anchor_pos"] >= 0
         if not np.array_equal(m["anchor_addr"][am], ref["anchor_addr"][am]):
             ok = False
