@@ -14,10 +14,10 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-fi
 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file gpurun_out/launches_fastq.csv \
     python bench.py --fastq --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_launches_fastq.log 2>&1; echo "ncu launches fastq rc=$?"
 ncu --set full --clock-control none --import-source on \
-    -k 'regex:k_range_encode|k_walk|k_msd_scatter|k_msd_hist|k_bucket_count|k_chunk_ranks|k_extract|k_anchor_lookup|k_part_scatter' -c 20 -f -o gpurun_out/full \
+    -k 'regex:k_range_encode|k_walk|k_msd_scatter|k_msd_hist|k_bucket_count|k_chunk_ranks|k_extract|k_anchor_lookup|k_part_scatter' -c 12 -f -o gpurun_out/full \
     python bench.py --steps 1 --warmup 0 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1; echo "ncu full rc=$?"
 ncu --set full --clock-control none --import-source on \
-    -k 'regex:k_quals|k_deflate_count|k_deflate_codes|k_deflate_emit|k_deflate_gather' -c 10 -f -o gpurun_out/full_fastq \
+    -k 'regex:k_quals|k_deflate_count|k_deflate_codes|k_deflate_emit|k_deflate_gather' -c 6 -f -o gpurun_out/full_fastq \
     python bench.py --fastq --steps 1 --warmup 0 --no-cpu-baseline > gpurun_out/ncu_full_fastq.log 2>&1; echo "ncu full fastq rc=$?"
 python tools/file_bench.py --inproc 3 --out gpurun_out/file_bench_fasta.json > gpurun_out/file_bench_fasta.log 2>&1; echo "file bench fasta rc=$?"
 python tools/file_bench.py --fastq --inproc 3 --out gpurun_out/file_bench_fastq.json > gpurun_out/file_bench_fastq.log 2>&1; echo "file bench fastq rc=$?"
