@@ -206,6 +206,17 @@ typedef struct leon_container_info {
 } leon_container_info;
 int leon_write_container(const char *path, const leon_result *result, const leon_container_info *info);
 
+/* Reading a `.leon` container (the decompression side; host only).  Handles the files written by leon_write_container
+ * and the ones the reference writes through the HDF5 library (chunked, extendible, unfiltered datasets,
+ * storage/impl/CollectionHDF5Patch.hpp:164-200).  Dataset paths are like "leon/dna/dna_0"; the returned pointers stay
+ * valid until leon_container_close(). */
+typedef struct leon_container leon_container;
+int  leon_container_open(const char *path, leon_container **out);
+void leon_container_close(leon_container *c);
+int  leon_container_has(leon_container *c, const char *path);                       /* 1 when the group or dataset exists */
+int  leon_container_dataset(leon_container *c, const char *path, const uint8_t **data, uint64_t *nbytes);
+int  leon_container_attr(leon_container *c, const char *dataset_path, const char *name, const char **value);
+
 /* File level: `leon -file X -c` end to end (C/Leon.cpp:342-470 executeCompression).  Reads the FASTA/FASTQ file like the
  * reference's bank (bank/impl/BankFasta.cpp:484-570; format from the file name as C/Leon.cpp:392-416), codes the header
  * stream on host threads while the GPU codes the sequence stream, writes `out_path` (NULL: in_path + ".leon").

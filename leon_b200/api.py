@@ -13,6 +13,7 @@ ABI_SYMBOLS = [
     "leon_get_timings", "leon_get_kernel_times", "leon_set_stream", "leon_comm_unique_id", "leon_comm_init",
     "leon_comm_batch_reads", "leon_debug_bloom_query", "leon_debug_hashes", "leon_debug_fetch", "leon_write_container",
     "leon_headers_encode", "leon_headers_free", "leon_compress_file", "leon_read_file", "leon_file_reads_free",
+    "leon_container_open", "leon_container_close", "leon_container_has", "leon_container_dataset", "leon_container_attr",
 ]
 
 
@@ -138,6 +139,12 @@ def load_library(path=LIB_PATH):
     L.leon_read_file.argtypes = [C.c_char_p, C.c_int, C.c_int, C.POINTER(C.POINTER(FileReads))]
     L.leon_file_reads_free.argtypes = [C.POINTER(FileReads)]
     L.leon_file_reads_free.restype = None
+    L.leon_container_open.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
+    L.leon_container_close.argtypes = [C.c_void_p]
+    L.leon_container_close.restype = None
+    L.leon_container_has.argtypes = [C.c_void_p, C.c_char_p]
+    L.leon_container_dataset.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.POINTER(C.c_uint8)), C.POINTER(C.c_uint64)]
+    L.leon_container_attr.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.POINTER(C.c_char_p)]
     _lib = L
     return L
 
@@ -147,6 +154,45 @@ def _arr(ptr, n, dtype, copy=True):
         return np.zeros(0, dtype)
     a = np.ctypeslib.as_array(ptr, shape=(int(n),))
     return a.astype(dtype, copy=True) if copy else a
+
+
+class Container:
+    """Reader of a `.leon` container (ours or one written by the reference through HDF5)."""
+
+    def __init__(self, path):
+        self.L = load_library()
+        self.h = C.c_void_p()
+        rc = self.L.leon_container_open(os.fsencode(path), C.byref(self.h))
+        if rc != 0:
+            raise LeonError(rc, self.L.leon_last_error(None).decode())
+
+    def close(self):
+        if self.h:
+            self.L.leon_container_close(self.h)
+            self.h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def has(self, path):
+        return bool(self.L.leon_container_has(self.h, path.encode()))
+
+    def dataset(self, path):
+        p, n = C.POINTER(C.c_uint8)(), C.c_uint64()
+        rc = self.L.leon_container_dataset(self.h, path.encode(), C.byref(p), C.byref(n))
+        if rc != 0:
+            raise LeonError(rc, self.L.leon_last_error(None).decode())
+        return _arr(p, n.value, np.uint8)
+
+    def attr(self, dataset_path, name):
+        v = C.c_char_p()
+        rc = self.L.leon_container_attr(self.h, dataset_path.encode(), name.encode(), C.byref(v))
+        if rc != 0:
+            raise LeonError(rc, self.L.leon_last_error(None).decode())
+        return v.value.decode()
 
 
 def read_file(path, want_quals=True, want_headers=True):
