@@ -217,6 +217,24 @@ int  leon_container_has(leon_container *c, const char *path);                   
 int  leon_container_dataset(leon_container *c, const char *path, const uint8_t **data, uint64_t *nbytes);
 int  leon_container_attr(leon_container *c, const char *dataset_path, const char *name, const char **value);
 
+/* Decompression of the sequence stream (C/DnaCoder.cpp:1221-1622, C/Leon.cpp:1948-2015): the datasets
+ * of a container (leon_container_dataset) in, the reads of every block out as text, one sequence per line.  Blocks are
+ * decoded by nthreads host threads (0 = all cores): range decoding and the Bloom walk of a block are one sequential
+ * chain (see leon_b200/csrc/decode.cu). */
+typedef struct leon_dna_stream {
+    int32_t kmer_size, max_read_size;      /* max_read_size: metadata/maxSequenceSize, bounds what a corrupt block can claim (-1: unchecked) */
+    const uint8_t *bloom;         uint64_t bloom_nbytes;  uint64_t bloom_bits;      /* leon/bloom + its "size" attribute */
+    const uint8_t *anchors_dict;  uint64_t anchors_dict_nbytes;  uint64_t anchor_count;
+    uint64_t nblocks;  const uint64_t *blocksizes;         /* leon/dna/blocksizes: bytes, reads per block */
+    const uint8_t *dna;           uint64_t dna_nbytes;     /* dna_<id> blocks, concatenated */
+} leon_dna_stream;
+typedef struct leon_decoded leon_decoded;     /* decoded text of a stream, block by block */
+/* Inverse of leon_headers_encode (C/HeaderCoder.cpp:526-789): the names of every block, one per line. */
+int  leon_headers_decode(const leon_header_stream *stream, int32_t nthreads, leon_decoded **out);
+int  leon_decode_dna(const leon_dna_stream *stream, int32_t nthreads, leon_decoded **out);
+int  leon_decoded_block(const leon_decoded *d, uint64_t block, const uint8_t **text, uint64_t *nbytes);
+void leon_decoded_free(leon_decoded *d);
+
 /* File level: `leon -file X -c` end to end (C/Leon.cpp:342-470 executeCompression).  Reads the FASTA/FASTQ file like the
  * reference's bank (bank/impl/BankFasta.cpp:484-570; format from the file name as C/Leon.cpp:392-416), codes the header
  * stream on host threads while the GPU codes the sequence stream, writes `out_path` (NULL: in_path + ".leon").
@@ -242,6 +260,10 @@ typedef struct leon_file_stats {
     leon_timings gpu;
 } leon_file_stats;
 int leon_compress_file(const char *in_path, const char *out_path, const leon_file_opts *opts, leon_file_stats *stats);
+/* `leon -file X.leon -d` (C/Leon.cpp:1311-1470, 1697-1860): decodes the three streams of a container (ours or the
+ * reference's) on host threads and writes <dir>/<prefix>.fasta.d or .fastq.d (out_path NULL) in the reference's
+ * output layout.  stats: parse_ms = container, compress_ms = decoding, reserved1[0..1] = sequence / quality stream. */
+int leon_decompress_file(const char *in_path, const char *out_path, int32_t nthreads, leon_file_stats *stats);
 
 /* The record reader of leon_compress_file on its own (bank/impl/BankFasta.cpp:484-570): reads a FASTA/FASTQ file (multi-line
  * sequences, blank lines and CR LF accepted) into the layout leon_compress takes (exactly sized pageable host memory).

@@ -12,7 +12,8 @@ ABI_SYMBOLS = [
     "leon_compress", "leon_upload", "leon_count", "leon_bloom_build", "leon_encode", "leon_run_device", "leon_fetch",
     "leon_get_timings", "leon_get_kernel_times", "leon_set_stream", "leon_comm_unique_id", "leon_comm_init",
     "leon_comm_batch_reads", "leon_debug_bloom_query", "leon_debug_hashes", "leon_debug_fetch", "leon_write_container",
-    "leon_headers_encode", "leon_headers_free", "leon_compress_file", "leon_read_file", "leon_file_reads_free",
+    "leon_headers_encode", "leon_headers_free", "leon_compress_file", "leon_decompress_file", "leon_read_file", "leon_file_reads_free",
+    "leon_decode_dna", "leon_decoded_block", "leon_decoded_free", "leon_headers_decode",
     "leon_container_open", "leon_container_close", "leon_container_has", "leon_container_dataset", "leon_container_attr",
 ]
 
@@ -93,6 +94,13 @@ class FileReads(C.Structure):
                 ("is_fastq", C.c_int32), ("threads_used", C.c_int32)]
 
 
+class DnaStream(C.Structure):
+    _fields_ = [("kmer_size", C.c_int32), ("max_read_size", C.c_int32),
+                ("bloom", C.c_void_p), ("bloom_nbytes", C.c_uint64), ("bloom_bits", C.c_uint64),
+                ("anchors_dict", C.c_void_p), ("anchors_dict_nbytes", C.c_uint64), ("anchor_count", C.c_uint64),
+                ("nblocks", C.c_uint64), ("blocksizes", C.c_void_p), ("dna", C.c_void_p), ("dna_nbytes", C.c_uint64)]
+
+
 class KernelTime(C.Structure):
     _fields_ = [("name", C.c_char * 32), ("ms_total", C.c_float), ("launches", C.c_uint32)]
 
@@ -136,9 +144,15 @@ def load_library(path=LIB_PATH):
     L.leon_headers_free.argtypes = [C.POINTER(HeaderStream)]
     L.leon_headers_free.restype = None
     L.leon_compress_file.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(FileOpts), C.POINTER(FileStats)]
+    L.leon_decompress_file.argtypes = [C.c_char_p, C.c_char_p, C.c_int32, C.POINTER(FileStats)]
     L.leon_read_file.argtypes = [C.c_char_p, C.c_int, C.c_int, C.POINTER(C.POINTER(FileReads))]
     L.leon_file_reads_free.argtypes = [C.POINTER(FileReads)]
     L.leon_file_reads_free.restype = None
+    L.leon_headers_decode.argtypes = [C.POINTER(HeaderStream), C.c_int32, C.POINTER(C.c_void_p)]
+    L.leon_decode_dna.argtypes = [C.POINTER(DnaStream), C.c_int32, C.POINTER(C.c_void_p)]
+    L.leon_decoded_block.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.POINTER(C.c_uint8)), C.POINTER(C.c_uint64)]
+    L.leon_decoded_free.argtypes = [C.c_void_p]
+    L.leon_decoded_free.restype = None
     L.leon_container_open.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
     L.leon_container_close.argtypes = [C.c_void_p]
     L.leon_container_close.restype = None
@@ -154,6 +168,59 @@ def _arr(ptr, n, dtype, copy=True):
         return np.zeros(0, dtype)
     a = np.ctypeslib.as_array(ptr, shape=(int(n),))
     return a.astype(dtype, copy=True) if copy else a
+
+
+def _decoded_lines(L, h, nblocks):
+    lines = []
+    for b in range(nblocks):
+        p, n = C.POINTER(C.c_uint8)(), C.c_uint64()
+        L.leon_decoded_block(h, b, C.byref(p), C.byref(n))
+        lines += _arr(p, n.value, np.uint8).tobytes().split(b"\n")[:-1]
+    return lines
+
+
+def decode_headers(header, nthreads=0):
+    """Inverse of encode_headers: header = dict(first_header, blocksizes, data); returns the names as a list of bytes."""
+    L = load_library()
+    fh = np.frombuffer(bytes(header["first_header"]), np.uint8)
+    bs = np.ascontiguousarray(header["blocksizes"], np.uint64)
+    data = np.ascontiguousarray(header["data"], np.uint8)
+    hs = HeaderStream()
+    hs.first_header = fh.ctypes.data_as(C.POINTER(C.c_uint8)) if len(fh) else None
+    hs.first_header_nbytes = len(fh)
+    hs.nblocks = len(bs) // 2
+    hs.blocksizes = bs.ctypes.data_as(C.POINTER(C.c_uint64))
+    hs.data = data.ctypes.data_as(C.POINTER(C.c_uint8))
+    hs.data_nbytes = len(data)
+    h = C.c_void_p()
+    rc = L.leon_headers_decode(C.byref(hs), int(nthreads), C.byref(h))
+    if rc != 0:
+        raise LeonError(rc, L.leon_last_error(None).decode())
+    try:
+        return _decoded_lines(L, h, len(bs) // 2)
+    finally:
+        L.leon_decoded_free(h)
+
+
+def decode_dna(result, kmer_size, nthreads=0):
+    """Decodes the sequence stream of a result dict (bloom, bloom_bits, anchors_dict, anchor_count, blocksizes, dna,
+    max_read_size) back to reads: returns a list of bytes, one per read (C/DnaCoder.cpp:1221-1622)."""
+    L = load_library()
+    keep = [np.ascontiguousarray(result[k], np.uint8) for k in ("bloom", "anchors_dict", "dna")]
+    bs = np.ascontiguousarray(result["blocksizes"], np.uint64)
+    # the filter is read 8 bytes at a time: pad it like the device copy
+    bloom = np.concatenate([keep[0], np.zeros(16, np.uint8)])
+    s = DnaStream(int(kmer_size), int(result.get("max_read_size", -1)), bloom.ctypes.data, len(bloom), int(result["bloom_bits"]),
+                  keep[1].ctypes.data, len(keep[1]), int(result["anchor_count"]), len(bs) // 2, bs.ctypes.data,
+                  keep[2].ctypes.data, len(keep[2]))
+    h = C.c_void_p()
+    rc = L.leon_decode_dna(C.byref(s), int(nthreads), C.byref(h))
+    if rc != 0:
+        raise LeonError(rc, L.leon_last_error(None).decode())
+    try:
+        return _decoded_lines(L, h, len(bs) // 2)
+    finally:
+        L.leon_decoded_free(h)
 
 
 class Container:
@@ -232,6 +299,18 @@ def compress_file(in_path, out_path=None, kmer_size=31, reads_per_block=50000, l
         raise LeonError(rc, L.leon_last_error(None).decode())
     d = {n: getattr(st, n) for n, _ in FileStats._fields_ if not n.startswith("reserved") and n != "gpu"}
     d["gpu"] = {n: getattr(st.gpu, n) for n, _ in Timings._fields_ if n != "reserved"}
+    return d
+
+
+def decompress_file(in_path, out_path=None, nthreads=0):
+    """`leon -file in_path -d` (C/Leon.cpp:1311-1470, 1697-1860) on host threads; returns the statistics as a dict."""
+    L = load_library()
+    st = FileStats()
+    rc = L.leon_decompress_file(os.fsencode(in_path), os.fsencode(out_path) if out_path else None, int(nthreads), C.byref(st))
+    if rc != 0:
+        raise LeonError(rc, L.leon_last_error(None).decode())
+    d = {n: getattr(st, n) for n, _ in FileStats._fields_ if not n.startswith("reserved") and n != "gpu"}
+    d["dna_ms"], d["qual_ms"] = st.reserved1[0], st.reserved1[1]
     return d
 
 

@@ -32,7 +32,8 @@ def build(force=False, verbose=False):
     cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
         ["-I", SRC_DIR, "-o", LIB, os.path.join(SRC_DIR, "leon_b200.cu"), os.path.join(SRC_DIR, "container.cpp"),
          os.path.join(SRC_DIR, "headers.cpp"), os.path.join(SRC_DIR, "fileio.cpp"),
-         os.path.join(SRC_DIR, "container_read.cpp"), "-lz"]
+         os.path.join(SRC_DIR, "container_read.cpp"), os.path.join(SRC_DIR, "decode.cu"),
+         os.path.join(SRC_DIR, "decompress.cpp"), "-lz"]
     subprocess.run(cmd, check=True)
     # the command line tool (host only), finds the library next to it
     os.makedirs(os.path.dirname(CLI), exist_ok=True)

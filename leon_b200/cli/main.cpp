@@ -1,7 +1,8 @@
 // Command line of the B200 path, option for option the `leon -c` of the reference (C/Leon.cpp:102-140):
 //   leon_b200 -file reads.fastq -c [-kmer-size 31] [-abundance N] [-nb-cores N] [-lossless] [-seq-only] [-noheader]
 //             [-noqual] [-reads 50000] [-out file.leon] [-device 0] [-verbose 0|1]
-// writes reads.fastq.leon, which the reference's `leon -d` decodes.  Decompression (-d) is not part of this tool yet.
+//   leon_b200 -file reads.fastq.leon -d [-nb-cores N] [-out file]
+// -c writes reads.fastq.leon, which the reference's `leon -d` decodes too; -d reads containers of either tool (host threads).
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -12,6 +13,7 @@
 static void usage() {
     fprintf(stderr,
             "usage: leon_b200 -file <in.fa|in.fasta|in.fq|in.fastq> -c [options]\n"
+            "       leon_b200 -file <in.leon> -d [-nb-cores N] [-out FILE]\n"
             "  -kmer-size N   k-mer size, 2..63 (default 31)\n"
             "  -abundance N   abundance threshold given explicitly (disables the automatic cutoff)\n"
             "  -nb-cores N    host threads for the header stream and zlib (default: all)\n"
@@ -55,11 +57,21 @@ int main(int argc, char **argv) {
         else { fprintf(stderr, "unknown option %s\n", a.c_str()); usage(); return 2; }
     }
     if (in.empty() || compress == decompress) { usage(); return 2; }
-    if (decompress) {
-        fprintf(stderr, "leon_b200: -d is not implemented here; the files written by -c are decoded by the reference's `leon -d`\n");
-        return 2;
-    }
     leon_file_stats s;
+    if (decompress) {
+        int rc = leon_decompress_file(in.c_str(), out.empty() ? nullptr : out.c_str(), o.nthreads, &s);
+        if (rc) {
+            fprintf(stderr, "leon_b200: error %d: %s\n", rc, leon_last_error(nullptr));
+            return 1;
+        }
+        if (verbose) {
+            printf("reads %llu  bases %llu  blocks %llu  %s, headers %s\n", (unsigned long long)s.nreads, (unsigned long long)s.total_bases,
+                   (unsigned long long)s.nblocks, s.is_fasta ? "FASTA" : "FASTQ", s.has_header ? "stored" : "numbered");
+            printf("time: container %.1f ms, decode %.1f ms (sequences %.1f ms, headers %.1f ms, qualities %.1f ms, side by side), write %.1f ms, total %.1f ms\n",
+                   s.parse_ms, s.compress_ms, s.reserved1[0], s.header_ms, s.reserved1[1], s.write_ms, s.total_ms);
+        }
+        return 0;
+    }
     int rc = leon_compress_file(in.c_str(), out.empty() ? nullptr : out.c_str(), &o, &s);
     if (rc) {
         fprintf(stderr, "leon_b200: error %d: %s\n", rc, leon_last_error(nullptr));

@@ -9,11 +9,14 @@
 #include <algorithm>
 #include <atomic>
 #include <cstring>
+#include <memory>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
 
 #include "../../include/leon_b200.h"
+#include "decoded.h"
 #include "kmer_math.cuh"
 #include "simplehash_table.h"
 
@@ -119,7 +122,7 @@ template <typename K> unsigned contains4(const BloomDev &b, K fwd, bool right) {
     for (unsigned nt = 0; nt < 4; nt++) pos[nt] = right ? bloom_cano2((fixed << 2) + nt) : bloom_cano2((nt << 2) + fixed);
     unsigned alive = 15u;
     for (int i = 0; i < 7 && alive; i++) {
-        const uint64_t bit = racine + (i ? (kmer_simplehash16(hp, i, LB_SIMPLEHASH_TABLE) & 4095) : 0);
+        const uint64_t bit = racine + (i ? (kmer_simplehash16(hp, i, kSimpleHashTable) & 4095) : 0);
         uint64_t w;
         memcpy(&w, (const uint8_t *)b.words + (bit >> 5) * 4, 8);     // 64 filter bits from the word holding `bit`
         const uint32_t f = (uint32_t)(w >> (bit & 31));
@@ -254,7 +257,7 @@ int decode_dna(const leon_dna_stream *s, int nthreads, std::vector<std::string> 
     bloom.k = s->kmer_size;
     bloom.words = (uint32_t *)s->bloom;
     bloom.reduced_tai = s->bloom_bits;
-    bloom.magic = s->bloom_bits ? ~0ull / s->bloom_bits + 1 : 0;
+    bloom.magic = s->bloom_bits ? ~0ull / s->bloom_bits : 0;
     if (s->bloom_nbytes < s->bloom_bits / 8 + 8) { err = "Bloom array shorter than its size attribute says"; return LEON_E_ARG; }
     std::vector<K> anchors;
     decode_anchor_dict<K>(s->anchors_dict, s->anchors_dict_nbytes, s->anchor_count, s->kmer_size, anchors);
@@ -292,11 +295,6 @@ int decode_dna(const leon_dna_stream *s, int nthreads, std::vector<std::string> 
 
 }  // namespace lbdecode
 
-struct leon_decoded {
-    std::vector<std::string> blocks;
-    std::vector<const uint8_t *> ptrs;
-    std::vector<uint64_t> sizes;
-};
 
 extern "C" int leon_decode_dna(const leon_dna_stream *s, int32_t nthreads, leon_decoded **out) {
     try {
@@ -307,7 +305,6 @@ extern "C" int leon_decode_dna(const leon_dna_stream *s, int32_t nthreads, leon_
         const int rc = s->kmer_size <= 31 ? lbdecode::decode_dna<uint64_t>(s, nthreads, d->blocks, err)
                                           : lbdecode::decode_dna<u128>(s, nthreads, d->blocks, err);
         if (rc) { leon_internal_set_error(("leon_decode_dna: " + err).c_str()); return rc; }
-        for (const std::string &b : d->blocks) { d->ptrs.push_back((const uint8_t *)b.data()); d->sizes.push_back(b.size()); }
         *out = d.release();
         return LEON_OK;
     } catch (const std::bad_alloc &) {
@@ -318,8 +315,8 @@ extern "C" int leon_decode_dna(const leon_dna_stream *s, int32_t nthreads, leon_
 
 extern "C" int leon_decoded_block(const leon_decoded *d, uint64_t block, const uint8_t **text, uint64_t *nbytes) {
     if (!d || block >= d->blocks.size() || !text || !nbytes) { leon_internal_set_error("leon_decoded_block: bad argument"); return LEON_E_ARG; }
-    *text = d->ptrs[block];
-    *nbytes = d->sizes[block];
+    *text = (const uint8_t *)d->blocks[block].data();
+    *nbytes = d->blocks[block].size();
     return LEON_OK;
 }
 

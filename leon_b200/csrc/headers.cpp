@@ -21,6 +21,7 @@
 #include <vector>
 
 #include "../../include/leon_b200.h"
+#include "decoded.h"
 
 extern "C" void leon_internal_set_error(const char *msg);
 
@@ -53,6 +54,16 @@ struct Model {
         return s;
     }
     void update(unsigned c) { cnt[c]++; grp[c >> 4]++; total++; }
+    // largest symbol c with low(c) <= count (RangeDecoder::nextByte, C/RangeCoder.cpp:194-206); *lo gets low(c)
+    unsigned find(uint64_t count, uint64_t *lo) const {
+        uint64_t s = 0;
+        size_t g = 0;
+        while (g + 1 < grp.size() && s + grp[g] <= count) { s += grp[g]; g++; }
+        unsigned c = (unsigned)g * 16;
+        while ((int)c < n - 1 && s + cnt[c] <= count) { s += cnt[c]; c++; }
+        *lo = s;
+        return c;
+    }
 };
 
 struct RangeEncoder {
@@ -77,6 +88,31 @@ struct RangeEncoder {
     void clear() { low = 0; range = ~0ull; buf.clear(); }
 };
 
+struct RangeDecoder {                                    // C/RangeCoder.cpp:179-244
+    uint64_t low = 0, range = ~0ull, code = 0;
+    const uint8_t *p = nullptr, *end = nullptr;
+    uint8_t next() { return p < end ? *p++ : (uint8_t)0xff; }
+    void start(const uint8_t *data, uint64_t n) {
+        low = 0; range = ~0ull; code = 0; p = data; end = data + n;
+        for (int i = 0; i < 8; i++) code = (code << 8) | next();
+    }
+    unsigned decode(Model &m) {
+        range /= m.total;
+        uint64_t lo;
+        const unsigned c = m.find((code - low) / range, &lo);
+        low += lo * range;
+        range *= m.cnt[c];
+        while ((low ^ (low + range)) < RC_TOP || range < RC_BOTTOM) {
+            if (range < RC_BOTTOM && (low ^ (low + range)) >= RC_TOP) range = (0 - low) & (RC_BOTTOM - 1);
+            code = (code << 8) | next();
+            range <<= 8;
+            low <<= 8;
+        }
+        m.update(c);
+        return c;
+    }
+};
+
 struct Column {                                          // AbstractHeaderCoder::addFieldColumn, C/HeaderCoder.cpp:41-62
     Model type{HEADER_TYPE_COUNT + 1}, field_index{256}, field_column{256}, mis_size{256}, ascii{128}, zero{256};
     std::vector<Model> numeric;
@@ -88,13 +124,13 @@ struct Column {                                          // AbstractHeaderCoder:
 
 struct View { const char *p; size_t n; char at(size_t i) const { return i < n ? p[i] : '\0'; } };
 
-class HeaderEncoder {
+// AbstractHeaderCoder (C/HeaderCoder.cpp:33-213): field splitting and the per-column state both directions share.
+class HeaderCoderBase {
   public:
-    RangeEncoder rc;
     bool leftover_used = false;     // a member the reference never resets was consulted before this object set it
     bool bad_char = false;          // a character >= 128 (outside the reference's 128-symbol text model)
 
-    HeaderEncoder(View first) : first_(first) {}
+    explicit HeaderCoderBase(View first) : first_(first) {}
 
     void start_block() {                                 // C/HeaderCoder.cpp:188-213
         cur_ = first_;
@@ -107,15 +143,9 @@ class HeaderEncoder {
         end_header();
         processed_ = 0;
     }
-    void encode(View h) {                                // processNextHeader, C/HeaderCoder.cpp:290-299
-        cur_ = h;
-        split_header();
-        compare_header();
-        end_header();
-    }
     int processed() const { return processed_; }
 
-  private:
+  protected:
     View first_, prev_{nullptr, 0}, cur_{nullptr, 0};
     std::vector<Column> col_;
     Model header_size_{256};
@@ -186,6 +216,24 @@ class HeaderEncoder {
         processed_ += 1;
     }
 
+    Column &col_at(int i) {
+        while ((int)col_.size() <= i) add_column();      // the reference indexes its vectors unchecked; only reachable
+        return col_[i];                                  // for an empty header on a fresh object
+    }
+};
+
+class HeaderEncoder : public HeaderCoderBase {
+  public:
+    RangeEncoder rc;
+    explicit HeaderEncoder(View first) : HeaderCoderBase(first) {}
+    void encode(View h) {                                // processNextHeader, C/HeaderCoder.cpp:290-299
+        cur_ = h;
+        split_header();
+        compare_header();
+        end_header();
+    }
+
+  private:
     void compare_header() {                              // C/HeaderCoder.cpp:301-426
         field_pos_ = 0;
         mis_start_ = -1;
@@ -232,10 +280,6 @@ class HeaderEncoder {
         }
     }
     void set_match() { last_match_ = field_index_; last_match_set_ = true; }
-    Column &col_at(int i) {
-        while ((int)col_.size() <= i) add_column();      // the reference indexes its vectors unchecked; only reachable
-        return col_[i];                                  // for an empty header on a fresh object
-    }
 
     void encode_numeric() {                              // C/HeaderCoder.cpp:428-489
         Column &f = col_[field_index_];
@@ -288,6 +332,98 @@ class HeaderEncoder {
         rc.encode(m.mis_size, (unsigned)(miss & 255));
         for (int i = mis_start_; i < mis_start_ + miss; i++) rc.encode(m.ascii, (unsigned char)cur_.p[f.cur_pos + i] & 127);
         mis_index_ += 1;
+    }
+};
+
+// HeaderDecoder (C/HeaderCoder.cpp:526-789): rebuilds every header from the previous one and the coded differences.
+class HeaderDecoder : public HeaderCoderBase {
+  public:
+    RangeDecoder rc;
+    explicit HeaderDecoder(View first) : HeaderCoderBase(first) {}
+
+    // Decodes `count` headers of one header_<id> block into out, one per line (HeaderDecoder::_buffer).
+    void run(const uint8_t *data, uint64_t nbytes, uint64_t count, std::string &out) {
+        start_block();
+        rc.start(data, nbytes);
+        buf_.clear();
+        mis_index_ = 0;
+        field_index_ = 0;
+        while ((uint64_t)processed_ < count) {
+            const unsigned type = rc.decode(col_at(mis_index_).type);
+            if (type == HEADER_END) {
+                finish_header(out);
+            } else if (type == HEADER_END_MATCH) {
+                const unsigned header_size = rc.decode(header_size_);     // 8 bits of the real size, as coded
+                for (; field_index_ < prev_count_; field_index_++) {
+                    append_prev_field(field_index_);
+                    if (buf_.size() >= header_size) break;
+                }
+                finish_header(out);
+            } else {
+                const int mis_field = (int)rc.decode(col_at(mis_index_).field_index);    // decodeMatch
+                for (; field_index_ < mis_field; field_index_++) append_prev_field(field_index_);
+                if (type == FIELD_ASCII) {
+                    Column &m = col_at(mis_index_);
+                    const unsigned column = rc.decode(m.field_column), size = rc.decode(m.mis_size);
+                    if (field_index_ < prev_count_)
+                        for (unsigned i = 0; i < column; i++) buf_ += prev_.at(col_at(field_index_).prev_pos + i);
+                    for (unsigned i = 0; i < size; i++) buf_ += (char)rc.decode(m.ascii);
+                    field_index_++; mis_index_++;
+                } else if (type == FIELD_NUMERIC || type == FIELD_DELTA || type == FIELD_DELTA_2) {
+                    uint64_t v = numeric(col_at(mis_index_).numeric);
+                    if (type != FIELD_NUMERIC) {
+                        if (field_index_ >= prev_count_) leftover_used = true;       // previous value of a field the previous header lacks
+                        const uint64_t prev = col_at(field_index_).prev_value;
+                        v = type == FIELD_DELTA ? prev + v : prev - v;
+                    }
+                    buf_ += std::to_string(v);
+                    field_index_++; mis_index_++;
+                } else if (type == FIELD_ZERO_ONLY || type == FIELD_ZERO_AND_NUMERIC) {
+                    const unsigned zeros = rc.decode(col_at(mis_index_).zero);
+                    buf_.append(zeros, '0');
+                    if (type == FIELD_ZERO_ONLY) field_index_++;
+                    mis_index_++;
+                } else {
+                    bad_stream = true;                                               // not a header type: corrupt block
+                    return;
+                }
+            }
+            if (buf_.size() > (1u << 20)) { bad_stream = true; return; }
+        }
+    }
+    bool bad_stream = false;
+
+  private:
+    std::string buf_, prev_buf_;
+    void append_prev_field(int f) {
+        if (f + 1 >= (int)col_.size()) return;
+        const unsigned a = col_[f].prev_pos, b = col_[f + 1].prev_pos;
+        if (a > prev_.n) { bad_stream = true; return; }                              // the reference's substr throws here
+        if (b > a) buf_.append(prev_.p + a, std::min<size_t>(b - a, prev_.n - a));
+    }
+    uint64_t numeric(std::vector<Model> &models) {                                   // C/CompressionUtils.hpp:114-137
+        uint64_t value = 0;
+        int shift = 0, i = 0;
+        unsigned byte;
+        do {
+            if (i >= 8) leftover_used = true;
+            byte = rc.decode(models[i < NB_MODELS_PER_NUMERIC ? i : NB_MODELS_PER_NUMERIC - 1]);
+            if (shift < 64) value += (uint64_t)(byte & 127) << shift;
+            shift += 7;
+            i++;
+        } while (byte > 127);
+        return value;
+    }
+    void finish_header(std::string &out) {                                           // HeaderDecoder::endHeader
+        out += buf_;
+        out += '\n';
+        cur_ = View{buf_.data(), buf_.size()};
+        split_header();
+        end_header();                                                                // prev_ = cur_ (a view of buf_)
+        prev_buf_.swap(buf_);
+        prev_ = View{prev_buf_.data(), prev_buf_.size()};
+        buf_.clear();
+        mis_index_ = 0;
     }
 };
 
@@ -374,6 +510,58 @@ extern "C" int leon_headers_encode(const uint8_t *text, const uint64_t *offsets,
         return LEON_OK;
     } catch (const std::bad_alloc &) {
         leon_internal_set_error("leon_headers_encode: out of host memory");
+        return LEON_E_NOMEM;
+    }
+}
+
+// Inverse of leon_headers_encode: the names of every block, one per line.  Blocks are decoded in parallel with a fresh
+// object each; when a block consulted state an earlier block would have left (see the top of this file) the whole
+// stream is decoded again by one serial object, like the reference with -nb-cores 1.
+extern "C" int leon_headers_decode(const leon_header_stream *hs, int32_t nthreads, leon_decoded **out) {
+    try {
+        if (!hs || !out || (hs->nblocks && (!hs->blocksizes || !hs->data))) { leon_internal_set_error("leon_headers_decode: null argument"); return LEON_E_ARG; }
+        std::unique_ptr<leon_decoded> d(new leon_decoded());
+        const uint64_t nb = hs->nblocks;
+        std::vector<uint64_t> start(nb + 1, 0);
+        for (uint64_t b = 0; b < nb; b++) start[b + 1] = start[b] + hs->blocksizes[2 * b];
+        if (start[nb] > hs->data_nbytes) { leon_internal_set_error("leon_headers_decode: blocksizes exceed data_nbytes"); return LEON_E_ARG; }
+        const View first{(const char *)hs->first_header, (size_t)hs->first_header_nbytes};
+        std::atomic<int> leftover(0), bad(0);
+        unsigned nt = nthreads > 0 ? (unsigned)nthreads : std::max(1u, std::thread::hardware_concurrency());
+        nt = (unsigned)std::min<uint64_t>(nt, std::max<uint64_t>(nb, 1));
+        bool serial = nt <= 1;
+        if (!serial) {
+            d->blocks.assign(nb, std::string());
+            std::atomic<uint64_t> next(0);
+            auto work = [&]() {
+                for (;;) {
+                    const uint64_t b = next.fetch_add(1);
+                    if (b >= nb || leftover.load() || bad.load()) return;
+                    HeaderDecoder h(first);
+                    h.run(hs->data + start[b], hs->blocksizes[2 * b], hs->blocksizes[2 * b + 1], d->blocks[b]);
+                    if (h.leftover_used) leftover.store(1);
+                    if (h.bad_stream) bad.store(1);
+                }
+            };
+            std::vector<std::thread> pool;
+            for (unsigned i = 1; i < nt; i++) pool.emplace_back(work);
+            work();
+            for (auto &t : pool) t.join();
+            serial = leftover.load() != 0;
+        }
+        if (serial) {
+            bad.store(0);
+            d->blocks.assign(nb, std::string());
+            HeaderDecoder h(first);
+            for (uint64_t b = 0; b < nb && !h.bad_stream; b++)
+                h.run(hs->data + start[b], hs->blocksizes[2 * b], hs->blocksizes[2 * b + 1], d->blocks[b]);
+            if (h.bad_stream) bad.store(1);
+        }
+        if (bad.load()) { leon_internal_set_error("leon_headers_decode: corrupt header stream"); return LEON_E_ARG; }
+        *out = d.release();
+        return LEON_OK;
+    } catch (const std::bad_alloc &) {
+        leon_internal_set_error("leon_headers_decode: out of host memory");
         return LEON_E_NOMEM;
     }
 }
