@@ -97,6 +97,26 @@ def main():
             assert open(inp + ".inproc.leon", "rb").read() == open(inp + ".leon", "rb").read()
         res["ours_stdout"] = p.stdout.strip().splitlines()
         res["ours_output_bytes"] = os.path.getsize(inp + ".leon")
+        # our own decompressor on our file: back to the input (names, reads; qualities when lossless)
+        t = time.time()
+        p = subprocess.run([CLI, "-file", inp + ".leon", "-d", "-out", os.path.join(ours, "ours.d")], capture_output=True, text=True)
+        dt = time.time() - t
+        assert p.returncode == 0, p.stdout + p.stderr
+        res["ours_decode_wall_s"] = dt
+        res["ours_decode_stdout"] = p.stdout.strip().splitlines()
+        print("ours -d: %.3f s\n%s" % (dt, p.stdout.strip()), flush=True)
+        if not ({"-seq-only", "-noheader", "-noqual"} & set(flags)):
+            step = 4 if a.fastq else 2
+            same = True
+            with open(os.path.join(ours, "ours.d"), "rb") as fd, open(inp, "rb") as fi:
+                i = 0
+                for ld, li in zip(fd, fi):
+                    if ld != li and (i % step != 3 or "-lossless" in flags):
+                        same = False
+                        break
+                    i += 1
+            res["ours_decode_equals_input"] = same and i == a.reads * step
+            print("ours -d output equals the input (qualities compared only when lossless):", res["ours_decode_equals_input"], flush=True)
         if not a.no_reference and os.path.exists(REF):
             t = time.time()
             p = subprocess.run([REF, "-file", os.path.join(ref, "in." + ext), "-c", "-nb-cores", str(os.cpu_count())] + flags,
