@@ -100,6 +100,42 @@ LB_D const uint8_t *stage_reads(const uint8_t *__restrict__ bases, uint64_t o0, 
     return smem + (o0 & 15ull);
 }
 
+// The same in two halves, for callers with work to overlap with the copy: begin() returns nullptr (and starts nothing)
+// when the span does not fit, else the address as above; wait() must then be called by every thread before the bases are
+// read (and before the next __syncthreads-separated use of the barrier).
+LB_D const uint8_t *stage_reads_begin(const uint8_t *__restrict__ bases, uint64_t o0, uint64_t o1, uint8_t *smem, uint32_t smem_bytes,
+                                      uint64_t *bar)
+{
+    const uint8_t *src = bases + (o0 & ~15ull);
+    uint64_t bytes = ((o1 - (o0 & ~15ull)) + 15ull) & ~15ull;
+    if (bytes > smem_bytes) return nullptr;        // CTA-uniform
+    uint32_t bar_a = (uint32_t)__cvta_generic_to_shared(bar);
+    uint32_t dst_a = (uint32_t)__cvta_generic_to_shared(smem);
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_a));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"((uint32_t)bytes) : "memory");
+        if (bytes)
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(dst_a), "l"(src), "r"((uint32_t)bytes), "r"(bar_a) : "memory");
+    }
+    return smem + (o0 & 15ull);
+}
+LB_D void stage_reads_wait(uint64_t *bar)
+{
+    uint32_t bar_a = (uint32_t)__cvta_generic_to_shared(bar);
+    uint32_t done = 0;
+    while (!done) {
+        asm volatile("{\n\t.reg .pred p;\n\t"
+                     "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(bar_a) : "memory");
+    }
+}
+
 // Canonical k-mer of every window of every read; an INVALID key when the window holds an invalid character ((c>>3)&1,
 // MI/api/Data.hpp:176).  One THREAD per read: the bases of the 256 reads of a CTA are staged in shared memory by one
 // bulk copy, the forward k-mer and its reverse complement are rolled base by base (4 operations each, K/Model.hpp:725-764)

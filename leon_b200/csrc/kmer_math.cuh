@@ -200,6 +200,38 @@ template <typename K> LB_D bool bloom_contains(const BloomDev &b, K item, const 
     return true;
 }
 
+// contains() for a k-mer given as its forward and reverse-complement words (rolled by the caller), in two halves so
+// that a caller can have the probes of several k-mers in flight: the canonical middle k-2 nucleotides are the smaller
+// of the two middles; all 7 probe words are loaded (no early exit), their bit positions packed 5 bits each in `sh`.
+template <typename K> LB_D void bloom_probe_issue(const BloomDev &b, K fwd, K rc, const uint64_t *tbl, uint32_t (&w)[7], uint64_t &sh)
+{
+    const K m2 = kmer_mask(K(0), b.k - 2);
+    const K mf = (fwd >> 2) & m2, mr = (rc >> 2) & m2;
+    const K hp = mr < mf ? mr : mf;
+    const K item = rc < fwd ? rc : fwd;
+    // branch-free modulo (the estimate is at most 2 short) so that the chains of several k-mers can be interleaved
+    const uint64_t x = kmer_hash1(hp, LB_BLOOM_SEED0);
+    uint64_t rr = x - umulhi64(x, b.magic) * b.reduced_tai;
+    rr -= rr >= b.reduced_tai ? b.reduced_tai : 0;
+    rr -= rr >= b.reduced_tai ? b.reduced_tai : 0;
+    const uint64_t h0 = rr + bloom_prefval(item, b.k);
+    w[0] = __ldg(b.words + (h0 >> 5));
+    sh = h0 & 31u;
+#pragma unroll
+    for (int i = 1; i < 7; i++) {
+        const uint64_t h1 = h0 + (kmer_simplehash16(hp, i, tbl) & 4095);
+        w[i] = __ldg(b.words + (h1 >> 5));
+        sh |= (h1 & 31u) << (5 * i);
+    }
+}
+LB_D bool bloom_probe_test(const uint32_t (&w)[7], uint64_t sh)
+{
+    uint32_t all = 1u;
+#pragma unroll
+    for (int i = 0; i < 7; i++) all &= w[i] >> (unsigned)((sh >> (5 * i)) & 31u);
+    return (all & 1u) != 0;
+}
+
 // 2-bit code of an ASCII base as the k-mer models see it (MI/api/Data.hpp:176); 'N' is coded as 'A' because the
 // encoder rewrites N to A before building k-mers (C/DnaCoder.cpp:519-528).
 LB_HD unsigned base_code_n_as_a(uint8_t c) { return c == 'N' ? 0u : ((c >> 1) & 3u); }

@@ -164,8 +164,11 @@ void do_upload(leon_ctx *c, const leon_reads *rd)
     CUDA_TRY(cudaMemcpyAsync(c->d_bases.p, rd->bases, c->nbases, cudaMemcpyHostToDevice, c->st));
     CUDA_TRY(cudaMemcpyAsync(c->d_offsets.p, rd->offsets, (c->nreads + 1) * 8, cudaMemcpyHostToDevice, c->st));
     if (c->opts.has_qual) {
+        // Qualities are first needed by k_quals on the third stream, long after counting has started: their copy goes
+        // there, beside the counting kernels, instead of in front of them (one-shot calls from pinned memory: -9 ms).
         c->d_quals.reserve(c->nbases + 128);
-        CUDA_TRY(cudaMemcpyAsync(c->d_quals.p, rd->quals, c->nbases, cudaMemcpyHostToDevice, c->st));
+        CUDA_TRY(cudaStreamWaitEvent(c->st3, c->ev[0], 0));
+        CUDA_TRY(cudaMemcpyAsync(c->d_quals.p, rd->quals, c->nbases, cudaMemcpyHostToDevice, c->st3));
     }
     CUDA_TRY(cudaEventRecord(c->ev[1], c->st));
     // min / max read length for the metadata datasets (host side, offsets are already here)
@@ -920,8 +923,16 @@ template <typename K> void do_encode_body(leon_ctx *c)
         if (R) {
             CUDA_TRY(cudaEventRecord(c->ev_q[0], st));
             CUDA_TRY(cudaStreamWaitEvent(c->st3, c->ev_q[0], 0));
-            LB_TIMED(c->kt, "k_quals", c->st3, LB_LAUNCH(c->lc, (lbwalk::k_quals<K>), warp_grid(R), 256, 0, c->st3, bases, c->d_quals.as<uint8_t>(), offsets, koff, R,
-                      c->bloom, c->d_tbl.as<uint64_t>(), c->opts.lossless, c->d_err.as<uint32_t>(), c->d_qout.as<uint8_t>()));
+            {
+                // bases and the output text of the QT reads of a CTA are staged in shared memory when they fit
+                uint64_t need = (((uint64_t)lbwalk::QT * (uint64_t)c->max_len + 31) & ~15ull) + 16;
+                uint32_t stage_bytes = need <= 100000 ? (uint32_t)need : 16u;
+                size_t smem = 2 * (size_t)stage_bytes + lbwalk::QT + 32;
+                // 4 k-mers in flight per thread, 4 CTAs per SM: the best of the (2..8, 2..8) combinations measured on the B200
+                CUDA_TRY(cudaFuncSetAttribute(lbwalk::k_quals<K, 4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 100000 + lbwalk::QT + 32));
+                LB_TIMED(c->kt, "k_quals", c->st3, LB_LAUNCH(c->lc, (lbwalk::k_quals<K, 4, 4>), cdiv_u(R, lbwalk::QT), lbwalk::QT, smem, c->st3, bases,
+                          c->d_quals.as<uint8_t>(), offsets, R, c->bloom, c->d_tbl.as<uint64_t>(), c->opts.lossless, c->d_qout.as<uint8_t>(), stage_bytes));
+            }
             CUDA_TRY(cudaEventRecord(c->ev_q[1], c->st3));
             if (c->opts.qual_zlib_on_device) deflate_quals(c);
         }
@@ -1273,6 +1284,8 @@ int leon_upload(leon_ctx *c, const leon_reads *reads)
     LB_API_BEGIN
     CUDA_TRY(cudaSetDevice(c->opts.device));
     do_upload(c, reads);
+    CUDA_TRY(cudaStreamSynchronize(c->st));          // the caller's buffers are free again when this call returns
+    CUDA_TRY(cudaStreamSynchronize(c->st3));
     LB_API_END(c)
 }
 

@@ -11,6 +11,8 @@ namespace lbwalk {
 
 using lbcount::pack32;
 using lbcount::stage_reads;
+using lbcount::stage_reads_begin;
+using lbcount::stage_reads_wait;
 using lbcount::window_kmer;
 
 // what the walk leaves per read for the entropy stage
@@ -157,62 +159,110 @@ __global__ void __launch_bounds__(256) k_walk(const uint8_t *__restrict__ bases,
 // nb_solids[p] = number of Bloom-positive (canonical) k-mers of the read covering position p
 // (storeSolidCoverageInfo, C/DnaCoder.cpp:490-516), then smoothQuals/apply_smoothing_at_pos (:428-486).
 // Output text: quality string + '\n' per read at qout[offsets[r] + r].  `pref` = scratch, one u32 per k-mer slot.
-template <typename K> struct SolidFn {
-    const BloomDev &b; const uint64_t *tbl; int k; int lane;
-    uint32_t carry; uint32_t *pref;
-    LB_D bool operator()(uint64_t p, K kmer, bool active)
-    {
-        bool solid = active && bloom_contains<K>(b, kmer_canon(kmer, k), tbl);
-        unsigned bal = __ballot_sync(0xffffffffu, solid);
-        if (active) pref[p] = carry + __popc(bal & (0xffffffffu >> (31 - lane)));   // inclusive prefix count
-        carry += __popc(bal);
-        return false;
-    }
-};
-
-template <typename K>
-__global__ void __launch_bounds__(256) k_quals(const uint8_t *__restrict__ bases, const uint8_t *__restrict__ quals,
-                                               const uint64_t *__restrict__ offsets, const uint64_t *__restrict__ koff,
-                                               uint64_t nreads, BloomDev b, const uint64_t *__restrict__ tbl_g, int lossless,
-                                               uint32_t *__restrict__ pref_all, uint8_t *__restrict__ qout)
+// One THREAD per read (like k_walk): the bases of the CTA's QT reads are staged in shared memory by one bulk copy and
+// their qualities are copied straight to where the output text of the CTA (one contiguous range of qout, a newline
+// after every read) is assembled in shared memory; the canonical k-mer is rolled base by base, a k-bit shift register
+// of the last k contains() answers gives nb_solids at every position, the qualities are smoothed in place and the
+// text is written out with 16-byte stores.  stage_bytes = size of the bases area, the text area has stage_bytes + QT
+// + 32.  The 7 Bloom probes of QB consecutive k-mers are issued together, branch-free, so that QB hash chains
+// interleave and 7 * QB loads are in flight per thread (most k-mers of a read are solid: the early exit of contains()
+// would only serialise 7 L2 round trips).
+constexpr int QT = 128;
+template <typename K, int QB, int MINB>
+__global__ void __launch_bounds__(QT, MINB) k_quals(const uint8_t *__restrict__ bases, const uint8_t *__restrict__ quals,
+                                               const uint64_t *__restrict__ offsets, uint64_t nreads, BloomDev b,
+                                               const uint64_t *__restrict__ tbl_g, int lossless, uint8_t *__restrict__ qout,
+                                               uint32_t stage_bytes)
 {
+    extern __shared__ __align__(128) uint8_t qstage[];
     __shared__ uint64_t tbl[256];
-    tbl[threadIdx.x] = tbl_g[threadIdx.x];
-    __syncthreads();
+    __shared__ __align__(8) uint64_t bar;
+    for (int i = threadIdx.x; i < 256; i += QT) tbl[i] = tbl_g[i];
     const int k = b.k;
-    const int lane = threadIdx.x & 31;
-    uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
-    for (uint64_t r = warp; r < nreads; r += nwarps) {
-        uint64_t o = offsets[r], L = offsets[r + 1] - o;
-        const uint8_t *q = quals + o;
-        uint8_t *out = qout + o + r;
-        bool smooth = !lossless && L >= (uint64_t)k;
-        uint32_t *pref = pref_all + koff[r];
-        uint64_t n = 0;
-        if (smooth) {
-            n = L - k + 1;
-            SolidFn<K> f{b, tbl, k, lane, 0, pref};
-            lbanchor::warp_for_kmers<K>(bases + o, L, k, 0, n, lane, f);
-            __syncwarp();
+    const uint64_t r0 = (uint64_t)blockIdx.x * QT;
+    const uint64_t r1 = r0 + QT < nreads ? r0 + QT : nreads;
+    const uint64_t o0 = offsets[r0], o1 = offsets[r1];
+    // the CTA's text goes to qout[o0 + r0, o1 + r1): staged at the same offset modulo 16
+    uint8_t *gout = qout + o0 + r0;
+    const uint64_t out_bytes = (o1 - o0) + (r1 - r0);
+    const uint32_t mis = (uint32_t)((uintptr_t)gout & 15u);
+    // the bulk copy of the bases is in flight while the warps copy the qualities, one read per warp at a time
+    const uint8_t *sb = stage_reads_begin(bases, o0, o1, qstage, stage_bytes, &bar);
+    uint8_t *so = sb ? qstage + (uint64_t)stage_bytes + mis : nullptr;
+    if (so) {
+        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+        for (uint64_t t = warp; t < r1 - r0; t += QT / 32) {
+            const uint64_t o = offsets[r0 + t], L = offsets[r0 + t + 1] - o;
+            uint8_t *dst = so + (o - o0) + t;
+            for (uint64_t p = lane; p < L; p += 32) dst[p] = quals[o + p];
         }
-        for (uint64_t p = lane; p < L; p += 32) {
-            uint8_t c = q[p];
-            if (smooth) {
-                uint64_t hi_i = p < n ? p : n - 1;
-                uint32_t nb = pref[hi_i] - (p >= (uint64_t)k ? pref[p - k] : 0u);
+        stage_reads_wait(&bar);
+    }
+    __syncthreads();
+    const uint64_t r = r0 + threadIdx.x;
+    if (r < r1) {
+        const uint64_t o = offsets[r], L = offsets[r + 1] - o;
+        const uint8_t *s = sb ? sb + (o - o0) : bases + o;
+        uint8_t *out = so ? so + (o - o0) + (r - r0) : qout + o + r;
+        const uint8_t *q = so ? out : quals + o;                  // in place when staged
+        const bool smooth = !lossless && L >= (uint64_t)k;
+        if (!smooth) {
+            if (!so)
+                for (uint64_t p = 0; p < L; p++) out[p] = q[p];
+        } else {
+            const K mask = kmer_mask(K(0), k);
+            const int top = 2 * (k - 1);
+            const uint64_t wmask = (k >= 64) ? ~0ull : ((1ull << k) - 1ull);
+            K fwd = K(0), rc = K(0);
+            uint64_t window = 0;
+            auto roll = [&](uint8_t ch) {
+                const unsigned code = base_code_n_as_a(ch);
+                fwd = ((fwd << 2) | K((uint64_t)code)) & mask;
+                rc = (rc >> 2) | (K((uint64_t)(code ^ 2u)) << top);
+            };
+            auto emit = [&](uint64_t p, bool solid) {            // all k-mers covering position p are known now
+                window = ((window << 1) | (solid ? 1ull : 0ull)) & wmask;
+                const int nb = __popcll(window);
+                uint8_t c = q[p];
                 if (nb >= 2 || c > (uint8_t)'@') {
-                    int phred = (int)c - 33;
+                    const int phred = (int)c - 33;
                     if (!(phred == 0 || phred == 2)) {
-                        int diff = (int)'@' - (int)c;
-                        if (!(diff > 10 && !((int)nb > diff - 5))) c = '@';
+                        const int diff = (int)'@' - (int)c;
+                        if (!(diff > 10 && !(nb > diff - 5))) c = '@';
                     }
                 }
+                out[p] = c;
+            };
+            for (int i = 0; i < k - 1; i++) roll(s[i]);
+            const uint64_t n = L - (uint64_t)k + 1;
+            for (uint64_t j0 = 0; j0 < n; j0 += QB) {             // QB k-mers = 7 * QB probes in flight per thread
+                uint32_t w[QB][7];
+                uint64_t sh[QB];
+#pragma unroll
+                for (int jj = 0; jj < QB; jj++) {                 // past the last k-mer: the last base again, result unused
+                    const uint64_t bi = (uint64_t)k - 1 + j0 + jj;
+                    roll(s[bi < L ? bi : L - 1]);
+                    bloom_probe_issue<K>(b, fwd, rc, tbl, w[jj], sh[jj]);
+                }
+#pragma unroll
+                for (int jj = 0; jj < QB; jj++)
+                    if (j0 + jj < n) emit(j0 + jj, bloom_probe_test(w[jj], sh[jj]));
             }
-            out[p] = c;
+            for (uint64_t p = n; p < L; p++) emit(p, false);
         }
-        if (lane == 0) out[L] = '\n';
-        __syncwarp();
+        out[L] = '\n';
+    }
+    if (so) {                                                       // CTA-uniform
+        __syncthreads();
+        // head bytes up to the first 16-byte boundary, 16-byte body, tail bytes
+        const uint64_t head = mis ? (16 - mis < out_bytes ? 16 - mis : out_bytes) : 0;
+        const uint64_t body = (out_bytes - head) / 16;
+        if (threadIdx.x < head) gout[threadIdx.x] = so[threadIdx.x];
+        const uint4 *s4 = (const uint4 *)(so + head);
+        uint4 *g4 = (uint4 *)(gout + head);
+        for (uint64_t i = threadIdx.x; i < body; i += QT) g4[i] = s4[i];
+        const uint64_t done = head + body * 16;
+        if (threadIdx.x < out_bytes - done) gout[done + threadIdx.x] = so[done + threadIdx.x];
     }
 }
 
