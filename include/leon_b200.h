@@ -232,6 +232,11 @@ typedef struct leon_decoded leon_decoded;     /* decoded text of a stream, block
 /* Inverse of leon_headers_encode (C/HeaderCoder.cpp:526-789): the names of every block, one per line. */
 int  leon_headers_decode(const leon_header_stream *stream, int32_t nthreads, leon_decoded **out);
 int  leon_decode_dna(const leon_dna_stream *stream, int32_t nthreads, leon_decoded **out);
+/* The same stream decoded on GPU `device` (mirrors DnaDecoder::execute, C/DnaCoder.cpp:1221-1622): one
+ * warp per block runs the range decoder and the walk through the filter, the lanes share each step (model search, the 28
+ * bit tests of contains4).  Needs max_read_size >= 0.  kernel_ms (may be NULL): device time of the decoding kernel.
+ * Fails with LEON_E_CUDA when there is no usable device; there is no silent host substitute. */
+int  leon_decode_dna_device(const leon_dna_stream *stream, int32_t device, leon_decoded **out, float *kernel_ms);
 int  leon_decoded_block(const leon_decoded *d, uint64_t block, const uint8_t **text, uint64_t *nbytes);
 void leon_decoded_free(leon_decoded *d);
 
@@ -264,6 +269,9 @@ int leon_compress_file(const char *in_path, const char *out_path, const leon_fil
  * reference's) on host threads and writes <dir>/<prefix>.fasta.d or .fastq.d (out_path NULL) in the reference's
  * output layout.  stats: parse_ms = container, compress_ms = decoding, reserved1[0..1] = sequence / quality stream. */
 int leon_decompress_file(const char *in_path, const char *out_path, int32_t nthreads, leon_file_stats *stats);
+/* The same with the sequence stream decoded on GPU `device` (leon_decode_dna_device) while host threads decode the names
+ * and the qualities; stats->reserved1[2] = device time of the decoding kernel. */
+int leon_decompress_file_device(const char *in_path, const char *out_path, int32_t nthreads, int32_t device, leon_file_stats *stats);
 
 /* The record reader of leon_compress_file on its own (bank/impl/BankFasta.cpp:484-570): reads a FASTA/FASTQ file (multi-line
  * sequences, blank lines and CR LF accepted) into the layout leon_compress takes (exactly sized pageable host memory).

@@ -13,7 +13,7 @@ ABI_SYMBOLS = [
     "leon_get_timings", "leon_get_kernel_times", "leon_set_stream", "leon_comm_unique_id", "leon_comm_init",
     "leon_comm_batch_reads", "leon_debug_bloom_query", "leon_debug_hashes", "leon_debug_fetch", "leon_write_container",
     "leon_headers_encode", "leon_headers_free", "leon_compress_file", "leon_decompress_file", "leon_read_file", "leon_file_reads_free",
-    "leon_decode_dna", "leon_decoded_block", "leon_decoded_free", "leon_headers_decode",
+    "leon_decode_dna", "leon_decode_dna_device", "leon_decompress_file_device", "leon_decoded_block", "leon_decoded_free", "leon_headers_decode",
     "leon_container_open", "leon_container_close", "leon_container_has", "leon_container_dataset", "leon_container_attr",
 ]
 
@@ -150,6 +150,8 @@ def load_library(path=LIB_PATH):
     L.leon_file_reads_free.restype = None
     L.leon_headers_decode.argtypes = [C.POINTER(HeaderStream), C.c_int32, C.POINTER(C.c_void_p)]
     L.leon_decode_dna.argtypes = [C.POINTER(DnaStream), C.c_int32, C.POINTER(C.c_void_p)]
+    L.leon_decode_dna_device.argtypes = [C.POINTER(DnaStream), C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_float)]
+    L.leon_decompress_file_device.argtypes = [C.c_char_p, C.c_char_p, C.c_int32, C.c_int32, C.POINTER(FileStats)]
     L.leon_decoded_block.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.POINTER(C.c_uint8)), C.POINTER(C.c_uint64)]
     L.leon_decoded_free.argtypes = [C.c_void_p]
     L.leon_decoded_free.restype = None
@@ -202,10 +204,7 @@ def decode_headers(header, nthreads=0):
         L.leon_decoded_free(h)
 
 
-def decode_dna(result, kmer_size, nthreads=0):
-    """Decodes the sequence stream of a result dict (bloom, bloom_bits, anchors_dict, anchor_count, blocksizes, dna,
-    max_read_size) back to reads: returns a list of bytes, one per read (C/DnaCoder.cpp:1221-1622)."""
-    L = load_library()
+def _dna_stream(result, kmer_size):
     keep = [np.ascontiguousarray(result[k], np.uint8) for k in ("bloom", "anchors_dict", "dna")]
     bs = np.ascontiguousarray(result["blocksizes"], np.uint64)
     # the filter is read 8 bytes at a time: pad it like the device copy
@@ -213,14 +212,39 @@ def decode_dna(result, kmer_size, nthreads=0):
     s = DnaStream(int(kmer_size), int(result.get("max_read_size", -1)), bloom.ctypes.data, len(bloom), int(result["bloom_bits"]),
                   keep[1].ctypes.data, len(keep[1]), int(result["anchor_count"]), len(bs) // 2, bs.ctypes.data,
                   keep[2].ctypes.data, len(keep[2]))
+    return s, (keep, bs, bloom)
+
+
+def decode_dna(result, kmer_size, nthreads=0):
+    """Decodes the sequence stream of a result dict (bloom, bloom_bits, anchors_dict, anchor_count, blocksizes, dna,
+    max_read_size) back to reads: returns a list of bytes, one per read (C/DnaCoder.cpp:1221-1622)."""
+    L = load_library()
+    s, keep = _dna_stream(result, kmer_size)
     h = C.c_void_p()
     rc = L.leon_decode_dna(C.byref(s), int(nthreads), C.byref(h))
     if rc != 0:
         raise LeonError(rc, L.leon_last_error(None).decode())
     try:
-        return _decoded_lines(L, h, len(bs) // 2)
+        return _decoded_lines(L, h, int(s.nblocks))
     finally:
         L.leon_decoded_free(h)
+
+
+def decode_dna_device(result, kmer_size, device=0, with_time=False):
+    """decode_dna on the GPU (k_decode_blocks, one warp per block); result needs max_read_size.  with_time: also the
+    kernel's device time in ms."""
+    L = load_library()
+    s, keep = _dna_stream(result, kmer_size)
+    h = C.c_void_p()
+    ms = C.c_float(0)
+    rc = L.leon_decode_dna_device(C.byref(s), int(device), C.byref(h), C.byref(ms))
+    if rc != 0:
+        raise LeonError(rc, L.leon_last_error(None).decode())
+    try:
+        lines = _decoded_lines(L, h, int(s.nblocks))
+    finally:
+        L.leon_decoded_free(h)
+    return (lines, ms.value) if with_time else lines
 
 
 class Container:
@@ -300,6 +324,17 @@ def compress_file(in_path, out_path=None, kmer_size=31, reads_per_block=50000, l
     d = {n: getattr(st, n) for n, _ in FileStats._fields_ if not n.startswith("reserved") and n != "gpu"}
     d["gpu"] = {n: getattr(st.gpu, n) for n, _ in Timings._fields_ if n != "reserved"}
     return d
+
+
+def decompress_file_device(in_path, out_path=None, nthreads=0, device=0):
+    """decompress_file with the sequence stream decoded on the GPU (names and qualities on host threads beside it)."""
+    L = load_library()
+    st = FileStats()
+    rc = L.leon_decompress_file_device(os.fsencode(in_path), os.fsencode(out_path) if out_path else None, int(nthreads),
+                                       int(device), C.byref(st))
+    if rc != 0:
+        raise LeonError(rc, L.leon_last_error(None).decode())
+    return st
 
 
 def decompress_file(in_path, out_path=None, nthreads=0):

@@ -1,8 +1,9 @@
 // Command line of the B200 path, option for option the `leon -c` of the reference (C/Leon.cpp:102-140):
 //   leon_b200 -file reads.fastq -c [-kmer-size 31] [-abundance N] [-nb-cores N] [-lossless] [-seq-only] [-noheader]
 //             [-noqual] [-reads 50000] [-out file.leon] [-device 0] [-verbose 0|1]
-//   leon_b200 -file reads.fastq.leon -d [-nb-cores N] [-out file]
-// -c writes reads.fastq.leon, which the reference's `leon -d` decodes too; -d reads containers of either tool (host threads).
+//   leon_b200 -file reads.fastq.leon -d [-nb-cores N] [-out file] [-gpu-decode] [-device 0]
+// -c writes reads.fastq.leon, which the reference's `leon -d` decodes too; -d reads containers of either tool: the
+// sequence stream on host threads, or with -gpu-decode one warp per block on the GPU (k_decode_blocks).
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -13,7 +14,7 @@
 static void usage() {
     fprintf(stderr,
             "usage: leon_b200 -file <in.fa|in.fasta|in.fq|in.fastq> -c [options]\n"
-            "       leon_b200 -file <in.leon> -d [-nb-cores N] [-out FILE]\n"
+            "       leon_b200 -file <in.leon> -d [-nb-cores N] [-out FILE] [-gpu-decode] [-device N]\n"
             "  -kmer-size N   k-mer size, 2..63 (default 31)\n"
             "  -abundance N   abundance threshold given explicitly (disables the automatic cutoff)\n"
             "  -nb-cores N    host threads for the header stream and zlib (default: all)\n"
@@ -24,6 +25,7 @@ static void usage() {
             "  -reads N       reads per block (default 50000)\n"
             "  -out FILE      output file (default: <in>.leon)\n"
             "  -device N      CUDA device (default 0)\n"
+            "  -gpu-decode    with -d: decode the sequence stream on the GPU (one warp per block)\n"
             "  -verbose N     0: quiet, 1: summary (default 1)\n");
 }
 
@@ -31,7 +33,7 @@ int main(int argc, char **argv) {
     leon_file_opts o;
     memset(&o, 0, sizeof o);
     std::string in, out;
-    bool compress = false, decompress = false;
+    bool compress = false, decompress = false, gpu_decode = false;
     int verbose = 1;
     for (int i = 1; i < argc; i++) {
         std::string a = argv[i];
@@ -52,6 +54,7 @@ int main(int argc, char **argv) {
         else if (a == "-reads") o.reads_per_block = atoi(value("-reads"));
         else if (a == "-out") out = value("-out");
         else if (a == "-device") o.device = atoi(value("-device"));
+        else if (a == "-gpu-decode") gpu_decode = true;
         else if (a == "-verbose") verbose = atoi(value("-verbose"));
         else if (a == "-h" || a == "-help" || a == "--help") { usage(); return 0; }
         else { fprintf(stderr, "unknown option %s\n", a.c_str()); usage(); return 2; }
@@ -59,7 +62,8 @@ int main(int argc, char **argv) {
     if (in.empty() || compress == decompress) { usage(); return 2; }
     leon_file_stats s;
     if (decompress) {
-        int rc = leon_decompress_file(in.c_str(), out.empty() ? nullptr : out.c_str(), o.nthreads, &s);
+        int rc = gpu_decode ? leon_decompress_file_device(in.c_str(), out.empty() ? nullptr : out.c_str(), o.nthreads, o.device, &s)
+                            : leon_decompress_file(in.c_str(), out.empty() ? nullptr : out.c_str(), o.nthreads, &s);
         if (rc) {
             fprintf(stderr, "leon_b200: error %d: %s\n", rc, leon_last_error(nullptr));
             return 1;
@@ -69,6 +73,7 @@ int main(int argc, char **argv) {
                    (unsigned long long)s.nblocks, s.is_fasta ? "FASTA" : "FASTQ", s.has_header ? "stored" : "numbered");
             printf("time: container %.1f ms, decode %.1f ms (sequences %.1f ms, headers %.1f ms, qualities %.1f ms, side by side), write %.1f ms, total %.1f ms\n",
                    s.parse_ms, s.compress_ms, s.reserved1[0], s.header_ms, s.reserved1[1], s.write_ms, s.total_ms);
+            if (gpu_decode) printf("sequences on the GPU: k_decode_blocks %.1f ms\n", s.reserved1[2]);
         }
         return 0;
     }

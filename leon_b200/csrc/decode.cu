@@ -19,6 +19,7 @@
 #include "decoded.h"
 #include "kmer_math.cuh"
 #include "simplehash_table.h"
+#include "decode_device.cuh"
 
 extern "C" void leon_internal_set_error(const char *msg);
 
@@ -293,6 +294,106 @@ int decode_dna(const leon_dna_stream *s, int nthreads, std::vector<std::string> 
     return LEON_OK;
 }
 
+// ---- the same stream decoded on the GPU: k_decode_blocks (decode_device.cuh), one warp per block --------------------
+// The anchor dictionary is one never-reset coder over all anchors (C/Leon.cpp:1948-2007), a single dependent chain: it
+// is decoded by the calling host thread (like its encoder) while the filter and the blocks are uploaded.
+template <typename K>
+int decode_dna_device(const leon_dna_stream *s, int device, std::vector<std::string> &blocks, float *kernel_ms, std::string &err) {
+    if (s->max_read_size < 0) { err = "the device decoder needs max_read_size (metadata/maxSequenceSize) to size its output"; return LEON_E_ARG; }
+    if (s->bloom_nbytes < s->bloom_bits / 8 + 8) { err = "Bloom array shorter than its size attribute says"; return LEON_E_ARG; }
+    std::vector<uint64_t> start(s->nblocks + 1, 0);
+    for (uint64_t b = 0; b < s->nblocks; b++) start[b + 1] = start[b] + s->blocksizes[2 * b];
+    if (start[s->nblocks] > s->dna_nbytes) { err = "blocksizes exceed dna_nbytes"; return LEON_E_ARG; }
+    blocks.assign(s->nblocks, std::string());
+    if (!s->nblocks) return LEON_OK;
+    DevBuf d_bloom, d_tbl, d_anchors, d_dna, d_blocks, d_ws, d_out, d_len, d_status;
+    cudaStream_t st = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    int rc = LEON_OK;
+    try {
+        CUDA_TRY(cudaSetDevice(device));
+        CUDA_TRY(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        int sms = 0;
+        CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+        const uint64_t max_read = (uint64_t)s->max_read_size;
+        std::vector<lbdd::BlockIn> bin(s->nblocks);
+        uint64_t out_total = 0;
+        for (uint64_t b = 0; b < s->nblocks; b++) {
+            bin[b] = lbdd::BlockIn{start[b], s->blocksizes[2 * b], s->blocksizes[2 * b + 1], out_total};
+            out_total += s->blocksizes[2 * b + 1] * (max_read + 1);
+        }
+        const uint32_t map_words = (uint32_t)((max_read + 31) / 32 + 1);
+        const size_t smem = 2048 + 2 * (size_t)map_words * 4;
+        if (smem > 200 * 1024) throw LeonError(LEON_E_ARG, "reads longer than the device decoder's position bitmaps hold");
+        const unsigned grid = (unsigned)std::min<uint64_t>(s->nblocks, (uint64_t)sms * 8);
+        d_bloom.reserve(s->bloom_nbytes + 16);
+        d_tbl.reserve(256 * 8);
+        d_dna.reserve(s->dna_nbytes + 16);
+        d_blocks.reserve(bin.size() * sizeof(lbdd::BlockIn));
+        d_ws.reserve((size_t)grid * lbdd::MODEL_WORDS * 4);
+        d_out.reserve(out_total + 16);
+        d_len.reserve(s->nblocks * 8);
+        d_status.reserve(s->nblocks * 4);
+        CUDA_TRY(cudaMemsetAsync(d_bloom.p, 0, s->bloom_nbytes + 16, st));
+        CUDA_TRY(cudaMemcpyAsync(d_bloom.p, s->bloom, s->bloom_nbytes, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync(d_tbl.p, kSimpleHashTable, 256 * 8, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync(d_dna.p, s->dna, s->dna_nbytes, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync(d_blocks.p, bin.data(), bin.size() * sizeof(lbdd::BlockIn), cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemsetAsync(d_status.p, 0xff, s->nblocks * 4, st));
+        std::vector<K> anchors;
+        decode_anchor_dict<K>(s->anchors_dict, s->anchors_dict_nbytes, s->anchor_count, s->kmer_size, anchors);
+        d_anchors.reserve(anchors.size() * sizeof(K) + 16);
+        CUDA_TRY(cudaMemcpyAsync(d_anchors.p, anchors.data(), anchors.size() * sizeof(K), cudaMemcpyHostToDevice, st));
+        BloomDev bloom;
+        memset(&bloom, 0, sizeof bloom);
+        bloom.k = s->kmer_size;
+        bloom.words = d_bloom.as<uint32_t>();
+        bloom.reduced_tai = s->bloom_bits;
+        bloom.magic = s->bloom_bits ? ~0ull / s->bloom_bits : 0;
+        bloom.nbytes = s->bloom_nbytes;
+        CUDA_TRY(cudaFuncSetAttribute(lbdd::k_decode_blocks<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CUDA_TRY(cudaEventCreate(&e0));
+        CUDA_TRY(cudaEventCreate(&e1));
+        CUDA_TRY(cudaEventRecord(e0, st));
+        lbdd::k_decode_blocks<K><<<grid, 32, smem, st>>>(bloom, d_tbl.as<uint64_t>(), d_anchors.as<K>(), (uint64_t)anchors.size(),
+                                                          d_dna.as<uint8_t>(), d_blocks.as<lbdd::BlockIn>(), s->nblocks, d_ws.as<uint32_t>(),
+                                                          d_out.as<uint8_t>(), d_len.as<uint64_t>(), d_status.as<uint32_t>(),
+                                                          (uint32_t)max_read, map_words);
+        CUDA_TRY(cudaGetLastError());
+        CUDA_TRY(cudaEventRecord(e1, st));
+        std::vector<uint64_t> len(s->nblocks);
+        std::vector<uint32_t> status(s->nblocks);
+        CUDA_TRY(cudaMemcpyAsync(len.data(), d_len.p, s->nblocks * 8, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaMemcpyAsync(status.data(), d_status.p, s->nblocks * 4, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        if (kernel_ms) CUDA_TRY(cudaEventElapsedTime(kernel_ms, e0, e1));
+        static const char *const why[] = {"", "corrupt block: anchor address, anchor position or read length out of range",
+                                          "corrupt block: more N positions than bases", "corrupt block: more error positions than bases",
+                                          "sequencing error recorded where the graph has no successor", "corrupt block: read length out of range"};
+        for (uint64_t b = 0; b < s->nblocks && rc == LEON_OK; b++) {
+            if (status[b] != lbdd::DE_OK) {
+                err = "block " + std::to_string(b) + ": " + (status[b] < 6 ? why[status[b]] : "not decoded");
+                rc = LEON_E_ARG;
+            }
+        }
+        if (rc == LEON_OK) {
+            for (uint64_t b = 0; b < s->nblocks; b++) {
+                blocks[b].resize((size_t)len[b]);
+                if (len[b]) CUDA_TRY(cudaMemcpyAsync(&blocks[b][0], d_out.as<uint8_t>() + bin[b].out_off, len[b], cudaMemcpyDeviceToHost, st));
+            }
+            CUDA_TRY(cudaStreamSynchronize(st));
+        }
+    } catch (const LeonError &e) {
+        err = e.msg;
+        rc = e.code;
+    }
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    if (st) cudaStreamDestroy(st);
+    for (DevBuf *b : {&d_bloom, &d_tbl, &d_anchors, &d_dna, &d_blocks, &d_ws, &d_out, &d_len, &d_status}) b->release();
+    return rc;
+}
+
 }  // namespace lbdecode
 
 
@@ -309,6 +410,23 @@ extern "C" int leon_decode_dna(const leon_dna_stream *s, int32_t nthreads, leon_
         return LEON_OK;
     } catch (const std::bad_alloc &) {
         leon_internal_set_error("leon_decode_dna: out of host memory");
+        return LEON_E_NOMEM;
+    }
+}
+
+extern "C" int leon_decode_dna_device(const leon_dna_stream *s, int32_t device, leon_decoded **out, float *kernel_ms) {
+    try {
+        if (!s || !out || !s->bloom || (s->nblocks && (!s->dna || !s->blocksizes))) { leon_internal_set_error("leon_decode_dna_device: null argument"); return LEON_E_ARG; }
+        if (s->kmer_size < 2 || s->kmer_size > 63) { leon_internal_set_error("leon_decode_dna_device: bad kmer_size"); return LEON_E_ARG; }
+        std::unique_ptr<leon_decoded> d(new leon_decoded());
+        std::string err;
+        const int rc = s->kmer_size <= 31 ? lbdecode::decode_dna_device<uint64_t>(s, device, d->blocks, kernel_ms, err)
+                                          : lbdecode::decode_dna_device<u128>(s, device, d->blocks, kernel_ms, err);
+        if (rc) { leon_internal_set_error(("leon_decode_dna_device: " + err).c_str()); return rc; }
+        *out = d.release();
+        return LEON_OK;
+    } catch (const std::bad_alloc &) {
+        leon_internal_set_error("leon_decode_dna_device: out of host memory");
         return LEON_E_NOMEM;
     }
 }

@@ -87,7 +87,8 @@ inline bool next_line(const std::string &s, size_t &pos, const char **line, size
 
 }  // namespace
 
-extern "C" int leon_decompress_file(const char *in_path, const char *out_path, int32_t nthreads, leon_file_stats *stats) {
+// device < 0: the sequence stream on host threads (leon_decode_dna); device >= 0: on that GPU (leon_decode_dna_device)
+static int decompress_file_impl(const char *in_path, const char *out_path, int32_t nthreads, int32_t device, leon_file_stats *stats) {
     leon_container *c = nullptr;
     leon_decoded *dna = nullptr, *names = nullptr;
     int rc = LEON_OK;
@@ -197,7 +198,8 @@ extern "C" int leon_decompress_file(const char *in_path, const char *out_path, i
             });
         }
         const double t1 = now_ms();
-        const int drc = leon_decode_dna(&ds, nthreads, &dna);
+        float dna_kernel_ms = 0;
+        const int drc = device >= 0 ? leon_decode_dna_device(&ds, device, &dna, &dna_kernel_ms) : leon_decode_dna(&ds, nthreads, &dna);
         std::string derr = drc ? leon_last_error(nullptr) : "";
         dna_ms = now_ms() - t1;
         if (header_thread.joinable()) header_thread.join();
@@ -261,6 +263,7 @@ extern "C" int leon_decompress_file(const char *in_path, const char *out_path, i
             stats->total_ms = (float)(t3 - t0);
             stats->reserved1[0] = (float)dna_ms;
             stats->reserved1[1] = (float)qual_ms;
+            stats->reserved1[2] = dna_kernel_ms;         // device time of k_decode_blocks (0 on host threads)
         }
     } catch (const Fail &fl) {
         rc = fl.code;
@@ -277,4 +280,13 @@ extern "C" int leon_decompress_file(const char *in_path, const char *out_path, i
     if (c) leon_container_close(c);
     if (rc) leon_internal_set_error(err.c_str());
     return rc;
+}
+
+extern "C" int leon_decompress_file(const char *in_path, const char *out_path, int32_t nthreads, leon_file_stats *stats) {
+    return decompress_file_impl(in_path, out_path, nthreads, -1, stats);
+}
+
+extern "C" int leon_decompress_file_device(const char *in_path, const char *out_path, int32_t nthreads, int32_t device, leon_file_stats *stats) {
+    if (device < 0) { leon_internal_set_error("leon_decompress_file_device: device must be >= 0"); return LEON_E_ARG; }
+    return decompress_file_impl(in_path, out_path, nthreads, device, stats);
 }
