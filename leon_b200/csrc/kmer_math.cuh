@@ -143,6 +143,19 @@ struct BloomDev {
     int k;
 };
 
+// One filter word of a probe whose result is consumed later: a volatile asm keeps the loads of a probe (and of the
+// probes a caller wants in flight together) in program order ahead of their uses.  With plain __ldg the compiler sank
+// each pair of loads down to its funnel shift in k_walk -- 5 dependent round trips per step instead of 1 -- which cost
+// 3x at configs[3] scale, where every probe goes to DRAM (profiles/r1g_c4_walk_ncu_metrics.json).
+#ifdef __CUDACC__
+__device__ __forceinline__ uint32_t bloom_ldw(const uint32_t *p)
+{
+    uint32_t v;
+    asm volatile("ld.global.nc.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+#endif
+
 LB_HD uint64_t umulhi64(uint64_t a, uint64_t b)
 {
 #ifdef __CUDA_ARCH__
@@ -215,12 +228,12 @@ template <typename K> LB_D void bloom_probe_issue(const BloomDev &b, K fwd, K rc
     rr -= rr >= b.reduced_tai ? b.reduced_tai : 0;
     rr -= rr >= b.reduced_tai ? b.reduced_tai : 0;
     const uint64_t h0 = rr + bloom_prefval(item, b.k);
-    w[0] = __ldg(b.words + (h0 >> 5));
+    w[0] = bloom_ldw(b.words + (h0 >> 5));
     sh = h0 & 31u;
 #pragma unroll
     for (int i = 1; i < 7; i++) {
         const uint64_t h1 = h0 + (kmer_simplehash16(hp, i, tbl) & 4095);
-        w[i] = __ldg(b.words + (h1 >> 5));
+        w[i] = bloom_ldw(b.words + (h1 >> 5));
         sh |= (h1 & 31u) << (5 * i);
     }
 }

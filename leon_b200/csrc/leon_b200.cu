@@ -982,14 +982,8 @@ template <typename K> void do_encode_body(leon_ctx *c)
         // bases of the 256 reads of a CTA are staged in shared memory when they fit (40 KB), else read from global
         uint64_t need = ((256ull * (uint64_t)c->max_len + 31) & ~15ull) + 16;
         uint32_t stage_bytes = need <= 40960 ? (uint32_t)need : 16u;
-        // LEON_B200_WALK_KEEP=1 (experiment): filter words loaded with an L2 evict_last policy
-        static const bool keep = getenv("LEON_B200_WALK_KEEP") && atoi(getenv("LEON_B200_WALK_KEEP")) != 0;
-        if (keep)
-            LB_TIMED(c->kt, "k_walk", st, LB_LAUNCH(c->lc, (lbwalk::k_walk<K, true>), cdiv_u(R, 256), 256, stage_bytes, st, bases, offsets, koff, R, c->bloom,
-                      c->d_tbl.as<uint64_t>(), apos, c->d_bif.as<uint8_t>(), c->d_err.as<uint32_t>(), c->d_recs.as<lbwalk::ReadRec>(), stage_bytes));
-        else
-            LB_TIMED(c->kt, "k_walk", st, LB_LAUNCH(c->lc, (lbwalk::k_walk<K, false>), cdiv_u(R, 256), 256, stage_bytes, st, bases, offsets, koff, R, c->bloom,
-                      c->d_tbl.as<uint64_t>(), apos, c->d_bif.as<uint8_t>(), c->d_err.as<uint32_t>(), c->d_recs.as<lbwalk::ReadRec>(), stage_bytes));
+        LB_TIMED(c->kt, "k_walk", st, LB_LAUNCH(c->lc, (lbwalk::k_walk<K>), cdiv_u(R, 256), 256, stage_bytes, st, bases, offsets, koff, R, c->bloom,
+                  c->d_tbl.as<uint64_t>(), apos, c->d_bif.as<uint8_t>(), c->d_err.as<uint32_t>(), c->d_recs.as<lbwalk::ReadRec>(), stage_bytes));
     }
     CUDA_TRY(cudaEventRecord(c->ev[9], st));
 

@@ -35,21 +35,8 @@ template <typename K> LB_D K seed_step(K kmer, unsigned nt, bool right, int k)  
 // caller).  The 28 tested bits are racine + cano2(c) + {0, simplehash16(i) & 4095}: for each of the 7 hashes the four
 // candidates sit inside one 14-bit field, so a query is 7 independent 2-word gathers (no early exit: in a walk one of
 // the four neighbours is almost always present and needs all 7).  tbl12 = low 12 bits of the simplehash16 table.
-// KEEP: the filter words are loaded with an L2 evict_last policy (filters larger than what L2 keeps by itself).
-LB_D uint64_t l2_keep_policy()
-{
-    uint64_t pol;
-    asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
-    return pol;
-}
-LB_D uint32_t ldg_keep(const uint32_t *p, uint64_t pol)
-{
-    uint32_t v;
-    asm("ld.global.nc.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
-    return v;
-}
-template <typename K, bool KEEP = false>
-LB_D unsigned thread_contains4(const BloomDev &b, K fwd, K rc, bool right, const uint16_t *tbl12, uint64_t pol = 0)
+template <typename K>
+LB_D unsigned thread_contains4(const BloomDev &b, K fwd, K rc, bool right, const uint16_t *tbl12)
 {
     const int k = b.k;
     const K m2 = kmer_mask(K(0), k - 2);
@@ -76,14 +63,21 @@ LB_D unsigned thread_contains4(const BloomDev &b, K fwd, K rc, bool right, const
         if (i) off = (tbl12[(hlow >> i) & 255] ^ tbl12[(hlow >> (i + 8)) & 255] ^ t0) & 4095u;
         uint64_t bit = racine + off;
         const uint32_t *w = b.words + (bit >> 5);
-        w0[i] = KEEP ? ldg_keep(w, pol) : __ldg(w);
-        w1[i] = KEEP ? ldg_keep(w + 1, pol) : __ldg(w + 1);
+        w0[i] = bloom_ldw(w);
+        w1[i] = bloom_ldw(w + 1);
         sh[i] = (unsigned)bit & 31u;
     }
+    // All 14 loads must be in flight together: a warp issues in order, and ptxas otherwise puts each funnel shift right
+    // behind its pair of loads (5 dependent round trips per step; 3x slower where the probes go to DRAM).  z is always 0
+    // (nbytes < 2^63) but only at run time, and it depends on every loaded word, so no shift can issue before the last load.
+    uint32_t any = 0;
+#pragma unroll
+    for (int i = 0; i < 7; i++) any |= w0[i] | w1[i];
+    const uint32_t z = any & (uint32_t)(b.nbytes >> 63);
     unsigned alive = 15u;
 #pragma unroll
     for (int i = 0; i < 7; i++) {
-        uint32_t f = __funnelshift_r(w0[i], w1[i], sh[i]);        // 32 filter bits starting at racine + off
+        uint32_t f = __funnelshift_r(w0[i], w1[i], sh[i] | z);    // 32 filter bits starting at racine + off
         alive &= ((f >> p0) & 1u) | (((f >> p1) & 1u) << 1) | (((f >> p2) & 1u) << 2) | (((f >> p3) & 1u) << 3);
     }
     return alive;
@@ -91,7 +85,7 @@ LB_D unsigned thread_contains4(const BloomDev &b, K fwd, K rc, bool right, const
 
 // One thread per read.  Left walk (positions anchor-1 .. 0) then right walk (anchor+k .. L-1), as one loop of L-k
 // direction-generic steps so that the threads of a warp stay converged whatever their anchor positions.
-template <typename K, bool KEEP = false>
+template <typename K>
 __global__ void __launch_bounds__(256) k_walk(const uint8_t *__restrict__ bases, const uint64_t *__restrict__ offsets,
                                               const uint64_t *__restrict__ koff, uint64_t nreads, BloomDev b,
                                               const uint64_t *__restrict__ tbl_g, const int32_t *__restrict__ apos,
@@ -103,7 +97,6 @@ __global__ void __launch_bounds__(256) k_walk(const uint8_t *__restrict__ bases,
     __shared__ __align__(8) uint64_t bar;
     tbl12[threadIdx.x] = (uint16_t)(tbl_g[threadIdx.x] & 4095u);
     const int k = b.k;
-    const uint64_t pol = KEEP ? l2_keep_policy() : 0ull;
     const uint64_t r0 = (uint64_t)blockIdx.x * 256;
     const uint64_t r1 = r0 + 256 < nreads ? r0 + 256 : nreads;
     const uint64_t o0 = offsets[r0];
@@ -137,7 +130,7 @@ __global__ void __launch_bounds__(256) k_walk(const uint8_t *__restrict__ bases,
             unsigned nt = 0;
             if (c != 'N') {   // at an N the walk advances with 'A' and emits nothing (C/DnaCoder.cpp:772-790)
                 const unsigned ntb = leon_nt2bin(c);
-                const unsigned res4 = thread_contains4<K, KEEP>(b, fwd, rc, right, tbl12, pol);
+                const unsigned res4 = thread_contains4<K>(b, fwd, rc, right, tbl12);
                 const int cnt = __popc(res4);
                 const unsigned first = res4 ? (unsigned)(__ffs(res4) - 1) : 0u;
                 const bool solid = (res4 >> ntb) & 1u;

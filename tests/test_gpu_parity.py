@@ -191,3 +191,4 @@ def test_indels_n_runs_variable_lengths(k, fastq, lossless, seed):
     r = eng.compress(bases, offs, quals)
     eng.close()
     _same(r, ref, fastq)
+
