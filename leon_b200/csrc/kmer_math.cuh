@@ -154,6 +154,12 @@ __device__ __forceinline__ uint32_t bloom_ldw(const uint32_t *p)
     asm volatile("ld.global.nc.u32 %0, [%1];" : "=r"(v) : "l"(p));
     return v;
 }
+__device__ __forceinline__ uint2 bloom_ldw2(const uint2 *p)      // 8-byte aligned
+{
+    uint2 v;
+    asm volatile("ld.global.nc.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+    return v;
+}
 #endif
 
 LB_HD uint64_t umulhi64(uint64_t a, uint64_t b)

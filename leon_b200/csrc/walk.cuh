@@ -55,29 +55,36 @@ LB_D unsigned thread_contains4(const BloomDev &b, K fwd, K rc, bool right, const
     }
     const uint64_t hlow = kmer_low64(hp);
     const unsigned t0 = sizeof(K) == 8 ? tbl12[hlow & 255] : 0u;     // third table term of the one-word variant
-    uint32_t w0[7], w1[7];
+    // Per hash: the aligned 64-bit word holding bit racine + off, plus (13 positions out of 64) the low half of the next
+    // one when the 14-bit field of the four candidates runs past it: 7 LDG.64 and 7 mostly predicated-off LDG per step
+    // instead of 14 LDG (the kernel is L1-request bound when the filter sits in L2).
+    uint32_t lo[7], hi[7], nx[7];
     unsigned sh[7];
 #pragma unroll
     for (int i = 0; i < 7; i++) {
         unsigned off = 0;
         if (i) off = (tbl12[(hlow >> i) & 255] ^ tbl12[(hlow >> (i + 8)) & 255] ^ t0) & 4095u;
         uint64_t bit = racine + off;
-        const uint32_t *w = b.words + (bit >> 5);
-        w0[i] = bloom_ldw(w);
-        w1[i] = bloom_ldw(w + 1);
-        sh[i] = (unsigned)bit & 31u;
+        const uint2 *w = (const uint2 *)b.words + (bit >> 6);
+        sh[i] = (unsigned)bit & 63u;
+        const uint2 q = bloom_ldw2(w);
+        lo[i] = q.x;
+        hi[i] = q.y;
+        nx[i] = 0;
+        if (sh[i] > 50u) nx[i] = bloom_ldw((const uint32_t *)(w + 1));
     }
-    // All 14 loads must be in flight together: a warp issues in order, and ptxas otherwise puts each funnel shift right
-    // behind its pair of loads (5 dependent round trips per step; 3x slower where the probes go to DRAM).  z is always 0
+    // All loads of a step must be in flight together: a warp issues in order, and ptxas otherwise puts each funnel shift
+    // right behind its own loads (5 dependent round trips per step; 3x slower where the probes go to DRAM).  z is always 0
     // (nbytes < 2^63) but only at run time, and it depends on every loaded word, so no shift can issue before the last load.
     uint32_t any = 0;
 #pragma unroll
-    for (int i = 0; i < 7; i++) any |= w0[i] | w1[i];
+    for (int i = 0; i < 7; i++) any |= lo[i] | hi[i] | nx[i];
     const uint32_t z = any & (uint32_t)(b.nbytes >> 63);
     unsigned alive = 15u;
 #pragma unroll
     for (int i = 0; i < 7; i++) {
-        uint32_t f = __funnelshift_r(w0[i], w1[i], sh[i] | z);    // 32 filter bits starting at racine + off
+        const bool up = sh[i] >= 32u;
+        const uint32_t f = __funnelshift_r(up ? hi[i] : lo[i], up ? nx[i] : hi[i], (sh[i] & 31u) | z);   // filter bits from racine + off on
         alive &= ((f >> p0) & 1u) | (((f >> p1) & 1u) << 1) | (((f >> p2) & 1u) << 2) | (((f >> p3) & 1u) << 3);
     }
     return alive;
@@ -86,7 +93,7 @@ LB_D unsigned thread_contains4(const BloomDev &b, K fwd, K rc, bool right, const
 // One thread per read.  Left walk (positions anchor-1 .. 0) then right walk (anchor+k .. L-1), as one loop of L-k
 // direction-generic steps so that the threads of a warp stay converged whatever their anchor positions.
 template <typename K>
-__global__ void __launch_bounds__(256) k_walk(const uint8_t *__restrict__ bases, const uint64_t *__restrict__ offsets,
+__global__ void __launch_bounds__(256, sizeof(K) == 8 ? 4 : 3) k_walk(const uint8_t *__restrict__ bases, const uint64_t *__restrict__ offsets,
                                               const uint64_t *__restrict__ koff, uint64_t nreads, BloomDev b,
                                               const uint64_t *__restrict__ tbl_g, const int32_t *__restrict__ apos,
                                               uint8_t *__restrict__ bif, uint32_t *__restrict__ err, ReadRec *__restrict__ recs,
