@@ -1,13 +1,17 @@
 #!/usr/bin/env python3
-"""bench.py — throughput of the Leon compression hot path (leon -c sequence stream) on B200.
+"""bench.py — throughput of the Leon compression hot path (leon -c: count -> Bloom -> anchors -> walk -> range coding,
+plus lossy quality smoothing and the quality blocks' zlib streams) on B200.
 
-    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path (torchrun for N > 1)
     python bench.py --impl reference --steps K --warmup W     # the reference's own CPU implementation (oracle/_ref/leon)
 
-A step = one pass of the whole hot path (k-mer counting -> Bloom build -> anchors -> walk -> range coding) over the
-BASELINE.json configs[1] read set (4.6 Mbp random genome, 100 bp reads at 100x, 0.5 % substitutions, k=31,
-sequence only).  `value` = reads/s with the read set already resident in HBM; `e2e` = the same through the C ABI with
-pinned HOST buffers (H2D of the reads and D2H of every output inside the timed region).  One JSON line on stdout.
+Workload = BASELINE.json configs[2] (the configuration the metric is quoted on at 1/2/4/8 GPUs): 4.6 Mbp genome, 4.6 M x
+100 bp FASTQ reads, lossy qualities, k = 31.  A step = one pass of the whole hot path over that read set.  `value` =
+reads/s with the read set already resident in HBM; `e2e` = the same through the C ABI with pinned HOST buffers (H2D of
+the reads and D2H of every output inside the timed region).  Both arms use the SAME full-size seeded read set; every
+line carries `output_digest` / `digest_ok`: the digest of all output streams against the one committed from a run of the
+unmodified reference with -nb-cores 1 on that exact read set (tests/golden/digest_*.json, tools/make_digest.py).
+configs[1] (FASTA, seq-only) is measured as the extra key `configs1`.  One JSON line on stdout.
 """
 import argparse
 import json
@@ -25,13 +29,12 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-METRIC = "reads/s compressed (leon -c sequence stream: count + bloom + anchors + walk + range coding)"
-GENOME_LEN = 4_600_000
-READ_LEN = 100
-COVERAGE = 100
-KMER = 31
-RPB = 50000
-WORKLOAD = "configs[1]: 4.6 Mbp random genome, 100 bp FASTA reads at 100x, 0.5% substitutions, k=31, seq-only"
+from leon_b200 import workloads as W  # noqa: E402  (numpy only)
+
+METRIC = "reads/s compressed (leon -c: count + bloom + anchors + walk + range coding + lossy quality stream)"
+KMER = W.KMER
+RPB = W.RPB
+REF_WALL_BUDGET_S = 170.0      # reference arm: timed repetitions stop when this much wall time has been spent in them
 
 
 def parse_args():
@@ -40,13 +43,23 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--reads", type=int, default=0, help="override the number of reads per GPU (debug; marks the line invalid)")
+    ap.add_argument("--workload", default="configs[2]", choices=sorted(W.CONFIGS))
+    ap.add_argument("--reads", type=int, default=0, help="override the number of reads (debug; marks the line invalid)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--fastq", action="store_true", help="configs[2] shape: FASTQ with synthetic qualities, lossy (debug line)")
-    ap.add_argument("--host-zlib", action="store_true", help="with --fastq: return the quality text instead of zlib streams written by the GPU")
+    ap.add_argument("--no-extra", action="store_true", help="skip the configs[1] extra measurement")
+    ap.add_argument("--host-zlib", action="store_true", help="return the quality text instead of zlib streams written by the GPU")
     ap.add_argument("--anchor-batch", type=int, default=0, help="reads per anchor-resolution batch (0 = library default)")
     ap.add_argument("--phases", action="store_true", help="print per-phase / per-kernel device times to stderr")
     return ap.parse_args()
+
+
+def config_block(name, reads):
+    """The `config` object: identical in both arms (same workload, same size)."""
+    c = W.CONFIGS[name]
+    return {"workload": c["text"] if reads == c["reads"] else "DEBUG SIZE (invalid as a bench line): %d reads of %s" % (reads, name),
+            "reads": reads, "read_len": c["read_len"], "kmer_size": KMER, "reads_per_block": RPB,
+            "quality": "lossy" if c["fastq"] else "none (seq-only)",
+            "l2": "inputs larger than L2 (460 MB of bases, 2.6 GB of keys per step); no flush needed"}
 
 
 def peaks():
@@ -57,6 +70,11 @@ def peaks():
         except Exception:
             pass
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def golden_digest(name):
+    p = os.path.join(ROOT, "tests", "golden", "digest_%s.json" % name.replace("[", "").replace("]", ""))
+    return json.load(open(p)) if os.path.exists(p) else None
 
 
 # ---------------------------------------------------------------------------------------------------------------
@@ -113,56 +131,54 @@ class ClockSampler:
 
 # ---------------------------------------------------------------------------------------------------------------
 # reference arm / cpu baseline: the UNMODIFIED reference binary (oracle/_ref/leon, built by oracle/build_ref.sh from
-# /root/reference) on the host cores.  Test infrastructure executed as the thing to compare with, never as product.
+# /root/reference) on the host cores, on the SAME full-size read set.  Test infrastructure executed as the thing to
+# compare with, never as product.
 # ---------------------------------------------------------------------------------------------------------------
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "leon")
-SAMPLE_FRACTION = 0.1   # genome and read count scaled together: same 100x coverage, same read shape
-
-
-def make_sample_fasta(tmpdir, fraction=SAMPLE_FRACTION):
-    from leon_b200 import synth
-    glen = int(GENOME_LEN * fraction)
-    nreads = glen * COVERAGE // READ_LEN
-    g = synth.make_genome(glen, 1)
-    bases, offs, _ = synth.sample_reads(g, nreads, READ_LEN, 2)
-    path = os.path.join(tmpdir, "sample.fasta")
-    synth.write_fasta(path, bases, offs)
-    return path, nreads, glen
-
-
-def run_reference_once(fasta, cores, workdir):
-    """One `leon -c -kmer-size 31 -seq-only -nb-cores <cores>` run; returns wall seconds."""
-    for f in os.listdir(workdir):
-        if f.endswith(".leon") or f.endswith(".h5") or f.startswith("trashme"):
-            p = os.path.join(workdir, f)
-            shutil.rmtree(p, ignore_errors=True) if os.path.isdir(p) else os.remove(p)
-    t0 = time.perf_counter()
-    r = subprocess.run([REF_BIN, "-file", fasta, "-c", "-kmer-size", str(KMER), "-seq-only", "-nb-cores", str(cores),
-                        "-verbose", "0"], cwd=workdir, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
-    dt = time.perf_counter() - t0
-    if r.returncode != 0 or not os.path.exists(fasta + ".leon"):
-        raise RuntimeError("reference leon failed (rc %d): %s" % (r.returncode, r.stdout[-400:]))
-    return dt
 
 
 def reference_available():
     return os.path.exists(REF_BIN) and os.access(REF_BIN, os.X_OK)
 
 
-def cpu_baseline_block(runs=1):
-    """Bounded sample of the same workload through the reference binary with all host cores."""
+def write_workload_file(name, tmpdir, reads=0):
+    c = W.CONFIGS[name]
+    bases, offs, quals = W.generate(name, reads=reads)
+    path = os.path.join(tmpdir, "w.fastq" if c["fastq"] else "w.fasta")
+    W.write_fixed(path, bases, c["read_len"], quals)
+    return path, len(offs) - 1
+
+
+def reference_command(name, path, cores):
+    return [REF_BIN, "-file", path, "-c", "-kmer-size", str(KMER), "-nb-cores", str(cores), "-verbose", "0"] + W.CONFIGS[name]["ref_flags"]
+
+
+def run_reference_once(name, path, cores, workdir):
+    """One `leon -c` run of the reference on the workload file; returns wall seconds."""
+    for f in os.listdir(workdir):
+        if f.endswith(".leon") or f.endswith(".h5") or f.startswith("trashme"):
+            p = os.path.join(workdir, f)
+            shutil.rmtree(p, ignore_errors=True) if os.path.isdir(p) else os.remove(p)
+    t0 = time.perf_counter()
+    r = subprocess.run(reference_command(name, path, cores), cwd=workdir, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    dt = time.perf_counter() - t0
+    if r.returncode != 0 or not os.path.exists(path + ".leon"):
+        raise RuntimeError("reference leon failed (rc %d): %s" % (r.returncode, r.stdout[-400:]))
+    return dt
+
+
+def cpu_baseline_block(name, reads):
+    """The reference binary with all host cores on the full workload file: one untimed run (page cache), one timed."""
     cores = os.cpu_count() or 1
     if not reference_available():
-        return {"value": None, "unit": "reads/s", "cores": cores, "kind": "reference",
-                "sample": "oracle/_ref/leon missing on this box"}
+        return {"value": None, "unit": "reads/s", "cores": cores, "kind": "reference", "sample": "oracle/_ref/leon missing on this box"}
     tmp = tempfile.mkdtemp(prefix="leonref_")
     try:
-        fasta, nreads, glen = make_sample_fasta(tmp)
-        best = min(run_reference_once(fasta, cores, tmp) for _ in range(runs))
-        return {"value": nreads / best, "unit": "reads/s", "cores": cores, "kind": "reference",
-                "sample": "%d reads x %d bp at %dx of a %d bp genome (1/%d of the workload, same coverage), "
-                          "leon -c -kmer-size %d -seq-only -nb-cores %d, wall %.2f s incl. file read" % (
-                              nreads, READ_LEN, COVERAGE, glen, round(1 / SAMPLE_FRACTION), KMER, cores, best)}
+        path, n = write_workload_file(name, tmp, reads)
+        t = run_reference_once(name, path, cores, tmp)
+        return {"value": n / t, "unit": "reads/s", "cores": cores, "kind": "reference", "same_config": True,
+                "sample": "the full workload (%d reads), one run of `%s`, wall %.2f s incl. file read" % (
+                    n, " ".join(["leon"] + reference_command(name, "X", cores)[3:]), t)}
     finally:
         shutil.rmtree(tmp, ignore_errors=True)
 
@@ -174,29 +190,38 @@ def main_reference(args):
     if not reference_available():
         print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/leon not built on this box"}))
         return 0
+    name = args.workload
     cores = os.cpu_count() or 1
     tmp = tempfile.mkdtemp(prefix="leonref_")
     try:
-        fasta, nreads, glen = make_sample_fasta(tmp)
-        for _ in range(args.warmup):
-            run_reference_once(fasta, cores, tmp)
-        t = [run_reference_once(fasta, cores, tmp) for _ in range(args.steps)]
+        path, n = write_workload_file(name, tmp, args.reads)
+        warm = []
+        for _ in range(min(args.warmup, 1)):           # one warm-up run brings the file into the page cache; more would only
+            warm.append(run_reference_once(name, path, cores, tmp))   # spend the wall budget (every run is ~10 s of 16 cores)
+        t = []
+        while len(t) < args.steps and (not t or sum(t) + t[-1] <= REF_WALL_BUDGET_S):
+            t.append(run_reference_once(name, path, cores, tmp))
+        digest = W.digest_of_container(path + ".leon", W.CONFIGS[name]["fastq"])
     finally:
         shutil.rmtree(tmp, ignore_errors=True)
     total = sum(t)
-    value = nreads * args.steps / total
-    sample = "each step = %d reads x %d bp at %dx of a %d bp genome (1/%d of the workload, same coverage)" % (
-        nreads, READ_LEN, COVERAGE, glen, round(1 / SAMPLE_FRACTION))
+    value = n * len(t) / total
+    gold = golden_digest(name)
+    # with more than one thread the reference's anchor order (and with it dna / anchorsDict) is not deterministic; the
+    # Bloom filter and the quality text are
+    same = {k: (gold is not None and digest.get(k) == gold.get(k)) for k in ("bloom", "qual_text") if k in digest}
+    sample = "the full workload, %d timed runs of %d requested (wall budget %.0f s), %d warm-up" % (len(t), args.steps, REF_WALL_BUDGET_S, len(warm))
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "reads/s", "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1000.0 * total / args.steps, "higher_is_better": True, "scaling": "strong",
-        "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "kmer_size": KMER, "reads_per_block": RPB, "sample": sample,
-                   "command": "leon -c -kmer-size %d -seq-only -nb-cores %d" % (KMER, cores)},
-        "input_gbs": value * READ_LEN / 1e9,
-        "cpu_baseline": {"value": value, "unit": "reads/s", "cores": cores, "kind": "reference", "sample": sample},
+        "warmup": args.warmup, "steps_timed": len(t), "warmup_run": len(warm), "ms_per_step": 1000.0 * total / len(t),
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": config_block(name, n),
+        "command": " ".join(["leon"] + reference_command(name, "X", cores)[3:]),
+        "input_gbs": value * W.CONFIGS[name]["read_len"] / 1e9,
+        "cpu_baseline": {"value": value, "unit": "reads/s", "cores": cores, "kind": "reference", "sample": sample, "same_config": True},
         "e2e": {"value": value, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
+        "deterministic_streams_equal_nb_cores_1": same,
     }
     print(json.dumps(line))
     return 0
@@ -207,29 +232,30 @@ def main_reference(args):
 # ---------------------------------------------------------------------------------------------------------------
 def algorithmic_bytes(kernel, st):
     """Algorithmic bytes ONE launch of `kernel` moves (DESIGN.md 'kernels and rooflines').
-    st: nreads, nbases, nkmers, nruns, nsym."""
+    st: nreads, nbases, nkmers, nruns, nsym, launches (per step, of this kernel)."""
     R, NB, NK = st["nreads"], st["nbases"], st["nkmers"]
     kb = 8 if KMER <= 31 else 16
+    n = max(1.0, st.get("launches", {}).get(kernel, 1.0))      # kernels launched once per anchor batch share the totals
     if kernel == "k_walk":            # one 544-byte Bloom window per extension step: (L - k) steps per read
-        return 544.0 * (NB - KMER * R)
+        return 544.0 * (NB - KMER * R) / n
     if kernel == "k_msd_scatter":     # read every key once, write it once (one launch per 8-bit level of the hash partition)
         return 2.0 * NK * kb
     if kernel == "k_msd_hist":
         return 1.0 * NK * kb
     if kernel == "k_part_scatter":    # stable radix pass over the 8-byte symbol records
-        return 2.0 * st["nsym"] * 8.0
+        return 2.0 * st["nsym"] * 8.0 / n * 2.0
     if kernel == "k_part_hist":
-        return 1.0 * st["nsym"] * 8.0
+        return 1.0 * st["nsym"] * 8.0 / n * 2.0
     if kernel == "k_bucket_count":    # read every key once, write (key, count) of the solid ones; averaged over its two launches
         return (1.0 * NK * kb + st["nruns"] * (kb + 4.0)) / 2.0
     if kernel == "k_extract":         # read the bases, write one key per k-mer
         return NB + NK * kb
     if kernel == "k_chunk_ranks":     # read the 8-byte sorted record, write the 17-byte coder record; histogram row per chunk
-        return st["nsym"] * (8.0 + 17.0 + 2.0)
+        return st["nsym"] * (8.0 + 17.0 + 2.0) / n
     if kernel == "k_emit_syms":
-        return st["nsym"] * 8.0 + NB
+        return (st["nsym"] * 8.0 + NB) / n
     if kernel == "k_range_encode":    # read the 17-byte record of every symbol, write the output bytes
-        return st["nsym"] * 17.0 + st["dna_bytes"]
+        return (st["nsym"] * 17.0 + st["dna_bytes"]) / n
     if kernel == "k_deflate_count":   # read the quality text once (frequencies and Adler sums are small)
         return st["qual_bytes"]
     if kernel == "k_deflate_emit":    # read the quality text once, write the compressed chunk once
@@ -238,63 +264,49 @@ def algorithmic_bytes(kernel, st):
         return 2.0 * st.get("qual_z_bytes", 0.0)
     if kernel == "k_quals":           # read bases + qualities, write the smoothed text (Bloom lookups not counted)
         return 2.0 * NB + st["qual_bytes"]
-    if kernel == "k_run_stats" or kernel == "k_insert_runs":
-        return st["nruns"] * (8.0 + kb)
     return None
 
 
-def main_b200(args):
-    import torch
-    import torch.distributed as dist
+def measure(args, name, torch, dist, world, rank, local_rank, want_e2e=True):
+    """Resident and end-to-end measurement of one workload; returns a dict (rank 0: complete; other ranks: partial)."""
     import leon_b200
-    from leon_b200 import synth
-
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if world != args.gpus:
-        if world == 1 and args.gpus > 1:
-            raise SystemExit("bench.py --gpus %d must be launched with torchrun (one rank per GPU)" % args.gpus)
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device; this path has no CPU fallback")
-    torch.cuda.set_device(local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    from leon_b200 import shard
+    c = W.CONFIGS[name]
+    fastq = c["fastq"]
+    read_len = c["read_len"]
+    total_reads = args.reads if args.reads else c["reads"]
 
     # ---- the workload: every rank generates the same seeded read set; with N > 1 ranks the set is dealt in rounds of
     # N * S consecutive reads, S to each rank in rank order (leon_b200.shard; include/leon_b200.h leon_comm_*), so the
     # total work is fixed as N grows ("strong").
-    from leon_b200 import shard
-    total_reads = args.reads if args.reads else GENOME_LEN * COVERAGE // READ_LEN
-    genome = synth.make_genome(GENOME_LEN, 1)
     S = 0
     if world == 1:
-        pin_b = leon_b200.api.PinnedArray(total_reads * READ_LEN)
-        pin_q = leon_b200.api.PinnedArray(total_reads * READ_LEN) if args.fastq else None
-        bases, offs, quals = synth.sample_reads(genome, total_reads, READ_LEN, 2, out_bases=pin_b.array, with_quals=args.fastq,
-                                                out_quals=pin_q.array if args.fastq else None)
+        pin_b = leon_b200.api.PinnedArray(total_reads * read_len)
+        pin_q = leon_b200.api.PinnedArray(total_reads * read_len) if fastq else None
+        bases, offs, quals = W.generate(name, out_bases=pin_b.array, out_quals=pin_q.array if fastq else None, reads=total_reads)
     else:
         S = args.anchor_batch if args.anchor_batch else shard.choose_batch_reads(total_reads, world, RPB)
-        fb, fo, fq = synth.sample_reads(genome, total_reads, READ_LEN, 2, with_quals=args.fastq)
+        fb, fo, fq = W.generate(name, reads=total_reads)
         sb, offs, sq = shard.shard_reads(fb, fo, fq, rank, world, S)
         del fb, fq
-        pin_b = leon_b200.api.PinnedArray(len(sb))
-        pin_b.array[:] = sb
-        bases = pin_b.array
+        pin_b = leon_b200.api.PinnedArray(max(1, len(sb)))
+        pin_b.array[:len(sb)] = sb
+        bases = pin_b.array[:len(sb)]
         quals = None
-        if args.fastq:
-            pin_q = leon_b200.api.PinnedArray(len(sq))
-            pin_q.array[:] = sq
-            quals = pin_q.array
+        if fastq:
+            pin_q = leon_b200.api.PinnedArray(max(1, len(sq)))
+            pin_q.array[:len(sq)] = sq
+            quals = pin_q.array[:len(sq)]
         del sb, sq
     local_reads = len(offs) - 1
     pin_o = leon_b200.api.PinnedArray((local_reads + 1) * 8, np.uint64)
     pin_o.array[:] = offs
     offs = pin_o.array
 
-    dev_zlib = args.fastq and not args.host_zlib
-    eng = leon_b200.Leon(kmer_size=KMER, reads_per_block=RPB, has_qual=args.fastq, device=local_rank,
-                         anchor_batch=S if world > 1 else args.anchor_batch, qual_zlib_on_device=dev_zlib, skip_qual_text=dev_zlib)
+    dev_zlib = fastq and not args.host_zlib
+    eng = leon_b200.Leon(kmer_size=KMER, reads_per_block=RPB, has_qual=fastq, device=local_rank,
+                         anchor_batch=S if world > 1 else args.anchor_batch, qual_zlib_on_device=dev_zlib, skip_qual_text=dev_zlib,
+                         skip_read_arrays=True)
     stream = torch.cuda.current_stream()
     eng.set_stream(stream.cuda_stream)
     if world > 1:
@@ -317,8 +329,7 @@ def main_b200(args):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches0 = eng.timings()["kernel_launches"]
     e0.record(stream)
-    ktimes = {}
-    phase = {}
+    ktimes, phase = {}, {}
     for _ in range(args.steps):
         eng.run_device()
         for k, (ms, n) in eng.kernel_times().items():
@@ -339,42 +350,91 @@ def main_b200(args):
         dev_ms = float(t.item())
     ms_per_step = dev_ms / args.steps
     value = total_reads / (ms_per_step / 1000.0)
-    res = eng.fetch(copy=False)
+    res = eng.fetch(copy=True)
+
+    # ---- output digest: all ranks' outputs merged in file order on rank 0, against the committed reference digest
+    digest, digest_ok, digest_diff = None, None, None
+    allr = [res]
+    if world > 1:
+        allr = [None] * world if rank == 0 else None
+        dist.gather_object(res, allr, dst=0)
+    if rank == 0:
+        merged = res if world == 1 else shard.merge_results(allr, total_reads, world, S, RPB)
+        digest = W.digest_of_result(merged, fastq)
+        gold = golden_digest(name)
+        if gold is not None and total_reads == gold.get("reads"):
+            digest_ok, digest_diff = W.digests_equal(digest, gold)
+    del allr
+
     # the roofline describes rank 0's launches: its own share of the reads
-    stats = {"nreads": local_reads, "nbases": local_reads * READ_LEN, "nkmers": local_reads * (READ_LEN - KMER + 1),
+    stats = {"nreads": local_reads, "nbases": local_reads * read_len, "nkmers": local_reads * (read_len - KMER + 1),
              "nruns": res["nb_distinct"], "dna_bytes": len(res["dna"]),
-             "qual_bytes": float(local_reads * (READ_LEN + 1)) if args.fastq else 0.0, "qual_z_bytes": float(len(res["qual_z"]))}
-    nsym = eng.debug_fetch("nsym", np.uint64)
-    stats["nsym"] = float(nsym.sum())
-    anchors = res["anchor_count"]
-    dna_bytes = len(res["dna"])
+             "qual_bytes": float(local_reads * (read_len + 1)) if fastq else 0.0, "qual_z_bytes": float(len(res["qual_z"])),
+             "launches": {k: v[1] / args.steps for k, v in ktimes.items()}}
+    stats["nsym"] = float(eng.timings().get("nsym", 0)) or float(eng.debug_fetch("nsym", np.uint64).sum())
+    out = dict(name=name, total_reads=total_reads, local_reads=local_reads, read_len=read_len, S=S, value=value, ms_per_step=ms_per_step,
+               dev_ms=dev_ms, launches=launches, clocks=clocks, ktimes=ktimes, phase=phase, stats=stats, digest=digest,
+               digest_ok=digest_ok, digest_diff=digest_diff, anchors=res["anchor_count"], dna_bytes=len(res["dna"]),
+               bloom_bytes=int(len(res["bloom"])), cutoff=res["cutoff"], solid=res["nb_solids_cutoff"])
 
     # ---- e2e: host buffers in, host buffers out, through the C ABI one-shot call
-    for _ in range(min(args.warmup, 2)):
-        eng.compress(bases, offs, quals, copy=False)
-    barrier()
-    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    g0.record(stream)
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        r = eng.compress(bases, offs, quals, copy=False)
-    g1.record(stream)
-    barrier()
-    e2e_wall = (time.perf_counter() - t0) * 1000.0
-    e2e_ms = max(g0.elapsed_time(g1), e2e_wall) / args.steps
-    if world > 1:
-        t = torch.tensor([e2e_ms], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_ms = float(t.item())
-    h2d = int(bases.nbytes + offs.nbytes + (quals.nbytes if quals is not None else 0))
-    d2h = int(len(r["bloom"]) + len(r["anchors_dict"]) + len(r["dna"]) + r["blocksizes"].nbytes +
-              r["anchor_pos"].nbytes + r["anchor_addr"].nbytes + len(r["qual_text"]) + len(r["qual_z"]))
-    if world > 1:   # bytes of all ranks
-        t = torch.tensor([h2d, d2h, launches], device="cuda", dtype=torch.int64)
-        dist.all_reduce(t)
-        h2d, d2h, launches = (int(x) for x in t.tolist())
-    e2e_value = total_reads / (e2e_ms / 1000.0)
+    if want_e2e:
+        for _ in range(min(args.warmup, 2)):
+            eng.compress(bases, offs, quals, copy=False)
+        barrier()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record(stream)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            r = eng.compress(bases, offs, quals, copy=False)
+        g1.record(stream)
+        barrier()
+        e2e_wall = (time.perf_counter() - t0) * 1000.0
+        e2e_ms = max(g0.elapsed_time(g1), e2e_wall) / args.steps
+        if world > 1:
+            t = torch.tensor([e2e_ms], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e2e_ms = float(t.item())
+        h2d = int(bases.nbytes + offs.nbytes + (quals.nbytes if quals is not None else 0))
+        d2h = int(len(r["bloom"]) + len(r["anchors_dict"]) + len(r["dna"]) + r["blocksizes"].nbytes +
+                  r["anchor_pos"].nbytes + r["anchor_addr"].nbytes + len(r["qual_text"]) + len(r["qual_z"]))
+        if world > 1:   # bytes of all ranks
+            t = torch.tensor([h2d, d2h, launches], device="cuda", dtype=torch.int64)
+            dist.all_reduce(t)
+            h2d, d2h, out["launches"] = (int(x) for x in t.tolist())
+        out.update(e2e_ms=e2e_ms, e2e_value=total_reads / (e2e_ms / 1000.0), h2d=h2d, d2h=d2h)
+    eng.close()
+    pin_b.free()
+    pin_o.free()
+    if fastq:
+        pin_q.free()
+    return out
 
+
+def main_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("bench.py --gpus %d must be launched with torchrun (one rank per GPU)" % args.gpus)
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    name = args.workload
+    m = measure(args, name, torch, dist, world, rank, local_rank)
+    extra = None
+    if not args.no_extra and name != "configs[1]" and not args.reads:
+        extra = measure(args, "configs[1]", torch, dist, world, rank, local_rank, want_e2e=False)
+
+    ktimes, stats, clocks = m["ktimes"], m["stats"], m["clocks"]
+    read_len = m["read_len"]
     # ---- roofline of the dominant kernel (largest share of the device time of the timed region)
     peak, peak_src = peaks()
     dom = max(ktimes.items(), key=lambda kv: kv[1][0])[0] if ktimes else None
@@ -387,14 +447,15 @@ def main_b200(args):
         roofline = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s",
                     "frac": (ach / peak) if ach else None, "traffic": None, "peak_source": peak_src,
                     "launch_ms": per_launch_ms, "launches_per_step": n / args.steps,
-                    "share_of_step": ms_tot / dev_ms, "algorithmic_bytes_per_launch": ab}
+                    "share_of_step": ms_tot / m["dev_ms"], "algorithmic_bytes_per_launch": ab}
         if dom == "k_range_encode":
-            # one warp per block stream runs the serial low/range recurrence: bound by single-warp issue latency, not by
-            # bytes -- the figure that describes it is cycles per symbol of the longest stream
-            nblk = max(1, -(-local_reads // RPB))
+            # one warp per block stream runs the serial low/range recurrence: bound by single-warp dependent-issue latency,
+            # not by bytes -- the figure that describes it is cycles per symbol of a stream
+            nblk = max(1, -(-m["local_reads"] // RPB))
             sym_per_block = stats["nsym"] / nblk
-            roofline["note"] = "latency-bound serial recurrence (one warp per 50000-read block); HBM fraction is not its limit"
-            roofline["ns_per_symbol"] = per_launch_ms * 1e6 / sym_per_block
+            roofline["note"] = "latency-bound serial recurrence (one warp per 50000-read block); HBM fraction is not its limit; " \
+                               "launches of different anchor batches overlap each other and the other kernels"
+            roofline["ns_per_symbol"] = per_launch_ms * 1e6 / (sym_per_block)
             if clocks.get("sm_mhz"):
                 roofline["cycles_per_symbol"] = roofline["ns_per_symbol"] * clocks["sm_mhz"] / 1e3
         tr = os.path.join(ROOT, "profiles", "traffic.json")   # dram bytes per launch from the committed ncu --set full capture
@@ -406,68 +467,67 @@ def main_b200(args):
     kernel_rooflines = {}
     for kname, (ms_tot_k, n_k) in ktimes.items():
         ab_k = algorithmic_bytes(kname, stats)
-        if ab_k and n_k:
+        if ab_k and n_k and kname != "k_walk":     # k_walk: see probe_roofline (its filter is L2-resident here; an HBM fraction is meaningless)
             gbs = (ab_k / 1e9) / ((ms_tot_k / n_k) / 1e3)
             kernel_rooflines[kname] = {"ms_per_launch": ms_tot_k / n_k, "launches_per_step": n_k / args.steps,
                                        "achieved_gbs": gbs, "frac_of_hbm_peak": gbs / peak}
-    # Bloom-probe roofline of k_walk (north_star): extension steps (= contains4 windows) per second against what the
-    # memory system delivers for that access pattern on a filter of this size (tools/probe_roofline.cu, measured on B200)
+    # Bloom-probe roofline of k_walk (north_star): extension steps (= contains4 windows) per second against the plateau of
+    # an independent microbenchmark with the kernel's access shape (tools/probe_roofline.cu, measured on B200)
     probe = None
     if "k_walk" in ktimes and ktimes["k_walk"][1]:
-        wms = ktimes["k_walk"][0] / ktimes["k_walk"][1]
+        wms = ktimes["k_walk"][0] / args.steps
         steps = float(stats["nbases"] - KMER * stats["nreads"])
         wps = steps / (wms / 1e3)
-        probe = {"kernel": "k_walk", "windows_per_s": wps, "filter_bytes": int(len(res["bloom"])), "peak_windows_per_s": None,
+        probe = {"kernel": "k_walk", "windows_per_s": wps, "filter_bytes": m["bloom_bytes"], "peak_windows_per_s": None,
                  "frac": None, "regime": None}
         try:
-            pr = json.load(open(os.path.join(ROOT, "profiles", "probe_roofline.json")))["windows_per_s"]
-            fb = len(res["bloom"])
+            prj = json.load(open(os.path.join(ROOT, "profiles", "probe_roofline.json")))
+            pr = prj["windows_per_s"]
+            fb = m["bloom_bytes"]
             key = "l2_resident_6.9MB" if fb <= 64e6 else ("150MB" if fb <= 300e6 else ("dram_1GB" if fb <= 2e9 else "dram_4.5GB"))
-            probe.update(peak_windows_per_s=pr[key], frac=wps / pr[key], regime=key, peak_source="tools/probe_roofline.cu microbenchmark")
-            if wps > pr[key]:
-                # the kernel issues fewer loads per window than the microbenchmark item and runs above its figure: the
-                # bound that applies is the L1 request rate of the committed ncu capture of this kernel
-                l1 = json.load(open(os.path.join(ROOT, "profiles", "probe_roofline.json")))["k_walk_ncu"]["l1tex_throughput_pct"] / 100.0
-                probe.update(peak_windows_per_s=wps / l1, frac=l1, microbenchmark_windows_per_s=pr[key],
-                             peak_source="ncu l1tex__throughput of k_walk (profiles/r1i_ncu_full.csv); above the microbenchmark figure")
+            probe.update(peak_windows_per_s=pr[key], frac=wps / pr[key], regime=key, peak_source=prj.get("source", "tools/probe_roofline.cu microbenchmark"),
+                         ncu_context=prj.get("k_walk_ncu"))
         except Exception:
             pass
     if args.phases and rank == 0:
-        print("phases (ms/step):", {k: round(v / args.steps, 3) for k, v in phase.items()}, file=sys.stderr)
+        print("phases (ms/step):", {k: round(v / args.steps, 3) for k, v in m["phase"].items()}, file=sys.stderr)
         print("kernels (ms/step, launches/step):",
               {k: (round(v[0] / args.steps, 3), v[1] // args.steps) for k, v in sorted(ktimes.items(), key=lambda kv: -kv[1][0])},
               file=sys.stderr)
         print("anchors %d, dna bytes %d, symbols %d, solid %d, cutoff %d" % (
-            anchors, dna_bytes, int(stats["nsym"]), res["nb_solids_cutoff"], res["cutoff"]), file=sys.stderr)
+            m["anchors"], m["dna_bytes"], int(stats["nsym"]), m["solid"], m["cutoff"]), file=sys.stderr)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu = cpu_baseline_block()
-    eng.close()
+        cpu = cpu_baseline_block(name, args.reads)
     if rank != 0:
         return 0
     line = {
-        "metric": METRIC, "value": value, "unit": "reads/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u64",
+        "metric": METRIC, "value": m["value"], "unit": "reads/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": m["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u64",
         "data": "synthetic",
-        "config": {"workload": (WORKLOAD if not args.fastq else "DEBUG (configs[2] shape, FASTQ lossy)") if not args.reads else "DEBUG SIZE (invalid as a bench line): %d reads" % total_reads,
-                   "reads": total_reads, "read_len": READ_LEN, "kmer_size": KMER, "reads_per_block": RPB,
-                   "l2": "inputs larger than L2 (460 MB of bases, 2.6 GB of keys per step); no flush needed",
-                   "parallelism": "1 process per GPU" if world == 1 else
-                   "%d ranks, reads dealt in rounds of %d x %d; NCCL: k-mer all-to-all by hash owner, Bloom all-gather + OR, "
-                   "anchor candidates all-gathered per batch" % (world, world, S)},
-        "input_gbs": value * READ_LEN / 1e9,
-        "e2e": {"value": e2e_value, "unit": "reads/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "ms_per_step": e2e_ms, "input_gbs": e2e_value * READ_LEN / 1e9},
-        "gpu_launches": int(launches),
+        "config": config_block(name, m["total_reads"]),
+        "parallelism": "1 process per GPU" if world == 1 else
+        "%d ranks, reads dealt in rounds of %d x %d; NCCL: k-mer all-to-all by hash owner, Bloom all-gather + OR, "
+        "anchor candidates all-gathered per batch" % (world, world, m["S"]),
+        "input_gbs": m["value"] * read_len * (2 if W.CONFIGS[name]["fastq"] else 1) / 1e9,
+        "e2e": {"value": m["e2e_value"], "unit": "reads/s", "h2d_bytes_per_step": m["h2d"], "d2h_bytes_per_step": m["d2h"],
+                "ms_per_step": m["e2e_ms"], "input_gbs": m["e2e_value"] * read_len * (2 if W.CONFIGS[name]["fastq"] else 1) / 1e9},
+        "gpu_launches": int(m["launches"]),
         "clocks": clocks,
+        "output_digest": m["digest"], "digest_ok": m["digest_ok"], "digest_mismatch": m["digest_diff"],
+        "digest_reference": "tests/golden/digest_%s.json: oracle/_ref/leon -nb-cores 1 on the same seeded read set" % name.replace("[", "").replace("]", ""),
         "roofline": roofline,
         "kernel_rooflines": kernel_rooflines,
         "probe_roofline": probe,
         "cpu_baseline": cpu,
-        "phases_ms_per_step": {k: v / args.steps for k, v in phase.items()},
+        "phases_ms_per_step": {k: v / args.steps for k, v in m["phase"].items()},
         "kernels_ms_per_step": {k: v[0] / args.steps for k, v in ktimes.items()},
     }
+    if extra is not None:
+        line["configs1"] = {"workload": W.CONFIGS["configs[1]"]["text"], "value": extra["value"], "unit": "reads/s",
+                            "ms_per_step": extra["ms_per_step"], "digest_ok": extra["digest_ok"], "digest_mismatch": extra["digest_diff"],
+                            "phases_ms_per_step": {k: v / args.steps for k, v in extra["phase"].items()}}
     print(json.dumps(line))
     return 0
 

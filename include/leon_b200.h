@@ -47,7 +47,8 @@ typedef struct leon_opts {
     int32_t qual_zlib_on_device; /* 1: the GPU also writes the zlib streams of the quality blocks (leon_result.qual_z, what
                                  C/Leon.cpp:581-607 makes with host zlib; run matches + dynamic Huffman, leon_b200/csrc/deflate.cuh) */
     int32_t skip_qual_text;   /* 1: do not copy the quality text to the host (qual_text stays NULL; needs qual_zlib_on_device) */
-    int32_t reserved[6];
+    int32_t skip_read_arrays; /* 1: do not copy the per-read parity arrays (anchor_pos / anchor_addr, 8 bytes per read) to the host */
+    int32_t reserved[5];
 } leon_opts;
 
 /* A set of reads: concatenated ASCII bases (upper-case ACGTN for reference parity) + R+1 offsets

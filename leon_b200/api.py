@@ -27,7 +27,8 @@ class LeonError(RuntimeError):
 class Opts(C.Structure):
     _fields_ = [("kmer_size", C.c_int32), ("reads_per_block", C.c_int32), ("has_qual", C.c_int32), ("lossless", C.c_int32),
                 ("abundance_set", C.c_int32), ("device", C.c_int32), ("anchor_batch", C.c_int32), ("dict_on_device", C.c_int32),
-                ("qual_zlib_on_device", C.c_int32), ("skip_qual_text", C.c_int32), ("reserved", C.c_int32 * 6)]
+                ("qual_zlib_on_device", C.c_int32), ("skip_qual_text", C.c_int32), ("skip_read_arrays", C.c_int32),
+                ("reserved", C.c_int32 * 5)]
 
 
 class Reads(C.Structure):
@@ -439,10 +440,10 @@ class Leon:
     """
 
     def __init__(self, kmer_size=31, reads_per_block=50000, lossless=False, abundance=None, has_qual=False, device=0,
-                 anchor_batch=0, dict_on_device=False, qual_zlib_on_device=False, skip_qual_text=False):
+                 anchor_batch=0, dict_on_device=False, qual_zlib_on_device=False, skip_qual_text=False, skip_read_arrays=False):
         self.L = load_library()
         self.opts = Opts(kmer_size, reads_per_block, int(has_qual), int(lossless), int(abundance is not None), device,
-                         anchor_batch, int(dict_on_device), int(qual_zlib_on_device), int(skip_qual_text))
+                         anchor_batch, int(dict_on_device), int(qual_zlib_on_device), int(skip_qual_text), int(skip_read_arrays))
         self.ctx = C.c_void_p()
         rc = self.L.leon_create(C.byref(self.opts), C.byref(self.ctx))
         if rc != 0:
@@ -488,8 +489,8 @@ class Leon:
             qual_block_sizes=_arr(r.qual_block_sizes, r.nblocks if hq else 0, np.uint64, copy),
             read_count=int(r.read_count), total_dna_size=int(r.total_dna_size),
             min_read_size=int(r.min_read_size), max_read_size=int(r.max_read_size),
-            anchor_pos=_arr(r.anchor_pos, r.read_count, np.int32, copy),
-            anchor_addr=_arr(r.anchor_addr, r.read_count, np.uint32, copy),
+            anchor_pos=_arr(r.anchor_pos, r.read_count if r.anchor_pos else 0, np.int32, copy),
+            anchor_addr=_arr(r.anchor_addr, r.read_count if r.anchor_addr else 0, np.uint32, copy),
             reads_without_anchor=int(r.reads_without_anchor),
         )
 

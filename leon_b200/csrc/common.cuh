@@ -48,6 +48,10 @@ struct DevBuf {
     }
     void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
     template <typename T> T *as() const { return (T *)p; }
+    DevBuf() = default;
+    DevBuf(const DevBuf &) = delete;
+    DevBuf &operator=(const DevBuf &) = delete;
+    ~DevBuf() { release(); }              // a member of a context can never be forgotten in a release list
 };
 
 // grow-only pinned host allocation
@@ -64,6 +68,10 @@ struct PinBuf {
     }
     void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
     template <typename T> T *as() const { return (T *)p; }
+    PinBuf() = default;
+    PinBuf(const PinBuf &) = delete;
+    PinBuf &operator=(const PinBuf &) = delete;
+    ~PinBuf() { release(); }
 };
 
 // Per-kernel device time, CUDA events on the launching stream around selected launches.  Slots are named after

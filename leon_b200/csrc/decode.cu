@@ -148,6 +148,7 @@ template <typename K> struct BlockDecoder {
     std::vector<uint64_t> npos, errpos;
     std::string err;
 
+    static constexpr uint64_t MAX_SANE_READ = 1ull << 31;     // leon_upload refuses longer reads; containers without maxSequenceSize
     BlockDecoder(const BloomDev &b, const std::vector<K> &a) : bloom(b), anchors(a), k(b.k) {}
 
     // one step of DnaDecoder::extendAnchor (C/DnaCoder.cpp:1482-1605); returns the character at `pos`
@@ -197,7 +198,7 @@ template <typename K> struct BlockDecoder {
                 const uint64_t L = rc.numeric(m.readSize);
                 const uint64_t apos = rc.numeric(m.anchorPos);
                 const uint64_t addr = rc.numeric(m.anchorAddress);
-                if (addr >= anchors.size() || apos + (uint64_t)k > L || (max_read >= 0 && L > (uint64_t)max_read)) {
+                if (addr >= anchors.size() || apos + (uint64_t)k > L || L > (max_read >= 0 ? (uint64_t)max_read : MAX_SANE_READ)) {
                     err = "corrupt block: anchor address, anchor position or read length out of range";
                     return false;
                 }
@@ -221,7 +222,7 @@ template <typename K> struct BlockDecoder {
                 for (uint64_t p : npos) if (p < L) seq[p] = 'N';
             } else {
                 const uint64_t L = rc.numeric(m.noAnchorReadSize);
-                if (max_read >= 0 && L > (uint64_t)max_read) { err = "corrupt block: read length out of range"; return false; }
+                if (L > (max_read >= 0 ? (uint64_t)max_read : MAX_SANE_READ)) { err = "corrupt block: read length out of range"; return false; }
                 seq.resize((size_t)L);
                 for (uint64_t i = 0; i < L; i++) seq[i] = BIN2NT[rc.decode(m.noAnchorRead)];
             }
@@ -259,7 +260,11 @@ int decode_dna(const leon_dna_stream *s, int nthreads, std::vector<std::string> 
     bloom.words = (uint32_t *)s->bloom;
     bloom.reduced_tai = s->bloom_bits;
     bloom.magic = s->bloom_bits ? ~0ull / s->bloom_bits : 0;
-    if (s->bloom_nbytes < s->bloom_bits / 8 + 8) { err = "Bloom array shorter than its size attribute says"; return LEON_E_ARG; }
+    // contains4 probes bits up to reduced_tai + 4095 + 13 with 8-byte loads: what BloomNeighborCoherent allocates
+    // (1 + (bits + 2 * 4096) / 8, COL/Bloom.hpp:187,438) plus the load width
+    if (s->bloom_nbytes < (s->bloom_bits + 2 * 4096) / 8 + 1 + 8) { err = "Bloom array shorter than its size attribute says"; return LEON_E_ARG; }
+    // an anchor takes at least 2 * k / 8 bytes of information only loosely; bound the count by what the stream can hold
+    if (s->anchor_count > s->anchors_dict_nbytes * 64 + 64) { err = "anchor count exceeds what the dictionary stream can hold"; return LEON_E_ARG; }
     std::vector<K> anchors;
     decode_anchor_dict<K>(s->anchors_dict, s->anchors_dict_nbytes, s->anchor_count, s->kmer_size, anchors);
     blocks.assign(s->nblocks, std::string());
@@ -271,16 +276,25 @@ int decode_dna(const leon_dna_stream *s, int nthreads, std::vector<std::string> 
     std::string first_err;
     std::mutex *mu = new std::mutex();
     auto work = [&]() {
-        BlockDecoder<K> d(bloom, anchors);
-        for (;;) {
-            const uint64_t b = next.fetch_add(1);
-            if (b >= s->nblocks || failed.load()) return;
-            blocks[b].reserve((size_t)(s->blocksizes[2 * b + 1] * 102));
-            if (!d.run(s->dna + start[b], s->blocksizes[2 * b], s->blocksizes[2 * b + 1], s->max_read_size, blocks[b])) {
-                std::lock_guard<std::mutex> g(*mu);
-                if (!failed.exchange(1)) first_err = "block " + std::to_string(b) + ": " + d.err;
-                return;
+        // nothing may leave a pool thread as an exception (std::terminate): sizes come from an untrusted container
+        uint64_t b = 0;
+        try {
+            BlockDecoder<K> d(bloom, anchors);
+            for (;;) {
+                b = next.fetch_add(1);
+                if (b >= s->nblocks || failed.load()) return;
+                // a coded read takes at least a few bits: cap the reservation by what the block's bytes can expand to
+                const uint64_t want = s->blocksizes[2 * b + 1] * 102, cap = s->blocksizes[2 * b] * 64 + 4096;
+                blocks[b].reserve((size_t)std::min(want, cap));
+                if (!d.run(s->dna + start[b], s->blocksizes[2 * b], s->blocksizes[2 * b + 1], s->max_read_size, blocks[b])) {
+                    std::lock_guard<std::mutex> g(*mu);
+                    if (!failed.exchange(1)) first_err = "block " + std::to_string(b) + ": " + d.err;
+                    return;
+                }
             }
+        } catch (const std::exception &e) {
+            std::lock_guard<std::mutex> g(*mu);
+            if (!failed.exchange(1)) first_err = "block " + std::to_string(b) + ": " + e.what();
         }
     };
     unsigned nt = nthreads > 0 ? (unsigned)nthreads : std::max(1u, std::thread::hardware_concurrency());
@@ -300,7 +314,7 @@ int decode_dna(const leon_dna_stream *s, int nthreads, std::vector<std::string> 
 template <typename K>
 int decode_dna_device(const leon_dna_stream *s, int device, std::vector<std::string> &blocks, float *kernel_ms, std::string &err) {
     if (s->max_read_size < 0) { err = "the device decoder needs max_read_size (metadata/maxSequenceSize) to size its output"; return LEON_E_ARG; }
-    if (s->bloom_nbytes < s->bloom_bits / 8 + 8) { err = "Bloom array shorter than its size attribute says"; return LEON_E_ARG; }
+    if (s->bloom_nbytes < (s->bloom_bits + 2 * 4096) / 8 + 1 + 8) { err = "Bloom array shorter than its size attribute says"; return LEON_E_ARG; }
     std::vector<uint64_t> start(s->nblocks + 1, 0);
     for (uint64_t b = 0; b < s->nblocks; b++) start[b + 1] = start[b] + s->blocksizes[2 * b];
     if (start[s->nblocks] > s->dna_nbytes) { err = "blocksizes exceed dna_nbytes"; return LEON_E_ARG; }

@@ -181,11 +181,13 @@ static int decompress_file_impl(const char *in_path, const char *out_path, int32
                 std::atomic<uint64_t> next(0);
                 std::atomic<int> bad(0);
                 auto work = [&]() {
-                    for (;;) {
-                        const uint64_t b = next.fetch_add(1);
-                        if (b >= nblocks) return;
-                        if (!inflate_block(zq[b].p, zq[b].n, quals[b])) bad.store(1);
-                    }
+                    try {                                       // bad_alloc / length_error in a pool thread would be std::terminate
+                        for (;;) {
+                            const uint64_t b = next.fetch_add(1);
+                            if (b >= nblocks) return;
+                            if (!inflate_block(zq[b].p, zq[b].n, quals[b])) bad.store(1);
+                        }
+                    } catch (const std::exception &) { bad.store(1); }
                 };
                 unsigned nt = nthreads > 0 ? (unsigned)nthreads : std::max(1u, std::thread::hardware_concurrency());
                 nt = (unsigned)std::min<uint64_t>(nt, std::max<uint64_t>(nblocks, 1));

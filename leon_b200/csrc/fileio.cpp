@@ -7,6 +7,7 @@
 #include <sys/mman.h>
 #include <sys/stat.h>
 #include <unistd.h>
+#include <zlib.h>
 
 #include <algorithm>
 #include <chrono>
@@ -28,8 +29,12 @@ struct Mapped {
     const uint8_t *p = nullptr;
     size_t n = 0;
     int fd = -1;
+    size_t file_bytes = 0;                   // size of the file itself (== n unless it was gzipped)
+    std::vector<uint8_t> inflated;           // gzipped input: the text, p points here
+    const uint8_t *map_p = nullptr;
+    size_t map_n = 0;
     ~Mapped() {
-        if (p && n) munmap((void *)p, n);
+        if (map_p && map_n) munmap((void *)map_p, map_n);
         if (fd >= 0) close(fd);
     }
 };
@@ -242,12 +247,49 @@ int map_file(const char *path, Mapped &m, std::string &err) {
     m.fd = open(path, O_RDONLY);
     struct stat st;
     if (m.fd < 0 || fstat(m.fd, &st) != 0) { err = std::string("cannot open ") + path + ": " + strerror(errno); return LEON_E_IO; }
-    m.n = (size_t)st.st_size;
+    m.n = m.file_bytes = (size_t)st.st_size;
     if (m.n) {
         void *q = mmap(nullptr, m.n, PROT_READ, MAP_PRIVATE, m.fd, 0);
         if (q == MAP_FAILED) { m.n = 0; err = std::string("cannot map ") + path + ": " + strerror(errno); return LEON_E_IO; }
-        m.p = (const uint8_t *)q;
+        m.p = m.map_p = (const uint8_t *)q;
+        m.map_n = m.n;
         madvise(q, m.n, MADV_SEQUENTIAL);
+    }
+    // The reference reads every input through gzopen / gzread (bank/impl/BankFasta.cpp:652), so `leon -file x.fastq.gz -c`
+    // works there: a gzip file (magic 1f 8b; several members as bgzip writes them included) is inflated here first.
+    if (m.n >= 2 && m.p[0] == 0x1f && m.p[1] == 0x8b) {
+        z_stream zs;
+        memset(&zs, 0, sizeof zs);
+        if (inflateInit2(&zs, 15 + 16) != Z_OK) { err = "zlib: inflateInit2 failed"; return LEON_E_IO; }
+        std::vector<uint8_t> &o = m.inflated;
+        o.resize(std::max<size_t>(m.n * 4, 1u << 20));
+        size_t in_at = 0, out_at = 0;
+        int zr = Z_OK;
+        while (in_at < m.n) {
+            zs.next_in = (Bytef *)(m.p + in_at);
+            const size_t in_chunk = std::min<size_t>(m.n - in_at, 1u << 30);
+            zs.avail_in = (uInt)in_chunk;
+            if (out_at == o.size()) o.resize(o.size() * 2);
+            const size_t out_chunk = std::min<size_t>(o.size() - out_at, 1u << 30);
+            zs.next_out = o.data() + out_at;
+            zs.avail_out = (uInt)out_chunk;
+            zr = inflate(&zs, Z_NO_FLUSH);
+            in_at += in_chunk - zs.avail_in;
+            out_at += out_chunk - zs.avail_out;
+            if (zr == Z_STREAM_END) {                    // next member, if any
+                if (in_at >= m.n) break;
+                if (inflateReset(&zs) != Z_OK) break;
+                zr = Z_OK;
+                continue;
+            }
+            if (zr != Z_OK && zr != Z_BUF_ERROR) break;
+            if (zr == Z_BUF_ERROR && zs.avail_in == 0 && in_at >= m.n) break;
+        }
+        inflateEnd(&zs);
+        if (zr != Z_STREAM_END) { err = std::string("cannot inflate ") + path + ": corrupt or truncated gzip data"; return LEON_E_IO; }
+        o.resize(out_at);
+        m.p = o.data();
+        m.n = o.size();
     }
     return LEON_OK;
 }
@@ -305,7 +347,20 @@ extern "C" int leon_compress_file(const char *in_path, const char *out_path, con
     try {
         if (!in_path || !o) { leon_internal_set_error("leon_compress_file: null argument"); return LEON_E_ARG; }
         const double t0 = now_ms();
-        const std::string in(in_path), out = out_path ? std::string(out_path) : in + ".leon";
+        const std::string in(in_path);
+        // output name, C/Leon.cpp:466-479: X.leon, or <dir>/<name minus its last suffix>.leon when the extension holds "gz"
+        std::string out = out_path ? std::string(out_path) : in + ".leon";
+        if (!out_path) {
+            const size_t dot = in.find_last_of('.');
+            if (dot != std::string::npos && in.substr(dot + 1).find("gz") != std::string::npos) {
+                const size_t slash = in.find_last_of('/');
+                const std::string dir = slash == std::string::npos ? "." : in.substr(0, slash);
+                std::string name = slash == std::string::npos ? in : in.substr(slash + 1);
+                const size_t nd = name.find_last_of('.');
+                if (nd != std::string::npos) name = name.substr(0, nd);
+                out = dir + "/" + name + ".leon";
+            }
+        }
         // format from the file name, as C/Leon.cpp:392-416
         bool fastq_input;
         if (has_any(in, ".fq", ".fastq")) fastq_input = true;
@@ -324,6 +379,7 @@ extern "C" int leon_compress_file(const char *in_path, const char *out_path, con
         lo.device = o->device;
         lo.qual_zlib_on_device = lo.has_qual;                 // quality blocks leave the GPU as zlib streams
         lo.skip_qual_text = lo.has_qual;
+        lo.skip_read_arrays = 1;                              // per-read parity arrays are not stored in the container
         // the CUDA context comes up (a few hundred ms) while the host threads read the file
         int crc = LEON_OK;
         std::string cerr_msg;
@@ -387,7 +443,7 @@ extern "C" int leon_compress_file(const char *in_path, const char *out_path, con
             memset(stats, 0, sizeof *stats);
             stats->nreads = nreads;
             stats->total_bases = rs.offsets.back();
-            stats->input_bytes = m.n;
+            stats->input_bytes = m.file_bytes;
             struct stat so;
             if (stat(out.c_str(), &so) == 0) stats->output_bytes = (uint64_t)so.st_size;
             stats->header_bytes_in = rs.header_bytes;

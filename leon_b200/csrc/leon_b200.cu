@@ -285,10 +285,12 @@ template <typename K> void do_count(leon_ctx *c)
         uint64_t *pcur = (nlevels & 1) ? c->d_pstart_alt.as<uint64_t>() : c->d_bstart.as<uint64_t>();
         uint64_t *pnext = (nlevels & 1) ? c->d_bstart.as<uint64_t>() : c->d_pstart_alt.as<uint64_t>();
         if (bits == 0 || nk == 0) pcur = bstart;
-        c->h_small.reserve(256);
+        // pinned staging slots of in-flight H2D copies must not be reused before the copy has run: distinct offsets of
+        // h_small (sized once here, so no reallocation in between): +0 scalars read back, +1024 this table, +2048 / +4096 below
+        c->h_small.reserve(8192);
         uint64_t init[2] = {0, nk};
-        memcpy(c->h_small.p, init, 16);
-        CUDA_TRY(cudaMemcpyAsync(pcur, c->h_small.p, 16, cudaMemcpyHostToDevice, st));
+        memcpy((char *)c->h_small.p + 1024, init, 16);
+        CUDA_TRY(cudaMemcpyAsync(pcur, (char *)c->h_small.p + 1024, 16, cudaMemcpyHostToDevice, st));
         if (nk == 0 && bits) CUDA_TRY(cudaMemsetAsync(bstart, 0, (nbuckets + 1) * 8, st));
         uint64_t P = 1;
         int off = 0;
@@ -340,15 +342,14 @@ template <typename K> void do_count(leon_ctx *c)
         c->d_pick.reserve((uint64_t)N * (N + 1) * 8);
         std::vector<uint64_t> los(N + 1);
         for (int p = 0; p <= N; p++) los[p] = lo_of(p);
-        c->h_small.reserve(4096);
-        memcpy(c->h_small.p, los.data(), (N + 1) * 8);
-        CUDA_TRY(cudaMemcpyAsync(c->d_xchg.as<uint8_t>() + 64, c->h_small.p, (N + 1) * 8, cudaMemcpyHostToDevice, st));
+        memcpy((char *)c->h_small.p + 2048, los.data(), (N + 1) * 8);
+        CUDA_TRY(cudaMemcpyAsync(c->d_xchg.as<uint8_t>() + 64, (char *)c->h_small.p + 2048, (N + 1) * 8, cudaMemcpyHostToDevice, st));
         LB_LAUNCH(c->lc, k_pick_bounds, 1, 128, 0, st, ball, nbuckets + 1, N, (const uint64_t *)(c->d_xchg.as<uint8_t>() + 64),
                   c->d_pick.as<uint64_t>());
         std::vector<uint64_t> pick((size_t)N * (N + 1));
-        CUDA_TRY(cudaMemcpyAsync(c->h_small.p, c->d_pick.p, pick.size() * 8, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaMemcpyAsync((char *)c->h_small.p + 4096, c->d_pick.p, pick.size() * 8, cudaMemcpyDeviceToHost, st));
         CUDA_TRY(cudaStreamSynchronize(st));
-        memcpy(pick.data(), c->h_small.p, pick.size() * 8);
+        memcpy(pick.data(), (char *)c->h_small.p + 4096, pick.size() * 8);
         auto B = [&](int s_, int p) { return pick[(size_t)s_ * (N + 1) + p]; };
         uint64_t recv_total = 0;
         std::vector<uint64_t> recv_off(N);
@@ -1038,7 +1039,7 @@ template <typename K> void do_encode_body(leon_ctx *c)
         c->d_dnaoff.reserve(c->nblocks * 8);
         c->d_bs.reserve(c->nblocks * 16);
         LB_LAUNCH(c->lc, k_block_descs, cdiv_u(c->nblocks, 128), 128, 0, st, symoff, R, rpb, c->nblocks, c->d_descs.as<StreamDesc>());
-        LB_TIMED(c->kt, "k_range_encode", st, LB_LAUNCH(c->lc, k_range_encode, (unsigned)c->nblocks, 32, 0, st, c->d_rec.as<uint4>(), c->d_sh.as<uint8_t>(),
+        LB_TIMED(c->kt, "k_range_encode", st, LB_LAUNCH(c->lc, k_range_encode2, (unsigned)c->nblocks, 32, 0, st, c->d_rec.as<uint4>(), c->d_sh.as<uint8_t>(),
                   c->d_descs.as<StreamDesc>(), c->d_outall.as<uint8_t>(), c->d_outsize.as<uint64_t>(), 0, ovf));
         uint64_t *dtot = lbscan::exclusive_scan<uint64_t>(c->nblocks, SizeIn{c->d_outsize.as<uint64_t>()},
                                                           SizeOut{c->d_dnaoff.as<uint64_t>()}, c->d_scan, st, c->lc);
@@ -1105,7 +1106,8 @@ void do_fetch(leon_ctx *c, leon_result *out)
     }
     c->h_apos.reserve((R + 1) * 4);
     c->h_aaddr.reserve((R + 1) * 4);
-    if (R) {
+    const bool want_arrays = !c->opts.skip_read_arrays;
+    if (R && want_arrays) {
         CUDA_TRY(cudaMemcpyAsync(c->h_apos.p, c->d_apos.p, R * 4, cudaMemcpyDeviceToHost, st));
         CUDA_TRY(cudaMemcpyAsync(c->h_aaddr.p, c->d_aaddr.p, R * 4, cudaMemcpyDeviceToHost, st));
     }
@@ -1138,7 +1140,7 @@ void do_fetch(leon_ctx *c, leon_result *out)
     if (zbytes) { out->qual_z = c->h_qz_out.as<uint8_t>(); out->qual_z_nbytes = zbytes; out->qual_z_block_sizes = c->h_qz_sizes.as<uint64_t>(); }
     out->read_count = R; out->total_dna_size = c->nbases;
     out->min_read_size = c->min_len; out->max_read_size = c->max_len;
-    out->anchor_pos = c->h_apos.as<int32_t>(); out->anchor_addr = c->h_aaddr.as<uint32_t>();
+    out->anchor_pos = want_arrays ? c->h_apos.as<int32_t>() : nullptr; out->anchor_addr = want_arrays ? c->h_aaddr.as<uint32_t>() : nullptr;
     out->reads_without_anchor = c->reads_without_anchor;
     if (c->opts.has_qual && !c->qsizes.empty()) memcpy(c->h_qsizes.p, c->qsizes.data(), c->qsizes.size() * 8);
     CUDA_TRY(cudaEventRecord(c->ev[12], st));
@@ -1225,6 +1227,7 @@ int leon_create(const leon_opts *opts, leon_ctx **out)
         CUDA_TRY(cudaEventCreateWithFlags(&c->ev_qz, cudaEventDisableTiming));
         for (int i = 0; i < 16; i++) CUDA_TRY(cudaEventCreate(&c->ev[i]));
         for (int i = 0; i < 16; i++) CUDA_TRY(cudaEventRecord(c->ev[i], c->st));
+        c->h_small.reserve(8192);      // staging slots at fixed offsets (do_count): never reallocated while a copy is in flight
     } catch (const LeonError &er) {
         g_create_error = er.msg;
         delete c;

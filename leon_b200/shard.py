@@ -85,6 +85,8 @@ def merge_results(results, nreads, nranks, S, reads_per_block):
                 zs[b] = nz
         loc = 0
         for lo, hi in rank_read_ranges(nreads, rank, nranks, S):
+            if not len(r["anchor_pos"]):     # skip_read_arrays: the per-read parity arrays were not fetched
+                break
             apos[lo:hi] = r["anchor_pos"][loc:loc + hi - lo]
             aaddr[lo:hi] = r["anchor_addr"][loc:loc + hi - lo]
             loc += hi - lo

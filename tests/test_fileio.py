@@ -106,3 +106,52 @@ def test_irregular_big_fastq_falls_back_to_one_thread(tmp_path):
     assert r["threads_used"] == 1
     assert _split(r["bases"], r["offsets"]) == reads and _split(r["quals"], r["offsets"]) == quals
     assert _split(r["headers"], r["header_offsets"]) == names
+
+
+def test_gzip_input_is_inflated(tmp_path):
+    """The reference reads its input through gzopen (bank/impl/BankFasta.cpp:652): a .gz file parses like its text, also
+    when it is a concatenation of gzip members (bgzip), and a truncated one is an error, not a bogus read set."""
+    import gzip
+    import leon_b200
+    from leon_b200.api import LeonError
+    txt = b"".join(b"@r%d\nACGTNACGTTGCA%s\n+\nIIIIIIIIIIIII%s\n" % (i, b"ACGT"[i % 4:], b"#!+@"[i % 4:]) for i in range(3000))
+    plain = _read(tmp_path, "a.fastq", txt)
+    (tmp_path / "b.fastq.gz").write_bytes(gzip.compress(txt))
+    gz = leon_b200.read_file(str(tmp_path / "b.fastq.gz"))
+    half = len(txt) // 2
+    cut = txt.rfind(b"\n@r", 0, half) + 1
+    (tmp_path / "c.fastq.gz").write_bytes(gzip.compress(txt[:cut]) + gzip.compress(txt[cut:]))
+    gz2 = leon_b200.read_file(str(tmp_path / "c.fastq.gz"))
+    for r in (gz, gz2):
+        for key in ("bases", "offsets", "quals", "headers", "header_offsets"):
+            assert np.array_equal(r[key], plain[key]), key
+    (tmp_path / "d.fastq.gz").write_bytes(gzip.compress(txt)[:-40])
+    with pytest.raises(LeonError):
+        leon_b200.read_file(str(tmp_path / "d.fastq.gz"))
+
+
+def test_workload_writer_and_digest(tmp_path):
+    """leon_b200.workloads: the vectorised file writer equals the per-read one, chunk-seeded generation is independent of
+    which chunks are asked for, and the digest tells streams apart."""
+    from leon_b200 import synth, workloads as W
+    g = synth.make_genome(5000, 1)
+    b, o, q = synth.sample_reads(g, 1234, 100, 2, with_quals=True)
+    W.write_fixed(str(tmp_path / "a.fq"), b, 100, q)
+    synth.write_fasta(str(tmp_path / "b.fq"), b, o, q)
+    assert (tmp_path / "a.fq").read_bytes() == (tmp_path / "b.fq").read_bytes()
+    W.write_fixed(str(tmp_path / "a.fa"), b, 100)
+    synth.write_fasta(str(tmp_path / "b.fa"), b, o)
+    assert (tmp_path / "a.fa").read_bytes() == (tmp_path / "b.fa").read_bytes()
+    n = W.C3_CHUNK + 1000
+    fb, fo, fq = W.generate_c3(300000, n)
+    cb, co, cq = W.generate_c3(300000, n, chunks=[1])
+    assert len(co) - 1 == 1000 and np.array_equal(cb, fb[int(fo[W.C3_CHUNK]):]) and np.array_equal(cq, fq[int(fo[W.C3_CHUNK]):])
+    lens = np.diff(fo.astype(np.int64))
+    assert lens.max() == 150 and lens.min() < 150 and (fb == ord("N")).any()
+    r = dict(bloom=np.arange(10, dtype=np.uint8), anchors_dict=np.zeros(3, np.uint8), dna=np.ones(7, np.uint8),
+             blocksizes=np.array([7, 2], np.uint64), qual_text=np.frombuffer(b"II\n#I\n", np.uint8), qual_block_sizes=np.array([6], np.uint64))
+    d1 = W.digest_of_result(r, True)
+    r2 = dict(r, dna=np.zeros(7, np.uint8))
+    ok, diff = W.digests_equal(d1, W.digest_of_result(r2, True))
+    assert not ok and diff == ["dna"]
+    assert W.digests_equal(d1, W.digest_of_result(dict(r), True))[0]

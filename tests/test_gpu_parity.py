@@ -192,3 +192,92 @@ def test_indels_n_runs_variable_lengths(k, fastq, lossless, seed):
     eng.close()
     _same(r, ref, fastq)
 
+
+
+def test_configs3_shape_at_one_hundredth_scale():
+    """BASELINE configs[3] at x0.01: 1 Mbp genome, 333 333 FASTQ reads of 150 bp with indels, N bases, N runs and
+    trimmed reads, lossy, 50000-read blocks (7 blocks, 2 levels of the hash partition, several deflate chunks per block),
+    byte for byte against the oracle."""
+    from oracle import oracle_py as O
+    from leon_b200 import workloads as W
+    bases, offs, quals = W.generate_c3(1_000_000, 333_333)
+    ref = O.compress(bases, offs, quals, kmer_size=31, reads_per_block=50000)
+    eng = _engine(kmer_size=31, reads_per_block=50000, has_qual=True)
+    r = eng.compress(bases, offs, quals)
+    eng.close()
+    _same(r, ref, True)
+    # the same set with the quality blocks deflated on the device: every stream inflates to the reference's text
+    import zlib
+    eng = _engine(kmer_size=31, reads_per_block=50000, has_qual=True, qual_zlib_on_device=True, skip_qual_text=True, skip_read_arrays=True)
+    r = eng.compress(bases, offs, quals)
+    eng.close()
+    assert len(r["anchor_pos"]) == 0 and len(r["qual_text"]) == 0
+    at, parts = 0, []
+    for nz in r["qual_z_block_sizes"]:
+        parts.append(zlib.decompress(r["qual_z"][at:at + int(nz)].tobytes()))
+        at += int(nz)
+    assert b"".join(parts) == ref["qual_text"].tobytes()
+    assert np.array_equal(r["dna"], ref["dna"]) and np.array_equal(r["anchors_dict"], ref["anchors_dict"])
+
+
+def _long_reads(seed, genome_len, lengths, n_rate=0.001, fastq=False):
+    """Reads of the given lengths sampled from a random genome with 0.5 % substitutions (both strands)."""
+    from leon_b200 import synth
+    rng = np.random.Generator(np.random.PCG64(seed))
+    g = synth.make_genome(genome_len, seed)
+    bs, qs = [], []
+    for L in lengths:
+        p = int(rng.integers(0, genome_len - L + 1))
+        r = g[p:p + L].copy()
+        if rng.random() < 0.5:
+            r = synth._COMP[r[::-1]]
+        e = rng.random(L) < 0.005
+        r[e] = synth.ACGT[(np.searchsorted(synth.ACGT, r[e]) + rng.integers(1, 4, int(e.sum()))) % 4]
+        r[rng.random(L) < n_rate] = ord("N")
+        bs.append(r)
+        if fastq:
+            q = rng.integers(2, 41, L).astype(np.uint8) + 33
+            qs.append(q)
+    offs = np.zeros(len(lengths) + 1, np.uint64)
+    np.cumsum(np.array(lengths, np.int64), out=offs[1:])
+    return np.concatenate(bs), offs, (np.concatenate(qs) if fastq else None)
+
+
+@pytest.mark.parametrize("k,fastq,kind,seed", [(31, False, "miseq250", 31), (31, True, "miseq300", 32), (63, False, "kb", 33),
+                                               (31, True, "mixed", 34), (63, True, "mixed", 35), (31, False, "kb", 36)])
+def test_long_reads_unstaged_paths(k, fastq, kind, seed):
+    """Reads longer than the shared-memory staging of k_extract / k_anchor_lookup / k_walk (159 bp) and of k_quals: 250 /
+    300 bp, several kb, and short and long reads mixed inside one CTA tile -- the global-memory paths, byte for byte."""
+    from oracle import oracle_py as O
+    rng = np.random.Generator(np.random.PCG64(seed))
+    if kind == "miseq250":
+        lengths = [250] * 6000
+    elif kind == "miseq300":
+        lengths = [int(x) for x in rng.integers(200, 301, 5000)]
+    elif kind == "kb":
+        lengths = [int(x) for x in rng.integers(1500, 9000, 400)]
+    else:
+        lengths = [int(x) for x in rng.choice([40, 100, 151, 250, 1000, 4000], 1500, p=[0.1, 0.4, 0.2, 0.2, 0.07, 0.03])]
+    bases, offs, quals = _long_reads(seed, 60000, lengths, fastq=fastq)
+    rpb = 700
+    ref = O.compress(bases, offs, quals, kmer_size=k, reads_per_block=rpb)
+    eng = _engine(kmer_size=k, reads_per_block=rpb, has_qual=fastq)
+    r = eng.compress(bases, offs, quals)
+    eng.close()
+    _same(r, ref, fastq)
+
+
+def test_create_destroy_does_not_leak():
+    """leon_destroy returns every device and pinned allocation of the context (FASTQ path with device deflate included)."""
+    import torch
+    from leon_b200 import synth
+    g = synth.make_genome(30000, 5)
+    bases, offs, quals = synth.sample_reads(g, 20000, 100, 6, with_quals=True)
+    free = []
+    for i in range(4):
+        eng = _engine(kmer_size=31, reads_per_block=5000, has_qual=True, qual_zlib_on_device=True)
+        eng.compress(bases, offs, quals)
+        eng.close()
+        torch.cuda.synchronize()
+        free.append(torch.cuda.mem_get_info()[0])
+    assert free[-1] >= free[1] - (8 << 20), free      # after the first cycle (context warm-up) nothing is held back

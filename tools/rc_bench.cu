@@ -68,6 +68,80 @@ static void host_encode(const std::vector<Sym> &syms, std::vector<uint8_t> &out)
     for (int i = 0; i < 8; i++) { out.push_back((uint8_t)(low >> 56)); low <<= 8; }
 }
 
+
+// ---- version 2 on the HOST: the same LB_HD step functions the kernel runs, same grouping and fallback -------------
+struct HostStb { std::vector<uint8_t> *o; void operator()(uint32_t at, uint32_t v) const { if (o->size() <= at) o->resize(at + 1); (*o)[at] = (uint8_t)v; } };
+struct HostPut { std::vector<uint8_t> *o; uint32_t &on; void operator()(uint8_t b) { if (o->size() <= on) o->resize(on + 1); (*o)[on++] = b; } };
+static uint64_t g_rare_groups = 0, g_groups = 0;
+static void host_encode_v2(const std::vector<Sym> &syms, std::vector<uint8_t> &out)
+{
+    using namespace lbent;
+    const size_t n = syms.size();
+    std::vector<uint64_t> mp(n + 8, 1); std::vector<uint32_t> ell(n + 8, 0), lo(n + 8, 0), w(n + 8, 1);
+    for (size_t i = 0; i < n; i++) { div_magic65(syms[i].tot, mp[i], ell[i]); lo[i] = syms[i].lo; w[i] = syms[i].w; }
+    uint64_t low = 0, q = div65(~0ull, mp[0], ell[0]);
+    uint32_t on = 0;
+    out.clear();
+    HostStb stb{&out};
+    for (size_t j = 0; j < n; j += 4) {
+        bool wide = false;
+        for (int i = 0; i <= 4; i++) wide |= ell[j + i] > RC2_MAX_ELL;
+        const uint64_t low_g = low, q_g = q; const uint32_t on_g = on;
+        uint32_t rmin = 0xffffffffu;
+        g_groups++;
+        if (!wide) {
+            for (int i = 0; i < 4; i++)
+                rc_step_fast(low, q, on, rmin, lo[j + i], w[j + i], lo[j + i] + w[j + i], (uint32_t)mp[j + i + 1], (uint32_t)(mp[j + i + 1] >> 32), ell[j + i + 1], stb);
+        }
+        if (wide || rmin < (1u << 16)) {
+            g_rare_groups++;
+            low = low_g; q = q_g; on = on_g;
+            HostPut put{&out, on};
+            for (int i = 0; i < 4; i++) rc_step_gen(low, q, lo[j + i], w[j + i], mp[j + i + 1], ell[j + i + 1], put);
+        }
+    }
+    out.resize(on);
+    for (int i = 0; i < 8; i++) { out.push_back((uint8_t)(low >> 56)); low <<= 8; }
+}
+
+static int host_selftest(int streams, int reads)
+{
+    using namespace lbent;
+    // div65 == n / d: every d in [2, 2^20] with adversarial n, then random (n, d) up to 2^32 - 1
+    std::mt19937_64 rng(7);
+    uint64_t bad = 0, checked = 0;
+    for (uint32_t d = 1; d < (1u << 20); d++) {
+        uint64_t mp; uint32_t ell; div_magic65(d, mp, ell);
+        const uint64_t ns[6] = {~0ull, ~0ull - d, (~0ull / d) * d, (~0ull / d) * d - 1, rng(), rng() >> (rng() % 40)};
+        for (uint64_t nn : ns) { checked++; if (div65(nn, mp, ell) != nn / d) bad++; }
+    }
+    for (int i = 0; i < 20000000; i++) {
+        uint32_t d = (uint32_t)(rng() >> (32 + rng() % 31)); if (d < 1) d = 1;
+        uint64_t nn = rng() >> (rng() % 17);
+        uint64_t mp; uint32_t ell; div_magic65(d, mp, ell);
+        checked++; if (div65(nn, mp, ell) != nn / d) bad++;
+    }
+    printf("host: div65 mismatches %llu of %llu\n", (unsigned long long)bad, (unsigned long long)checked);
+    int badstreams = 0; uint64_t nsym = 0;
+    for (int s = 0; s < streams; s++) {
+        std::vector<Sym> syms; gen_stream(1000 + s, reads, syms);
+        if (s % 3 == 1) {        // adversarial: huge totals (ell > 23) and tiny alphabets mixed in
+            HostModel big(5); big.total = (s % 2) ? 40000000u : 9000000u; big.cnt.assign(5, big.total / 5);
+            std::vector<Sym> t2;
+            for (size_t i = 0; i < syms.size(); i++) { t2.push_back(syms[i]); if (i % 7 == 0) { Sym y; big.get(rng() % 5, y.lo, y.w, y.tot); t2.push_back(y); } }
+            syms.swap(t2);
+        }
+        std::vector<uint8_t> want, got;
+        host_encode(syms, want);
+        host_encode_v2(syms, got);
+        nsym += syms.size();
+        if (want != got) { badstreams++; printf("host: stream %d differs (%zu vs %zu bytes)\n", s, want.size(), got.size()); }
+    }
+    printf("host: v2 coder on %d streams, %llu symbols: %d mismatching streams; %llu of %llu groups recoded (%.3f %%)\n", streams,
+           (unsigned long long)nsym, badstreams, (unsigned long long)g_rare_groups, (unsigned long long)g_groups, 100.0 * g_rare_groups / g_groups);
+    return (bad || badstreams) ? 1 : 0;
+}
+
 __global__ void k_magic_check(uint32_t d0, uint32_t n, uint32_t stride, const uint64_t *want_m, const uint8_t *want_s, uint32_t *bad)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -82,6 +156,7 @@ __global__ void k_magic_check(uint32_t d0, uint32_t n, uint32_t stride, const ui
 
 int main(int argc, char **argv)
 {
+    if (argc > 1 && !strcmp(argv[1], "--host")) return host_selftest(argc > 2 ? atoi(argv[2]) : 12, argc > 3 ? atoi(argv[3]) : 20000);
     int streams = argc > 1 ? atoi(argv[1]) : 92, reads = argc > 2 ? atoi(argv[2]) : 50000;
     using namespace lbent;
     {   // div_magic on the device == exact host arithmetic: every d in [2, 2^22], then a stride through the 32-bit range
@@ -100,7 +175,7 @@ int main(int argc, char **argv)
         }
         cudaFree(d_m); cudaFree(d_s); cudaFree(d_bad);
     }
-    std::vector<uint4> rec; std::vector<uint8_t> sh; std::vector<StreamDesc> descs; std::vector<std::vector<uint8_t>> want(streams);
+    std::vector<uint4> rec, rec2; std::vector<uint8_t> sh, sh2; std::vector<StreamDesc> descs; std::vector<std::vector<uint8_t>> want(streams);
     uint64_t base = 0, rare = 0;
     for (int s = 0; s < streams; s++) {
         std::vector<Sym> syms; gen_stream(1000 + s, reads, syms);
@@ -108,6 +183,8 @@ int main(int argc, char **argv)
         for (const Sym &y : syms) {
             uint64_t m; uint32_t sft, inc; host_magic(y.tot, m, sft, inc);
             rec.push_back(make_uint4(y.lo, y.w, (uint32_t)m, (uint32_t)(m >> 32))); sh.push_back((uint8_t)(sft | (inc << 7)));
+            uint64_t mp; uint32_t ell; div_magic65(y.tot, mp, ell);
+            rec2.push_back(make_uint4(y.lo, y.w, (uint32_t)mp, (uint32_t)(mp >> 32))); sh2.push_back((uint8_t)ell);
         }
         StreamDesc d; d.rec_base = base; d.nsym = syms.size(); d.out_base = 2 * base + 1024 * s; d.out_cap = 2 * syms.size() + 1024;
         descs.push_back(d); base += syms.size();
@@ -126,12 +203,15 @@ int main(int argc, char **argv)
     CK(cudaMemcpy(d_desc, descs.data(), streams * sizeof(StreamDesc), cudaMemcpyHostToDevice));
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
     std::vector<uint8_t> got(outcap); std::vector<uint64_t> sizes(streams);
-    for (int variant = 1; variant < 2; variant++) {
+    for (int variant = 1; variant <= 2; variant++) {
         float best = 1e9f;
+        CK(cudaMemcpy(d_rec, variant == 1 ? rec.data() : rec2.data(), base * 16, cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(d_sh, variant == 1 ? sh.data() : sh2.data(), base, cudaMemcpyHostToDevice));
         for (int it = 0; it < 4; it++) {
             CK(cudaMemset(d_out, 0xEE, outcap)); CK(cudaMemset(d_ovf, 0, 4));
             CK(cudaEventRecord(e0));
-            k_range_encode<<<streams, 32>>>(d_rec, d_sh, d_desc, d_out, d_size, 0, d_ovf);
+            if (variant == 1) k_range_encode<<<streams, 32>>>(d_rec, d_sh, d_desc, d_out, d_size, 0, d_ovf);
+            else k_range_encode2<<<streams, 32>>>(d_rec, d_sh, d_desc, d_out, d_size, 0, d_ovf);
             CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1)); CK(cudaGetLastError());
             float ms; cudaEventElapsedTime(&ms, e0, e1); if (ms < best) best = ms;
         }
