@@ -371,7 +371,7 @@ def measure(args, name, torch, dist, world, rank, local_rank, want_e2e=True):
              "nruns": res["nb_distinct"], "dna_bytes": len(res["dna"]),
              "qual_bytes": float(local_reads * (read_len + 1)) if fastq else 0.0, "qual_z_bytes": float(len(res["qual_z"])),
              "launches": {k: v[1] / args.steps for k, v in ktimes.items()}}
-    stats["nsym"] = float(eng.timings().get("nsym", 0)) or float(eng.debug_fetch("nsym", np.uint64).sum())
+    stats["nsym"] = float(eng.timings()["nsym_total"])
     out = dict(name=name, total_reads=total_reads, local_reads=local_reads, read_len=read_len, S=S, value=value, ms_per_step=ms_per_step,
                dev_ms=dev_ms, launches=launches, clocks=clocks, ktimes=ktimes, phase=phase, stats=stats, digest=digest,
                digest_ok=digest_ok, digest_diff=digest_diff, anchors=res["anchor_count"], dna_bytes=len(res["dna"]),

@@ -101,6 +101,10 @@ typedef struct leon_result {
 
 /* Device-side phase timings of the last leon_compress()/phase calls, CUDA events on the context's stream. */
 typedef struct leon_timings {
+    /* anchor_ms: the anchor batches on the main stream; the walk / entropy stage of a super-block runs beside the later
+     * batches on its own streams, so walk_ms = how long the main stream then still waited for that stage (its exposed
+     * tail: mostly the range coder chains of the last super-block) and entropy_ms = the wait for the dictionary coder and
+     * the quality streams after that */
     float h2d_ms, count_ms, sort_ms, bloom_ms, anchor_ms, walk_ms, qual_ms, entropy_ms, d2h_ms, total_ms;
     uint64_t kernel_launches;     /* kernels launched by the library since leon_create */
     uint32_t sort_passes;         /* radix passes executed by the counting sort */
@@ -111,6 +115,7 @@ typedef struct leon_timings {
     float dict_wait_ms;           /* how long the stream's work had been finished before that thread was */
     float dict_copy_wait_ms;      /* part of dict_host_ms spent waiting for the records to arrive from the device */
     float reserved[3];
+    uint64_t nsym_total;          /* symbols coded by the per-block range coders in the last run */
 } leon_timings;
 
 typedef struct leon_ctx leon_ctx;

@@ -62,7 +62,7 @@ class Timings(C.Structure):
                [("kernel_launches", C.c_uint64), ("sort_passes", C.c_uint32), ("anchor_batches", C.c_uint32),
                 ("anchor_rounds", C.c_uint32), ("sort_pass_ms", C.c_float), ("sort_keys", C.c_uint64),
                 ("dict_host_ms", C.c_float), ("dict_wait_ms", C.c_float), ("dict_copy_wait_ms", C.c_float),
-                ("reserved", C.c_float * 3)]
+                ("reserved", C.c_float * 3), ("nsym_total", C.c_uint64)]
 
 
 class ContainerInfo(C.Structure):

@@ -30,6 +30,7 @@ static void usage() {
 }
 
 int main(int argc, char **argv) {
+    setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);     // the path uses more streams than the default 8 hardware queues
     leon_file_opts o;
     memset(&o, 0, sizeof o);
     std::string in, out;

@@ -19,6 +19,7 @@
 #include <thread>
 #include <atomic>
 #include <chrono>
+#include <deque>
 
 namespace {
 
@@ -67,6 +68,48 @@ enum Phase { PH_NONE = 0, PH_UPLOADED, PH_COUNTED, PH_BLOOM, PH_ENCODED };
 
 }  // namespace
 
+// One host thread's private launch context: stream, scratch of the scan / partition helpers, pinned scalar slot,
+// launch counter and kernel timer (none of them is shared between threads).
+struct Lane {
+    cudaStream_t st = nullptr;
+    DevBuf d_scan, d_tile_hist, d_tile_off;
+    PinBuf h_small;
+    LaunchCounter lc;
+    KernelTimer kt;
+};
+
+// A super-block of the walk / entropy stage: whole blocks [first_block, first_block + nblocks) = reads [lo, hi) of this
+// rank.  What its range coders read and write lives here until they have finished; the rest of the stage's buffers are
+// transient and shared by all super-blocks (used in stream order on the worker's lane).
+struct SbState {
+    uint64_t lo = 0, hi = 0, nk = 0, nbases = 0, first_block = 0, nblocks = 0, nsym = 0;
+    bool launched = false, fetched = false;
+    DevBuf d_rec, d_sh, d_descs, d_outall, d_outsize;
+    PinBuf h_sizes, h_descs;
+    cudaStream_t rc_stream = nullptr;
+    cudaEvent_t ev_anchored = nullptr, ev_records = nullptr, ev_coded = nullptr;
+    KernelTimer kt;
+    void ensure()
+    {
+        if (rc_stream) return;
+        int lo_pri = 0, hi_pri = 0;
+        CUDA_TRY(cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri));
+        CUDA_TRY(cudaStreamCreateWithPriority(&rc_stream, cudaStreamNonBlocking, hi_pri));   // one warp per block: never queue behind bulk kernels
+        CUDA_TRY(cudaEventCreateWithFlags(&ev_anchored, cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&ev_records, cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&ev_coded, cudaEventDisableTiming));
+    }
+    void destroy()
+    {
+        if (rc_stream) { cudaStreamSynchronize(rc_stream); cudaStreamDestroy(rc_stream); rc_stream = nullptr; }
+        if (ev_anchored) cudaEventDestroy(ev_anchored);
+        if (ev_records) cudaEventDestroy(ev_records);
+        if (ev_coded) cudaEventDestroy(ev_coded);
+        ev_anchored = ev_records = ev_coded = nullptr;
+        kt.release();
+    }
+};
+
 struct leon_ctx {
     leon_opts opts;
     std::string err;
@@ -90,6 +133,10 @@ struct leon_ctx {
     DevBuf d_retry, d_pstart_alt, d_tstart, d_mcnt, d_mcur, d_bstart, d_solid_cnt, d_bstart_all, d_keys_recv, d_solid_keys, d_pick, d_bloom_all, d_xchg;
     Comm comm;
     uint64_t nkmers_total = 0;
+    // counting in pieces (count_begin / count_add / count_close / count_finish)
+    uint32_t count_npasses = 1, count_pass = 0;
+    uint64_t keys_fill = 0, keys_cap = 0, count_reads_total = 0, count_bases_total = 0;
+    DevBuf d_keys_batch;
     PinBuf h_histo, h_small;
     leon_count_result cres;
     int32_t min_abundance = 0;
@@ -128,6 +175,18 @@ struct leon_ctx {
     bool qz_done = false;
     uint64_t reads_without_anchor = 0;
     int32_t min_len = 0, max_len = 0;
+    // walk / entropy stage (stage_b_worker)
+    Lane wk;
+    std::deque<SbState> sbs;
+    uint64_t sbs_used = 0;
+    std::atomic<uint64_t> sb_pub{0};
+    std::atomic<bool> sb_abort{false};
+    std::thread sb_thread;
+    std::string sb_err;
+    int sb_err_code = 0;
+    // caller's stream (leon_set_stream): the library's own streams are ordered after it at entry and it after them at exit
+    cudaStream_t user_st = nullptr;
+    cudaEvent_t ev_user_in = nullptr, ev_user_out = nullptr;
 };
 
 namespace {
@@ -225,35 +284,125 @@ template <typename K> void radix_sort(leon_ctx *c, K *&keys, K *&alt, uint64_t n
     for (int p = 0; p < passes && n > 1; p++) partition_pass(c, keys, alt, n, lbcount::ShiftDigit<K>{shift0 + 8 * p});
 }
 
-template <typename K> void do_count(leon_ctx *c)
+// keys of the current counting pass whose pass id (a hash of the key, independent of the partition bits) is `pass`:
+// appended to dst in any order (only the multiset matters); INVALID keys are dropped
+template <typename K>
+__global__ void __launch_bounds__(256) k_select_pass(const K *__restrict__ src, uint64_t n, uint32_t npasses, uint32_t pass,
+                                                     K *__restrict__ dst, unsigned long long *__restrict__ fill)
 {
-    using namespace lbcount;
-    const int k = c->opts.kmer_size;
+    __shared__ unsigned long long base;
+    __shared__ uint32_t cnt;
+    const uint64_t i0 = (uint64_t)blockIdx.x * 256 * 8;
+    if (threadIdx.x == 0) cnt = 0;
+    __syncthreads();
+    K keep[8];
+    uint32_t slot[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        const uint64_t i = i0 + (uint64_t)j * 256 + threadIdx.x;
+        slot[j] = 0xffffffffu;
+        if (i < n) {
+            const K key = src[i];
+            if (!kmer_invalid(key) && (uint32_t)(((lbcount::mix64(lbcount::key_mix(key) + 0x51ed270b0f1fULL) >> 32) * npasses) >> 32) == pass) {
+                keep[j] = key;
+                slot[j] = atomicAdd(&cnt, 1u);
+            }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) base = atomicAdd(fill, (unsigned long long)cnt);
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < 8; j++)
+        if (slot[j] != 0xffffffffu) dst[base + slot[j]] = keep[j];
+}
+
+// ---- counting in pieces: begin -> add (once per batch of reads) -> close (once per pass) -> finish ---------------------
+// In-memory read sets use one pass and one batch (do_count).  The streaming path (leon_count(batch, last)) adds the k-mers
+// of one batch at a time; with more than one pass every pass sees all batches again and keeps the keys whose pass id is
+// its own, so the key buffer is 1 / npasses of the k-mers (K/SortingCountAlgorithm.cpp:545-552: DSK's passes over
+// partitions, here without the disk).
+template <typename K> void count_begin(leon_ctx *c, uint32_t npasses, uint64_t key_capacity)
+{
     cudaStream_t st = c->st;
     c->kt.reset();
-    CUDA_TRY(cudaEventRecord(c->ev[2], st));
     if (!c->d_tbl.p) {
         c->d_tbl.reserve(256 * 8);
         CUDA_TRY(cudaMemcpyAsync(c->d_tbl.p, kSimpleHashTable, 256 * 8, cudaMemcpyHostToDevice, st));
     }
-    // k-mer slot offsets per read
+    c->count_npasses = npasses ? npasses : 1;
+    c->count_pass = 0;
+    c->keys_fill = 0;
+    c->keys_cap = key_capacity;
+    c->count_reads_total = 0;
+    c->count_bases_total = 0;
+    c->d_keys.reserve((key_capacity + 1) * sizeof(K));
+    c->d_keys_alt.reserve((key_capacity + 1) * (sizeof(K) > 8 ? sizeof(K) : 8));
+    c->d_histo.reserve(10001 * 8);
+    c->d_stats.reserve(sizeof(lbcount::CountStats) + 16);
+    CUDA_TRY(cudaMemsetAsync(c->d_histo.p, 0, 10001 * 8, st));
+    CUDA_TRY(cudaMemsetAsync(c->d_stats.p, 0, sizeof(lbcount::CountStats) + 16, st));
+    c->nsolid = 0;
+    c->tm.sort_passes = 0;
+    c->tm.sort_keys = 0;
+}
+
+// k-mer slot offsets of the reads in d_bases / d_offsets (c->nreads of them); returns the number of slots
+uint64_t count_koff(leon_ctx *c)
+{
+    using namespace lbcount;
+    cudaStream_t st = c->st;
     c->d_koff.reserve((c->nreads + 1) * 8);
     uint64_t *koff = c->d_koff.as<uint64_t>();
-    uint64_t *tot = lbscan::exclusive_scan<uint64_t>(c->nreads, NkIn{c->d_offsets.as<uint64_t>(), k}, NkOut{koff}, c->d_scan, st, c->lc);
+    uint64_t *tot = lbscan::exclusive_scan<uint64_t>(c->nreads, NkIn{c->d_offsets.as<uint64_t>(), c->opts.kmer_size}, NkOut{koff}, c->d_scan, st, c->lc);
     uint64_t nk = c->nreads ? fetch_scalar(c, tot) : 0;
     c->nkmers = nk;
-    CUDA_TRY(cudaMemcpyAsync(koff + c->nreads, &c->nkmers, 8, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(koff + c->nreads, tot, 8, cudaMemcpyDeviceToDevice, st));
+    if (c->nreads == 0) CUDA_TRY(cudaMemsetAsync(koff, 0, 8, st));
+    return nk;
+}
 
-    c->d_keys.reserve((nk + 1) * sizeof(K));
-    c->d_keys_alt.reserve((nk + 1) * (sizeof(K) > 8 ? sizeof(K) : 8));
-    K *keys = c->d_keys.as<K>(), *alt = c->d_keys_alt.as<K>();
-    if (nk) {
-        // bases of the 256 reads of a CTA are staged in shared memory when they fit (40 KB), else read from global
-        uint64_t need = ((256ull * (uint64_t)c->max_len + 31) & ~15ull) + 16;
-        uint32_t stage_bytes = need <= 40960 ? (uint32_t)need : 16u;
+// the keys of those reads appended to the pass buffer (count_koff has run for them)
+template <typename K> void count_add(leon_ctx *c)
+{
+    using namespace lbcount;
+    const int k = c->opts.kmer_size;
+    cudaStream_t st = c->st;
+    uint64_t *koff = c->d_koff.as<uint64_t>();
+    const uint64_t nk = c->nkmers;
+    if (c->count_pass == 0) { c->count_reads_total += c->nreads; c->count_bases_total += c->nbases; }
+    if (!nk) return;
+    // bases of the 256 reads of a CTA are staged in shared memory when they fit (40 KB), else read from global
+    uint64_t need = ((256ull * (uint64_t)c->max_len + 31) & ~15ull) + 16;
+    uint32_t stage_bytes = need <= 40960 ? (uint32_t)need : 16u;
+    if (c->count_npasses == 1) {
+        if (c->keys_fill + nk > c->keys_cap) throw LeonError(LEON_E_OVERFLOW, "k-mer counting: more k-mers than the plan announced");
+        K *keys = c->d_keys.as<K>() + c->keys_fill;
         LB_TIMED(c->kt, "k_extract", st, LB_LAUNCH(c->lc, (k_extract<K>), cdiv_u(c->nreads, 256), 256, stage_bytes, st, c->d_bases.as<uint8_t>(),
                   c->d_offsets.as<uint64_t>(), koff, c->nreads, k, keys, stage_bytes));
+        c->keys_fill += nk;
+    } else {
+        // all keys of the batch, then the ones of this pass appended to the pass buffer
+        c->d_keys_batch.reserve((nk + 1) * sizeof(K));
+        K *tmp = c->d_keys_batch.as<K>();
+        LB_TIMED(c->kt, "k_extract", st, LB_LAUNCH(c->lc, (k_extract<K>), cdiv_u(c->nreads, 256), 256, stage_bytes, st, c->d_bases.as<uint8_t>(),
+                  c->d_offsets.as<uint64_t>(), koff, c->nreads, k, tmp, stage_bytes));
+        unsigned long long *fill = (unsigned long long *)(c->d_stats.as<uint8_t>() + sizeof(CountStats) + 8);
+        LB_TIMED(c->kt, "k_select_pass", st, LB_LAUNCH(c->lc, (k_select_pass<K>), cdiv_u(nk, 2048), 256, 0, st, tmp, nk, c->count_npasses, c->count_pass,
+                  c->d_keys.as<K>(), fill));
+        c->keys_fill = fetch_scalar(c, fill);
+        if (c->keys_fill > c->keys_cap) throw LeonError(LEON_E_OVERFLOW, "k-mer counting: a pass holds more keys than its buffer (raise the number of passes)");
     }
+}
+
+// Partition, exchange (multi-GPU) and count the keys gathered for the current pass; solid k-mers are appended to the list.
+template <typename K> void count_close(leon_ctx *c)
+{
+    using namespace lbcount;
+    cudaStream_t st = c->st;
+    const uint64_t nk = c->keys_fill;
+    K *keys = c->d_keys.as<K>(), *alt = c->d_keys_alt.as<K>();
+    const bool append = c->count_npasses > 1;          // several passes: the solid list lives in its own buffer and grows
     CUDA_TRY(cudaEventRecord(c->ev[3], st));
 
     // partition by hash into buckets of ~BcCfg::TARGET keys: LSD passes over the top `bits` bits of key_mix.
@@ -262,14 +411,13 @@ template <typename K> void do_count(leon_ctx *c)
     uint64_t nk_total = nk;
     if (c->comm.active()) {
         c->d_xchg.reserve(256);
-        CUDA_TRY(cudaMemcpyAsync(c->d_xchg.p, &c->nkmers, 8, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync(c->d_xchg.p, &nk, 8, cudaMemcpyHostToDevice, st));
         NCCL_TRY(nccl_api().AllReduce(c->d_xchg.p, c->d_xchg.p, 1, ncclUint64, ncclSum, c->comm.comm, st));
         nk_total = fetch_scalar(c, c->d_xchg.as<uint64_t>());
     }
     c->nkmers_total = nk_total;
     int bits = 0;
     while (bits < 24 && ((nk_total >> bits) > (uint64_t)BcCfg<K>::TARGET || (1 << bits) < N)) bits++;
-    c->tm.sort_passes = 0;
     const uint64_t nbuckets = 1ull << bits;
     // two tables of partition starts (ping-pong over the levels); the last one is the bucket table bstart
     c->d_bstart.reserve((nbuckets + 2) * 8);
@@ -315,17 +463,11 @@ template <typename K> void do_count(leon_ctx *c)
             c->tm.sort_passes++;
         }
     }
-    c->tm.sort_keys = nk;
+    c->tm.sort_keys += nk;
     CUDA_TRY(cudaEventRecord(c->ev[4], st));
 
     // per-bucket counting in shared-memory tables -> abundance histogram, solid list
-    c->d_histo.reserve(10001 * 8);
-    c->d_stats.reserve(sizeof(CountStats) + 8);
-    CUDA_TRY(cudaMemsetAsync(c->d_histo.p, 0, 10001 * 8, st));
-    CUDA_TRY(cudaMemsetAsync(c->d_stats.p, 0, sizeof(CountStats) + 8, st));
-    c->nsolid = 0;
-    c->solid_keys = alt;
-    CountStats stats = {0, 0, 0};
+    if (!append) c->solid_keys = alt;
     BucketSrc src;
     memset(&src, 0, sizeof src);
     const K *count_keys = keys;
@@ -374,11 +516,29 @@ template <typename K> void do_count(leon_ctx *c)
         count_keys = recv;
         count_buckets = lo_of(me + 1) - lo_of(me);
         count_n = recv_total;
-        c->d_solid_keys.reserve((recv_total / 2 + 2) * sizeof(K));
+        if (!append) {
+            c->d_solid_keys.reserve((recv_total / 2 + 2) * sizeof(K));
+            c->solid_keys = c->d_solid_keys.p;
+        }
+    }
+    if (append) {     // room for the solid k-mers of this pass behind those of the earlier ones
+        const uint64_t want = c->nsolid + count_n / 2 + 2;
+        if (want * sizeof(K) > c->d_solid_keys.cap || want * 4 > c->d_solid_cnt.cap) {
+            DevBuf nk_, nc_;
+            nk_.reserve(want * sizeof(K) * 3 / 2);
+            nc_.reserve(want * 4 * 3 / 2);
+            if (c->nsolid) {
+                CUDA_TRY(cudaMemcpyAsync(nk_.p, c->d_solid_keys.p, c->nsolid * sizeof(K), cudaMemcpyDeviceToDevice, st));
+                CUDA_TRY(cudaMemcpyAsync(nc_.p, c->d_solid_cnt.p, c->nsolid * 4, cudaMemcpyDeviceToDevice, st));
+            }
+            CUDA_TRY(cudaStreamSynchronize(st));
+            std::swap(c->d_solid_keys.p, nk_.p); std::swap(c->d_solid_keys.cap, nk_.cap);
+            std::swap(c->d_solid_cnt.p, nc_.p); std::swap(c->d_solid_cnt.cap, nc_.cap);
+        }
         c->solid_keys = c->d_solid_keys.p;
     }
     if (count_n && count_buckets) {
-        c->d_solid_cnt.reserve((count_n / 2 + 2) * 4);
+        if (!append) c->d_solid_cnt.reserve((count_n / 2 + 2) * 4);
         CUDA_TRY(cudaFuncSetAttribute(k_bucket_count<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BcCfg<K>::SMEM));
         unsigned long long *nsolid_d = (unsigned long long *)(c->d_stats.as<uint8_t>() + sizeof(CountStats));
         // first launch: small tables; buckets whose distinct keys do not fit are listed and redone with full-size tables
@@ -396,11 +556,25 @@ template <typename K> void do_count(leon_ctx *c)
                       (const uint32_t *)retry_list));
         c->nsolid = fetch_scalar(c, nsolid_d);
     }
+    CUDA_TRY(cudaEventRecord(c->ev[4], st));
+    c->count_pass++;
+    c->keys_fill = 0;
+    if (c->count_npasses > 1) {
+        unsigned long long *fill = (unsigned long long *)(c->d_stats.as<uint8_t>() + sizeof(CountStats) + 8);
+        CUDA_TRY(cudaMemsetAsync(fill, 0, 8, st));
+    }
+}
+
+// Histogram and counters of the whole set (all ranks), cutoff (Histogram::compute_threshold)
+void count_finish(leon_ctx *c)
+{
+    using namespace lbcount;
+    cudaStream_t st = c->st;
     if (c->comm.active()) {   // global histogram and counters
         NCCL_TRY(nccl_api().AllReduce(c->d_histo.p, c->d_histo.p, 10001, ncclUint64, ncclSum, c->comm.comm, st));
         NCCL_TRY(nccl_api().AllReduce(c->d_stats.p, c->d_stats.p, 3, ncclUint64, ncclSum, c->comm.comm, st));
     }
-    stats = fetch_scalar(c, c->d_stats.as<CountStats>());
+    CountStats stats = fetch_scalar(c, c->d_stats.as<CountStats>());
     if (stats.nb_valid >> 62) throw LeonError(LEON_E_OVERFLOW, "k-mer counting: a bucket could not be split any further");
     c->h_histo.reserve(10001 * 8);
     CUDA_TRY(cudaMemcpyAsync(c->h_histo.p, c->d_histo.p, 10001 * 8, cudaMemcpyDeviceToHost, st));
@@ -414,6 +588,20 @@ template <typename K> void do_count(leon_ctx *c)
     r.nb_kmers = stats.nb_valid;
     compute_threshold(r.histogram, 4, &r.cutoff, &r.nb_solids_cutoff);
     c->phase = PH_COUNTED;
+}
+
+// in-memory read set: one pass, one batch
+template <typename K> void do_count(leon_ctx *c)
+{
+    const int k = c->opts.kmer_size;
+    // exact number of k-mer slots: bases - (k - 1) per read, reads shorter than k have none (upper bound used as capacity)
+    CUDA_TRY(cudaEventRecord(c->ev[2], c->st));
+    const uint64_t nk = count_koff(c);
+    count_begin<K>(c, 1, nk + 1);
+    count_add<K>(c);
+    count_close<K>(c);
+    count_finish(c);
+    (void)k;
 }
 
 template <typename K> void do_bloom(leon_ctx *c)
@@ -662,10 +850,212 @@ uint64_t anchor_batch_reads(const leon_ctx *c)
 {
     if (c->opts.anchor_batch > 0) return (uint64_t)c->opts.anchor_batch;
     if (c->comm.n > 1) return 10ull * (uint64_t)c->opts.reads_per_block;
-    return 524288;   // measured on B200 (4.6 M reads): 32 k -> 30 ms, 256 k -> 12 ms, 1 M -> 11 ms, one batch -> 27 ms
+    // measured on B200 (4.6 M reads): 32 k -> 30 ms, 256 k -> 12 ms, 1 M -> 11 ms, one batch -> 27 ms; a whole number of
+    // blocks, so that a batch is also a super-block of the walk / entropy stage
+    const uint64_t rpb = (uint64_t)c->opts.reads_per_block;
+    return rpb >= 524288 ? rpb : (524288 / rpb) * rpb;
 }
 
-// Phase 3a: anchors for all reads, in ordered batches (see anchors.cuh)
+// Reads per super-block of the walk / entropy stage: whole blocks, about one anchor batch.
+uint64_t superblock_reads(const leon_ctx *c)
+{
+    const uint64_t rpb = (uint64_t)c->opts.reads_per_block, S = anchor_batch_reads(c);
+    return S <= rpb ? rpb : (S / rpb) * rpb;
+}
+
+// ---- pipeline between the anchor resolution (main thread, in file order) and the walk / entropy stage (worker) -----
+// A super-block can be walked and coded as soon as the anchors of all reads up to its end are known; its blocks'
+// range coders (one warp each, tens of milliseconds of a dependent chain) then run beside everything that follows.
+// The main thread records an event when the anchor batches have passed a super-block boundary and publishes it; the
+// worker thread owns its own streams, scratch buffers and launch counter.
+template <typename T> T fetch_scalar_on(Lane &ln, const T *dptr)
+{
+    ln.h_small.reserve(256);
+    CUDA_TRY(cudaMemcpyAsync(ln.h_small.p, dptr, sizeof(T), cudaMemcpyDeviceToHost, ln.st));
+    CUDA_TRY(cudaStreamSynchronize(ln.st));
+    T v;
+    memcpy(&v, ln.h_small.p, sizeof(T));
+    return v;
+}
+
+// One stable 8-bit partition pass on a lane (the symbol records of a super-block)
+template <typename K, typename D> void partition_pass_on(Lane &ln, K *&keys, K *&alt, uint64_t n, D digit)
+{
+    using namespace lbcount;
+    uint32_t ntiles = cdiv_u(n, RsCfg<K>::TILE);
+    if (ntiles == 0) ntiles = 1;
+    ln.d_tile_hist.reserve((uint64_t)ntiles * 256 * 4);
+    ln.d_tile_off.reserve((uint64_t)ntiles * 256 * 8);
+    LB_TIMED(ln.kt, "k_part_hist", ln.st, LB_LAUNCH(ln.lc, (k_part_hist<K, D>), ntiles, RS_THREADS, 0, ln.st, keys, n, digit, ln.d_tile_hist.as<uint32_t>(), ntiles));
+    lbscan::exclusive_scan<uint64_t>((uint64_t)ntiles * 256, HistIn{ln.d_tile_hist.as<uint32_t>()},
+                                     HistOut{ln.d_tile_off.as<uint64_t>()}, ln.d_scan, ln.st, ln.lc);
+    LB_TIMED(ln.kt, "k_part_scatter", ln.st, LB_LAUNCH(ln.lc, (k_part_scatter<K, D>), ntiles, RS_THREADS, 0, ln.st, keys, alt, n, digit, ln.d_tile_off.as<uint64_t>(), ntiles));
+    std::swap(keys, alt);
+}
+
+__global__ void k_sb_info(const uint64_t *__restrict__ offsets, const uint64_t *__restrict__ koff, uint64_t nreads, uint64_t S,
+                          uint64_t nsb, uint64_t *__restrict__ out)
+{
+    uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= nsb) return;
+    uint64_t lo = g * S, hi = lo + S < nreads ? lo + S : nreads;
+    out[2 * g] = koff[hi] - koff[lo];
+    out[2 * g + 1] = offsets[hi] - offsets[lo];
+}
+
+// Walk, symbol records, per-(block, model) ranks and the launch of the range coder for super-block g.
+template <typename K> void sb_prepare(leon_ctx *c, uint64_t g)
+{
+    using namespace lbent;
+    Lane &ln = c->wk;
+    cudaStream_t st = ln.st;
+    SbState &sb = c->sbs[g];
+    const int k = c->opts.kmer_size;
+    const uint32_t rpb = (uint32_t)c->opts.reads_per_block;
+    const uint64_t R = sb.hi - sb.lo;
+    if (!R) return;
+    const uint8_t *bases = c->d_bases.as<uint8_t>();
+    const uint64_t *offsets = c->d_offsets.as<uint64_t>() + sb.lo;
+    const uint64_t *koff = c->d_koff.as<uint64_t>() + sb.lo;
+    const int32_t *apos = c->d_apos.as<int32_t>() + sb.lo;
+    const uint32_t *aaddr = c->d_aaddr.as<uint32_t>() + sb.lo;
+    // Waits are taken on the HOST, never as a stream wait sitting at the head of a queue: with more streams than hardware
+    // connections (8 by default) a stream that waits for an event holds up every other stream mapped to its connection
+    // (measured: the anchor kernels and the chains of other super-blocks queued behind such waits, 83 -> 199 ms per run).
+    CUDA_TRY(cudaEventSynchronize(sb.ev_anchored));
+    // the transient buffers of the stage are reused by the next super-block: in stream order on this lane
+    c->d_bif.reserve(sb.nk + 1);
+    c->d_err.reserve((sb.nk + 1) * 4);
+    c->d_recs.reserve((R + 1) * sizeof(lbwalk::ReadRec));
+    ReadRec *recs = c->d_recs.as<ReadRec>();
+    {
+        // bases of the 256 reads of a CTA are staged in shared memory when they fit (40 KB), else read from global
+        uint64_t need = ((256ull * (uint64_t)c->max_len + 31) & ~15ull) + 16;
+        uint32_t stage_bytes = need <= 40960 ? (uint32_t)need : 16u;
+        LB_TIMED(ln.kt, "k_walk", st, LB_LAUNCH(ln.lc, (lbwalk::k_walk<K>), cdiv_u(R, 256), 256, stage_bytes, st, bases, offsets, koff, R, c->bloom,
+                  c->d_tbl.as<uint64_t>(), apos, c->d_bif.as<uint8_t>(), c->d_err.as<uint32_t>(), recs, stage_bytes));
+    }
+    sb.nblocks = (R + rpb - 1) / rpb;
+    if (sb.nblocks >= (1ull << 18)) throw LeonError(LEON_E_OVERFLOW, "more than 2^18 blocks in one super-block");
+    c->d_symoff.reserve((R + 2) * 8);
+    uint64_t *symoff = c->d_symoff.as<uint64_t>();
+    SymCountIn cin{bases, offsets, koff, apos, aaddr, recs, c->d_bif.as<uint8_t>(), c->d_err.as<uint32_t>()};
+    uint64_t *symtot = lbscan::exclusive_scan<uint64_t>(R, cin, SymOffOut{symoff}, ln.d_scan, st, ln.lc);
+    CUDA_TRY(cudaMemcpyAsync(symoff + R, symtot, 8, cudaMemcpyDeviceToDevice, st));
+    const uint64_t nsym = fetch_scalar_on(ln, symtot);
+    if (nsym >= 0xffffff00ull) throw LeonError(LEON_E_OVERFLOW, "more than 2^32 symbols in one super-block");
+    sb.nsym = nsym;
+    c->d_srec.reserve((nsym + 1) * 8);
+    c->d_srec_alt.reserve((nsym + 1) * 8);
+    uint64_t *srec = c->d_srec.as<uint64_t>(), *salt = c->d_srec_alt.as<uint64_t>();
+    LB_TIMED(ln.kt, "k_emit_syms", st, LB_LAUNCH(ln.lc, k_emit_syms, cdiv_u(R, 256), 256, 0, st, bases, offsets, koff, R, rpb, apos, aaddr, recs,
+              c->d_bif.as<uint8_t>(), c->d_err.as<uint32_t>(), symoff, srec));
+    // stable sort by (block, model): key bits [40, 46 + bits(nblocks - 1))
+    int keybits = REC_MODEL_BITS;
+    while (keybits < 24 && ((sb.nblocks - 1) >> (keybits - REC_MODEL_BITS))) keybits++;
+    for (int p = 0; p < (keybits + 7) / 8 && nsym > 1; p++)
+        partition_pass_on(ln, srec, salt, nsym, lbcount::ShiftDigit<uint64_t>{REC_KEY_SHIFT + 8 * p});
+    // segments and chunks
+    c->d_segstart.reserve((sb.nblocks * NUM_MODELS + 2) * 8);
+    c->d_chunkoff.reserve((sb.nblocks * NUM_MODELS + 2) * 8);
+    uint64_t *segstart = c->d_segstart.as<uint64_t>(), *chunkoff = c->d_chunkoff.as<uint64_t>();
+    uint64_t nseg = 0, nchunks = 0;
+    if (nsym) {
+        uint64_t *segtot = lbscan::exclusive_scan<uint64_t>(nsym, SegHeadIn{srec}, SegHeadOut{segstart}, ln.d_scan, st, ln.lc);
+        nseg = fetch_scalar_on(ln, segtot);
+        CUDA_TRY(cudaMemcpyAsync(segstart + nseg, symoff + R, 8, cudaMemcpyDeviceToDevice, st));
+        uint64_t *chtot = lbscan::exclusive_scan<uint64_t>(nseg, SegChunksIn{segstart}, SegChunksOut{chunkoff}, ln.d_scan, st, ln.lc);
+        nchunks = fetch_scalar_on(ln, chtot);
+    }
+    // what the range coder reads stays with the super-block until its chains have finished
+    sb.d_rec.reserve((nsym + 1) * sizeof(uint4));
+    sb.d_sh.reserve(nsym + 1);
+    if (nchunks) {
+        c->d_chist.reserve(nchunks * 256 * 4);
+        uint32_t *H = c->d_chist.as<uint32_t>();
+        LB_TIMED(ln.kt, "k_chunk_hist", st, LB_LAUNCH(ln.lc, k_chunk_hist, (unsigned)nchunks, 256, 0, st, srec, segstart, chunkoff, nseg, H));
+        LB_TIMED(ln.kt, "k_seg_scan", st, LB_LAUNCH(ln.lc, k_seg_scan, (unsigned)nseg, 256, 0, st, chunkoff, nseg, nchunks, H));
+        LB_TIMED(ln.kt, "k_chunk_ranks", st, LB_LAUNCH(ln.lc, k_chunk_ranks, (unsigned)nchunks, CHUNK, 0, st, srec, segstart, chunkoff, nseg, H,
+                  sb.d_rec.as<uint4>(), sb.d_sh.as<uint8_t>()));
+    }
+    sb.d_descs.reserve(sb.nblocks * sizeof(StreamDesc));
+    sb.d_outall.reserve(2 * nsym + 1024 * sb.nblocks + 1024);
+    sb.d_outsize.reserve(sb.nblocks * 8 + 8);
+    LB_LAUNCH(ln.lc, k_block_descs, cdiv_u(sb.nblocks, 128), 128, 0, st, symoff, R, rpb, sb.nblocks, sb.d_descs.as<StreamDesc>());
+    sb.h_descs.reserve(sb.nblocks * sizeof(StreamDesc) + 8);
+    CUDA_TRY(cudaMemcpyAsync(sb.h_descs.p, sb.d_descs.p, sb.nblocks * sizeof(StreamDesc), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaEventRecord(sb.ev_records, st));
+    // the chains of this super-block on their own stream: they do not hold up the next super-block's preparation
+    CUDA_TRY(cudaEventSynchronize(sb.ev_records));
+    LB_TIMED(sb.kt, "k_range_encode", sb.rc_stream, LB_LAUNCH(ln.lc, k_range_encode, (unsigned)sb.nblocks, 32, 0, sb.rc_stream, sb.d_rec.as<uint4>(), sb.d_sh.as<uint8_t>(),
+              sb.d_descs.as<StreamDesc>(), sb.d_outall.as<uint8_t>(), sb.d_outsize.as<uint64_t>(), 0, c->d_counters.as<uint32_t>() + 2));
+    sb.h_sizes.reserve(sb.nblocks * 8 + 8);
+    CUDA_TRY(cudaMemcpyAsync(sb.h_sizes.p, sb.d_outsize.p, sb.nblocks * 8, cudaMemcpyDeviceToHost, sb.rc_stream));
+    CUDA_TRY(cudaEventRecord(sb.ev_coded, sb.rc_stream));
+    sb.launched = true;
+}
+
+// Output of super-block g: sizes -> block table, streams copied back to back into the host payload.
+void sb_finish(leon_ctx *c, uint64_t g)
+{
+    using namespace lbent;
+    SbState &sb = c->sbs[g];
+    if (!sb.launched) return;
+    const uint32_t rpb = (uint32_t)c->opts.reads_per_block;
+    CUDA_TRY(cudaEventSynchronize(sb.ev_coded));
+    const uint64_t *sz = sb.h_sizes.as<uint64_t>();
+    const StreamDesc *descs = sb.h_descs.as<StreamDesc>();      // out_base of every block's region (k_block_descs)
+    uint64_t *bs = c->h_bs.as<uint64_t>();
+    uint8_t *dna = c->h_dna.as<uint8_t>();
+    const uint64_t R = sb.hi - sb.lo;
+    for (uint64_t b = 0; b < sb.nblocks; b++) {
+        const uint64_t gb = sb.first_block + b;
+        const uint64_t r0 = b * rpb, r1 = std::min<uint64_t>(R, r0 + rpb);
+        if (sz[b] > descs[b].out_cap) throw LeonError(LEON_E_OVERFLOW, "range coder output exceeded its capacity bound");
+        if (c->dna_nbytes + sz[b] > c->h_dna.cap) throw LeonError(LEON_E_OVERFLOW, "sequence stream larger than the host payload buffer");
+        bs[2 * gb] = sz[b];
+        bs[2 * gb + 1] = r1 - r0;
+        if (sz[b]) CUDA_TRY(cudaMemcpyAsync(dna + c->dna_nbytes, sb.d_outall.as<uint8_t>() + descs[b].out_base, sz[b], cudaMemcpyDeviceToHost, sb.rc_stream));
+        c->dna_nbytes += sz[b];
+    }
+    CUDA_TRY(cudaEventRecord(sb.ev_coded, sb.rc_stream));       // now: "outputs are on the host"
+    sb.launched = false;
+    sb.fetched = true;
+}
+
+constexpr uint64_t SB_PIPELINE_MIN = 16;
+
+template <typename K> void stage_b_worker(leon_ctx *c)
+{
+    try {
+        CUDA_TRY(cudaSetDevice(c->opts.device));
+        const uint64_t nsb = c->sbs_used;
+        // Small read sets (up to SB_PIPELINE_MIN super-blocks, i.e. about one wave of range coder warps): the stage starts when
+        // the last anchor batch is done.  Walking super-block g beside the anchor batches g+1.. was measured on B200 at
+        // 4.6 M reads (10 super-blocks): the bulk kernels take the SMs from the small latency-critical anchor kernels
+        // (anchor stage 8.6 -> 15.5 ms) and that costs what the overlap gains (72.4 vs 72.2 ms; FASTQ 87.4 vs 82.8 ms), since
+        // the run ends one chain length (40 ms) after the LAST chain is launched either way.  Larger sets are pipelined.
+        const uint64_t gate = nsb <= SB_PIPELINE_MIN ? nsb - 1 : 0;
+        for (uint64_t g = 0; g < nsb; g++) {
+            while (c->sb_pub.load(std::memory_order_acquire) <= std::max(g, gate)) {
+                if (c->sb_abort.load()) return;
+                std::this_thread::sleep_for(std::chrono::microseconds(10));
+            }
+            sb_prepare<K>(c, g);
+        }
+        // outputs in file order; by the time the last super-block is launched the first chains have long finished
+        for (uint64_t g = 0; g < nsb; g++) sb_finish(c, g);
+        for (uint64_t g = 0; g < nsb; g++)
+            if (c->sbs[g].fetched) CUDA_TRY(cudaEventSynchronize(c->sbs[g].ev_coded));
+    } catch (const LeonError &e) {
+        c->sb_err = e.msg; c->sb_err_code = e.code;
+    } catch (const std::exception &e) {
+        c->sb_err = e.what(); c->sb_err_code = LEON_E_NOMEM;
+    }
+}
+
+// Phase 3a: anchors for all reads, in ordered batches (see anchors.cuh); every time the batches pass the end of a
+// super-block it is handed to the walk / entropy stage.
 template <typename K> void do_anchors(leon_ctx *c)
 {
     using namespace lbanchor;
@@ -676,17 +1066,10 @@ template <typename K> void do_anchors(leon_ctx *c)
     const uint8_t *bases = c->d_bases.as<uint8_t>();
     const uint64_t *offsets = c->d_offsets.as<uint64_t>();
 
-    c->d_apos.reserve((R + 1) * 4);
-    c->d_aaddr.reserve((R + 1) * 4);
-    c->d_insflag.reserve(R + 1);
-    CUDA_TRY(cudaMemsetAsync(c->d_apos.p, 0xff, (R + 1) * 4, st));     // -1
-    CUDA_TRY(cudaMemsetAsync(c->d_aaddr.p, 0, (R + 1) * 4, st));
-    CUDA_TRY(cudaMemsetAsync(c->d_insflag.p, 0, R + 1, st));
     int32_t *apos = c->d_apos.as<int32_t>();
     uint32_t *aaddr = c->d_aaddr.as<uint32_t>();
     uint8_t *insflag = c->d_insflag.as<uint8_t>();
-    c->d_counters.reserve(64);
-    uint32_t *counters = c->d_counters.as<uint32_t>();   // [0] collision, [1] remaining
+    uint32_t *counters = c->d_counters.as<uint32_t>();   // [0] collision, [1] remaining, [2], [3] range coder overflow flags
     c->dict_cap = 1 << 16;
     c->dict_cur = 0;
     c->dict_count = 0;
@@ -711,7 +1094,8 @@ template <typename K> void do_anchors(leon_ctx *c)
         R_total = fetch_scalar(c, c->d_xchg.as<uint64_t>() + 1);
     }
     if (R_total >= 0xfffffff0ull) throw LeonError(LEON_E_ARG, "more than 2^32-16 reads in one read set");
-    if ((uint64_t)k * R_total >= 0xffffff00ull) throw LeonError(LEON_E_OVERFLOW, "anchor dictionary stream could exceed 2^32 symbols");
+    if (c->opts.dict_on_device && (uint64_t)k * R_total >= 0xffffff00ull)
+        throw LeonError(LEON_E_OVERFLOW, "dict_on_device: the anchor dictionary stream could exceed 2^32 symbols");
     // every read inserts at most one anchor: sized once, so that the dictionary thread can read the list while it grows
     c->d_anchors.reserve((R_total + 1) * sizeof(K));
     uint64_t anchors_cap = c->d_anchors.cap / sizeof(K);
@@ -725,6 +1109,7 @@ template <typename K> void do_anchors(leon_ctx *c)
         c->dict_thread = std::thread(dict_host_worker<K>, c);
     }
     std::vector<uint32_t> m_all(N, 0), m_off(N, 0);
+    uint64_t sb_next = 0;                                    // first super-block not handed over yet
 
     for (uint64_t g = 0; g < nbatches; g++) {
         const uint64_t lo = std::min(R, g * S), hi = std::min(R, (g + 1) * S);
@@ -747,7 +1132,6 @@ template <typename K> void do_anchors(leon_ctx *c)
         if (N > 1) {   // sizes of everybody's P list
             CUDA_TRY(cudaMemcpyAsync(c->d_xchg.as<uint32_t>() + 16 + me, &m_own, 4, cudaMemcpyHostToDevice, st));
             NCCL_TRY(nccl_api().AllGather(c->d_xchg.as<uint32_t>() + 16 + me, c->d_xchg.as<uint32_t>() + 16, 1, ncclUint32, c->comm.comm, st));
-            c->h_small.reserve(256);
             CUDA_TRY(cudaMemcpyAsync(c->h_small.p, c->d_xchg.as<uint32_t>() + 16, 4 * N, cudaMemcpyDeviceToHost, st));
             CUDA_TRY(cudaStreamSynchronize(st));
             memcpy(m_all.data(), c->h_small.p, 4 * N);
@@ -800,19 +1184,24 @@ template <typename K> void do_anchors(leon_ctx *c)
                 if (attempt > 8) throw LeonError(LEON_E_OVERFLOW, "anchor candidate table: repeated proxy collisions");
                 salt = salt * 6364136223846793005ULL + 1442695040888963407ULL;
             }
-            // R: rounds of deterministic reservations; every rank decides its own reads, states are shared per round
+            // R: rounds of deterministic reservations; every rank decides its own reads, states are shared per round.
+            // A round after the last undecided read changes nothing, so rounds are launched in groups and the "undecided"
+            // counter is only read once per group: fewer host round trips than one per round.
+            const int group = N > 1 ? 1 : 3;
             while (true) {
-                c->tm.anchor_rounds++;
-                CUDA_TRY(cudaMemsetAsync(t.fu, 0xff, tcap * 4, st));
-                CUDA_TRY(cudaMemsetAsync(counters + 1, 0, 4, st));
-                LB_LAUNCH(c->lc, k_round_fu, cdiv_u(m, 256), 256, 0, st, state, cand_slot, m, t.fu);
-                if (m_own)
-                    LB_LAUNCH(c->lc, (k_round_decide<K>), warp_grid(m_own), 256, 0, st, bases, offsets, plist, m_own, joff, k, t, salt,
-                              cand_slot, state, counters + 1);
-                if (N > 1) {
-                    allgather_v(c, state, m_off, m_all, 1);
-                    LB_LAUNCH(c->lc, k_ins_update, cdiv_u(m, 256), 256, 0, st, state, cand_slot, m, t.ins);
-                    NCCL_TRY(nccl_api().AllReduce(counters + 1, counters + 1, 1, ncclUint32, ncclSum, c->comm.comm, st));
+                for (int it = 0; it < group; it++) {
+                    c->tm.anchor_rounds++;
+                    CUDA_TRY(cudaMemsetAsync(t.fu, 0xff, tcap * 4, st));
+                    CUDA_TRY(cudaMemsetAsync(counters + 1, 0, 4, st));
+                    LB_LAUNCH(c->lc, k_round_fu, cdiv_u(m, 256), 256, 0, st, state, cand_slot, m, t.fu);
+                    if (m_own)
+                        LB_LAUNCH(c->lc, (k_round_decide<K>), warp_grid(m_own), 256, 0, st, bases, offsets, plist, m_own, joff, k, t, salt,
+                                  cand_slot, state, counters + 1);
+                    if (N > 1) {
+                        allgather_v(c, state, m_off, m_all, 1);
+                        LB_LAUNCH(c->lc, k_ins_update, cdiv_u(m, 256), 256, 0, st, state, cand_slot, m, t.ins);
+                        NCCL_TRY(nccl_api().AllReduce(counters + 1, counters + 1, 1, ncclUint32, ncclSum, c->comm.comm, st));
+                    }
                 }
                 if (!fetch_scalar(c, counters + 1)) break;
             }
@@ -830,6 +1219,17 @@ template <typename K> void do_anchors(leon_ctx *c)
                 LB_LAUNCH(c->lc, (k_anchor_lookup<K>), cdiv_u(nb, 256), 256, look_stage, st, bases, offsets, lo, hi, delta, k,
                           dict_view<K>(c, c->dict_cur), apos, aaddr, (const uint8_t *)insflag, look_stage);
         }
+        // hand over every super-block whose reads are all anchored now
+        while (sb_next < c->sbs_used && (c->sbs[sb_next].hi <= hi || g + 1 == nbatches)) {
+            CUDA_TRY(cudaEventRecord(c->sbs[sb_next].ev_anchored, st));
+            sb_next++;
+            c->sb_pub.store(sb_next, std::memory_order_release);
+        }
+    }
+    while (sb_next < c->sbs_used) {      // no batches at all on this rank
+        CUDA_TRY(cudaEventRecord(c->sbs[sb_next].ev_anchored, st));
+        sb_next++;
+        c->sb_pub.store(sb_next, std::memory_order_release);
     }
     if (dict_thread_on) c->dict_fin.store(true, std::memory_order_release);
     CUDA_TRY(cudaEventRecord(c->ev[7], st));
@@ -912,12 +1312,9 @@ template <typename K> void do_encode_body(leon_ctx *c)
     const uint32_t rpb = (uint32_t)c->opts.reads_per_block;
     const uint8_t *bases = c->d_bases.as<uint8_t>();
     const uint64_t *offsets = c->d_offsets.as<uint64_t>();
-    const uint64_t *koff = c->d_koff.as<uint64_t>();
 
-    // Quality smoothing only needs the Bloom filter: it runs on a third stream beside the anchor resolution, whose many
-    // small kernels and host round trips leave most of the GPU idle.  It borrows the error-position buffer as its
-    // prefix-count scratch, so the walk waits for it.
-    c->d_err.reserve((c->nkmers + 1) * 4);
+    // Quality smoothing only needs the Bloom filter: it runs on a third (low priority) stream beside everything else;
+    // the run ends when its zlib streams are written too.
     c->qz_done = false;
     if (c->opts.has_qual) {
         c->d_qout.reserve(c->nbases + R + 16);
@@ -938,15 +1335,57 @@ template <typename K> void do_encode_body(leon_ctx *c)
             if (c->opts.qual_zlib_on_device) deflate_quals(c);
         }
     }
+
+    // ---- super-blocks of the walk / entropy stage
+    c->d_apos.reserve((R + 1) * 4);
+    c->d_aaddr.reserve((R + 1) * 4);
+    c->d_insflag.reserve(R + 1);
+    c->d_counters.reserve(64);
+    CUDA_TRY(cudaMemsetAsync(c->d_apos.p, 0xff, (R + 1) * 4, st));     // -1
+    CUDA_TRY(cudaMemsetAsync(c->d_aaddr.p, 0, (R + 1) * 4, st));
+    CUDA_TRY(cudaMemsetAsync(c->d_insflag.p, 0, R + 1, st));
+    CUDA_TRY(cudaMemsetAsync(c->d_counters.p, 0, 64, st));
+    const uint64_t SB = superblock_reads(c);
+    const uint64_t nsb = R ? (R + SB - 1) / SB : 0;
+    c->nblocks = R ? (R + rpb - 1) / rpb : 0;
+    c->dna_nbytes = 0;
+    c->nsym_total = 0;
+    if (c->sbs.size() < nsb) c->sbs.resize(nsb);
+    c->sbs_used = nsb;
+    std::vector<uint64_t> info(2 * nsb + 2, 0);
+    if (nsb) {
+        c->d_xchg.reserve(std::max<uint64_t>(256, nsb * 16 + 256));
+        uint64_t *dinfo = c->d_xchg.as<uint64_t>() + 16;
+        LB_LAUNCH(c->lc, k_sb_info, cdiv_u(nsb, 128), 128, 0, st, offsets, c->d_koff.as<uint64_t>(), R, SB, nsb, dinfo);
+        CUDA_TRY(cudaMemcpyAsync(info.data(), dinfo, nsb * 16, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+    }
+    for (uint64_t g = 0; g < nsb; g++) {
+        SbState &sb = c->sbs[g];
+        sb.lo = g * SB; sb.hi = std::min(R, sb.lo + SB);
+        sb.nk = info[2 * g]; sb.nbases = info[2 * g + 1];
+        sb.first_block = sb.lo / rpb;
+        sb.nblocks = 0; sb.nsym = 0; sb.launched = false; sb.fetched = false;
+        sb.kt.reset();
+        sb.ensure();
+    }
+    // host payload: a coded read takes at most a few bits per base plus its varints
+    c->h_dna.reserve(c->nbases / 2 + 32 * R + 1024 * c->nblocks + 4096);
+    c->h_bs.reserve(c->nblocks * 16 + 16);
+    c->wk.kt.reset();
+    c->sb_pub.store(0);
+    c->sb_abort.store(false);
+    c->sb_err.clear();
+    if (c->sb_thread.joinable()) c->sb_thread.join();
+    if (nsb) c->sb_thread = std::thread(stage_b_worker<K>, c);
+
     do_anchors<K>(c);
     int32_t *apos = c->d_apos.as<int32_t>();
-    uint32_t *aaddr = c->d_aaddr.as<uint32_t>();
 
     // anchor dictionary stream: one coder over all anchors, flushed once (C/Leon.cpp:1034-1042,1245-1260).  By default
     // the host thread started by do_anchors is already coding it; dict_on_device runs it as one more stream of
     // k_range_encode on the second stream next to everything below.
     uint32_t *ovf = c->d_counters.as<uint32_t>() + 2;
-    CUDA_TRY(cudaMemsetAsync(c->d_counters.p, 0, 64, st));
     if (c->comm.rank == 0 && c->opts.dict_on_device) {
         cudaStream_t s2 = c->st2;
         uint64_t A = c->dict_count;
@@ -971,90 +1410,22 @@ template <typename K> void do_encode_body(leon_ctx *c)
                   c->d_dict_desc.as<StreamDesc>(), c->d_dict_out.as<uint8_t>(), c->d_dict_size.as<uint64_t>(), 1, ovf + 1));
         CUDA_TRY(cudaEventRecord(c->ev[14], s2));
     }
-
-    if (c->opts.has_qual && R) CUDA_TRY(cudaStreamWaitEvent(st, c->ev_q[1], 0));
     CUDA_TRY(cudaEventRecord(c->ev[8], st));
-
-    // walk
-    c->d_bif.reserve(c->nkmers + 1);
-    c->d_recs.reserve((R + 1) * sizeof(lbwalk::ReadRec));
-    if (R)
     {
-        // bases of the 256 reads of a CTA are staged in shared memory when they fit (40 KB), else read from global
-        uint64_t need = ((256ull * (uint64_t)c->max_len + 31) & ~15ull) + 16;
-        uint32_t stage_bytes = need <= 40960 ? (uint32_t)need : 16u;
-        LB_TIMED(c->kt, "k_walk", st, LB_LAUNCH(c->lc, (lbwalk::k_walk<K>), cdiv_u(R, 256), 256, stage_bytes, st, bases, offsets, koff, R, c->bloom,
-                  c->d_tbl.as<uint64_t>(), apos, c->d_bif.as<uint8_t>(), c->d_err.as<uint32_t>(), c->d_recs.as<lbwalk::ReadRec>(), stage_bytes));
+        unsigned long long *cnt = (unsigned long long *)(c->d_counters.as<uint8_t>() + 32);
+        if (R) LB_LAUNCH(c->lc, k_count_noanchor, (unsigned)std::min<uint64_t>((R + 255) / 256, 1024), 256, 0, st, apos, R, cnt);
+        c->reads_without_anchor = fetch_scalar(c, cnt);
     }
+    // join the walk / entropy stage: every block is coded and on the host
+    if (c->sb_thread.joinable()) c->sb_thread.join();
+    if (!c->sb_err.empty()) throw LeonError(c->sb_err_code, "walk / entropy stage: " + c->sb_err);
+    for (uint64_t g = 0; g < nsb; g++) c->nsym_total += c->sbs[g].nsym;
     CUDA_TRY(cudaEventRecord(c->ev[9], st));
-
-    // per-block entropy coding
-    c->nblocks = R ? (R + rpb - 1) / rpb : 0;
-    c->dna_nbytes = 0;
-    if (c->nblocks) {
-        if (c->nblocks >= (1ull << 18)) throw LeonError(LEON_E_OVERFLOW, "more than 2^18 blocks in one read set");
-        ReadRec *recs = c->d_recs.as<ReadRec>();
-        c->d_symoff.reserve((R + 2) * 8);
-        uint64_t *symoff = c->d_symoff.as<uint64_t>();
-        SymCountIn cin{bases, offsets, koff, apos, aaddr, recs, c->d_bif.as<uint8_t>(), c->d_err.as<uint32_t>()};
-        uint64_t *symtot = lbscan::exclusive_scan<uint64_t>(R, cin, SymOffOut{symoff}, c->d_scan, st, c->lc);
-        CUDA_TRY(cudaMemcpyAsync(symoff + R, symtot, 8, cudaMemcpyDeviceToDevice, st));
-        uint64_t nsym = fetch_scalar(c, symtot);
-        if (nsym >= 0xffffff00ull) throw LeonError(LEON_E_OVERFLOW, "more than 2^32 symbols in one read set");
-        c->nsym_total = nsym;
-        c->d_srec.reserve((nsym + 1) * 8);
-        c->d_srec_alt.reserve((nsym + 1) * 8);
-        uint64_t *srec = c->d_srec.as<uint64_t>(), *salt = c->d_srec_alt.as<uint64_t>();
-        LB_TIMED(c->kt, "k_emit_syms", st, LB_LAUNCH(c->lc, k_emit_syms, cdiv_u(R, 256), 256, 0, st, bases, offsets, koff, R, rpb, apos, aaddr, recs,
-                  c->d_bif.as<uint8_t>(), c->d_err.as<uint32_t>(), symoff, srec));
-        // stable sort by (block, model): key bits [40, 46 + bits(nblocks - 1))
-        int keybits = REC_MODEL_BITS;
-        while (keybits < 24 && ((c->nblocks - 1) >> (keybits - REC_MODEL_BITS))) keybits++;
-        radix_sort<uint64_t>(c, srec, salt, nsym, REC_KEY_SHIFT, (keybits + 7) / 8);
-        // segments and chunks
-        c->d_segstart.reserve((c->nblocks * NUM_MODELS + 2) * 8);
-        c->d_chunkoff.reserve((c->nblocks * NUM_MODELS + 2) * 8);
-        uint64_t *segstart = c->d_segstart.as<uint64_t>(), *chunkoff = c->d_chunkoff.as<uint64_t>();
-        uint64_t nseg = 0, nchunks = 0;
-        if (nsym) {
-            uint64_t *segtot = lbscan::exclusive_scan<uint64_t>(nsym, SegHeadIn{srec}, SegHeadOut{segstart}, c->d_scan, st, c->lc);
-            nseg = fetch_scalar(c, segtot);
-            CUDA_TRY(cudaMemcpyAsync(segstart + nseg, symoff + R, 8, cudaMemcpyDeviceToDevice, st));
-            uint64_t *chtot = lbscan::exclusive_scan<uint64_t>(nseg, SegChunksIn{segstart}, SegChunksOut{chunkoff}, c->d_scan, st, c->lc);
-            nchunks = fetch_scalar(c, chtot);
-        }
-        c->d_rec.reserve((nsym + 1) * sizeof(uint4));
-        c->d_sh.reserve(nsym + 1);
-        if (nchunks) {
-            c->d_chist.reserve(nchunks * 256 * 4);
-            uint32_t *H = c->d_chist.as<uint32_t>();
-            LB_TIMED(c->kt, "k_chunk_hist", st, LB_LAUNCH(c->lc, k_chunk_hist, (unsigned)nchunks, 256, 0, st, srec, segstart, chunkoff, nseg, H));
-            LB_TIMED(c->kt, "k_seg_scan", st, LB_LAUNCH(c->lc, k_seg_scan, (unsigned)nseg, 256, 0, st, chunkoff, nseg, nchunks, H));
-            LB_TIMED(c->kt, "k_chunk_ranks", st, LB_LAUNCH(c->lc, k_chunk_ranks, (unsigned)nchunks, CHUNK, 0, st, srec, segstart, chunkoff, nseg, H,
-                      c->d_rec.as<uint4>(), c->d_sh.as<uint8_t>()));
-        }
-        c->d_descs.reserve(c->nblocks * sizeof(StreamDesc));
-        c->d_outall.reserve(2 * nsym + 1024 * c->nblocks + 1024);
-        c->d_outsize.reserve(c->nblocks * 8);
-        c->d_dnaoff.reserve(c->nblocks * 8);
-        c->d_bs.reserve(c->nblocks * 16);
-        LB_LAUNCH(c->lc, k_block_descs, cdiv_u(c->nblocks, 128), 128, 0, st, symoff, R, rpb, c->nblocks, c->d_descs.as<StreamDesc>());
-        LB_TIMED(c->kt, "k_range_encode", st, LB_LAUNCH(c->lc, k_range_encode2, (unsigned)c->nblocks, 32, 0, st, c->d_rec.as<uint4>(), c->d_sh.as<uint8_t>(),
-                  c->d_descs.as<StreamDesc>(), c->d_outall.as<uint8_t>(), c->d_outsize.as<uint64_t>(), 0, ovf));
-        uint64_t *dtot = lbscan::exclusive_scan<uint64_t>(c->nblocks, SizeIn{c->d_outsize.as<uint64_t>()},
-                                                          SizeOut{c->d_dnaoff.as<uint64_t>()}, c->d_scan, st, c->lc);
-        c->dna_nbytes = fetch_scalar(c, dtot);
-        c->d_dna.reserve(c->dna_nbytes + 16);
-        LB_LAUNCH(c->lc, k_gather_streams, (unsigned)c->nblocks, 256, 0, st, c->d_outall.as<uint8_t>(), c->d_descs.as<StreamDesc>(),
-                  c->d_outsize.as<uint64_t>(), c->d_dnaoff.as<uint64_t>(), c->d_dna.as<uint8_t>());
-        LB_LAUNCH(c->lc, k_blocksizes, cdiv_u(c->nblocks, 128), 128, 0, st, c->d_outsize.as<uint64_t>(), R, rpb, c->nblocks,
-                  c->d_bs.as<uint64_t>());
-    }
     // join the dictionary coder
     if (c->comm.rank != 0) {
         c->dict_nbytes = 0;
     } else if (c->opts.dict_on_device) {
-        CUDA_TRY(cudaStreamWaitEvent(st, c->ev[14], 0));
+        CUDA_TRY(cudaEventSynchronize(c->ev[14]));
         c->dict_nbytes = fetch_scalar(c, c->d_dict_size.as<uint64_t>());
         if (fetch_scalar(c, ovf + 1)) throw LeonError(LEON_E_OVERFLOW, "range coder output of the anchor dictionary exceeded its capacity bound");
     } else {
@@ -1065,24 +1436,22 @@ template <typename K> void do_encode_body(leon_ctx *c)
         c->dict_nbytes = c->dict_host_out.size();
     }
     if (fetch_scalar(c, ovf)) throw LeonError(LEON_E_OVERFLOW, "range coder output exceeded its capacity bound");
-    {
-        unsigned long long *cnt = (unsigned long long *)(c->d_counters.as<uint8_t>() + 32);
-        if (R) LB_LAUNCH(c->lc, k_count_noanchor, (unsigned)std::min<uint64_t>((R + 255) / 256, 1024), 256, 0, st, apos, R, cnt);
-        c->reads_without_anchor = fetch_scalar(c, cnt);
-    }
-    if (c->qz_done) CUDA_TRY(cudaStreamWaitEvent(st, c->ev_qz, 0));   // the run ends when the quality streams are written too
+    if (c->qz_done) CUDA_TRY(cudaEventSynchronize(c->ev_qz));   // the run ends when the quality streams are written too
+    else if (c->opts.has_qual && R) CUDA_TRY(cudaEventSynchronize(c->ev_q[1]));
     CUDA_TRY(cudaEventRecord(c->ev[10], st));
     c->phase = PH_ENCODED;
 }
 
-// do_encode_body with the dictionary thread stopped on every error path
+// do_encode_body with the helper threads stopped on every error path
 template <typename K> void do_encode(leon_ctx *c)
 {
     try {
         do_encode_body<K>(c);
     } catch (...) {
         c->dict_abort.store(true);
+        c->sb_abort.store(true);
         if (c->dict_thread.joinable()) c->dict_thread.join();
+        if (c->sb_thread.joinable()) c->sb_thread.join();
         throw;
     }
 }
@@ -1098,12 +1467,7 @@ void do_fetch(leon_ctx *c, leon_result *out)
     if (c->comm.rank != 0) { }
     else if (c->opts.dict_on_device) CUDA_TRY(cudaMemcpyAsync(c->h_dict.p, c->d_dict_out.p, c->dict_nbytes, cudaMemcpyDeviceToHost, st));
     else memcpy(c->h_dict.p, c->dict_host_out.data(), c->dict_nbytes);
-    c->h_dna.reserve(c->dna_nbytes + 8);
-    c->h_bs.reserve(c->nblocks * 16 + 8);
-    if (c->nblocks) {
-        CUDA_TRY(cudaMemcpyAsync(c->h_dna.p, c->d_dna.p, c->dna_nbytes, cudaMemcpyDeviceToHost, st));
-        CUDA_TRY(cudaMemcpyAsync(c->h_bs.p, c->d_bs.p, c->nblocks * 16, cudaMemcpyDeviceToHost, st));
-    }
+    // dna / blocksizes were copied to the host by the walk / entropy stage as the blocks finished
     c->h_apos.reserve((R + 1) * 4);
     c->h_aaddr.reserve((R + 1) * 4);
     const bool want_arrays = !c->opts.skip_read_arrays;
@@ -1166,6 +1530,21 @@ static thread_local std::string g_create_error;
         if ((ctx)->opts.kmer_size <= 31) fn<uint64_t>(ctx); else fn<u128>(ctx); \
     } while (0)
 
+// caller's stream (leon_set_stream): order the library's main stream after it / it after the main stream
+static void user_stream_in(leon_ctx *c)
+{
+    if (!c->user_st) return;
+    CUDA_TRY(cudaEventRecord(c->ev_user_in, c->user_st));
+    CUDA_TRY(cudaStreamWaitEvent(c->st, c->ev_user_in, 0));
+    CUDA_TRY(cudaStreamWaitEvent(c->st3, c->ev_user_in, 0));
+}
+static void user_stream_out(leon_ctx *c)
+{
+    if (!c->user_st) return;
+    CUDA_TRY(cudaEventRecord(c->ev_user_out, c->st));
+    CUDA_TRY(cudaStreamWaitEvent(c->user_st, c->ev_user_out, 0));
+}
+
 static void fill_timings(leon_ctx *c)
 {
     auto el = [&](int a, int b) { float ms = 0; if (cudaEventElapsedTime(&ms, c->ev[a], c->ev[b]) != cudaSuccess) { cudaGetLastError(); ms = 0; } return ms; };
@@ -1184,6 +1563,10 @@ static void fill_timings(leon_ctx *c)
     c->tm.dict_copy_wait_ms = c->opts.dict_on_device ? 0.f : (float)c->dict_copy_wait_ms;
     c->tm.dict_wait_ms = c->opts.dict_on_device ? 0.f : el(15, 14);
     c->kt.resolve();
+    c->wk.kt.resolve();
+    for (uint64_t g = 0; g < c->sbs_used; g++) c->sbs[g].kt.resolve();
+    c->tm.kernel_launches += c->wk.lc.n;
+    c->tm.nsym_total = c->nsym_total;
     c->tm.sort_pass_ms = 0;
     for (auto &sl : c->kt.slots)
         if (!strcmp(sl.name, "k_rs_scatter") && sl.n) c->tm.sort_pass_ms = (float)(sl.ms / sl.n);
@@ -1215,14 +1598,20 @@ int leon_create(const leon_opts *opts, leon_ctx **out)
     memset(&c->bloom, 0, sizeof c->bloom);
     try {
         CUDA_TRY(cudaSetDevice(opts->device));
-        CUDA_TRY(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
-        {   // the second stream carries the small record kernels and copies of the dictionary thread: highest priority,
-            // so that they slot in between the thread blocks of the big kernels instead of queueing behind them
+        {   // Priorities (lower number = more urgent).  The anchor resolution on the main stream is a train of small,
+            // latency-critical kernels: it must not queue behind the bulk kernels of the walk / entropy stage, which in turn
+            // go before the quality stream.  The second stream carries the small record kernels and copies of the dictionary
+            // thread: most urgent, so that they slot in between the thread blocks of the big kernels.
             int lo_pri = 0, hi_pri = 0;
             CUDA_TRY(cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri));
+            const int mid_pri = hi_pri < lo_pri - 1 ? lo_pri - 1 : lo_pri;
+            CUDA_TRY(cudaStreamCreateWithPriority(&c->st, cudaStreamNonBlocking, hi_pri < lo_pri - 2 ? lo_pri - 2 : hi_pri));
             CUDA_TRY(cudaStreamCreateWithPriority(&c->st2, cudaStreamNonBlocking, hi_pri));
+            CUDA_TRY(cudaStreamCreateWithPriority(&c->st3, cudaStreamNonBlocking, mid_pri));   // quality kernels: issued first, so they run first and are out of the way of the last chains
+            CUDA_TRY(cudaStreamCreateWithPriority(&c->wk.st, cudaStreamNonBlocking, mid_pri));
         }
-        CUDA_TRY(cudaStreamCreateWithFlags(&c->st3, cudaStreamNonBlocking));
+        CUDA_TRY(cudaEventCreateWithFlags(&c->ev_user_in, cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&c->ev_user_out, cudaEventDisableTiming));
         for (int i = 0; i < 2; i++) CUDA_TRY(cudaEventCreateWithFlags(&c->ev_q[i], cudaEventDisableTiming));
         CUDA_TRY(cudaEventCreateWithFlags(&c->ev_qz, cudaEventDisableTiming));
         for (int i = 0; i < 16; i++) CUDA_TRY(cudaEventCreate(&c->ev[i]));
@@ -1242,8 +1631,13 @@ void leon_destroy(leon_ctx *c)
     if (!c) return;
     cudaSetDevice(c->opts.device);
     c->dict_abort.store(true);
+    c->sb_abort.store(true);
     if (c->dict_thread.joinable()) c->dict_thread.join();
+    if (c->sb_thread.joinable()) c->sb_thread.join();
     if (c->st) cudaStreamSynchronize(c->st);
+    if (c->wk.st) { cudaStreamSynchronize(c->wk.st); }
+    for (auto &sb : c->sbs) sb.destroy();
+    c->wk.kt.release();
     if (c->comm.comm) nccl_api().CommDestroy(c->comm.comm);
     DevBuf *dev[] = {&c->d_retry, &c->d_pstart_alt, &c->d_tstart, &c->d_mcnt, &c->d_mcur, &c->d_bases, &c->d_offsets, &c->d_quals, &c->d_koff, &c->d_keys, &c->d_keys_alt, &c->d_tile_hist, &c->d_tile_off,
                      &c->d_scan, &c->d_bstart, &c->d_solid_cnt, &c->d_bstart_all, &c->d_keys_recv, &c->d_solid_keys, &c->d_pick,
@@ -1262,7 +1656,10 @@ void leon_destroy(leon_ctx *c)
     c->kt.release();
     for (int i = 0; i < 2; i++) if (c->ev_dstage[i]) cudaEventDestroy(c->ev_dstage[i]);
     if (c->ev_dtot) cudaEventDestroy(c->ev_dtot);
-    if (c->st && c->own_stream) cudaStreamDestroy(c->st);
+    if (c->st) cudaStreamDestroy(c->st);
+    if (c->wk.st) cudaStreamDestroy(c->wk.st);
+    if (c->ev_user_in) cudaEventDestroy(c->ev_user_in);
+    if (c->ev_user_out) cudaEventDestroy(c->ev_user_out);
     if (c->st2) { cudaStreamSynchronize(c->st2); cudaStreamDestroy(c->st2); }
     if (c->st3) { cudaStreamSynchronize(c->st3); cudaStreamDestroy(c->st3); }
     for (int i = 0; i < 2; i++) if (c->ev_q[i]) cudaEventDestroy(c->ev_q[i]);
@@ -1286,9 +1683,11 @@ int leon_upload(leon_ctx *c, const leon_reads *reads)
     if (!c) return LEON_E_ARG;
     LB_API_BEGIN
     CUDA_TRY(cudaSetDevice(c->opts.device));
+    user_stream_in(c);
     do_upload(c, reads);
     CUDA_TRY(cudaStreamSynchronize(c->st));          // the caller's buffers are free again when this call returns
     CUDA_TRY(cudaStreamSynchronize(c->st3));
+    user_stream_out(c);
     LB_API_END(c)
 }
 
@@ -1298,8 +1697,10 @@ int leon_count(leon_ctx *c, leon_count_result *out)
     LB_API_BEGIN
     if (c->phase < PH_UPLOADED) throw LeonError(LEON_E_STATE, "leon_count: no read set uploaded");
     CUDA_TRY(cudaSetDevice(c->opts.device));
+    user_stream_in(c);
     LB_DISPATCH(c, do_count);
     if (out) *out = c->cres;
+    user_stream_out(c);
     LB_API_END(c)
 }
 
@@ -1309,6 +1710,7 @@ int leon_bloom_build(leon_ctx *c, const uint8_t **bits, uint64_t *nbytes, uint64
     LB_API_BEGIN
     if (c->phase < PH_COUNTED) throw LeonError(LEON_E_STATE, "leon_bloom_build: leon_count has not run");
     CUDA_TRY(cudaSetDevice(c->opts.device));
+    user_stream_in(c);
     LB_DISPATCH(c, do_bloom);
     if (bits) {
         c->h_bloom.reserve(c->bloom.nbytes + 8);
@@ -1318,6 +1720,7 @@ int leon_bloom_build(leon_ctx *c, const uint8_t **bits, uint64_t *nbytes, uint64
     }
     if (nbytes) *nbytes = c->bloom.nbytes;
     if (reduced_bits) *reduced_bits = c->bloom.reduced_tai;
+    user_stream_out(c);
     LB_API_END(c)
 }
 
@@ -1327,8 +1730,10 @@ int leon_fetch(leon_ctx *c, leon_result *out)
     LB_API_BEGIN
     if (c->phase < PH_ENCODED) throw LeonError(LEON_E_STATE, "leon_fetch: nothing encoded yet");
     CUDA_TRY(cudaSetDevice(c->opts.device));
+    user_stream_in(c);
     do_fetch(c, out);
     fill_timings(c);
+    user_stream_out(c);
     LB_API_END(c)
 }
 
@@ -1338,9 +1743,11 @@ int leon_encode(leon_ctx *c, leon_result *out)
     LB_API_BEGIN
     if (c->phase < PH_BLOOM) throw LeonError(LEON_E_STATE, "leon_encode: leon_bloom_build has not run");
     CUDA_TRY(cudaSetDevice(c->opts.device));
+    user_stream_in(c);
     LB_DISPATCH(c, do_encode);
     if (out) do_fetch(c, out);
     fill_timings(c);
+    user_stream_out(c);
     LB_API_END(c)
 }
 
@@ -1350,11 +1757,13 @@ int leon_run_device(leon_ctx *c)
     LB_API_BEGIN
     if (c->phase < PH_UPLOADED) throw LeonError(LEON_E_STATE, "leon_run_device: no read set uploaded");
     CUDA_TRY(cudaSetDevice(c->opts.device));
+    user_stream_in(c);
     LB_DISPATCH(c, do_count);
     LB_DISPATCH(c, do_bloom);
     LB_DISPATCH(c, do_encode);
     CUDA_TRY(cudaStreamSynchronize(c->st));
     fill_timings(c);
+    user_stream_out(c);
     LB_API_END(c)
 }
 
@@ -1363,12 +1772,14 @@ int leon_compress(leon_ctx *c, const leon_reads *reads, leon_result *out)
     if (!c || !out) return LEON_E_ARG;
     LB_API_BEGIN
     CUDA_TRY(cudaSetDevice(c->opts.device));
+    user_stream_in(c);
     do_upload(c, reads);
     LB_DISPATCH(c, do_count);
     LB_DISPATCH(c, do_bloom);
     LB_DISPATCH(c, do_encode);
     do_fetch(c, out);
     fill_timings(c);
+    user_stream_out(c);
     LB_API_END(c)
 }
 
@@ -1423,19 +1834,31 @@ int leon_set_stream(leon_ctx *c, void *stream)
     if (!c) return LEON_E_ARG;
     LB_API_BEGIN
     CUDA_TRY(cudaSetDevice(c->opts.device));
-    CUDA_TRY(cudaStreamSynchronize(c->st));
-    if (c->own_stream && c->st) CUDA_TRY(cudaStreamDestroy(c->st));
-    c->st = (cudaStream_t)stream;
-    c->own_stream = false;
-    for (int i = 0; i < 16; i++) CUDA_TRY(cudaEventRecord(c->ev[i], c->st));
+    // The library keeps its own streams (their priorities order the stages of the path); the caller's stream is a
+    // synchronisation point: every call starts after what was enqueued on it and it waits for the call's device work.
+    c->user_st = (cudaStream_t)stream;
+    c->own_stream = stream == nullptr;
     LB_API_END(c)
 }
 
 int leon_get_kernel_times(const leon_ctx *c, leon_kernel_time *out, int cap, int *n)
 {
     if (!c || !n || (cap > 0 && !out)) return LEON_E_ARG;
+    // slots of the main thread, of the walk / entropy worker and of every super-block's range coder stream, merged by name
+    std::vector<KernelTimer::Slot> all;
+    auto add = [&](const KernelTimer &kt) {
+        for (auto &sl : kt.slots) {
+            bool found = false;
+            for (auto &a : all)
+                if (!strcmp(a.name, sl.name)) { a.ms += sl.ms; a.n += sl.n; found = true; break; }
+            if (!found) all.push_back(sl);
+        }
+    };
+    add(c->kt);
+    add(c->wk.kt);
+    for (uint64_t g = 0; g < c->sbs_used && g < c->sbs.size(); g++) add(c->sbs[g].kt);
     int m = 0;
-    for (auto &sl : c->kt.slots) {
+    for (auto &sl : all) {
         if (m < cap) {
             memset(&out[m], 0, sizeof out[m]);
             strncpy(out[m].name, sl.name, sizeof(out[m].name) - 1);

@@ -125,8 +125,9 @@ __global__ void __launch_bounds__(256, sizeof(K) == 8 ? 4 : 3) k_walk(const uint
         const K mask = kmer_mask(K(0), k);
         const int top = 2 * (k - 1);
         K fwd = anchor, rc = arc;
-        uint8_t *bp = bif + koff[r];
-        uint32_t *ep = err + koff[r];
+        const uint64_t kslot = koff[r] - koff[0];     // bif / err hold the k-mer slots of the super-block koff points at
+        uint8_t *bp = bif + kslot;
+        uint32_t *ep = err + kslot;
         uint32_t nBif = 0, nErr = 0;
         const uint32_t nsteps = (uint32_t)(L - k), nleft = (uint32_t)ap;
         for (uint32_t t = 0; t < nsteps; t++) {

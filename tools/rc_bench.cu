@@ -1,9 +1,10 @@
 // Micro-benchmark + self-check of the range coder kernels of entropy.cuh on synthetic symbol records shaped like a
 // C2 block (about 10.8 symbols and 3.5-4 output bytes per read).  Development tool, not part of the library:
-//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -I leon_b200/csrc -o tools/bin/rc_bench tools/rc_bench.cu
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -I leon_b200/csrc -I tools -o tools/bin/rc_bench tools/rc_bench.cu
 //   ./rc_bench [streams=92] [reads_per_stream=50000]
 // Every variant must reproduce the bytes of a plain host coder that divides (RangeCoder.cpp:106-145).
 #include "entropy.cuh"
+#include "rc_v2_experiment.cuh"
 #include <vector>
 #include <random>
 #include <chrono>
