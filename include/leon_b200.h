@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define LEON_B200_ABI_VERSION 2
+#define LEON_B200_ABI_VERSION 3
 
 enum {
     LEON_OK = 0,
@@ -136,7 +136,7 @@ int leon_compress(leon_ctx *ctx, const leon_reads *reads, leon_result *out);
 
 /* The same work phase by phase (what the CLI and multi-step hosts call): */
 int leon_upload(leon_ctx *ctx, const leon_reads *reads);                 /* H2D of the read set */
-int leon_count(leon_ctx *ctx, leon_count_result *out);                   /* K/SortingCountAlgorithm.cpp:499-644 as used by Leon */
+int leon_count_resident(leon_ctx *ctx, leon_count_result *out);          /* K/SortingCountAlgorithm.cpp:499-644 as used by Leon, on the uploaded set */
 int leon_bloom_build(leon_ctx *ctx, const uint8_t **bits, uint64_t *nbytes, uint64_t *reduced_bits); /* C/Leon.cpp:226-338 */
 int leon_encode(leon_ctx *ctx, leon_result *out);                        /* C/DnaCoder.cpp:279-405 over all blocks + range coding */
 /* Device-only run on the already uploaded read set (phases 1-4, outputs left in HBM); used to time the path with
@@ -147,6 +147,56 @@ int leon_fetch(leon_ctx *ctx, leon_result *out);
 int leon_get_timings(const leon_ctx *ctx, leon_timings *out);
 
 /* Device time of the main kernels of the last run (CUDA events on the context's stream around each launch). */
+/* ---- Streaming path: read sets that do not fit on the device (BASELINE configs[4]) -------------------------------------
+ * The reference never holds the read set: its Dispatcher hands the functors chunks of `-reads` consecutive sequences
+ * (DP/api/ICommand.hpp:304-331, driven from C/Leon.cpp:863 and :954) and DSK counts in passes over partitions
+ * (K/SortingCountAlgorithm.cpp:545-552).  These entry points are what those two call sites map to: the caller feeds
+ * the reads in batches, twice -- once to count, once to encode -- and the device only ever holds one batch, the k-mers
+ * of one counting pass, the Bloom filter and the anchor dictionary: its footprint does not depend on the number of
+ * reads.  Batches are read sets like leon_upload takes (offsets[0] = 0).
+ *
+ *   leon_count_begin(plan) -> npasses
+ *   repeat npasses times: leon_count(batch, last = 0) ... leon_count(batch, last = 1)       (the same batches every pass)
+ *   leon_count_finish(&count)          cutoff, histogram (Histogram::compute_threshold)
+ *   leon_bloom_build(...)              C/Leon.cpp:226-338
+ *   leon_encode_block(first_block, batch, &out) ... for every batch, in file order          DnaEncoder::operator() + writeBlock
+ *   leon_encode_finish(&result)        anchor dictionary, Bloom filter, totals (C/Leon.cpp:965-1081)
+ *
+ * Every batch but the last must hold whole blocks (a multiple of reads_per_block reads) and, with several ranks, whole
+ * rounds (a multiple of leon_comm_batch_reads(); every rank makes the same number of calls, with empty batches if it has
+ * run out of reads).  Output bytes equal those of the one-shot path whatever the batching and the number of passes. */
+typedef struct leon_stream_plan {
+    uint64_t total_reads;     /* reads this rank will feed (per pass) */
+    uint64_t total_bases;     /* their bases: bounds the number of k-mers */
+    uint32_t count_passes;    /* 0: chosen from the free device memory; n: n hash-partitioned passes over the batches */
+    uint32_t reserved[3];
+} leon_stream_plan;
+/* What one leon_encode_block call produced: the blocks [first_block, first_block + nblocks) of this rank. */
+typedef struct leon_block_out {
+    uint64_t first_block, nblocks, read_count;
+    const uint64_t *blocksizes;        /* [2 * nblocks]: bytes, reads */
+    const uint8_t  *dna;               uint64_t dna_nbytes;          /* dna_<id> of these blocks, concatenated */
+    const uint8_t  *qual_text;         uint64_t qual_nbytes;         /* as leon_result, for these blocks */
+    const uint64_t *qual_block_sizes;
+    const uint8_t  *qual_z;            uint64_t qual_z_nbytes;
+    const uint64_t *qual_z_block_sizes;
+    const int32_t  *anchor_pos;        /* per read of the batch (NULL with skip_read_arrays) */
+    const uint32_t *anchor_addr;
+    uint64_t reserved[4];
+} leon_block_out;
+int leon_count_begin(leon_ctx *ctx, const leon_stream_plan *plan, uint32_t *npasses);
+int leon_count(leon_ctx *ctx, const leon_reads *batch, int last);        /* Dispatcher::iterate(it, DSK functor, chunk) */
+int leon_count_finish(leon_ctx *ctx, leon_count_result *out);
+/* Codes the blocks of `batch`; first_block must be the number of blocks this rank has coded so far.  The outputs are on
+ * the host when it returns and stay valid until the next leon_encode_block / leon_encode_finish on the context. */
+int leon_encode_block(leon_ctx *ctx, uint64_t first_block, const leon_reads *batch, leon_block_out *out);
+/* Outputs of the last leon_encode_block again (the call is synchronous today; kept for hosts written against an
+ * asynchronous submission). */
+int leon_block_wait(leon_ctx *ctx, uint64_t first_block, leon_block_out *out);
+/* Closes the encoding pass: result holds the Bloom filter, the anchor dictionary stream, the counts and the totals of the
+ * whole set; its per-block fields (dna, blocksizes, quality streams) are empty -- they were handed out block by block. */
+int leon_encode_finish(leon_ctx *ctx, leon_result *out);
+
 typedef struct leon_kernel_time {
     char     name[32];
     float    ms_total;
@@ -260,7 +310,10 @@ typedef struct leon_file_opts {
     int32_t seq_only;         /* -seq-only = -noheader -noqual */
     int32_t device;           /* CUDA device */
     int32_t nthreads;         /* -nb-cores: host threads of the header coder and of zlib (0 = all) */
-    int32_t reserved[7];
+    int32_t stream_reads;     /* > 0: feed the device batches of this many reads through the streaming entry points (0: the
+                                 whole set at once when it fits the device, else batches sized from the free device memory) */
+    int32_t count_passes;     /* streaming: number of counting passes (0 = automatic) */
+    int32_t reserved[5];
 } leon_file_opts;
 typedef struct leon_file_stats {
     uint64_t nreads, total_bases, nblocks, input_bytes, output_bytes;

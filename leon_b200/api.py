@@ -9,7 +9,8 @@ LIB_PATH = os.path.join(HERE, "libleon_b200.so")
 
 ABI_SYMBOLS = [
     "leon_b200_abi_version", "leon_create", "leon_destroy", "leon_last_error", "leon_alloc_pinned", "leon_free_pinned",
-    "leon_compress", "leon_upload", "leon_count", "leon_bloom_build", "leon_encode", "leon_run_device", "leon_fetch",
+    "leon_compress", "leon_upload", "leon_count_resident", "leon_count_begin", "leon_count", "leon_count_finish",
+    "leon_encode_block", "leon_block_wait", "leon_encode_finish", "leon_bloom_build", "leon_encode", "leon_run_device", "leon_fetch",
     "leon_get_timings", "leon_get_kernel_times", "leon_set_stream", "leon_comm_unique_id", "leon_comm_init",
     "leon_comm_batch_reads", "leon_debug_bloom_query", "leon_debug_hashes", "leon_debug_fetch", "leon_write_container",
     "leon_headers_encode", "leon_headers_free", "leon_compress_file", "leon_decompress_file", "leon_read_file", "leon_file_reads_free",
@@ -54,6 +55,18 @@ class Result(C.Structure):
         ("reads_without_anchor", C.c_uint64),
         ("qual_z", C.POINTER(C.c_uint8)), ("qual_z_nbytes", C.c_uint64), ("qual_z_block_sizes", C.POINTER(C.c_uint64)),
     ]
+
+
+class StreamPlan(C.Structure):
+    _fields_ = [("total_reads", C.c_uint64), ("total_bases", C.c_uint64), ("count_passes", C.c_uint32), ("reserved", C.c_uint32 * 3)]
+
+
+class BlockOut(C.Structure):
+    _fields_ = [("first_block", C.c_uint64), ("nblocks", C.c_uint64), ("read_count", C.c_uint64),
+                ("blocksizes", C.POINTER(C.c_uint64)), ("dna", C.POINTER(C.c_uint8)), ("dna_nbytes", C.c_uint64),
+                ("qual_text", C.POINTER(C.c_uint8)), ("qual_nbytes", C.c_uint64), ("qual_block_sizes", C.POINTER(C.c_uint64)),
+                ("qual_z", C.POINTER(C.c_uint8)), ("qual_z_nbytes", C.c_uint64), ("qual_z_block_sizes", C.POINTER(C.c_uint64)),
+                ("anchor_pos", C.POINTER(C.c_int32)), ("anchor_addr", C.POINTER(C.c_uint32)), ("reserved", C.c_uint64 * 4)]
 
 
 class Timings(C.Structure):
@@ -126,7 +139,13 @@ def load_library(path=LIB_PATH):
     L.leon_free_pinned.argtypes = [C.c_void_p]
     L.leon_compress.argtypes = [C.c_void_p, C.POINTER(Reads), C.POINTER(Result)]
     L.leon_upload.argtypes = [C.c_void_p, C.POINTER(Reads)]
-    L.leon_count.argtypes = [C.c_void_p, C.POINTER(CountResult)]
+    L.leon_count_resident.argtypes = [C.c_void_p, C.POINTER(CountResult)]
+    L.leon_count_begin.argtypes = [C.c_void_p, C.POINTER(StreamPlan), C.POINTER(C.c_uint32)]
+    L.leon_count.argtypes = [C.c_void_p, C.POINTER(Reads), C.c_int]
+    L.leon_count_finish.argtypes = [C.c_void_p, C.POINTER(CountResult)]
+    L.leon_encode_block.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(Reads), C.POINTER(BlockOut)]
+    L.leon_block_wait.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(BlockOut)]
+    L.leon_encode_finish.argtypes = [C.c_void_p, C.POINTER(Result)]
     L.leon_bloom_build.argtypes = [C.c_void_p, C.POINTER(C.POINTER(C.c_uint8)), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     L.leon_encode.argtypes = [C.c_void_p, C.POINTER(Result)]
     L.leon_run_device.argtypes = [C.c_void_p]
@@ -508,7 +527,7 @@ class Leon:
 
     def count(self):
         r = CountResult()
-        self._check(self.L.leon_count(self.ctx, C.byref(r)))
+        self._check(self.L.leon_count_resident(self.ctx, C.byref(r)))
         return dict(cutoff=int(r.cutoff), nb_solids_cutoff=int(r.nb_solids_cutoff), nb_solid_total=int(r.nb_solid_total),
                     nb_distinct=int(r.nb_distinct), nb_kmers=int(r.nb_kmers), histogram=_arr(r.histogram, 10001, np.uint64))
 
@@ -522,6 +541,57 @@ class Leon:
         r = Result()
         self._check(self.L.leon_encode(self.ctx, C.byref(r)))
         return self._result(r)
+
+    # streaming path: batches of reads, counted in `count_passes` passes, then encoded batch by batch
+    def compress_stream(self, bases, offsets, quals=None, batch_reads=None, count_passes=0, batches=None):
+        """The whole set through leon_count_begin / leon_count / leon_count_finish / leon_bloom_build / leon_encode_block /
+        leon_encode_finish, `batch_reads` reads at a time (or the explicit list of (lo, hi) read ranges `batches`); returns the
+        result dict of compress() assembled from the per-batch outputs, plus `count_passes`."""
+        offsets = np.ascontiguousarray(offsets, np.uint64)
+        n = len(offsets) - 1
+        if batches is None:
+            batches = [(lo, min(n, lo + batch_reads)) for lo in range(0, n, batch_reads)] or [(0, 0)]
+
+        def batch(lo, hi):
+            o = offsets[lo:hi + 1] - offsets[lo]
+            b0, b1 = int(offsets[lo]), int(offsets[hi])
+            return self._reads(bases[b0:b1], o, quals[b0:b1] if quals is not None else None)
+
+        plan = StreamPlan(n, int(offsets[-1]), int(count_passes))
+        npass = C.c_uint32()
+        self._check(self.L.leon_count_begin(self.ctx, C.byref(plan), C.byref(npass)))
+        for _ in range(npass.value):
+            for i, (lo, hi) in enumerate(batches):
+                rd = batch(lo, hi)
+                self._check(self.L.leon_count(self.ctx, C.byref(rd), int(i == len(batches) - 1)))
+        cr = CountResult()
+        self._check(self.L.leon_count_finish(self.ctx, C.byref(cr)))
+        self.bloom_build()
+        parts = dict(dna=[], blocksizes=[], qual_text=[], qual_block_sizes=[], qual_z=[], qual_z_block_sizes=[], anchor_pos=[], anchor_addr=[])
+        first = 0
+        for lo, hi in batches:
+            rd = batch(lo, hi)
+            bo = BlockOut()
+            self._check(self.L.leon_encode_block(self.ctx, first, C.byref(rd), C.byref(bo)))
+            nb = int(bo.nblocks)
+            parts["dna"].append(_arr(bo.dna, bo.dna_nbytes, np.uint8))
+            parts["blocksizes"].append(_arr(bo.blocksizes, 2 * nb, np.uint64))
+            parts["qual_text"].append(_arr(bo.qual_text, bo.qual_nbytes, np.uint8))
+            hq = bo.qual_nbytes > 0 or bo.qual_z_nbytes > 0
+            parts["qual_block_sizes"].append(_arr(bo.qual_block_sizes, nb if hq else 0, np.uint64))
+            parts["qual_z"].append(_arr(bo.qual_z, bo.qual_z_nbytes, np.uint8))
+            parts["qual_z_block_sizes"].append(_arr(bo.qual_z_block_sizes, nb if bo.qual_z_nbytes else 0, np.uint64))
+            parts["anchor_pos"].append(_arr(bo.anchor_pos, bo.read_count if bo.anchor_pos else 0, np.int32))
+            parts["anchor_addr"].append(_arr(bo.anchor_addr, bo.read_count if bo.anchor_addr else 0, np.uint32))
+            first += nb
+        r = Result()
+        self._check(self.L.leon_encode_finish(self.ctx, C.byref(r)))
+        out = self._result(r)
+        for k, v in parts.items():
+            out[k] = np.concatenate(v) if v else np.zeros(0, np.uint8)
+        out["nblocks"] = first
+        out["count_passes"] = int(npass.value)
+        return out
 
     def run_device(self):
         self._check(self.L.leon_run_device(self.ctx))

@@ -175,6 +175,13 @@ struct leon_ctx {
     bool qz_done = false;
     uint64_t reads_without_anchor = 0;
     int32_t min_len = 0, max_len = 0;
+    // encoding pass state across leon_encode_block calls (encode_begin / encode_batch / encode_end)
+    bool enc_open = false;
+    uint64_t enc_rounds_done = 0, enc_reads_done = 0, enc_blocks_done = 0, enc_noanchor = 0, enc_total_reads = 0;
+    uint64_t enc_total_bases = 0;
+    bool enc_partial_seen = false, stream_counting = false;
+    uint64_t stream_reads_seen = 0;
+    leon_block_out last_block_out = {};
     // walk / entropy stage (stage_b_worker)
     Lane wk;
     std::deque<SbState> sbs;
@@ -1054,6 +1061,38 @@ template <typename K> void stage_b_worker(leon_ctx *c)
     }
 }
 
+// Start of the encoding pass over a read set of R_total reads (all ranks): empty anchor dictionary, the list the anchors
+// are appended to (every read inserts at most one, so it is sized once and the dictionary thread can read it while it
+// grows), the host thread that codes the dictionary stream.
+template <typename K> void encode_begin(leon_ctx *c, uint64_t R_total)
+{
+    const int k = c->opts.kmer_size;
+    if (R_total >= 0xfffffff0ull) throw LeonError(LEON_E_ARG, "more than 2^32-16 reads in one read set");
+    if (c->opts.dict_on_device && (uint64_t)k * R_total >= 0xffffff00ull)
+        throw LeonError(LEON_E_OVERFLOW, "dict_on_device: the anchor dictionary stream could exceed 2^32 symbols");
+    c->dict_cap = 1 << 16;
+    c->dict_cur = 0;
+    c->dict_count = 0;
+    dict_alloc<K>(c, 0, c->dict_cap);
+    c->tm.anchor_batches = 0;
+    c->tm.anchor_rounds = 0;
+    c->enc_rounds_done = 0;
+    c->enc_reads_done = 0;
+    c->enc_blocks_done = 0;
+    c->enc_noanchor = 0;
+    c->enc_total_reads = R_total;
+    c->d_anchors.reserve((R_total + 1) * sizeof(K));
+    if (c->comm.rank == 0 && !c->opts.dict_on_device) {
+        if (c->dict_thread.joinable()) c->dict_thread.join();
+        c->dict_thread_err.clear();
+        c->dict_pub.store(0);
+        c->dict_fin.store(false);
+        c->dict_abort.store(false);
+        c->dict_thread = std::thread(dict_host_worker<K>, c);
+    }
+    c->enc_open = true;
+}
+
 // Phase 3a: anchors for all reads, in ordered batches (see anchors.cuh); every time the batches pass the end of a
 // super-block it is handed to the walk / entropy stage.
 template <typename K> void do_anchors(leon_ctx *c)
@@ -1070,12 +1109,6 @@ template <typename K> void do_anchors(leon_ctx *c)
     uint32_t *aaddr = c->d_aaddr.as<uint32_t>();
     uint8_t *insflag = c->d_insflag.as<uint8_t>();
     uint32_t *counters = c->d_counters.as<uint32_t>();   // [0] collision, [1] remaining, [2], [3] range coder overflow flags
-    c->dict_cap = 1 << 16;
-    c->dict_cur = 0;
-    c->dict_count = 0;
-    dict_alloc<K>(c, 0, c->dict_cap);
-    c->tm.anchor_batches = 0;
-    c->tm.anchor_rounds = 0;
 
     // the lookups stage the bases of the 256 reads of a CTA in shared memory when they fit (40 KB)
     const uint64_t look_need = ((256ull * (uint64_t)c->max_len + 31) & ~15ull) + 16;
@@ -1083,38 +1116,25 @@ template <typename K> void do_anchors(leon_ctx *c)
     const uint64_t S = anchor_batch_reads(c);
     // number of batches: the same on every rank
     uint64_t nbatches = (R + S - 1) / S;
-    uint64_t R_total = R;
     if (N > 1) {
         c->d_xchg.reserve(256);
-        uint64_t v[2] = {nbatches, R};
+        uint64_t v[2] = {nbatches, 0};
         CUDA_TRY(cudaMemcpyAsync(c->d_xchg.p, v, 16, cudaMemcpyHostToDevice, st));
         NCCL_TRY(nccl_api().AllReduce(c->d_xchg.p, c->d_xchg.p, 1, ncclUint64, ncclMax, c->comm.comm, st));
-        NCCL_TRY(nccl_api().AllReduce(c->d_xchg.as<uint64_t>() + 1, c->d_xchg.as<uint64_t>() + 1, 1, ncclUint64, ncclSum, c->comm.comm, st));
         nbatches = fetch_scalar(c, c->d_xchg.as<uint64_t>());
-        R_total = fetch_scalar(c, c->d_xchg.as<uint64_t>() + 1);
     }
-    if (R_total >= 0xfffffff0ull) throw LeonError(LEON_E_ARG, "more than 2^32-16 reads in one read set");
-    if (c->opts.dict_on_device && (uint64_t)k * R_total >= 0xffffff00ull)
-        throw LeonError(LEON_E_OVERFLOW, "dict_on_device: the anchor dictionary stream could exceed 2^32 symbols");
-    // every read inserts at most one anchor: sized once, so that the dictionary thread can read the list while it grows
-    c->d_anchors.reserve((R_total + 1) * sizeof(K));
-    uint64_t anchors_cap = c->d_anchors.cap / sizeof(K);
+    const uint64_t anchors_cap = c->d_anchors.cap / sizeof(K);
     const bool dict_thread_on = c->comm.rank == 0 && !c->opts.dict_on_device;
-    if (dict_thread_on) {
-        if (c->dict_thread.joinable()) c->dict_thread.join();
-        c->dict_thread_err.clear();
-        c->dict_pub.store(0);
-        c->dict_fin.store(false);
-        c->dict_abort.store(false);
-        c->dict_thread = std::thread(dict_host_worker<K>, c);
-    }
+    // index in the whole read set of local read 0 of anchor batch g: the reads are dealt in rounds of N * S, S to each rank;
+    // enc_rounds_done rounds (single GPU: enc_reads_done reads) were coded by earlier leon_encode_block calls
+    const uint64_t delta0 = N > 1 ? c->enc_rounds_done * (uint64_t)N * S + (uint64_t)me * S : c->enc_reads_done;
     std::vector<uint32_t> m_all(N, 0), m_off(N, 0);
     uint64_t sb_next = 0;                                    // first super-block not handed over yet
 
     for (uint64_t g = 0; g < nbatches; g++) {
         const uint64_t lo = std::min(R, g * S), hi = std::min(R, (g + 1) * S);
         const uint64_t nb = hi - lo;
-        const uint64_t delta = g * (uint64_t)(N - 1) * S + (uint64_t)me * S;   // local read index + delta = index in the whole set
+        const uint64_t delta = delta0 + g * (uint64_t)(N - 1) * S;             // local read index + delta = index in the whole set
         c->tm.anchor_batches++;
         // A: lookup against the dictionary of earlier batches
         if (c->dict_count && nb)
@@ -1231,7 +1251,8 @@ template <typename K> void do_anchors(leon_ctx *c)
         sb_next++;
         c->sb_pub.store(sb_next, std::memory_order_release);
     }
-    if (dict_thread_on) c->dict_fin.store(true, std::memory_order_release);
+    c->enc_rounds_done += nbatches;
+    c->enc_reads_done += R;
     CUDA_TRY(cudaEventRecord(c->ev[7], st));
 }
 
@@ -1303,7 +1324,9 @@ void deflate_quals(leon_ctx *c)
     c->qz_done = true;
 }
 
-template <typename K> void do_encode_body(leon_ctx *c)
+// Quality stream, anchors, walk and entropy coding of the reads in d_bases / d_offsets (/ d_quals): all blocks of these
+// reads are coded and on the host when it returns.  encode_begin has run; count_koff has run for these reads.
+template <typename K> void encode_batch(leon_ctx *c)
 {
     using namespace lbent;
     cudaStream_t st = c->st;
@@ -1381,11 +1404,40 @@ template <typename K> void do_encode_body(leon_ctx *c)
 
     do_anchors<K>(c);
     int32_t *apos = c->d_apos.as<int32_t>();
+    uint32_t *ovf = c->d_counters.as<uint32_t>() + 2;
+    CUDA_TRY(cudaEventRecord(c->ev[8], st));
+    {
+        unsigned long long *cnt = (unsigned long long *)(c->d_counters.as<uint8_t>() + 32);
+        if (R) LB_LAUNCH(c->lc, k_count_noanchor, (unsigned)std::min<uint64_t>((R + 255) / 256, 1024), 256, 0, st, apos, R, cnt);
+        CUDA_TRY(cudaMemsetAsync(cnt, 0, 8, st));
+        if (R) LB_LAUNCH(c->lc, k_count_noanchor, (unsigned)std::min<uint64_t>((R + 255) / 256, 1024), 256, 0, st, apos, R, cnt);
+        c->enc_noanchor += fetch_scalar(c, cnt);
+        c->reads_without_anchor = c->enc_noanchor;
+    }
+    // join the walk / entropy stage: every block is coded and on the host
+    if (c->sb_thread.joinable()) c->sb_thread.join();
+    if (!c->sb_err.empty()) throw LeonError(c->sb_err_code, "walk / entropy stage: " + c->sb_err);
+    for (uint64_t g = 0; g < nsb; g++) c->nsym_total += c->sbs[g].nsym;
+    CUDA_TRY(cudaEventRecord(c->ev[9], st));
+    if (fetch_scalar(c, ovf)) throw LeonError(LEON_E_OVERFLOW, "range coder output exceeded its capacity bound");
+    if (c->qz_done) CUDA_TRY(cudaEventSynchronize(c->ev_qz));   // the run ends when the quality streams are written too
+    else if (c->opts.has_qual && R) CUDA_TRY(cudaEventSynchronize(c->ev_q[1]));
+    c->enc_blocks_done += c->nblocks;
+}
 
+// End of the encoding pass: the anchor dictionary stream (one coder over all anchors, flushed once; C/Leon.cpp:1034-1042,
+// 1245-1260).  By default the host thread started by encode_begin has been coding it all along; dict_on_device runs it
+// as one more stream of k_range_encode.
+template <typename K> void encode_end(leon_ctx *c)
+{
+    using namespace lbent;
+    cudaStream_t st = c->st;
+    const int k = c->opts.kmer_size;
+    uint32_t *ovf = c->d_counters.as<uint32_t>() + 2;
+    if (c->comm.rank == 0 && !c->opts.dict_on_device) c->dict_fin.store(true, std::memory_order_release);
     // anchor dictionary stream: one coder over all anchors, flushed once (C/Leon.cpp:1034-1042,1245-1260).  By default
     // the host thread started by do_anchors is already coding it; dict_on_device runs it as one more stream of
     // k_range_encode on the second stream next to everything below.
-    uint32_t *ovf = c->d_counters.as<uint32_t>() + 2;
     if (c->comm.rank == 0 && c->opts.dict_on_device) {
         cudaStream_t s2 = c->st2;
         uint64_t A = c->dict_count;
@@ -1410,17 +1462,6 @@ template <typename K> void do_encode_body(leon_ctx *c)
                   c->d_dict_desc.as<StreamDesc>(), c->d_dict_out.as<uint8_t>(), c->d_dict_size.as<uint64_t>(), 1, ovf + 1));
         CUDA_TRY(cudaEventRecord(c->ev[14], s2));
     }
-    CUDA_TRY(cudaEventRecord(c->ev[8], st));
-    {
-        unsigned long long *cnt = (unsigned long long *)(c->d_counters.as<uint8_t>() + 32);
-        if (R) LB_LAUNCH(c->lc, k_count_noanchor, (unsigned)std::min<uint64_t>((R + 255) / 256, 1024), 256, 0, st, apos, R, cnt);
-        c->reads_without_anchor = fetch_scalar(c, cnt);
-    }
-    // join the walk / entropy stage: every block is coded and on the host
-    if (c->sb_thread.joinable()) c->sb_thread.join();
-    if (!c->sb_err.empty()) throw LeonError(c->sb_err_code, "walk / entropy stage: " + c->sb_err);
-    for (uint64_t g = 0; g < nsb; g++) c->nsym_total += c->sbs[g].nsym;
-    CUDA_TRY(cudaEventRecord(c->ev[9], st));
     // join the dictionary coder
     if (c->comm.rank != 0) {
         c->dict_nbytes = 0;
@@ -1435,11 +1476,23 @@ template <typename K> void do_encode_body(leon_ctx *c)
         if (!c->dict_thread_err.empty()) throw LeonError(LEON_E_CUDA, "anchor dictionary coder: " + c->dict_thread_err);
         c->dict_nbytes = c->dict_host_out.size();
     }
-    if (fetch_scalar(c, ovf)) throw LeonError(LEON_E_OVERFLOW, "range coder output exceeded its capacity bound");
-    if (c->qz_done) CUDA_TRY(cudaEventSynchronize(c->ev_qz));   // the run ends when the quality streams are written too
-    else if (c->opts.has_qual && R) CUDA_TRY(cudaEventSynchronize(c->ev_q[1]));
     CUDA_TRY(cudaEventRecord(c->ev[10], st));
+    c->enc_open = false;
     c->phase = PH_ENCODED;
+}
+
+template <typename K> void do_encode_body(leon_ctx *c)
+{
+    uint64_t R_total = c->nreads;
+    if (c->comm.n > 1) {
+        c->d_xchg.reserve(256);
+        CUDA_TRY(cudaMemcpyAsync(c->d_xchg.p, &R_total, 8, cudaMemcpyHostToDevice, c->st));
+        NCCL_TRY(nccl_api().AllReduce(c->d_xchg.p, c->d_xchg.p, 1, ncclUint64, ncclSum, c->comm.comm, c->st));
+        R_total = fetch_scalar(c, c->d_xchg.as<uint64_t>());
+    }
+    encode_begin<K>(c, R_total);
+    encode_batch<K>(c);
+    encode_end<K>(c);
 }
 
 // do_encode_body with the helper threads stopped on every error path
@@ -1456,17 +1509,19 @@ template <typename K> void do_encode(leon_ctx *c)
     }
 }
 
-void do_fetch(leon_ctx *c, leon_result *out)
+void do_fetch(leon_ctx *c, leon_result *out, bool want_global = true)
 {
     cudaStream_t st = c->st;
     const uint64_t R = c->nreads;
     CUDA_TRY(cudaEventRecord(c->ev[11], st));
-    c->h_bloom.reserve(c->bloom.nbytes + 8);
-    CUDA_TRY(cudaMemcpyAsync(c->h_bloom.p, c->bloom.words, c->bloom.nbytes, cudaMemcpyDeviceToHost, st));
-    c->h_dict.reserve(c->dict_nbytes + 8);
-    if (c->comm.rank != 0) { }
-    else if (c->opts.dict_on_device) CUDA_TRY(cudaMemcpyAsync(c->h_dict.p, c->d_dict_out.p, c->dict_nbytes, cudaMemcpyDeviceToHost, st));
-    else memcpy(c->h_dict.p, c->dict_host_out.data(), c->dict_nbytes);
+    if (want_global) {
+        c->h_bloom.reserve(c->bloom.nbytes + 8);
+        CUDA_TRY(cudaMemcpyAsync(c->h_bloom.p, c->bloom.words, c->bloom.nbytes, cudaMemcpyDeviceToHost, st));
+        c->h_dict.reserve(c->dict_nbytes + 8);
+        if (c->comm.rank != 0) { }
+        else if (c->opts.dict_on_device) CUDA_TRY(cudaMemcpyAsync(c->h_dict.p, c->d_dict_out.p, c->dict_nbytes, cudaMemcpyDeviceToHost, st));
+        else memcpy(c->h_dict.p, c->dict_host_out.data(), c->dict_nbytes);
+    }
     // dna / blocksizes were copied to the host by the walk / entropy stage as the blocks finished
     c->h_apos.reserve((R + 1) * 4);
     c->h_aaddr.reserve((R + 1) * 4);
@@ -1496,8 +1551,10 @@ void do_fetch(leon_ctx *c, leon_result *out)
     CUDA_TRY(cudaStreamSynchronize(st));
     memset(out, 0, sizeof *out);
     out->count = c->cres;
-    out->bloom = c->h_bloom.as<uint8_t>(); out->bloom_nbytes = c->bloom.nbytes; out->bloom_bits = c->bloom.reduced_tai;
-    out->anchors_dict = c->h_dict.as<uint8_t>(); out->anchors_dict_nbytes = c->dict_nbytes; out->anchor_count = c->dict_count;
+    if (want_global) {
+        out->bloom = c->h_bloom.as<uint8_t>(); out->bloom_nbytes = c->bloom.nbytes; out->bloom_bits = c->bloom.reduced_tai;
+        out->anchors_dict = c->h_dict.as<uint8_t>(); out->anchors_dict_nbytes = c->dict_nbytes; out->anchor_count = c->dict_count;
+    }
     out->nblocks = c->nblocks; out->blocksizes = c->h_bs.as<uint64_t>();
     out->dna = c->h_dna.as<uint8_t>(); out->dna_nbytes = c->dna_nbytes;
     out->qual_text = qbytes ? c->h_qual.as<uint8_t>() : nullptr; out->qual_nbytes = qbytes; out->qual_block_sizes = c->h_qsizes.as<uint64_t>();
@@ -1691,11 +1748,11 @@ int leon_upload(leon_ctx *c, const leon_reads *reads)
     LB_API_END(c)
 }
 
-int leon_count(leon_ctx *c, leon_count_result *out)
+int leon_count_resident(leon_ctx *c, leon_count_result *out)
 {
     if (!c) return LEON_E_ARG;
     LB_API_BEGIN
-    if (c->phase < PH_UPLOADED) throw LeonError(LEON_E_STATE, "leon_count: no read set uploaded");
+    if (c->phase < PH_UPLOADED) throw LeonError(LEON_E_STATE, "leon_count_resident: no read set uploaded");
     CUDA_TRY(cudaSetDevice(c->opts.device));
     user_stream_in(c);
     LB_DISPATCH(c, do_count);
@@ -1723,6 +1780,233 @@ int leon_bloom_build(leon_ctx *c, const uint8_t **bits, uint64_t *nbytes, uint64
     user_stream_out(c);
     LB_API_END(c)
 }
+
+
+}  // extern "C"
+
+// One batch of the streaming path into the (reused) read buffers; the caller's buffers are free again on return.
+static void stream_upload(leon_ctx *c, const leon_reads *rd, bool with_quals, bool first_of_set)
+{
+    if (!rd || !rd->offsets || (rd->nreads && !rd->bases)) throw LeonError(LEON_E_ARG, "null read batch");
+    if (rd->offsets[0] != 0) throw LeonError(LEON_E_ARG, "a batch's offsets must start at 0");
+    if (with_quals && !rd->quals) throw LeonError(LEON_E_ARG, "has_qual set but the batch has no qualities");
+    c->nreads = rd->nreads;
+    c->nbases = rd->offsets[rd->nreads];
+    c->d_bases.reserve(c->nbases + 128);
+    c->d_offsets.reserve((c->nreads + 1) * 8);
+    CUDA_TRY(cudaMemcpyAsync(c->d_bases.p, rd->bases, c->nbases, cudaMemcpyHostToDevice, c->st));
+    CUDA_TRY(cudaMemcpyAsync(c->d_offsets.p, rd->offsets, (c->nreads + 1) * 8, cudaMemcpyHostToDevice, c->st));
+    if (with_quals) {
+        c->d_quals.reserve(c->nbases + 128);
+        CUDA_TRY(cudaMemcpyAsync(c->d_quals.p, rd->quals, c->nbases, cudaMemcpyHostToDevice, c->st));
+    }
+    int32_t mn = first_of_set ? 0x7fffffff : c->min_len, mx = first_of_set ? 0 : c->max_len;    // running over the set
+    for (uint64_t i = 0; i < rd->nreads; i++) {
+        uint64_t L = rd->offsets[i + 1] - rd->offsets[i];
+        if (L >= 0x7fffffffull) throw LeonError(LEON_E_ARG, "read longer than 2^31-1");
+        if ((int32_t)L < mn) mn = (int32_t)L;
+        if ((int32_t)L > mx) mx = (int32_t)L;
+    }
+    c->min_len = mn; c->max_len = mx;
+    c->qsizes.clear();
+    if (with_quals) {
+        uint64_t rpb = (uint64_t)c->opts.reads_per_block;
+        for (uint64_t r0 = 0; r0 < rd->nreads; r0 += rpb) {
+            uint64_t r1 = std::min(rd->nreads, r0 + rpb);
+            c->qsizes.push_back(rd->offsets[r1] - rd->offsets[r0] + (r1 - r0));
+        }
+    }
+    CUDA_TRY(cudaStreamSynchronize(c->st));
+}
+
+template <typename K> static void stream_count_begin(leon_ctx *c, const leon_stream_plan *plan, uint32_t *npasses_out)
+{
+    const uint64_t kb = sizeof(K);
+    uint32_t np = plan->count_passes;
+    // upper bound on the k-mer slots this rank extracts: one per base
+    const uint64_t nk_bound = plan->total_bases + 1;
+    if (np == 0) {
+        size_t free_b = 0, total_b = 0;
+        CUDA_TRY(cudaMemGetInfo(&free_b, &total_b));
+        // key buffer + its ping-pong twin (+ the receive buffer of the exchange with several ranks) within 60 % of what is free
+        const double per_key = (double)kb * (c->comm.n > 1 ? 3.2 : 2.1);
+        const double budget = 0.6 * (double)free_b;
+        np = (uint32_t)std::max(1.0, std::ceil((double)nk_bound * per_key / budget));
+    }
+    uint64_t cap = nk_bound;
+    if (np > 1) cap = (uint64_t)((double)nk_bound / np * 1.06) + (1u << 20);     // hash split: a few per cent of imbalance at most
+    count_begin<K>(c, np, cap);
+    CUDA_TRY(cudaEventRecord(c->ev[2], c->st));
+    c->stream_reads_seen = 0;
+    c->stream_counting = true;
+    if (npasses_out) *npasses_out = np;
+}
+
+template <typename K> static void stream_count_batch(leon_ctx *c, const leon_reads *batch, int last)
+{
+    if (!c->stream_counting) throw LeonError(LEON_E_STATE, "leon_count: leon_count_begin has not run");
+    if (c->count_pass >= c->count_npasses) throw LeonError(LEON_E_STATE, "leon_count: all counting passes are closed");
+    stream_upload(c, batch, false, c->count_pass == 0 && c->stream_reads_seen == 0);
+    c->stream_reads_seen += batch->nreads;
+    count_koff(c);
+    count_add<K>(c);
+    if (last) {
+        count_close<K>(c);
+        c->stream_reads_seen = 0;
+    }
+}
+
+template <typename K> static void stream_encode_block(leon_ctx *c, uint64_t first_block, const leon_reads *batch, leon_block_out *out)
+{
+    if (c->phase < PH_BLOOM) throw LeonError(LEON_E_STATE, "leon_encode_block: leon_bloom_build has not run");
+    if (!c->enc_open) {
+        uint64_t R_total = c->count_reads_total;
+        if (c->comm.n > 1) {
+            c->d_xchg.reserve(256);
+            CUDA_TRY(cudaMemcpyAsync(c->d_xchg.p, &R_total, 8, cudaMemcpyHostToDevice, c->st));
+            NCCL_TRY(nccl_api().AllReduce(c->d_xchg.p, c->d_xchg.p, 1, ncclUint64, ncclSum, c->comm.comm, c->st));
+            R_total = fetch_scalar(c, c->d_xchg.as<uint64_t>());
+        }
+        encode_begin<K>(c, R_total);
+        c->enc_total_bases = 0;
+        c->enc_partial_seen = false;
+    }
+    if (first_block != c->enc_blocks_done) throw LeonError(LEON_E_ARG, "leon_encode_block: blocks must be submitted in order (first_block = blocks coded so far)");
+    if (c->enc_partial_seen && batch->nreads) throw LeonError(LEON_E_ARG, "leon_encode_block: only the last batch may hold a partial block");
+    if (batch->nreads % (uint64_t)c->opts.reads_per_block) c->enc_partial_seen = true;
+    if (c->comm.n > 1 && batch->nreads % anchor_batch_reads(c)) c->enc_partial_seen = true;
+    const int32_t mn = c->min_len, mx = c->max_len;
+    stream_upload(c, batch, c->opts.has_qual != 0, false);
+    c->min_len = std::min(mn, c->min_len); c->max_len = std::max(mx, c->max_len);     // of the whole set (counting pass)
+    count_koff(c);
+    encode_batch<K>(c);
+    c->enc_total_bases += c->nbases;
+    leon_result r;
+    do_fetch(c, &r, false);
+    memset(out, 0, sizeof *out);
+    out->first_block = first_block; out->nblocks = r.nblocks; out->read_count = r.read_count;
+    out->blocksizes = r.blocksizes; out->dna = r.dna; out->dna_nbytes = r.dna_nbytes;
+    out->qual_text = r.qual_text; out->qual_nbytes = r.qual_nbytes; out->qual_block_sizes = r.qual_block_sizes;
+    out->qual_z = r.qual_z; out->qual_z_nbytes = r.qual_z_nbytes; out->qual_z_block_sizes = r.qual_z_block_sizes;
+    out->anchor_pos = r.anchor_pos; out->anchor_addr = r.anchor_addr;
+    c->last_block_out = *out;
+}
+
+template <typename K> static void stream_encode_finish(leon_ctx *c, leon_result *out)
+{
+    if (!c->enc_open) {      // no batch at all: an empty set
+        encode_begin<K>(c, 0);
+        c->enc_total_bases = 0;
+        CUDA_TRY(cudaMemsetAsync(c->d_counters.p, 0, 64, c->st));
+    }
+    encode_end<K>(c);
+    // whole-set fields only
+    const uint64_t nreads = c->nreads, nbases = c->nbases, nblocks = c->nblocks;
+    c->nreads = 0; c->nblocks = 0;
+    do_fetch(c, out, true);
+    c->nreads = nreads; c->nbases = nbases; c->nblocks = nblocks;
+    out->nblocks = c->enc_blocks_done;
+    out->blocksizes = nullptr; out->dna = nullptr; out->dna_nbytes = 0;
+    out->qual_text = nullptr; out->qual_nbytes = 0; out->qual_z = nullptr; out->qual_z_nbytes = 0;
+    out->qual_block_sizes = nullptr; out->qual_z_block_sizes = nullptr;
+    out->anchor_pos = nullptr; out->anchor_addr = nullptr;
+    out->read_count = c->enc_reads_done; out->total_dna_size = c->enc_total_bases;
+    out->reads_without_anchor = c->enc_noanchor;
+    out->min_read_size = c->min_len; out->max_read_size = c->max_len;
+}
+
+extern "C" {
+
+int leon_count_begin(leon_ctx *c, const leon_stream_plan *plan, uint32_t *npasses)
+{
+    if (!c || !plan) return LEON_E_ARG;
+    LB_API_BEGIN
+    CUDA_TRY(cudaSetDevice(c->opts.device));
+    user_stream_in(c);
+    if (c->opts.kmer_size <= 31) stream_count_begin<uint64_t>(c, plan, npasses); else stream_count_begin<u128>(c, plan, npasses);
+    user_stream_out(c);
+    LB_API_END(c)
+}
+
+int leon_count(leon_ctx *c, const leon_reads *batch, int last)
+{
+    if (!c || !batch) return LEON_E_ARG;
+    LB_API_BEGIN
+    CUDA_TRY(cudaSetDevice(c->opts.device));
+    user_stream_in(c);
+    if (c->opts.kmer_size <= 31) stream_count_batch<uint64_t>(c, batch, last); else stream_count_batch<u128>(c, batch, last);
+    user_stream_out(c);
+    LB_API_END(c)
+}
+
+int leon_count_finish(leon_ctx *c, leon_count_result *out)
+{
+    if (!c) return LEON_E_ARG;
+    LB_API_BEGIN
+    CUDA_TRY(cudaSetDevice(c->opts.device));
+    if (!c->stream_counting) throw LeonError(LEON_E_STATE, "leon_count_finish: leon_count_begin has not run");
+    if (c->count_pass < c->count_npasses) throw LeonError(LEON_E_STATE, "leon_count_finish: not every counting pass has been closed (last = 1)");
+    user_stream_in(c);
+    count_finish(c);
+    c->stream_counting = false;
+    if (out) *out = c->cres;
+    user_stream_out(c);
+    LB_API_END(c)
+}
+
+int leon_encode_block(leon_ctx *c, uint64_t first_block, const leon_reads *batch, leon_block_out *out)
+{
+    if (!c || !batch || !out) return LEON_E_ARG;
+    LB_API_BEGIN
+    CUDA_TRY(cudaSetDevice(c->opts.device));
+    user_stream_in(c);
+    try {
+        if (c->opts.kmer_size <= 31) stream_encode_block<uint64_t>(c, first_block, batch, out); else stream_encode_block<u128>(c, first_block, batch, out);
+    } catch (...) {
+        c->dict_abort.store(true);
+        c->sb_abort.store(true);
+        if (c->dict_thread.joinable()) c->dict_thread.join();
+        if (c->sb_thread.joinable()) c->sb_thread.join();
+        c->enc_open = false;
+        throw;
+    }
+    fill_timings(c);
+    user_stream_out(c);
+    LB_API_END(c)
+}
+
+int leon_block_wait(leon_ctx *c, uint64_t first_block, leon_block_out *out)
+{
+    if (!c || !out) return LEON_E_ARG;
+    if (c->last_block_out.first_block != first_block || !c->last_block_out.blocksizes) { c->err = "leon_block_wait: not the last submitted block"; return LEON_E_ARG; }
+    *out = c->last_block_out;
+    return LEON_OK;
+}
+
+int leon_encode_finish(leon_ctx *c, leon_result *out)
+{
+    if (!c || !out) return LEON_E_ARG;
+    LB_API_BEGIN
+    CUDA_TRY(cudaSetDevice(c->opts.device));
+    if (c->phase < PH_BLOOM) throw LeonError(LEON_E_STATE, "leon_encode_finish: leon_bloom_build has not run");
+    user_stream_in(c);
+    try {
+        if (c->opts.kmer_size <= 31) stream_encode_finish<uint64_t>(c, out); else stream_encode_finish<u128>(c, out);
+    } catch (...) {
+        c->dict_abort.store(true);
+        if (c->dict_thread.joinable()) c->dict_thread.join();
+        c->enc_open = false;
+        throw;
+    }
+    memset(&c->last_block_out, 0, sizeof c->last_block_out);
+    fill_timings(c);
+    user_stream_out(c);
+    LB_API_END(c)
+}
+
+}  // extern "C"
+
+extern "C" {
 
 int leon_fetch(leon_ctx *c, leon_result *out)
 {

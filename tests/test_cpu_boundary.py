@@ -25,7 +25,7 @@ def test_abi_exports_every_declared_symbol():
     for sym in sorted(declared):
         assert hasattr(L, sym), "libleon_b200.so does not export %s" % sym
     assert set(leon_b200.ABI_SYMBOLS) == declared
-    assert L.leon_b200_abi_version() == 2
+    assert L.leon_b200_abi_version() == 3
 
 
 def test_no_cpu_fallback():

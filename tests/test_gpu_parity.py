@@ -281,3 +281,59 @@ def test_create_destroy_does_not_leak():
         torch.cuda.synchronize()
         free.append(torch.cuda.mem_get_info()[0])
     assert free[-1] >= free[1] - (8 << 20), free      # after the first cycle (context warm-up) nothing is held back
+
+
+@pytest.mark.parametrize("k,fastq,lossless,passes,batch_blocks,seed", [(31, True, False, 1, 3, 41), (31, False, False, 3, 2, 42),
+                                                                      (63, True, True, 2, 5, 43), (31, True, False, 4, 1, 44)])
+def test_streaming_equals_one_shot(k, fastq, lossless, passes, batch_blocks, seed):
+    """Streaming entry points (leon_count_begin / leon_count / leon_count_finish / leon_encode_block / leon_encode_finish):
+    the set fed in batches of a few blocks, counted in 1-4 hash-partitioned passes, gives the bytes of the oracle (and so of
+    the one-shot path), whatever the batching; configs[4] shape (k = 63, lossless) included."""
+    from oracle import oracle_py as O
+    from leon_b200 import workloads as W
+    rpb = 3000
+    bases, offs, quals = W.generate_c3(80_000, 26_500, gseed=seed, rseed=seed + 1, with_quals=fastq)
+    ref = O.compress(bases, offs, quals, kmer_size=k, reads_per_block=rpb, lossless=lossless)
+    eng = _engine(kmer_size=k, reads_per_block=rpb, has_qual=fastq, lossless=lossless)
+    r = eng.compress_stream(bases, offs, quals, batch_reads=batch_blocks * rpb, count_passes=passes)
+    assert r["count_passes"] == passes
+    _same(r, ref, fastq)
+    # a second set on the same context, other batching, passes chosen by the library (1 at this size)
+    r2 = eng.compress_stream(bases, offs, quals, batch_reads=4 * rpb, count_passes=0)
+    eng.close()
+    assert r2["count_passes"] == 1
+    _same(r2, ref, fastq)
+
+
+def test_streaming_device_memory_is_independent_of_the_number_of_reads():
+    """The device footprint of the streaming path is set by the batch size, not by the number of reads: 4x the reads in the
+    same batches must not need more device memory (beyond the solid k-mer list and the dictionary, which follow the genome)."""
+    import torch
+    from leon_b200 import workloads as W
+    rpb = 5000
+    used = []
+    for nreads in (60_000, 240_000):
+        bases, offs, quals = W.generate_c3(200_000, nreads, with_quals=True)
+        torch.cuda.synchronize()
+        free0 = torch.cuda.mem_get_info()[0]
+        eng = _engine(kmer_size=31, reads_per_block=rpb, has_qual=True, qual_zlib_on_device=True, skip_qual_text=True, skip_read_arrays=True)
+        r = eng.compress_stream(bases, offs, quals, batch_reads=4 * rpb, count_passes=4 if nreads > 100_000 else 1)
+        torch.cuda.synchronize()
+        used.append(free0 - torch.cuda.mem_get_info()[0])
+        assert r["read_count"] == nreads and int(r["blocksizes"][1::2].sum()) == nreads
+        eng.close()
+    assert used[1] < used[0] * 1.5 + (64 << 20), used
+
+
+def test_pipelined_stage_many_superblocks(monkeypatch):
+    """More super-blocks than SB_PIPELINE_MIN: the walk / entropy stage of a super-block runs beside the later anchor
+    batches (the path large read sets take), byte for byte against the oracle."""
+    from oracle import oracle_py as O
+    from leon_b200 import synth
+    g = synth.make_genome(40000, 77)
+    bases, offs, quals = synth.sample_reads(g, 30000, 100, 78, n_rate=0.0005, with_quals=True)
+    ref = O.compress(bases, offs, quals, kmer_size=31, reads_per_block=500)
+    eng = _engine(kmer_size=31, reads_per_block=500, has_qual=True, anchor_batch=1000)     # 30 super-blocks of 2 blocks
+    r = eng.compress(bases, offs, quals)
+    eng.close()
+    _same(r, ref, True)
