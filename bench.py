@@ -50,6 +50,9 @@ def parse_args():
     ap.add_argument("--host-zlib", action="store_true", help="return the quality text instead of zlib streams written by the GPU")
     ap.add_argument("--anchor-batch", type=int, default=0, help="reads per anchor-resolution batch (0 = library default)")
     ap.add_argument("--phases", action="store_true", help="print per-phase / per-kernel device times to stderr")
+    ap.add_argument("--no-large", action="store_true", help="skip the configs[3] streaming measurement (extra key `large`)")
+    ap.add_argument("--large-reads", type=int, default=0, help="debug: reads of the configs[3]-shaped set (genome scaled with it)")
+    ap.add_argument("--only-large", action="store_true", help="debug: only the configs[3] measurement")
     return ap.parse_args()
 
 
@@ -411,6 +414,167 @@ def measure(args, name, torch, dist, world, rank, local_rank, want_e2e=True):
     return out
 
 
+def measure_large(args, torch, dist, world, rank, local_rank):
+    """BASELINE configs[3] (100 Mbp genome, 33.3 M x 150 bp FASTQ with N runs and indels, Bloom filter 150 MB > L2) through the
+    STREAMING entry points from pinned host memory on `world` ranks: every rank is dealt the chunks (250 000 reads) c with
+    c % world == rank, feeds them in batches, and hashes its own blocks; rank 0 combines the per-block digests."""
+    import concurrent.futures as cf
+    import hashlib
+    import zlib
+    import leon_b200
+    from leon_b200 import synth
+    name = "configs[3]"
+    c = W.CONFIGS[name]
+    total_reads = args.large_reads if args.large_reads else c["reads"]
+    genome_len = c["genome"] if not args.large_reads else max(1_000_000, int(c["genome"] * total_reads / c["reads"]))
+    S = W.C3_CHUNK
+    nchunks = (total_reads + S - 1) // S
+    mine = [ch for ch in range(nchunks) if ch % world == rank]
+    t0 = time.perf_counter()
+    g = synth.make_genome(genome_len, c["gseed"])
+    threads = max(1, min(16, (os.cpu_count() or 1) // world))
+    with cf.ThreadPoolExecutor(threads) as ex:
+        parts = list(ex.map(lambda ch: W.c3_chunk(g, ch, total_reads, c["read_len"], c["rseed"], True), mine))
+    lens = np.concatenate([p[1] for p in parts]) if parts else np.zeros(0, np.int64)
+    nb = int(lens.sum())
+    pin_b, pin_q = leon_b200.api.PinnedArray(max(1, nb)), leon_b200.api.PinnedArray(max(1, nb))
+    pin_o = leon_b200.api.PinnedArray((len(lens) + 1) * 8, np.uint64)
+    at = 0
+    for p in parts:
+        pin_b.array[at:at + len(p[0])] = p[0]
+        pin_q.array[at:at + len(p[0])] = p[2]
+        at += len(p[0])
+    pin_o.array[0] = 0
+    np.cumsum(lens, out=pin_o.array[1:])
+    del parts, g
+    bases, quals, offs = pin_b.array[:nb], pin_q.array[:nb], pin_o.array
+    gen_s = time.perf_counter() - t0
+    local_reads = len(lens)
+    # batches of M chunks per rank; every rank makes the same number of calls (empty batches at the end where it has run out)
+    M = 8
+    max_chunks = (nchunks + world - 1) // world
+    ncalls = max(1, (max_chunks + M - 1) // M)
+    batches = [(min(local_reads, i * M * S), min(local_reads, (i + 1) * M * S)) for i in range(ncalls)]
+
+    eng = leon_b200.Leon(kmer_size=KMER, reads_per_block=RPB, has_qual=True, device=local_rank, anchor_batch=S,
+                         qual_zlib_on_device=True, skip_qual_text=True, skip_read_arrays=True)
+    stream = torch.cuda.current_stream()
+    eng.set_stream(stream.cuda_stream)
+    if world > 1:
+        uid = [leon_b200.Leon.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        eng.comm_init(rank, world, uid[0])
+
+    def cut(lo, hi, with_q):
+        b0, b1 = int(offs[lo]), int(offs[hi])
+        return bases[b0:b1], offs[lo:hi + 1] - offs[lo], (quals[b0:b1] if with_q else None)
+
+    def one_run(keep):
+        phases = {}
+        t = time.perf_counter()
+        npass = eng.count_begin(local_reads, nb, 0)
+        for _ in range(npass):
+            for i, (lo, hi) in enumerate(batches):
+                b, o, _q = cut(lo, hi, False)
+                eng.count_batch(b, o, i == len(batches) - 1)
+        cnt = eng.count_finish()
+        phases["count_s"] = time.perf_counter() - t
+        t = time.perf_counter()
+        eng.bloom_build()
+        phases["bloom_s"] = time.perf_counter() - t
+        t = time.perf_counter()
+        first = 0
+        outs = []
+        for lo, hi in batches:
+            b, o, q = cut(lo, hi, True)
+            bo = eng.encode_block(first, b, o, q, copy=keep)
+            first += bo["nblocks"]
+            if keep:
+                outs.append(bo)
+        res = eng.encode_finish(copy=keep)
+        phases["encode_s"] = time.perf_counter() - t
+        return npass, cnt, outs, res, phases
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    one_run(False)                       # warm-up (allocations)
+    steps = max(1, min(args.steps, 2))
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    w0 = time.perf_counter()
+    for i in range(steps):
+        npass, cnt, outs, res, phases = one_run(i == steps - 1)
+    e1.record(stream)
+    barrier()
+    ms = max(e0.elapsed_time(e1), (time.perf_counter() - w0) * 1000.0) / steps
+    if world > 1:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    # ---- digest: per-block checksums on every rank, combined in file order on rank 0
+    def block_hashes(bo):
+        out = []
+        da, za = 0, 0
+        for j in range(bo["nblocks"]):
+            dn, zn = int(bo["blocksizes"][2 * j]), int(bo["qual_z_block_sizes"][j])
+            out.append((hashlib.sha256(bo["dna"][da:da + dn]).digest(), hashlib.sha256(zlib.decompress(bo["qual_z"][za:za + zn])).digest(),
+                        int(bo["blocksizes"][2 * j]), int(bo["blocksizes"][2 * j + 1])))
+            da += dn
+            za += zn
+        return out
+    with cf.ThreadPoolExecutor(threads) as ex:
+        per = [h for lst in ex.map(block_hashes, outs) for h in lst]
+    # local block j of chunk-round i on this rank is global block (i * world + rank) * (S / RPB) + j
+    bpc = S // RPB
+    gids = []
+    for i, ch in enumerate(mine):
+        n_in = min(S, total_reads - ch * S)
+        gids += [ch * bpc + j for j in range((n_in + RPB - 1) // RPB)]
+    assert len(gids) == len(per), (len(gids), len(per))
+    mine_out = dict(gids=gids, per=per, bloom=hashlib.sha256(res["bloom"]).hexdigest() if rank == 0 else None,
+                    dict=hashlib.sha256(res["anchors_dict"]).hexdigest() if rank == 0 else None, anchors=res["anchor_count"])
+    allo = [mine_out]
+    if world > 1:
+        allo = [None] * world if rank == 0 else None
+        dist.gather_object(mine_out, allo, dst=0)
+    eng.close()
+    pin_b.free(); pin_q.free(); pin_o.free()
+    if rank != 0:
+        return None
+    table = {}
+    for o in allo:
+        for gid, h in zip(o["gids"], o["per"]):
+            table[gid] = h
+    order = sorted(table)
+    bs = np.array([[table[b][2], table[b][3]] for b in order], np.uint64).reshape(-1)
+    digest = {"bloom": allo[0]["bloom"], "anchors_dict": allo[0]["dict"], "blocksizes": W._sha(bs), "nblocks": len(order),
+              "dna_nbytes": int(bs[0::2].sum()),
+              "dna_cc": hashlib.sha256(b"".join(table[b][0] for b in order)).hexdigest(),
+              "qual_text_cc": hashlib.sha256(b"".join(table[b][1] for b in order)).hexdigest()}
+    gold = golden_digest(name) if total_reads == c["reads"] else None
+    ok, diff = None, None
+    if gold is not None and "dna_cc" in gold:
+        keys = ["bloom", "anchors_dict", "blocksizes", "dna_cc", "qual_text_cc"]
+        diff = [k for k in keys if digest.get(k) != gold.get(k)]
+        ok = not diff
+    value = total_reads / (ms / 1000.0)
+    return {"workload": c["text"] if total_reads == c["reads"] else "DEBUG SIZE: %d reads of configs[3]" % total_reads,
+            "api": "streaming entry points (leon_count_begin / leon_count / leon_count_finish / leon_bloom_build / leon_encode_block / "
+                   "leon_encode_finish), host buffers in, host buffers out: this is an end-to-end figure",
+            "value": value, "unit": "reads/s", "ms_per_step": ms, "steps": steps, "n_gpus": world, "count_passes": npass,
+            "batches_per_rank": ncalls, "reads_per_batch_per_rank": M * S,
+            "input_gbs": value * c["read_len"] * 2 / 1e9, "phases_s_rank0": phases, "anchors": allo[0]["anchors"],
+            "cutoff": cnt["cutoff"], "solid": cnt["nb_solids_cutoff"], "bloom_bytes": int(len(res["bloom"])),
+            "output_digest": digest, "digest_ok": ok, "digest_mismatch": diff,
+            "digest_reference": "tests/golden/digest_configs3.json: oracle/_ref/leon -nb-cores 1 on the same seeded read set "
+                                "(dna_cc / qual_text_cc = checksum of the per-block checksums)",
+            "generation_s": gen_s}
+
+
 def main_b200(args):
     import torch
     import torch.distributed as dist
@@ -428,6 +592,11 @@ def main_b200(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     name = args.workload
+    if args.only_large:
+        lg = measure_large(args, torch, dist, world, rank, local_rank)
+        if rank == 0:
+            print(json.dumps({"large": lg}))
+        return 0
     m = measure(args, name, torch, dist, world, rank, local_rank)
     extra = None
     if not args.no_extra and name != "configs[1]" and not args.reads:
@@ -497,6 +666,9 @@ def main_b200(args):
         print("anchors %d, dna bytes %d, symbols %d, solid %d, cutoff %d" % (
             m["anchors"], m["dna_bytes"], int(stats["nsym"]), m["solid"], m["cutoff"]), file=sys.stderr)
 
+    large = None
+    if not args.no_large and not args.reads:
+        large = measure_large(args, torch, dist, world, rank, local_rank)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_baseline_block(name, args.reads)
@@ -528,6 +700,8 @@ def main_b200(args):
         line["configs1"] = {"workload": W.CONFIGS["configs[1]"]["text"], "value": extra["value"], "unit": "reads/s",
                             "ms_per_step": extra["ms_per_step"], "digest_ok": extra["digest_ok"], "digest_mismatch": extra["digest_diff"],
                             "phases_ms_per_step": {k: v / args.steps for k, v in extra["phase"].items()}}
+    if large is not None:
+        line["large"] = large
     print(json.dumps(line))
     return 0
 

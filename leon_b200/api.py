@@ -542,55 +542,78 @@ class Leon:
         self._check(self.L.leon_encode(self.ctx, C.byref(r)))
         return self._result(r)
 
-    # streaming path: batches of reads, counted in `count_passes` passes, then encoded batch by batch
+    # streaming path (include/leon_b200.h "Streaming path"): batches of reads, counted in passes, then encoded in file order
+    def count_begin(self, total_reads, total_bases, count_passes=0):
+        plan = StreamPlan(int(total_reads), int(total_bases), int(count_passes))
+        npass = C.c_uint32()
+        self._check(self.L.leon_count_begin(self.ctx, C.byref(plan), C.byref(npass)))
+        return int(npass.value)
+
+    def count_batch(self, bases, offsets, last):
+        rd = self._reads(bases, offsets, None)
+        self._check(self.L.leon_count(self.ctx, C.byref(rd), int(bool(last))))
+
+    def count_finish(self):
+        r = CountResult()
+        self._check(self.L.leon_count_finish(self.ctx, C.byref(r)))
+        return dict(cutoff=int(r.cutoff), nb_solids_cutoff=int(r.nb_solids_cutoff), nb_solid_total=int(r.nb_solid_total),
+                    nb_distinct=int(r.nb_distinct), nb_kmers=int(r.nb_kmers), histogram=_arr(r.histogram, 10001, np.uint64))
+
+    def encode_block(self, first_block, bases, offsets, quals=None, copy=True):
+        """Codes the blocks of one batch; returns their outputs (views into the context's buffers when copy=False: valid until
+        the next call)."""
+        rd = self._reads(bases, offsets, quals)
+        bo = BlockOut()
+        self._check(self.L.leon_encode_block(self.ctx, int(first_block), C.byref(rd), C.byref(bo)))
+        nb = int(bo.nblocks)
+        hq = bo.qual_nbytes > 0 or bo.qual_z_nbytes > 0
+        return dict(first_block=int(bo.first_block), nblocks=nb, read_count=int(bo.read_count),
+                    dna=_arr(bo.dna, bo.dna_nbytes, np.uint8, copy), blocksizes=_arr(bo.blocksizes, 2 * nb, np.uint64, copy),
+                    qual_text=_arr(bo.qual_text, bo.qual_nbytes, np.uint8, copy),
+                    qual_block_sizes=_arr(bo.qual_block_sizes, nb if hq else 0, np.uint64, copy),
+                    qual_z=_arr(bo.qual_z, bo.qual_z_nbytes, np.uint8, copy),
+                    qual_z_block_sizes=_arr(bo.qual_z_block_sizes, nb if bo.qual_z_nbytes else 0, np.uint64, copy),
+                    anchor_pos=_arr(bo.anchor_pos, bo.read_count if bo.anchor_pos else 0, np.int32, copy),
+                    anchor_addr=_arr(bo.anchor_addr, bo.read_count if bo.anchor_addr else 0, np.uint32, copy))
+
+    def encode_finish(self, copy=True):
+        r = Result()
+        self._check(self.L.leon_encode_finish(self.ctx, C.byref(r)))
+        return self._result(r, copy)
+
     def compress_stream(self, bases, offsets, quals=None, batch_reads=None, count_passes=0, batches=None):
-        """The whole set through leon_count_begin / leon_count / leon_count_finish / leon_bloom_build / leon_encode_block /
-        leon_encode_finish, `batch_reads` reads at a time (or the explicit list of (lo, hi) read ranges `batches`); returns the
-        result dict of compress() assembled from the per-batch outputs, plus `count_passes`."""
+        """The whole set through the streaming entry points, `batch_reads` reads at a time (or the explicit list of (lo, hi) read
+        ranges `batches`); returns the result dict of compress() assembled from the per-batch outputs, plus `count_passes`."""
         offsets = np.ascontiguousarray(offsets, np.uint64)
         n = len(offsets) - 1
         if batches is None:
             batches = [(lo, min(n, lo + batch_reads)) for lo in range(0, n, batch_reads)] or [(0, 0)]
 
-        def batch(lo, hi):
-            o = offsets[lo:hi + 1] - offsets[lo]
+        def cut(lo, hi):
             b0, b1 = int(offsets[lo]), int(offsets[hi])
-            return self._reads(bases[b0:b1], o, quals[b0:b1] if quals is not None else None)
+            return bases[b0:b1], offsets[lo:hi + 1] - offsets[lo], (quals[b0:b1] if quals is not None else None)
 
-        plan = StreamPlan(n, int(offsets[-1]), int(count_passes))
-        npass = C.c_uint32()
-        self._check(self.L.leon_count_begin(self.ctx, C.byref(plan), C.byref(npass)))
-        for _ in range(npass.value):
+        npass = self.count_begin(n, int(offsets[-1]), count_passes)
+        for _ in range(npass):
             for i, (lo, hi) in enumerate(batches):
-                rd = batch(lo, hi)
-                self._check(self.L.leon_count(self.ctx, C.byref(rd), int(i == len(batches) - 1)))
-        cr = CountResult()
-        self._check(self.L.leon_count_finish(self.ctx, C.byref(cr)))
+                b, o, _q = cut(lo, hi)
+                self.count_batch(b, o, i == len(batches) - 1)
+        self.count_finish()
         self.bloom_build()
-        parts = dict(dna=[], blocksizes=[], qual_text=[], qual_block_sizes=[], qual_z=[], qual_z_block_sizes=[], anchor_pos=[], anchor_addr=[])
+        keys = ("dna", "blocksizes", "qual_text", "qual_block_sizes", "qual_z", "qual_z_block_sizes", "anchor_pos", "anchor_addr")
+        parts = {k: [] for k in keys}
         first = 0
         for lo, hi in batches:
-            rd = batch(lo, hi)
-            bo = BlockOut()
-            self._check(self.L.leon_encode_block(self.ctx, first, C.byref(rd), C.byref(bo)))
-            nb = int(bo.nblocks)
-            parts["dna"].append(_arr(bo.dna, bo.dna_nbytes, np.uint8))
-            parts["blocksizes"].append(_arr(bo.blocksizes, 2 * nb, np.uint64))
-            parts["qual_text"].append(_arr(bo.qual_text, bo.qual_nbytes, np.uint8))
-            hq = bo.qual_nbytes > 0 or bo.qual_z_nbytes > 0
-            parts["qual_block_sizes"].append(_arr(bo.qual_block_sizes, nb if hq else 0, np.uint64))
-            parts["qual_z"].append(_arr(bo.qual_z, bo.qual_z_nbytes, np.uint8))
-            parts["qual_z_block_sizes"].append(_arr(bo.qual_z_block_sizes, nb if bo.qual_z_nbytes else 0, np.uint64))
-            parts["anchor_pos"].append(_arr(bo.anchor_pos, bo.read_count if bo.anchor_pos else 0, np.int32))
-            parts["anchor_addr"].append(_arr(bo.anchor_addr, bo.read_count if bo.anchor_addr else 0, np.uint32))
-            first += nb
-        r = Result()
-        self._check(self.L.leon_encode_finish(self.ctx, C.byref(r)))
-        out = self._result(r)
+            b, o, q = cut(lo, hi)
+            bo = self.encode_block(first, b, o, q)
+            for k in keys:
+                parts[k].append(bo[k])
+            first += bo["nblocks"]
+        out = self.encode_finish()
         for k, v in parts.items():
             out[k] = np.concatenate(v) if v else np.zeros(0, np.uint8)
         out["nblocks"] = first
-        out["count_passes"] = int(npass.value)
+        out["count_passes"] = npass
         return out
 
     def run_device(self):

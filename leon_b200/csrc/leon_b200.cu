@@ -628,7 +628,10 @@ template <typename K> void do_bloom(leon_ctx *c)
     b.magic = ~0ull / b.reduced_tai;
     b.nbytes = nbytes;
     b.k = c->opts.kmer_size;
-    uint64_t alloc = (nbytes + 3) / 4 * 4 + 64;
+    // with N ranks the array is cut into N equal parts of whole 16-byte units for the exchange below
+    const uint64_t N_ = (uint64_t)std::max(1, c->comm.n);
+    uint64_t part_words = (((nbytes + 3) / 4 + 64 / 4 + N_ - 1) / N_ + 3) & ~3ull;
+    uint64_t alloc = part_words * N_ * 4;
     c->d_bloom.reserve(alloc);
     b.words = c->d_bloom.as<uint32_t>();
     CUDA_TRY(cudaMemsetAsync(b.words, 0, alloc, st));
@@ -638,11 +641,24 @@ template <typename K> void do_bloom(leon_ctx *c)
                   c->d_solid_cnt.as<uint32_t>(), c->nsolid, (uint32_t)c->min_abundance, b, c->d_tbl.as<uint64_t>()));
     }
     if (c->comm.active()) {
-        uint64_t nwords = alloc / 4;
-        c->d_bloom_all.reserve((uint64_t)c->comm.n * alloc);
-        NCCL_TRY(nccl_api().AllGather(b.words, c->d_bloom_all.p, nwords, ncclUint32, c->comm.comm, st));
-        unsigned grid = (unsigned)std::min<uint64_t>((nwords + 255) / 256, (uint64_t)NUM_SMS * 8);
-        LB_TIMED(c->kt, "k_or_reduce", st, LB_LAUNCH(c->lc, lbbloom::k_or_reduce, grid, 256, 0, st, c->d_bloom_all.as<uint32_t>(), c->comm.n, nwords, b.words));
+        // Every rank inserted the solid k-mers it owns into a zeroed array of the full size; the filter is the OR of the N
+        // arrays.  NCCL has no bitwise reduction, so: reduce-scatter by hand (rank p receives part p of every rank's array over
+        // NVLink and ORs them), then an in-place all-gather of the reduced parts.  Traffic and receive buffer are 1x the
+        // filter each, whatever N (the all-gather of N whole arrays used before needed N x: 36 GB per rank at 3 Gbp).
+        const int N = c->comm.n, me = c->comm.rank;
+        c->d_bloom_all.reserve(alloc);
+        uint32_t *recv = c->d_bloom_all.as<uint32_t>();
+        NCCL_TRY(nccl_api().GroupStart());
+        for (int p = 0; p < N; p++) {
+            if (p == me) continue;
+            NCCL_TRY(nccl_api().Send(b.words + (uint64_t)p * part_words, part_words, ncclUint32, p, c->comm.comm, st));
+            NCCL_TRY(nccl_api().Recv(recv + (uint64_t)p * part_words, part_words, ncclUint32, p, c->comm.comm, st));
+        }
+        NCCL_TRY(nccl_api().GroupEnd());
+        CUDA_TRY(cudaMemcpyAsync(recv + (uint64_t)me * part_words, b.words + (uint64_t)me * part_words, part_words * 4, cudaMemcpyDeviceToDevice, st));
+        unsigned grid = (unsigned)std::min<uint64_t>((part_words + 255) / 256, (uint64_t)NUM_SMS * 8);
+        LB_TIMED(c->kt, "k_or_reduce", st, LB_LAUNCH(c->lc, lbbloom::k_or_reduce, grid, 256, 0, st, recv, N, part_words, b.words + (uint64_t)me * part_words));
+        NCCL_TRY(nccl_api().AllGather(b.words + (uint64_t)me * part_words, b.words, part_words, ncclUint32, c->comm.comm, st));
     }
     CUDA_TRY(cudaEventRecord(c->ev[6], st));
     c->phase = PH_BLOOM;

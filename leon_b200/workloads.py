@@ -72,20 +72,34 @@ def _sha(*parts):
     return h.hexdigest()
 
 
+def block_digests(blocks):
+    """sha256 of every block (an iterable of bytes-like objects), as a list of 32-byte digests."""
+    return [hashlib.sha256(memoryview(np.ascontiguousarray(b)).cast("B") if isinstance(b, np.ndarray) else b).digest() for b in blocks]
+
+
 def digest_of_streams(bloom, anchors_dict, dna, blocksizes, qual_text_blocks=None):
     """Digest of everything `leon -c` stores for the sequence (+ quality) streams.  qual_text_blocks: iterable of the
-    INFLATED quality text of every block in order (zlib bytes may differ between writers, the text may not)."""
-    d = {"bloom": _sha(bloom), "anchors_dict": _sha(anchors_dict), "dna": _sha(dna),
-         "blocksizes": _sha(np.ascontiguousarray(blocksizes, "<u8")),
-         "nblocks": int(len(blocksizes) // 2), "dna_nbytes": int(len(dna))}
+    INFLATED quality text of every block in order (zlib bytes may differ between writers, the text may not).
+    dna_cc / qual_text_cc are checksums of the per-block checksums (sha256 over the blocks' sha256 digests in file order): ranks
+    of a multi-GPU run can each hash their own blocks and only the 32-byte digests need to travel."""
+    bs = np.ascontiguousarray(blocksizes, "<u8")
+    dna = np.ascontiguousarray(dna)
+    ends = np.cumsum(bs[0::2].astype(np.int64))
+    starts = ends - bs[0::2].astype(np.int64)
+    d = {"bloom": _sha(bloom), "anchors_dict": _sha(anchors_dict), "dna": _sha(dna), "blocksizes": _sha(bs),
+         "nblocks": int(len(bs) // 2), "dna_nbytes": int(len(dna)),
+         "dna_cc": hashlib.sha256(b"".join(block_digests(dna[int(a):int(b)] for a, b in zip(starts, ends)))).hexdigest()}
     if qual_text_blocks is not None:
         h = hashlib.sha256()
         n = 0
+        per = []
         for t in qual_text_blocks:
             h.update(t)
+            per.append(hashlib.sha256(t).digest())
             n += len(t)
         d["qual_text"] = h.hexdigest()
         d["qual_text_nbytes"] = n
+        d["qual_text_cc"] = hashlib.sha256(b"".join(per)).hexdigest()
     return d
 
 
@@ -121,6 +135,22 @@ def digest_of_container(path, with_qual):
         return digest_of_streams(c.dataset("leon/bloom"), c.dataset("leon/anchors/anchorsDict"), dna, bs, qt)
 
 
+def write_ragged(path, bases, offsets, quals, first_index=0, append=False, chunk=1 << 16):
+    """FASTA / FASTQ writer for reads of any length, names r<i>."""
+    n = len(offsets) - 1
+    with open(path, "ab" if append else "wb") as f:
+        for lo in range(0, n, chunk):
+            hi = min(n, lo + chunk)
+            parts = []
+            for i in range(lo, hi):
+                a, b = int(offsets[i]), int(offsets[i + 1])
+                if quals is None:
+                    parts.append(b">r%d\n%s\n" % (first_index + i, bases[a:b].tobytes()))
+                else:
+                    parts.append(b"@r%d\n%s\n+\n%s\n" % (first_index + i, bases[a:b].tobytes(), quals[a:b].tobytes()))
+            f.write(b"".join(parts))
+
+
 def digests_equal(a, b):
     keys = ["bloom", "anchors_dict", "dna", "blocksizes"] + (["qual_text"] if "qual_text" in a and "qual_text" in b else [])
     return all(a.get(k) == b.get(k) for k in keys), [k for k in keys if a.get(k) != b.get(k)]
@@ -128,11 +158,11 @@ def digests_equal(a, b):
 
 # ---------------------------------------------------------------------------------------------------------------
 # configs[3] shape: 150 bp FASTQ at 50x with N bases, N runs and indels (fixed-length reads whose alignment to the genome
-# has an insertion or a deletion), a few reads trimmed (variable lengths).  Generated in chunks of 2^18 reads, chunk c
+# has an insertion or a deletion), a few reads trimmed (variable lengths).  Generated in chunks of 250 000 reads, chunk c
 # from its own generator PCG64([seed, c]), so that any rank can produce exactly its own reads and threads can work on
 # different chunks at once.
 # ---------------------------------------------------------------------------------------------------------------
-C3_CHUNK = 1 << 18
+C3_CHUNK = 250_000        # reads; 5 blocks of 50000, so a chunk is also a unit the reads can be dealt to ranks in
 CONFIGS["configs[3]"] = dict(genome=100_000_000, gseed=3, reads=33_333_333, read_len=150, rseed=4, fastq=True, n_rate=0.001,
                              text="configs[3]: 100 Mbp random genome, 150 bp FASTQ reads at 50x, 0.5% substitutions, N bases and "
                                   "N runs, indels, 2% trimmed reads, lossy quality mode, k=31 (Bloom filter 150 MB > L2)",

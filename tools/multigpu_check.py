@@ -24,7 +24,7 @@ KEYS = ("cutoff", "nb_solids_cutoff", "nb_solid_total", "bloom_bits", "anchor_co
 ARRS = ("histogram", "bloom", "anchors_dict", "blocksizes", "dna", "anchor_pos")
 
 
-def run_case(rank, world, k, L, nreads, rpb, fastq, seed, genome):
+def run_case(rank, world, k, L, nreads, rpb, fastq, seed, genome, stream=0, passes=0):
     from oracle import oracle_py as O
     g = synth.make_genome(genome, seed)
     bases, offs, quals = synth.sample_reads(g, nreads, L, seed + 100, n_rate=0.0005, with_quals=fastq)
@@ -34,7 +34,13 @@ def run_case(rank, world, k, L, nreads, rpb, fastq, seed, genome):
     eng.comm_init(rank, world, uid[0])
     S = eng.comm_batch_reads()
     b, o, q = shard.shard_reads(bases, offs, quals, rank, world, S)
-    r = eng.compress(b, o, q)
+    if stream:      # streaming entry points: batches of `stream` rounds, the same number of calls on every rank
+        rounds = -(-nreads // (world * S))
+        nloc = len(o) - 1
+        batches = [(min(nloc, i * stream * S), min(nloc, (i + 1) * stream * S)) for i in range(-(-rounds // stream))]
+        r = eng.compress_stream(b, o, q, batches=batches, count_passes=passes)
+    else:
+        r = eng.compress(b, o, q)
     eng.close()
     allr = [None] * world
     dist.all_gather_object(allr, r)
@@ -64,8 +70,8 @@ def run_case(rank, world, k, L, nreads, rpb, fastq, seed, genome):
         if not np.array_equal(m["anchor_addr"][am], ref["anchor_addr"][am]):
             ok = False
             print("  MISMATCH anchor_addr")
-        print("case k=%d L=%d reads=%d rpb=%d fastq=%s world=%d S=%d: %s (anchors %d, dna %d bytes)" % (
-            k, L, nreads, rpb, fastq, world, S, "OK" if ok else "FAILED", m["anchor_count"], len(m["dna"])))
+        print("case k=%d L=%d reads=%d rpb=%d fastq=%s world=%d S=%d stream=%d passes=%d: %s (anchors %d, dna %d bytes)" % (
+            k, L, nreads, rpb, fastq, world, S, stream, passes, "OK" if ok else "FAILED", m["anchor_count"], len(m["dna"])))
     flag = [ok]
     dist.broadcast_object_list(flag, src=0)
     return flag[0]
@@ -81,6 +87,9 @@ def main():
         (31, 100, 130500, 1000, True, 2, 40000),     # ragged: last round partial, some ranks short
         (63, 150, 60000, 1500, False, 3, 50000),
         (25, 76, 9000, 3000, False, 4, 20000),       # fewer rounds than ranks get reads
+        (31, 100, 130500, 1000, True, 5, 40000, 3, 1),    # streaming: 3 rounds per call, one counting pass
+        (31, 100, 120000, 2000, False, 6, 60000, 1, 3),   # streaming: one round per call, three counting passes
+        (63, 150, 60000, 1500, True, 7, 50000, 2, 2),
     ]
     ok = True
     for c in cases:
