@@ -451,7 +451,7 @@ def measure_large(args, torch, dist, world, rank, local_rank):
     gen_s = time.perf_counter() - t0
     local_reads = len(lens)
     # batches of M chunks per rank; every rank makes the same number of calls (empty batches at the end where it has run out)
-    M = 8
+    M = 32
     max_chunks = (nchunks + world - 1) // world
     ncalls = max(1, (max_chunks + M - 1) // M)
     batches = [(min(local_reads, i * M * S), min(local_reads, (i + 1) * M * S)) for i in range(ncalls)]

@@ -92,7 +92,7 @@ class HeaderStream(C.Structure):
 
 class FileOpts(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("kmer_size", "reads_per_block", "lossless", "abundance_set", "noheader", "noqual",
-                                         "seq_only", "device", "nthreads")] + [("reserved", C.c_int32 * 7)]
+                                         "seq_only", "device", "nthreads", "stream_reads", "count_passes")] + [("reserved", C.c_int32 * 5)]
 
 
 class FileStats(C.Structure):
@@ -332,11 +332,11 @@ def read_file(path, want_quals=True, want_headers=True):
 
 
 def compress_file(in_path, out_path=None, kmer_size=31, reads_per_block=50000, lossless=False, abundance=None, noheader=False,
-                  noqual=False, seq_only=False, device=0, nthreads=0):
+                  noqual=False, seq_only=False, device=0, nthreads=0, stream_reads=0, count_passes=0):
     """`leon -file in_path -c` end to end on the B200 path (C/Leon.cpp:342-470); returns the statistics as a dict."""
     L = load_library()
     o = FileOpts(kmer_size, reads_per_block, int(lossless), int(abundance is not None), int(noheader), int(noqual),
-                 int(seq_only), device, nthreads)
+                 int(seq_only), device, nthreads, int(stream_reads), int(count_passes))
     st = FileStats()
     rc = L.leon_compress_file(os.fsencode(in_path), os.fsencode(out_path) if out_path else None, C.byref(o), C.byref(st))
     if rc != 0:

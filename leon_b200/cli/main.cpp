@@ -18,6 +18,8 @@ static void usage() {
             "  -kmer-size N   k-mer size, 2..63 (default 31)\n"
             "  -abundance N   abundance threshold given explicitly (disables the automatic cutoff)\n"
             "  -nb-cores N    host threads for the header stream and zlib (default: all)\n"
+            "  -stream-reads N  feed the GPU batches of N reads (streaming path; default: whole set when it fits the device)\n"
+            "  -count-passes N  streaming: number of k-mer counting passes (default: from the free device memory)\n"
             "  -lossless      keep the qualities unchanged\n"
             "  -seq-only      store the sequences only (same as -noheader -noqual)\n"
             "  -noheader      do not store the read names\n"
@@ -48,6 +50,8 @@ int main(int argc, char **argv) {
         else if (a == "-kmer-size") o.kmer_size = atoi(value("-kmer-size"));
         else if (a == "-abundance") { value("-abundance"); o.abundance_set = 1; }   // only its presence matters
         else if (a == "-nb-cores") o.nthreads = atoi(value("-nb-cores"));
+        else if (a == "-stream-reads") o.stream_reads = atoi(value("-stream-reads"));
+        else if (a == "-count-passes") o.count_passes = atoi(value("-count-passes"));
         else if (a == "-lossless") o.lossless = 1;
         else if (a == "-seq-only") o.seq_only = 1;
         else if (a == "-noheader") o.noheader = 1;

@@ -420,7 +420,74 @@ extern "C" int leon_compress_file(const char *in_path, const char *out_path, con
         rd.quals = is_fasta ? nullptr : rs.quals.p;
         rd.nreads = nreads;
         leon_result res;
-        rc = leon_compress(ctx, &rd, &res);
+        // Read sets beyond what the device holds at once (or on request) go through the streaming entry points: counted in
+        // hash-partitioned passes and encoded batch by batch, the per-block outputs gathered here for the container.
+        uint64_t batch_reads = o->stream_reads > 0 ? (uint64_t)o->stream_reads : 0;
+        if (!batch_reads && rs.offsets.back() > 3000000000ull) batch_reads = 8000000;
+        std::vector<uint8_t> s_dna, s_qz;
+        std::vector<uint64_t> s_bs, s_qzs, s_qs;
+        if (batch_reads) {
+            const uint64_t rpb = (uint64_t)lo.reads_per_block;
+            batch_reads = std::max<uint64_t>(rpb, batch_reads / rpb * rpb);          // whole blocks
+            std::vector<uint64_t> boffs;
+            auto batch_of = [&](uint64_t r0, leon_reads &b) {
+                const uint64_t r1 = std::min(nreads, r0 + batch_reads), base = rs.offsets[r0];
+                boffs.resize(r1 - r0 + 1);
+                for (uint64_t i = r0; i <= r1; i++) boffs[i - r0] = rs.offsets[i] - base;
+                b.bases = rs.bases.p + base;
+                b.quals = is_fasta ? nullptr : rs.quals.p + base;
+                b.offsets = boffs.data();
+                b.nreads = r1 - r0;
+            };
+            leon_stream_plan plan;
+            memset(&plan, 0, sizeof plan);
+            plan.total_reads = nreads;
+            plan.total_bases = rs.offsets.back();
+            plan.count_passes = o->count_passes > 0 ? (uint32_t)o->count_passes : 0;
+            uint32_t npasses = 1;
+            rc = leon_count_begin(ctx, &plan, &npasses);
+            leon_reads b;
+            for (uint32_t p = 0; !rc && p < npasses; p++) {
+                uint64_t r0 = 0;
+                do {
+                    batch_of(r0, b);
+                    r0 += batch_reads;
+                    rc = leon_count(ctx, &b, r0 >= nreads);
+                } while (!rc && r0 < nreads);
+            }
+            leon_count_result cr;
+            if (!rc) rc = leon_count_finish(ctx, &cr);
+            if (!rc) rc = leon_bloom_build(ctx, nullptr, nullptr, nullptr);
+            uint64_t first_block = 0, r0 = 0;
+            do {
+                if (rc) break;
+                batch_of(r0, b);
+                r0 += batch_reads;
+                leon_block_out bo;
+                rc = leon_encode_block(ctx, first_block, &b, &bo);
+                if (rc) break;
+                s_dna.insert(s_dna.end(), bo.dna, bo.dna + bo.dna_nbytes);
+                s_bs.insert(s_bs.end(), bo.blocksizes, bo.blocksizes + 2 * bo.nblocks);
+                if (bo.qual_z_nbytes) {
+                    s_qz.insert(s_qz.end(), bo.qual_z, bo.qual_z + bo.qual_z_nbytes);
+                    s_qzs.insert(s_qzs.end(), bo.qual_z_block_sizes, bo.qual_z_block_sizes + bo.nblocks);
+                    s_qs.insert(s_qs.end(), bo.qual_block_sizes, bo.qual_block_sizes + bo.nblocks);
+                }
+                first_block += bo.nblocks;
+            } while (r0 < nreads);
+            if (!rc) rc = leon_encode_finish(ctx, &res);
+            if (!rc) {
+                res.nblocks = first_block;
+                res.blocksizes = s_bs.data();
+                res.dna = s_dna.data(); res.dna_nbytes = s_dna.size();
+                if (!s_qzs.empty()) {
+                    res.qual_z = s_qz.data(); res.qual_z_nbytes = s_qz.size();
+                    res.qual_z_block_sizes = s_qzs.data(); res.qual_block_sizes = s_qs.data();
+                }
+            }
+        } else {
+            rc = leon_compress(ctx, &rd, &res);
+        }
         if (rc) err = leon_last_error(ctx);
         if (header_thread.joinable()) header_thread.join();
         if (!rc && hrc) { rc = hrc; err = herr; }

@@ -1844,9 +1844,9 @@ template <typename K> static void stream_count_begin(leon_ctx *c, const leon_str
     if (np == 0) {
         size_t free_b = 0, total_b = 0;
         CUDA_TRY(cudaMemGetInfo(&free_b, &total_b));
-        // key buffer + its ping-pong twin (+ the receive buffer of the exchange with several ranks) within 60 % of what is free
+        // key buffer + its ping-pong twin (+ the receive buffer of the exchange with several ranks) within 70 % of what is free
         const double per_key = (double)kb * (c->comm.n > 1 ? 3.2 : 2.1);
-        const double budget = 0.6 * (double)free_b;
+        const double budget = 0.7 * (double)free_b;
         np = (uint32_t)std::max(1.0, std::ceil((double)nk_bound * per_key / budget));
     }
     uint64_t cap = nk_bound;
@@ -1965,6 +1965,19 @@ int leon_count_finish(leon_ctx *c, leon_count_result *out)
     user_stream_in(c);
     count_finish(c);
     c->stream_counting = false;
+    {   // the key buffers of the counting passes are dead weight from here on: keep only the solid list
+        const size_t kb = c->opts.kmer_size <= 31 ? 8 : 16;
+        if (c->solid_keys != c->d_solid_keys.p) {
+            DevBuf compact;
+            compact.reserve((c->nsolid + 1) * kb);
+            if (c->nsolid) CUDA_TRY(cudaMemcpyAsync(compact.p, c->solid_keys, c->nsolid * kb, cudaMemcpyDeviceToDevice, c->st));
+            CUDA_TRY(cudaStreamSynchronize(c->st));
+            c->d_solid_keys.release();
+            std::swap(c->d_solid_keys.p, compact.p); std::swap(c->d_solid_keys.cap, compact.cap);
+            c->solid_keys = c->d_solid_keys.p;
+        }
+        c->d_keys.release(); c->d_keys_alt.release(); c->d_keys_batch.release(); c->d_keys_recv.release();
+    }
     if (out) *out = c->cres;
     user_stream_out(c);
     LB_API_END(c)

@@ -112,3 +112,40 @@ def test_cli_file_equals_reference_container(tmp_path, ext, flags):
         if "-lossless" in flags:
             assert lines[3::4] == quals
     assert got_reads == reads
+
+
+@pytest.mark.parametrize("ext,flags", [("fastq", []), ("fastq", ["-lossless"]), ("fasta", [])])
+def test_cli_streaming_writes_the_same_container(tmp_path, ext, flags):
+    """`-stream-reads N -count-passes P`: the file fed to the GPU in batches of N reads (streaming entry points) gives the same
+    `.leon` file, byte for byte, as the whole set at once (which equals the reference's, test above)."""
+    fastq = ext == "fastq"
+    a, b = tmp_path / "a", tmp_path / "b"
+    a.mkdir(); b.mkdir()
+    _write_file(str(a / ("in." + ext)), fastq, 23000, 9)
+    os.link(str(a / ("in." + ext)), str(b / ("in." + ext)))
+    common = ["-c", "-kmer-size", "31", "-reads", "2000"] + flags
+    r1 = subprocess.run([CLI, "-file", str(a / ("in." + ext))] + common, capture_output=True, text=True, timeout=600)
+    r2 = subprocess.run([CLI, "-file", str(b / ("in." + ext))] + common + ["-stream-reads", "7000", "-count-passes", "3"],
+                        capture_output=True, text=True, timeout=600)
+    assert r1.returncode == 0 and r2.returncode == 0, r1.stderr + r2.stderr
+    assert (a / ("in.%s.leon" % ext)).read_bytes() == (b / ("in.%s.leon" % ext)).read_bytes()
+
+
+def test_cli_gzip_input_and_output_name(tmp_path):
+    """`leon -file x.fastq.gz -c` (the reference reads through gzopen): same streams as the plain file, and the output is
+    <dir>/x.fastq.leon (C/Leon.cpp:466-479)."""
+    import gzip
+    import leon_b200
+    d = tmp_path / "g"
+    d.mkdir()
+    _write_file(str(d / "in.fastq"), True, 6000, 11)
+    (d / "x.fastq.gz").write_bytes(gzip.compress((d / "in.fastq").read_bytes()))
+    common = ["-c", "-kmer-size", "31", "-reads", "2000"]
+    r1 = subprocess.run([CLI, "-file", str(d / "in.fastq")] + common, capture_output=True, text=True, timeout=600)
+    r2 = subprocess.run([CLI, "-file", str(d / "x.fastq.gz")] + common, capture_output=True, text=True, timeout=600)
+    assert r1.returncode == 0 and r2.returncode == 0, r1.stderr + r2.stderr
+    assert (d / "x.fastq.leon").exists() and not (d / "x.fastq.gz.leon").exists()
+    with leon_b200.Container(str(d / "in.fastq.leon")) as c1, leon_b200.Container(str(d / "x.fastq.leon")) as c2:
+        for ds in ("leon/bloom", "leon/anchors/anchorsDict", "leon/dna/blocksizes", "leon/dna/dna_0", "leon/dna/dna_2", "leon/qual/qual_1",
+                   "leon/header/header_0"):
+            assert np.array_equal(c1.dataset(ds), c2.dataset(ds)), ds
