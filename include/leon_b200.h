@@ -322,6 +322,10 @@ typedef struct leon_file_stats {
     float    parse_ms, compress_ms, header_ms, write_ms, total_ms;   /* host wall clock; compress_ms covers the GPU path and, in parallel, the header coder */
     float    reserved1[3];
     leon_timings gpu;
+    /* what the reference prints in its "Abundance threshold" / "End Sequence compression" sections (C/Leon.cpp:970-1015) */
+    int32_t  cutoff, abundance_auto;
+    uint64_t nb_solid_kmers, anchor_count, reads_without_anchor;
+    uint64_t bloom_bytes, anchors_dict_bytes, seq_bytes_out, qual_bytes_out;
 } leon_file_stats;
 int leon_compress_file(const char *in_path, const char *out_path, const leon_file_opts *opts, leon_file_stats *stats);
 /* `leon -file X.leon -d` (C/Leon.cpp:1311-1470, 1697-1860): decodes the three streams of a container (ours or the

@@ -100,7 +100,9 @@ class FileStats(C.Structure):
                                           "header_bytes_in", "header_bytes_out", "dna_bytes_out")] + \
                [(n, C.c_int32) for n in ("is_fasta", "has_header", "headers_coded_serially", "reserved0")] + \
                [(n, C.c_float) for n in ("parse_ms", "compress_ms", "header_ms", "write_ms", "total_ms")] + \
-               [("reserved1", C.c_float * 3), ("gpu", Timings)]
+               [("reserved1", C.c_float * 3), ("gpu", Timings), ("cutoff", C.c_int32), ("abundance_auto", C.c_int32)] + \
+               [(n, C.c_uint64) for n in ("nb_solid_kmers", "anchor_count", "reads_without_anchor", "bloom_bytes", "anchors_dict_bytes",
+                                          "seq_bytes_out", "qual_bytes_out")]
 
 
 class FileReads(C.Structure):

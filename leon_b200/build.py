@@ -39,6 +39,11 @@ def build(force=False, verbose=False):
     os.makedirs(os.path.dirname(CLI), exist_ok=True)
     subprocess.run([os.environ.get("CXX", "g++"), "-O2", "-std=c++17", "-o", CLI, CLI_SRC, "-L", HERE, "-lleon_b200",
                     "-Wl,-rpath,$ORIGIN/.."], check=True)
+    # the same program under the reference's name: `leon -file X -c|-d`
+    alias = os.path.join(os.path.dirname(CLI), "leon")
+    if os.path.lexists(alias):
+        os.remove(alias)
+    os.link(CLI, alias)
     return LIB
 
 

@@ -526,6 +526,15 @@ extern "C" int leon_compress_file(const char *in_path, const char *out_path, con
             stats->write_ms = (float)(t3 - t2);
             stats->total_ms = (float)(t3 - t0);
             leon_get_timings(ctx, &stats->gpu);
+            stats->cutoff = res.count.cutoff;
+            stats->abundance_auto = lo.abundance_set ? 0 : 1;
+            stats->nb_solid_kmers = lo.abundance_set ? res.count.nb_solid_total : res.count.nb_solids_cutoff;
+            stats->anchor_count = res.anchor_count;
+            stats->reads_without_anchor = res.reads_without_anchor;
+            stats->bloom_bytes = res.bloom_nbytes;
+            stats->anchors_dict_bytes = res.anchors_dict_nbytes;
+            stats->seq_bytes_out = res.dna_nbytes;
+            stats->qual_bytes_out = res.qual_z_nbytes;
         }
     } catch (const std::bad_alloc &) {
         rc = LEON_E_NOMEM;

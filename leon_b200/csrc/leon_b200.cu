@@ -68,6 +68,13 @@ enum Phase { PH_NONE = 0, PH_UPLOADED, PH_COUNTED, PH_BLOOM, PH_ENCODED };
 
 }  // namespace
 
+// tuning knobs read once from the environment (experiments; the defaults are what was measured best)
+static uint64_t env_u64(const char *name, uint64_t dflt)
+{
+    const char *v = getenv(name);
+    return v && *v ? strtoull(v, nullptr, 10) : dflt;
+}
+
 // One host thread's private launch context: stream, scratch of the scan / partition helpers, pinned scalar slot,
 // launch counter and kernel timer (none of them is shared between threads).
 struct Lane {
@@ -955,7 +962,12 @@ template <typename K> void sb_prepare(leon_ctx *c, uint64_t g)
         // bases of the 256 reads of a CTA are staged in shared memory when they fit (40 KB), else read from global
         uint64_t need = ((256ull * (uint64_t)c->max_len + 31) & ~15ull) + 16;
         uint32_t stage_bytes = need <= 40960 ? (uint32_t)need : 16u;
-        LB_TIMED(ln.kt, "k_walk", st, LB_LAUNCH(ln.lc, (lbwalk::k_walk<K>), cdiv_u(R, 256), 256, stage_bytes, st, bases, offsets, koff, R, c->bloom,
+        // LEON_B200_WALK_SMEM: dynamic shared memory claimed per CTA beyond the staging need (limits the CTAs per SM, so that the
+        // small kernels of the anchor stage find room beside a running walk)
+        static const uint64_t walk_smem = env_u64("LEON_B200_WALK_SMEM", 0);
+        size_t smem_claim = std::max<size_t>(stage_bytes, walk_smem);
+        if (walk_smem) CUDA_TRY(cudaFuncSetAttribute(lbwalk::k_walk<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_claim));
+        LB_TIMED(ln.kt, "k_walk", st, LB_LAUNCH(ln.lc, (lbwalk::k_walk<K>), cdiv_u(R, 256), 256, smem_claim, st, bases, offsets, koff, R, c->bloom,
                   c->d_tbl.as<uint64_t>(), apos, c->d_bif.as<uint8_t>(), c->d_err.as<uint32_t>(), recs, stage_bytes));
     }
     sb.nblocks = (R + rpb - 1) / rpb;
@@ -1046,7 +1058,8 @@ void sb_finish(leon_ctx *c, uint64_t g)
     sb.fetched = true;
 }
 
-constexpr uint64_t SB_PIPELINE_MIN = 16;
+constexpr uint64_t SB_PIPELINE_MIN_DEFAULT = 16;
+
 
 template <typename K> void stage_b_worker(leon_ctx *c)
 {
@@ -1058,6 +1071,7 @@ template <typename K> void stage_b_worker(leon_ctx *c)
         // 4.6 M reads (10 super-blocks): the bulk kernels take the SMs from the small latency-critical anchor kernels
         // (anchor stage 8.6 -> 15.5 ms) and that costs what the overlap gains (72.4 vs 72.2 ms; FASTQ 87.4 vs 82.8 ms), since
         // the run ends one chain length (40 ms) after the LAST chain is launched either way.  Larger sets are pipelined.
+        static const uint64_t SB_PIPELINE_MIN = env_u64("LEON_B200_SB_PIPELINE_MIN", SB_PIPELINE_MIN_DEFAULT);
         const uint64_t gate = nsb <= SB_PIPELINE_MIN ? nsb - 1 : 0;
         for (uint64_t g = 0; g < nsb; g++) {
             while (c->sb_pub.load(std::memory_order_acquire) <= std::max(g, gate)) {

@@ -149,3 +149,32 @@ def test_cli_gzip_input_and_output_name(tmp_path):
         for ds in ("leon/bloom", "leon/anchors/anchorsDict", "leon/dna/blocksizes", "leon/dna/dna_0", "leon/dna/dna_2", "leon/qual/qual_1",
                    "leon/header/header_0"):
             assert np.array_equal(c1.dataset(ds), c2.dataset(ds)), ds
+
+
+def test_cli_compress_summary_has_the_reference_keys(tmp_path):
+    """The lines users and CI logs read (C/Leon.cpp:402-416, 726-767, 970-1015) are printed by `leon -c`, the values of the
+    counting stage equal the reference's."""
+    _write_file(str(tmp_path / "in.fastq"), True, 12000, 13)
+    leon = os.path.join(ROOT, "leon_b200", "bin", "leon")
+    r = subprocess.run([leon, "-file", str(tmp_path / "in.fastq"), "-c", "-kmer-size", "31"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr
+    for key in ("Input format: FastQ", "Quality compression: lossy mode", "End Header compression", "cut-off (auto)", "nb solid kmers",
+                "End Sequence compression", "# blocks", "# sequences", "# nucleotides", "Reads per anchor", "Read without anchor",
+                "End compression", "Time:", "Speed:", "overall", "header only", "Sequence only", "Quality only"):
+        assert key in r.stdout, key
+    if ref_leon(31) is None:
+        pytest.skip("oracle/_ref not built")
+    d = tmp_path / "ref"
+    d.mkdir()
+    os.link(str(tmp_path / "in.fastq"), str(d / "in.fastq"))
+    rr = subprocess.run([ref_leon(31), "-file", str(d / "in.fastq"), "-c", "-kmer-size", "31", "-nb-cores", "1"], cwd=str(d),
+                        capture_output=True, text=True, timeout=900)
+    ref_out = rr.stdout.replace("\r", "\n")
+
+    def value(text, key):
+        for ln in text.split("\n"):
+            if ln.strip().startswith(key):
+                return ln.split(":")[-1].strip()
+        return None
+    for key in ("cut-off (auto)", "nb solid kmers", "# sequences", "# nucleotides"):
+        assert value(r.stdout, key) == value(ref_out, key), key
