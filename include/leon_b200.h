@@ -187,6 +187,12 @@ typedef struct leon_block_out {
 int leon_count_begin(leon_ctx *ctx, const leon_stream_plan *plan, uint32_t *npasses);
 int leon_count(leon_ctx *ctx, const leon_reads *batch, int last);        /* Dispatcher::iterate(it, DSK functor, chunk) */
 int leon_count_finish(leon_ctx *ctx, leon_count_result *out);
+/* Optional, any time between two leon_count / leon_encode_block calls: starts copying the batch that will be submitted NEXT
+ * into spare device buffers, so that its upload runs beside the work on the current one (the reference's bank iterator
+ * reads ahead the same way, DP/api/ICommand.hpp:304-331 hands chunks to free threads).  The batch's memory must stay
+ * valid and unchanged until the call it is then submitted to returns; a prefetched batch that is not the next one
+ * submitted is ignored. */
+int leon_stream_prefetch(leon_ctx *ctx, const leon_reads *next_batch, int with_quals);
 /* Codes the blocks of `batch`; first_block must be the number of blocks this rank has coded so far.  The outputs are on
  * the host when it returns and stay valid until the next leon_encode_block / leon_encode_finish on the context. */
 int leon_encode_block(leon_ctx *ctx, uint64_t first_block, const leon_reads *batch, leon_block_out *out);

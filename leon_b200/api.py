@@ -10,7 +10,7 @@ LIB_PATH = os.path.join(HERE, "libleon_b200.so")
 ABI_SYMBOLS = [
     "leon_b200_abi_version", "leon_create", "leon_destroy", "leon_last_error", "leon_alloc_pinned", "leon_free_pinned",
     "leon_compress", "leon_upload", "leon_count_resident", "leon_count_begin", "leon_count", "leon_count_finish",
-    "leon_encode_block", "leon_block_wait", "leon_encode_finish", "leon_bloom_build", "leon_encode", "leon_run_device", "leon_fetch",
+    "leon_encode_block", "leon_block_wait", "leon_encode_finish", "leon_stream_prefetch", "leon_bloom_build", "leon_encode", "leon_run_device", "leon_fetch",
     "leon_get_timings", "leon_get_kernel_times", "leon_set_stream", "leon_comm_unique_id", "leon_comm_init",
     "leon_comm_batch_reads", "leon_debug_bloom_query", "leon_debug_hashes", "leon_debug_fetch", "leon_write_container",
     "leon_headers_encode", "leon_headers_free", "leon_compress_file", "leon_decompress_file", "leon_read_file", "leon_file_reads_free",
@@ -146,6 +146,7 @@ def load_library(path=LIB_PATH):
     L.leon_count.argtypes = [C.c_void_p, C.POINTER(Reads), C.c_int]
     L.leon_count_finish.argtypes = [C.c_void_p, C.POINTER(CountResult)]
     L.leon_encode_block.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(Reads), C.POINTER(BlockOut)]
+    L.leon_stream_prefetch.argtypes = [C.c_void_p, C.POINTER(Reads), C.c_int]
     L.leon_block_wait.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(BlockOut)]
     L.leon_encode_finish.argtypes = [C.c_void_p, C.POINTER(Result)]
     L.leon_bloom_build.argtypes = [C.c_void_p, C.POINTER(C.POINTER(C.c_uint8)), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
@@ -551,8 +552,21 @@ class Leon:
         self._check(self.L.leon_count_begin(self.ctx, C.byref(plan), C.byref(npass)))
         return int(npass.value)
 
+    def _batch(self, bases, offsets, quals):
+        """A Reads struct over the caller's arrays WITHOUT copies (they must be contiguous u8 / u64 and stay alive)."""
+        assert bases.dtype == np.uint8 and offsets.dtype == np.uint64 and bases.flags.c_contiguous and offsets.flags.c_contiguous
+        q = quals if (self.opts.has_qual and quals is not None) else None
+        return Reads(bases.ctypes.data, offsets.ctypes.data, q.ctypes.data if q is not None else None, len(offsets) - 1), (bases, offsets, q)
+
+    def prefetch(self, bases, offsets, quals=None):
+        """Starts the upload of the batch that will be submitted next (leon_stream_prefetch); the arrays must be the very
+        ones passed to the next count_batch / encode_block call."""
+        rd, keep = self._batch(bases, offsets, quals)
+        self._pf_keep = keep
+        self._check(self.L.leon_stream_prefetch(self.ctx, C.byref(rd), int(quals is not None)))
+
     def count_batch(self, bases, offsets, last):
-        rd = self._reads(bases, offsets, None)
+        rd, keep = self._batch(np.ascontiguousarray(bases, np.uint8), np.ascontiguousarray(offsets, np.uint64), None)
         self._check(self.L.leon_count(self.ctx, C.byref(rd), int(bool(last))))
 
     def count_finish(self):
@@ -564,7 +578,8 @@ class Leon:
     def encode_block(self, first_block, bases, offsets, quals=None, copy=True):
         """Codes the blocks of one batch; returns their outputs (views into the context's buffers when copy=False: valid until
         the next call)."""
-        rd = self._reads(bases, offsets, quals)
+        rd, keep = self._batch(np.ascontiguousarray(bases, np.uint8), np.ascontiguousarray(offsets, np.uint64),
+                               np.ascontiguousarray(quals, np.uint8) if quals is not None else None)
         bo = BlockOut()
         self._check(self.L.leon_encode_block(self.ctx, int(first_block), C.byref(rd), C.byref(bo)))
         nb = int(bo.nblocks)
@@ -591,22 +606,27 @@ class Leon:
         if batches is None:
             batches = [(lo, min(n, lo + batch_reads)) for lo in range(0, n, batch_reads)] or [(0, 0)]
 
-        def cut(lo, hi):
+        bases = np.ascontiguousarray(bases, np.uint8)
+        quals = np.ascontiguousarray(quals, np.uint8) if (quals is not None and self.opts.has_qual) else None
+        cuts = []
+        for lo, hi in batches:          # the arrays of every batch once, so that a prefetched batch is recognised by its pointers
             b0, b1 = int(offsets[lo]), int(offsets[hi])
-            return bases[b0:b1], offsets[lo:hi + 1] - offsets[lo], (quals[b0:b1] if quals is not None else None)
+            cuts.append((bases[b0:b1], np.ascontiguousarray(offsets[lo:hi + 1] - offsets[lo]), quals[b0:b1] if quals is not None else None))
 
         npass = self.count_begin(n, int(offsets[-1]), count_passes)
         for _ in range(npass):
-            for i, (lo, hi) in enumerate(batches):
-                b, o, _q = cut(lo, hi)
-                self.count_batch(b, o, i == len(batches) - 1)
+            for i, (b, o, _q) in enumerate(cuts):
+                if i + 1 < len(cuts):
+                    self.prefetch(cuts[i + 1][0], cuts[i + 1][1])
+                self.count_batch(b, o, i == len(cuts) - 1)
         self.count_finish()
         self.bloom_build()
         keys = ("dna", "blocksizes", "qual_text", "qual_block_sizes", "qual_z", "qual_z_block_sizes", "anchor_pos", "anchor_addr")
         parts = {k: [] for k in keys}
         first = 0
-        for lo, hi in batches:
-            b, o, q = cut(lo, hi)
+        for i, (b, o, q) in enumerate(cuts):
+            if i + 1 < len(cuts) and i % 2 == 0:      # every other batch prefetched: both upload paths stay exercised
+                self.prefetch(*cuts[i + 1])
             bo = self.encode_block(first, b, o, q)
             for k in keys:
                 parts[k].append(bo[k])

@@ -429,8 +429,11 @@ extern "C" int leon_compress_file(const char *in_path, const char *out_path, con
         if (batch_reads) {
             const uint64_t rpb = (uint64_t)lo.reads_per_block;
             batch_reads = std::max<uint64_t>(rpb, batch_reads / rpb * rpb);          // whole blocks
-            std::vector<uint64_t> boffs;
+            std::vector<uint64_t> boffs2[2];
+            int flip = 0;
             auto batch_of = [&](uint64_t r0, leon_reads &b) {
+                std::vector<uint64_t> &boffs = boffs2[flip];          // two in turn: the batch prefetched and the one in work
+                flip ^= 1;
                 const uint64_t r1 = std::min(nreads, r0 + batch_reads), base = rs.offsets[r0];
                 boffs.resize(r1 - r0 + 1);
                 for (uint64_t i = r0; i <= r1; i++) boffs[i - r0] = rs.offsets[i] - base;
@@ -446,23 +449,26 @@ extern "C" int leon_compress_file(const char *in_path, const char *out_path, con
             plan.count_passes = o->count_passes > 0 ? (uint32_t)o->count_passes : 0;
             uint32_t npasses = 1;
             rc = leon_count_begin(ctx, &plan, &npasses);
-            leon_reads b;
+            leon_reads b, nextb;
             for (uint32_t p = 0; !rc && p < npasses; p++) {
                 uint64_t r0 = 0;
+                batch_of(0, b);
                 do {
-                    batch_of(r0, b);
                     r0 += batch_reads;
+                    if (r0 < nreads) { batch_of(r0, nextb); leon_stream_prefetch(ctx, &nextb, 0); }    // upload beside the counting of b
                     rc = leon_count(ctx, &b, r0 >= nreads);
+                    b = nextb;
                 } while (!rc && r0 < nreads);
             }
             leon_count_result cr;
             if (!rc) rc = leon_count_finish(ctx, &cr);
             if (!rc) rc = leon_bloom_build(ctx, nullptr, nullptr, nullptr);
             uint64_t first_block = 0, r0 = 0;
+            batch_of(0, b);
             do {
                 if (rc) break;
-                batch_of(r0, b);
                 r0 += batch_reads;
+                if (r0 < nreads) { batch_of(r0, nextb); leon_stream_prefetch(ctx, &nextb, 1); }
                 leon_block_out bo;
                 rc = leon_encode_block(ctx, first_block, &b, &bo);
                 if (rc) break;
@@ -474,6 +480,7 @@ extern "C" int leon_compress_file(const char *in_path, const char *out_path, con
                     s_qs.insert(s_qs.end(), bo.qual_block_sizes, bo.qual_block_sizes + bo.nblocks);
                 }
                 first_block += bo.nblocks;
+                b = nextb;
             } while (r0 < nreads);
             if (!rc) rc = leon_encode_finish(ctx, &res);
             if (!rc) {

@@ -189,6 +189,14 @@ struct leon_ctx {
     bool enc_partial_seen = false, stream_counting = false;
     uint64_t stream_reads_seen = 0;
     leon_block_out last_block_out = {};
+    // leon_stream_prefetch: spare read buffers and what is known about the batch in them
+    DevBuf d_bases_next, d_offsets_next, d_quals_next;
+    cudaStream_t st_copy = nullptr;
+    cudaEvent_t ev_copy = nullptr;
+    bool pf_valid = false, pf_quals = false;
+    leon_reads pf_reads = {};
+    int32_t pf_min = 0, pf_max = 0;
+    std::vector<uint64_t> pf_qsizes;
     // walk / entropy stage (stage_b_worker)
     Lane wk;
     std::deque<SbState> sbs;
@@ -1745,6 +1753,8 @@ void leon_destroy(leon_ctx *c)
     if (c->ev_dtot) cudaEventDestroy(c->ev_dtot);
     if (c->st) cudaStreamDestroy(c->st);
     if (c->wk.st) cudaStreamDestroy(c->wk.st);
+    if (c->st_copy) { cudaStreamSynchronize(c->st_copy); cudaStreamDestroy(c->st_copy); }
+    if (c->ev_copy) cudaEventDestroy(c->ev_copy);
     if (c->ev_user_in) cudaEventDestroy(c->ev_user_in);
     if (c->ev_user_out) cudaEventDestroy(c->ev_user_out);
     if (c->st2) { cudaStreamSynchronize(c->st2); cudaStreamDestroy(c->st2); }
@@ -1814,39 +1824,88 @@ int leon_bloom_build(leon_ctx *c, const uint8_t **bits, uint64_t *nbytes, uint64
 
 }  // extern "C"
 
-// One batch of the streaming path into the (reused) read buffers; the caller's buffers are free again on return.
-static void stream_upload(leon_ctx *c, const leon_reads *rd, bool with_quals, bool first_of_set)
+// Host-side facts of a batch the stages need: length range and the size of every block's quality text
+static void batch_host_scan(const leon_reads *rd, uint64_t rpb, bool with_quals, int32_t &mn, int32_t &mx, std::vector<uint64_t> &qsizes)
 {
-    if (!rd || !rd->offsets || (rd->nreads && !rd->bases)) throw LeonError(LEON_E_ARG, "null read batch");
-    if (rd->offsets[0] != 0) throw LeonError(LEON_E_ARG, "a batch's offsets must start at 0");
-    if (with_quals && !rd->quals) throw LeonError(LEON_E_ARG, "has_qual set but the batch has no qualities");
-    c->nreads = rd->nreads;
-    c->nbases = rd->offsets[rd->nreads];
-    c->d_bases.reserve(c->nbases + 128);
-    c->d_offsets.reserve((c->nreads + 1) * 8);
-    CUDA_TRY(cudaMemcpyAsync(c->d_bases.p, rd->bases, c->nbases, cudaMemcpyHostToDevice, c->st));
-    CUDA_TRY(cudaMemcpyAsync(c->d_offsets.p, rd->offsets, (c->nreads + 1) * 8, cudaMemcpyHostToDevice, c->st));
-    if (with_quals) {
-        c->d_quals.reserve(c->nbases + 128);
-        CUDA_TRY(cudaMemcpyAsync(c->d_quals.p, rd->quals, c->nbases, cudaMemcpyHostToDevice, c->st));
-    }
-    int32_t mn = first_of_set ? 0x7fffffff : c->min_len, mx = first_of_set ? 0 : c->max_len;    // running over the set
+    mn = 0x7fffffff; mx = 0;
     for (uint64_t i = 0; i < rd->nreads; i++) {
         uint64_t L = rd->offsets[i + 1] - rd->offsets[i];
         if (L >= 0x7fffffffull) throw LeonError(LEON_E_ARG, "read longer than 2^31-1");
         if ((int32_t)L < mn) mn = (int32_t)L;
         if ((int32_t)L > mx) mx = (int32_t)L;
     }
-    c->min_len = mn; c->max_len = mx;
-    c->qsizes.clear();
-    if (with_quals) {
-        uint64_t rpb = (uint64_t)c->opts.reads_per_block;
+    qsizes.clear();
+    if (with_quals)
         for (uint64_t r0 = 0; r0 < rd->nreads; r0 += rpb) {
             uint64_t r1 = std::min(rd->nreads, r0 + rpb);
-            c->qsizes.push_back(rd->offsets[r1] - rd->offsets[r0] + (r1 - r0));
+            qsizes.push_back(rd->offsets[r1] - rd->offsets[r0] + (r1 - r0));
         }
+}
+
+static void batch_check(const leon_reads *rd, bool with_quals)
+{
+    if (!rd || !rd->offsets || (rd->nreads && !rd->bases)) throw LeonError(LEON_E_ARG, "null read batch");
+    if (rd->offsets[0] != 0) throw LeonError(LEON_E_ARG, "a batch's offsets must start at 0");
+    if (with_quals && !rd->quals) throw LeonError(LEON_E_ARG, "has_qual set but the batch has no qualities");
+}
+
+// leon_stream_prefetch: the NEXT batch on its way into the spare read buffers while the current one is being processed
+static void stream_prefetch(leon_ctx *c, const leon_reads *rd, bool with_quals)
+{
+    batch_check(rd, with_quals);
+    if (!c->st_copy) {
+        CUDA_TRY(cudaStreamCreateWithFlags(&c->st_copy, cudaStreamNonBlocking));
+        CUDA_TRY(cudaEventCreateWithFlags(&c->ev_copy, cudaEventDisableTiming));
     }
-    CUDA_TRY(cudaStreamSynchronize(c->st));
+    if (c->pf_valid) CUDA_TRY(cudaEventSynchronize(c->ev_copy));       // an unused prefetch is simply replaced
+    const uint64_t nbases = rd->offsets[rd->nreads];
+    c->d_bases_next.reserve(nbases + 128);
+    c->d_offsets_next.reserve((rd->nreads + 1) * 8);
+    CUDA_TRY(cudaMemcpyAsync(c->d_bases_next.p, rd->bases, nbases, cudaMemcpyHostToDevice, c->st_copy));
+    CUDA_TRY(cudaMemcpyAsync(c->d_offsets_next.p, rd->offsets, (rd->nreads + 1) * 8, cudaMemcpyHostToDevice, c->st_copy));
+    if (with_quals) {
+        c->d_quals_next.reserve(nbases + 128);
+        CUDA_TRY(cudaMemcpyAsync(c->d_quals_next.p, rd->quals, nbases, cudaMemcpyHostToDevice, c->st_copy));
+    }
+    CUDA_TRY(cudaEventRecord(c->ev_copy, c->st_copy));
+    batch_host_scan(rd, (uint64_t)c->opts.reads_per_block, with_quals, c->pf_min, c->pf_max, c->pf_qsizes);   // while the copies run
+    c->pf_reads = *rd;
+    c->pf_quals = with_quals;
+    c->pf_valid = true;
+}
+
+// One batch of the streaming path into the read buffers (or the prefetched copy of it swapped in); the caller's buffers
+// are free again on return.
+static void stream_upload(leon_ctx *c, const leon_reads *rd, bool with_quals, bool first_of_set)
+{
+    batch_check(rd, with_quals);
+    c->nreads = rd->nreads;
+    c->nbases = rd->offsets[rd->nreads];
+    int32_t bmn, bmx;
+    const bool hit = c->pf_valid && c->pf_reads.bases == rd->bases && c->pf_reads.offsets == rd->offsets && c->pf_reads.nreads == rd->nreads &&
+                     (!with_quals || (c->pf_quals && c->pf_reads.quals == rd->quals));
+    if (hit) {
+        CUDA_TRY(cudaEventSynchronize(c->ev_copy));
+        std::swap(c->d_bases.p, c->d_bases_next.p); std::swap(c->d_bases.cap, c->d_bases_next.cap);
+        std::swap(c->d_offsets.p, c->d_offsets_next.p); std::swap(c->d_offsets.cap, c->d_offsets_next.cap);
+        if (with_quals) { std::swap(c->d_quals.p, c->d_quals_next.p); std::swap(c->d_quals.cap, c->d_quals_next.cap); }
+        bmn = c->pf_min; bmx = c->pf_max;
+        c->qsizes.swap(c->pf_qsizes);
+        c->pf_valid = false;
+    } else {
+        c->d_bases.reserve(c->nbases + 128);
+        c->d_offsets.reserve((c->nreads + 1) * 8);
+        CUDA_TRY(cudaMemcpyAsync(c->d_bases.p, rd->bases, c->nbases, cudaMemcpyHostToDevice, c->st));
+        CUDA_TRY(cudaMemcpyAsync(c->d_offsets.p, rd->offsets, (c->nreads + 1) * 8, cudaMemcpyHostToDevice, c->st));
+        if (with_quals) {
+            c->d_quals.reserve(c->nbases + 128);
+            CUDA_TRY(cudaMemcpyAsync(c->d_quals.p, rd->quals, c->nbases, cudaMemcpyHostToDevice, c->st));
+        }
+        batch_host_scan(rd, (uint64_t)c->opts.reads_per_block, with_quals, bmn, bmx, c->qsizes);
+        CUDA_TRY(cudaStreamSynchronize(c->st));
+    }
+    c->min_len = first_of_set ? bmn : std::min(c->min_len, bmn);        // running over the set
+    c->max_len = first_of_set ? bmx : std::max(c->max_len, bmx);
 }
 
 template <typename K> static void stream_count_begin(leon_ctx *c, const leon_stream_plan *plan, uint32_t *npasses_out)
@@ -1966,6 +2025,15 @@ int leon_count(leon_ctx *c, const leon_reads *batch, int last)
     user_stream_in(c);
     if (c->opts.kmer_size <= 31) stream_count_batch<uint64_t>(c, batch, last); else stream_count_batch<u128>(c, batch, last);
     user_stream_out(c);
+    LB_API_END(c)
+}
+
+int leon_stream_prefetch(leon_ctx *c, const leon_reads *next_batch, int with_quals)
+{
+    if (!c || !next_batch) return LEON_E_ARG;
+    LB_API_BEGIN
+    CUDA_TRY(cudaSetDevice(c->opts.device));
+    stream_prefetch(c, next_batch, with_quals != 0 && c->opts.has_qual);
     LB_API_END(c)
 }
 
