@@ -356,6 +356,21 @@ typedef struct leon_file_reads {
 int  leon_read_file(const char *path, int want_quals, int want_headers, leon_file_reads **out);
 void leon_file_reads_free(leon_file_reads *reads);
 
+/* NO COUNTERPART IN THE REFERENCE.  An entry point that allocates nothing, for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it): the
+ * k-mer slot scan of the counting stage.  d_offsets: DEVICE pointer to nreads + 1 read offsets (as leon_reads.offsets);
+ * d_koff: DEVICE pointer to nreads + 1 values, d_koff[r] = number of k-mer slots (max(L - k + 1, 0) per read) of the reads
+ * before r, d_koff[nreads] = their total -- what leon_upload + leon_count_resident compute as their first step
+ * (leon_debug_fetch "koff").  The work is enqueued on `stream` (a cudaStream_t, NULL = default stream) of `device`.
+ * The scan's scratch (tile sums) is a static device array of 64 KB per GPU, which bounds a call to
+ * LEON_NOALLOC_MAX_READS reads: more is refused with LEON_E_OVERFLOW (message via leon_last_error(NULL)).  The call makes
+ * no cudaMalloc / cudaFree / allocating library call; the first call on a device looks the array's address up once
+ * (cudaGetSymbolAddress), so make one call outside a capture.  Every call on a device shares the array: calls that overlap
+ * on the GPU (different streams without ordering) race. */
+#define LEON_NOALLOC_MAX_READS (1ull << 24)
+int leon_kmer_offsets_noalloc(int32_t device, const uint64_t *d_offsets, uint64_t nreads, int32_t kmer_size,
+                              uint64_t *d_koff, void *stream);
+
 /* Test hooks (parity tests only): Bloom queries on the device filter for host-provided forward k-mers.
  * kmers: n x (lo, hi) u64 pairs.  out4[i] = BloomNeighborCoherent::contains4 mask (COL Bloom.hpp:645-798),
  * out1[i] = contains() of the canonical form (Bloom.hpp:597-642). */

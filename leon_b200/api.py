@@ -15,7 +15,7 @@ ABI_SYMBOLS = [
     "leon_comm_batch_reads", "leon_debug_bloom_query", "leon_debug_hashes", "leon_debug_fetch", "leon_write_container",
     "leon_headers_encode", "leon_headers_free", "leon_compress_file", "leon_decompress_file", "leon_read_file", "leon_file_reads_free",
     "leon_decode_dna", "leon_decode_dna_device", "leon_decompress_file_device", "leon_decoded_block", "leon_decoded_free", "leon_headers_decode",
-    "leon_container_open", "leon_container_close", "leon_container_has", "leon_container_dataset", "leon_container_attr",
+    "leon_kmer_offsets_noalloc", "leon_container_open", "leon_container_close", "leon_container_has", "leon_container_dataset", "leon_container_attr",
 ]
 
 
@@ -161,6 +161,7 @@ def load_library(path=LIB_PATH):
     L.leon_comm_batch_reads.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
     L.leon_debug_bloom_query.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.c_void_p]
     L.leon_debug_hashes.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+    L.leon_kmer_offsets_noalloc.argtypes = [C.c_int32, C.c_void_p, C.c_uint64, C.c_int32, C.c_void_p, C.c_void_p]
     L.leon_debug_fetch.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
     L.leon_write_container.argtypes = [C.c_char_p, C.POINTER(Result), C.POINTER(ContainerInfo)]
     L.leon_headers_encode.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int32, C.c_int32, C.POINTER(C.POINTER(HeaderStream))]

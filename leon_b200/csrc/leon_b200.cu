@@ -20,6 +20,7 @@
 #include <atomic>
 #include <chrono>
 #include <deque>
+#include <mutex>
 
 namespace {
 
@@ -2345,3 +2346,67 @@ int leon_debug_fetch(leon_ctx *c, const char *name, void *dst, uint64_t cap, uin
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------------
+// Entry point that allocates nothing (no counterpart in the reference).
+// Some callers cannot call cudaMalloc: code under CUDA graph capture, tight serving loops, harnesses that forbid it.
+// leon_kmer_offsets_noalloc is the k-mer slot scan of the counting stage (count_koff above: koff[r] = number of k-mers of
+// the reads before r, K/Model.hpp:725-764 gives L - k + 1 windows per read) with the scratch of the device-wide scan -- the
+// tile sums -- in a file-scope device array instead of a grow-only DevBuf.  The array is shared by every call on a device
+// and keeps the last call's contents; nothing in it needs clearing, because every slot a call reads (tile sums 0..nb-1 and
+// the total behind them) is written by that same call first.  Calls that overlap on one GPU race on it.
+// ------------------------------------------------------------------------------------------------------------
+namespace {
+
+constexpr uint64_t NOALLOC_MAX_READS = LEON_NOALLOC_MAX_READS;                             // 2^24 reads per call
+constexpr uint64_t NOALLOC_MAX_TILES = (NOALLOC_MAX_READS + lbscan::TILE - 1) / lbscan::TILE;
+// tile sums + the grand total: 8193 x 8 bytes = 64 KB, held by every GPU that loads the library until exit
+static __device__ __align__(256) unsigned long long g_noalloc_scan_scratch[NOALLOC_MAX_TILES + 1];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+uint64_t *g_noalloc_ptr[NOALLOC_MAX_DEVICES];       // device address of the array on every device (set-up: once per device)
+std::mutex g_noalloc_mu;
+
+}  // namespace
+
+extern "C" int leon_kmer_offsets_noalloc(int32_t device, const uint64_t *d_offsets, uint64_t nreads, int32_t kmer_size,
+                                         uint64_t *d_koff, void *stream)
+{
+    if (!d_offsets || !d_koff) { g_create_error = "leon_kmer_offsets_noalloc: null argument"; return LEON_E_ARG; }
+    if (kmer_size < 2 || kmer_size > 63) { g_create_error = "leon_kmer_offsets_noalloc: kmer_size must be in [2,63]"; return LEON_E_ARG; }
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES) { g_create_error = "leon_kmer_offsets_noalloc: bad device ordinal"; return LEON_E_ARG; }
+    if (nreads > NOALLOC_MAX_READS) {
+        g_create_error = "leon_kmer_offsets_noalloc: " + std::to_string(nreads) + " reads exceed the static scratch of this entry point (maximum " +
+                         std::to_string(NOALLOC_MAX_READS) + " reads per call); split the set or use leon_upload + leon_count_resident";
+        return LEON_E_OVERFLOW;
+    }
+    try {
+        CUDA_TRY(cudaSetDevice(device));
+        uint64_t *partials = nullptr;
+        {   // In host code the array's name is a host-side stand-in, not a device address: ask the runtime for the address on
+            // THIS device, once, with the device current.
+            std::lock_guard<std::mutex> g(g_noalloc_mu);
+            if (!g_noalloc_ptr[device]) {
+                void *p = nullptr;
+                CUDA_TRY(cudaGetSymbolAddress(&p, g_noalloc_scan_scratch));
+                g_noalloc_ptr[device] = (uint64_t *)p;
+            }
+            partials = g_noalloc_ptr[device];
+        }
+        cudaStream_t st = (cudaStream_t)stream;
+        uint64_t nb = (nreads + lbscan::TILE - 1) / lbscan::TILE;
+        if (nb == 0) nb = 1;
+        uint64_t *total = partials + nb;
+        LaunchCounter lc;
+        lbcount::NkIn in{d_offsets, kmer_size};
+        lbcount::NkOut out{d_koff};
+        LB_LAUNCH(lc, (lbscan::k_reduce<uint64_t, lbcount::NkIn>), (unsigned)nb, lbscan::THREADS, 0, st, nreads, in, partials);
+        LB_LAUNCH(lc, (lbscan::k_scan_partials<uint64_t>), 1, lbscan::THREADS, 0, st, partials, nb, total);
+        LB_LAUNCH(lc, (lbscan::k_apply<uint64_t, lbcount::NkIn, lbcount::NkOut>), (unsigned)nb, lbscan::THREADS, 0, st, nreads, in, partials, out);
+        CUDA_TRY(cudaMemcpyAsync(d_koff + nreads, total, 8, cudaMemcpyDeviceToDevice, st));      // koff[nreads] = number of k-mer slots
+    } catch (const LeonError &e) {
+        g_create_error = e.msg;
+        return e.code;
+    }
+    return LEON_OK;
+}
