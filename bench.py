@@ -52,7 +52,12 @@ def parse_args():
     ap.add_argument("--phases", action="store_true", help="print per-phase / per-kernel device times to stderr")
     ap.add_argument("--no-large", action="store_true", help="skip the configs[3] streaming measurement (extra key `large`)")
     ap.add_argument("--large-reads", type=int, default=0, help="debug: reads of the configs[3]-shaped set (genome scaled with it)")
-    ap.add_argument("--only-large", action="store_true", help="debug: only the configs[3] measurement")
+    ap.add_argument("--only-large", action="store_true", help="only the streaming measurement (configs[3], or --large-shape configs4)")
+    ap.add_argument("--large-shape", default="configs3", choices=["configs3", "configs4"],
+                    help="configs4: a 1/20 sample of BASELINE configs[4] (k = 63, lossless, 30 M x 150 bp from a 150 Mbp genome)")
+    ap.add_argument("--large-genome", type=int, default=0, help="genome length of the streaming measurement (default: scaled with the reads)")
+    ap.add_argument("--large-batch-chunks", type=int, default=32, help="chunks of 250 000 reads per rank and streaming batch")
+    ap.add_argument("--large-passes", type=int, default=0, help="counting passes of the streaming measurement (0 = from free memory)")
     return ap.parse_args()
 
 
@@ -456,9 +461,21 @@ def measure_large(args, torch, dist, world, rank, local_rank):
     import leon_b200
     from leon_b200 import synth
     name = "configs[3]"
-    c = W.CONFIGS[name]
+    c = dict(W.CONFIGS[name])
+    kmer, lossless = KMER, False
+    if args.large_shape == "configs4":
+        # BASELINE configs[4] (3 Gbp, 600 M x 150 bp FASTQ at 30x, k = 63, lossless qualities, streamed) at 1/20 of its size by
+        # default: same read shape and coverage, genome and read count scaled together
+        name = "configs[4]"
+        frac = 20
+        c.update(genome=3_000_000_000 // frac, reads=600_000_000 // frac, gseed=5, rseed=6,
+                 text="configs[4] at 1/%d scale: %d Mbp random genome, 150 bp FASTQ reads at 30x, N bases and N runs, indels, k=63, "
+                      "lossless qualities, streamed in batches" % (frac, 3000 // frac))
+        kmer, lossless = 63, True
     total_reads = args.large_reads if args.large_reads else c["reads"]
     genome_len = c["genome"] if not args.large_reads else max(1_000_000, int(c["genome"] * total_reads / c["reads"]))
+    if args.large_genome:
+        genome_len = args.large_genome
     S = W.C3_CHUNK
     nchunks = (total_reads + S - 1) // S
     mine = [ch for ch in range(nchunks) if ch % world == rank]
@@ -483,13 +500,27 @@ def measure_large(args, torch, dist, world, rank, local_rank):
     gen_s = time.perf_counter() - t0
     local_reads = len(lens)
     # batches of M chunks per rank; every rank makes the same number of calls (empty batches at the end where it has run out)
-    M = 32
+    M = max(1, args.large_batch_chunks)
     max_chunks = (nchunks + world - 1) // world
     ncalls = max(1, (max_chunks + M - 1) // M)
     batches = [(min(local_reads, i * M * S), min(local_reads, (i + 1) * M * S)) for i in range(ncalls)]
 
-    eng = leon_b200.Leon(kmer_size=KMER, reads_per_block=RPB, has_qual=True, device=local_rank, anchor_batch=S,
+    torch.cuda.synchronize()
+    free_start = torch.cuda.mem_get_info()[0]
+    eng = leon_b200.Leon(kmer_size=kmer, reads_per_block=RPB, has_qual=True, lossless=lossless, device=local_rank, anchor_batch=S,
                          qual_zlib_on_device=True, skip_qual_text=True, skip_read_arrays=True)
+
+    class MemSampler(threading.Thread):      # peak device memory of this rank while the runs are going
+        def __init__(self):
+            super().__init__(daemon=True)
+            self.min_free, self.stop = free_start, False
+
+        def run(self):
+            while not self.stop:
+                self.min_free = min(self.min_free, torch.cuda.mem_get_info()[0])
+                time.sleep(0.01)
+    mem = MemSampler()
+    mem.start()
     stream = torch.cuda.current_stream()
     eng.set_stream(stream.cuda_stream)
     if world > 1:
@@ -505,7 +536,7 @@ def measure_large(args, torch, dist, world, rank, local_rank):
     def one_run(keep):
         phases = {}
         t = time.perf_counter()
-        npass = eng.count_begin(local_reads, nb, 0)
+        npass = eng.count_begin(local_reads, nb, args.large_passes)
         for _ in range(npass):
             for i, (b, o, _q) in enumerate(cuts):
                 if i + 1 < len(cuts):
@@ -570,6 +601,13 @@ def measure_large(args, torch, dist, world, rank, local_rank):
         n_in = min(S, total_reads - ch * S)
         gids += [ch * bpc + j for j in range((n_in + RPB - 1) // RPB)]
     assert len(gids) == len(per), (len(gids), len(per))
+    mem.stop = True
+    mem.join()
+    peak_bytes = int(free_start - mem.min_free)
+    if world > 1:
+        t = torch.tensor([peak_bytes], device="cuda", dtype=torch.int64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        peak_bytes = int(t.item())
     mine_out = dict(gids=gids, per=per, bloom=hashlib.sha256(res["bloom"]).hexdigest() if rank == 0 else None,
                     dict=hashlib.sha256(res["anchors_dict"]).hexdigest() if rank == 0 else None, anchors=res["anchor_count"])
     allo = [mine_out]
@@ -590,7 +628,7 @@ def measure_large(args, torch, dist, world, rank, local_rank):
               "dna_nbytes": int(bs[0::2].sum()),
               "dna_cc": hashlib.sha256(b"".join(table[b][0] for b in order)).hexdigest(),
               "qual_text_cc": hashlib.sha256(b"".join(table[b][1] for b in order)).hexdigest()}
-    gold = golden_digest(name) if total_reads == c["reads"] else None
+    gold = golden_digest(name) if (total_reads == c["reads"] and name == "configs[3]") else None
     ok, diff = None, None
     if gold is not None and "dna_cc" in gold:
         keys = ["bloom", "anchors_dict", "blocksizes", "dna_cc", "qual_text_cc"]
@@ -601,6 +639,8 @@ def measure_large(args, torch, dist, world, rank, local_rank):
             "api": "streaming entry points (leon_count_begin / leon_count / leon_count_finish / leon_bloom_build / leon_encode_block / "
                    "leon_encode_finish), host buffers in, host buffers out: this is an end-to-end figure",
             "value": value, "unit": "reads/s", "ms_per_step": ms, "steps": steps, "n_gpus": world, "count_passes": npass,
+            "kmer_size": kmer, "quality": "lossless" if lossless else "lossy", "reads": total_reads, "genome": genome_len,
+            "peak_device_bytes_per_rank": peak_bytes, "host_bytes_resident_per_rank": int(2 * nb),
             "batches_per_rank": ncalls, "reads_per_batch_per_rank": M * S,
             "input_gbs": value * c["read_len"] * 2 / 1e9, "phases_s_rank0": phases, "anchors": allo[0]["anchors"],
             "cutoff": cnt["cutoff"], "solid": cnt["nb_solids_cutoff"], "bloom_bytes": int(len(res["bloom"])),

@@ -99,7 +99,9 @@ static void test_file(const std::string &leon_in, const std::string &decoded, bo
 }
 
 int main(int argc, char **argv) {
-    setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);     // the path uses more streams than the default 8 hardware queues
+    // CUDA_DEVICE_MAX_CONNECTIONS is left at its default here: 32 hardware queues take 25 ms off the GPU path of a run but add
+    // 0.5-1 s to the creation of the CUDA context, which a one-shot process pays every time (measured); long-lived
+    // hosts (the Python package) set 32.
     const auto t_start = std::chrono::steady_clock::now();
     leon_file_opts o;
     memset(&o, 0, sizeof o);

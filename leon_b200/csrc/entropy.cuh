@@ -530,16 +530,25 @@ __global__ void __launch_bounds__(32) k_range_encode(const uint4 *__restrict__ r
                 rc_step_spec(low, rp, on, rmin, t2, s2.x, s3.y);
                 rc_step_spec(low, rp, on, rmin, t3, s3.x, s4.y);
                 if (__builtin_expect(rmin < (1u << 16), 0)) {
-                    // a step needed more than one byte or a range clamp: recode the group with the generic step
+                    // a step needed more than one byte or a range clamp (5.5 % of the groups): recode the group from its start
+                    // state, the common steps again with the straight-line step, only the rare ones with the generic step
                     low = low_g;
-                    range = rp_g - s0.y;
+                    rp = rp_g;
                     on = on_g;
 #pragma unroll 1
                     for (int i = j; i < j + 4; i++) {
-                        const uint2 sx = lds64(ss + 8 * i);
-                        rc_step_any(low, range, lds128(sr + 16 * i), sx.x, sx.y, on);
+                        const uint2 sx = lds64(ss + 8 * i), sn = lds64(ss + 8 * i + 8);
+                        const uint4 t = lds128(sr + 16 * i);
+                        uint64_t l2 = low, r2 = rp;
+                        uint32_t o2 = on, rm = 0xffffffffu;
+                        rc_step_spec(l2, r2, o2, rm, t, sx.x, sn.y);
+                        if (rm >= (1u << 16)) { low = l2; rp = r2; on = o2; }
+                        else {
+                            range = rp - sx.y;
+                            rc_step_any(low, range, t, sx.x, sx.y, on);
+                            rp = range + sn.y;
+                        }
                     }
-                    rp = range + s4.y;
                 }
                 t0 = t4;
                 s0 = s4;

@@ -1056,7 +1056,18 @@ void sb_finish(leon_ctx *c, uint64_t g)
         const uint64_t gb = sb.first_block + b;
         const uint64_t r0 = b * rpb, r1 = std::min<uint64_t>(R, r0 + rpb);
         if (sz[b] > descs[b].out_cap) throw LeonError(LEON_E_OVERFLOW, "range coder output exceeded its capacity bound");
-        if (c->dna_nbytes + sz[b] > c->h_dna.cap) throw LeonError(LEON_E_OVERFLOW, "sequence stream larger than the host payload buffer");
+        if (c->dna_nbytes + sz[b] > c->h_dna.cap) {
+            // the payload outgrew the pinned buffer (sized for typical reads): the copies issued so far must have landed, then
+            // a buffer twice as large takes over
+            for (uint64_t e = 0; e < g; e++)
+                if (c->sbs[e].fetched) CUDA_TRY(cudaEventSynchronize(c->sbs[e].ev_coded));
+            CUDA_TRY(cudaStreamSynchronize(sb.rc_stream));
+            PinBuf bigger;
+            bigger.reserve(2 * (c->dna_nbytes + sz[b]) + (1u << 20));
+            memcpy(bigger.p, c->h_dna.p, c->dna_nbytes);
+            std::swap(c->h_dna.p, bigger.p); std::swap(c->h_dna.cap, bigger.cap);
+            dna = c->h_dna.as<uint8_t>();
+        }
         bs[2 * gb] = sz[b];
         bs[2 * gb + 1] = r1 - r0;
         if (sz[b]) CUDA_TRY(cudaMemcpyAsync(dna + c->dna_nbytes, sb.d_outall.as<uint8_t>() + descs[b].out_base, sz[b], cudaMemcpyDeviceToHost, sb.rc_stream));
@@ -1431,8 +1442,9 @@ template <typename K> void encode_batch(leon_ctx *c)
         sb.kt.reset();
         sb.ensure();
     }
-    // host payload: a coded read takes at most a few bits per base plus its varints
-    c->h_dna.reserve(c->nbases / 2 + 32 * R + 1024 * c->nblocks + 4096);
+    // host payload: sized for typical reads (4-7 bytes per read measured on the BASELINE shapes); sb_finish grows it on demand
+    // (pinned memory is slow to allocate: 377 MB for the worst case of configs[2] cost more than the GPU path of a CLI run)
+    c->h_dna.reserve(c->nbases / 16 + 8 * R + 1024 * c->nblocks + 4096);
     c->h_bs.reserve(c->nblocks * 16 + 16);
     c->wk.kt.reset();
     c->sb_pub.store(0);

@@ -24,11 +24,11 @@ KEYS = ("cutoff", "nb_solids_cutoff", "nb_solid_total", "bloom_bits", "anchor_co
 ARRS = ("histogram", "bloom", "anchors_dict", "blocksizes", "dna", "anchor_pos")
 
 
-def run_case(rank, world, k, L, nreads, rpb, fastq, seed, genome, stream=0, passes=0):
+def run_case(rank, world, k, L, nreads, rpb, fastq, seed, genome, stream=0, passes=0, lossless=False):
     from oracle import oracle_py as O
     g = synth.make_genome(genome, seed)
     bases, offs, quals = synth.sample_reads(g, nreads, L, seed + 100, n_rate=0.0005, with_quals=fastq)
-    eng = leon_b200.Leon(kmer_size=k, reads_per_block=rpb, has_qual=fastq, device=rank, qual_zlib_on_device=fastq)
+    eng = leon_b200.Leon(kmer_size=k, reads_per_block=rpb, has_qual=fastq, lossless=lossless, device=rank, qual_zlib_on_device=fastq)
     uid = [leon_b200.Leon.comm_unique_id() if rank == 0 else None]
     dist.broadcast_object_list(uid, src=0)
     eng.comm_init(rank, world, uid[0])
@@ -47,7 +47,7 @@ def run_case(rank, world, k, L, nreads, rpb, fastq, seed, genome, stream=0, pass
     ok = True
     if rank == 0:
         m = shard.merge_results(allr, nreads, world, S, rpb)
-        ref = O.compress(bases, offs, quals, kmer_size=k, reads_per_block=rpb)
+        ref = O.compress(bases, offs, quals, kmer_size=k, reads_per_block=rpb, lossless=lossless)
         for key in KEYS:
             if m[key] != ref[key]:
                 ok = False
@@ -90,6 +90,7 @@ def main():
         (31, 100, 130500, 1000, True, 5, 40000, 3, 1),    # streaming: 3 rounds per call, one counting pass
         (31, 100, 120000, 2000, False, 6, 60000, 1, 3),   # streaming: one round per call, three counting passes
         (63, 150, 60000, 1500, True, 7, 50000, 2, 2),
+        (63, 150, 90000, 1500, True, 8, 70000, 2, 3, True),   # configs[4] shape: k = 63, lossless, streamed, 3 counting passes
     ]
     ok = True
     for c in cases:
