@@ -199,8 +199,9 @@ def cpu_baseline_block(name, reads):
             walls = []
             for _ in range(2):
                 t0 = time.perf_counter()
+                env = {k: v for k, v in os.environ.items() if k != "CUDA_DEVICE_MAX_CONNECTIONS"}     # what a user's shell has
                 r = subprocess.run([cli, "-file", path, "-c", "-kmer-size", str(KMER), "-verbose", "0", "-out", out] + flags,
-                                   stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+                                   stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env)
                 walls.append(time.perf_counter() - t0)
                 if r.returncode != 0:
                     raise RuntimeError(r.stdout[-300:])
@@ -559,6 +560,11 @@ def measure_large(args, torch, dist, world, rank, local_rank):
                 outs.append(bo)
         res = eng.encode_finish(copy=keep)
         phases["encode_s"] = time.perf_counter() - t
+        tm = eng.timings()
+        # the anchor dictionary is ONE never-reset range coder (C/Leon.cpp:1245-1260): a serial chain on a host thread of rank 0
+        # that runs beside the whole encoding pass; dict_wait = how long the pass then still waited for it
+        phases["dict_host_s"] = tm["dict_host_ms"] / 1e3
+        phases["dict_wait_s"] = tm["dict_wait_ms"] / 1e3
         return npass, cnt, outs, res, phases
 
     def barrier():
@@ -755,8 +761,8 @@ def main_b200(args):
         "data": "synthetic",
         "config": config_block(name, m["total_reads"]),
         "parallelism": "1 process per GPU" if world == 1 else
-        "%d ranks, reads dealt in rounds of %d x %d; NCCL: k-mer all-to-all by hash owner, Bloom all-gather + OR, "
-        "anchor candidates all-gathered per batch" % (world, world, m["S"]),
+        "%d ranks, reads dealt in rounds of %d x %d; NCCL: k-mer all-to-all by hash owner, Bloom OR as reduce-scatter + "
+        "all-gather, anchor candidates all-gathered per batch" % (world, world, m["S"]),
         "input_gbs": m["value"] * read_len * (2 if W.CONFIGS[name]["fastq"] else 1) / 1e9,
         "e2e": {"value": m["e2e_value"], "unit": "reads/s", "h2d_bytes_per_step": m["h2d"], "d2h_bytes_per_step": m["d2h"],
                 "ms_per_step": m["e2e_ms"], "input_gbs": m["e2e_value"] * read_len * (2 if W.CONFIGS[name]["fastq"] else 1) / 1e9},

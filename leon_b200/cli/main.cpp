@@ -13,7 +13,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <string>
+#include <thread>
 #include <sys/stat.h>
 
 #include "../../include/leon_b200.h"
@@ -35,6 +37,7 @@ static void usage() {
             "  -out FILE      output file (default: the reference's naming)\n"
             "  -device N      CUDA device (default 0)\n"
             "  -gpu-decode    with -d: decode the sequence stream on the GPU (one warp per block)\n"
+            "  -host-decode   with -d: decode the sequence stream on host threads (default: chosen from the number of blocks)\n"
             "  -stream-reads N  feed the GPU batches of N reads (streaming path; default: whole set when it fits the device)\n"
             "  -count-passes N  streaming: number of k-mer counting passes (default: from the free device memory)\n");
 }
@@ -106,7 +109,7 @@ int main(int argc, char **argv) {
     leon_file_opts o;
     memset(&o, 0, sizeof o);
     std::string in, out;
-    bool compress = false, decompress = false, gpu_decode = false, test = false;
+    bool compress = false, decompress = false, gpu_decode = false, host_decode = false, test = false;
     int verbose = 1;
     if (argc > 1 && (!strcmp(argv[1], "-version") || !strcmp(argv[1], "-v"))) {     // src/main.cpp:38-41
         printf("* Leon on the B200 path (leon_b200, ABI %d); container format of Leon 1.1.0\n", leon_b200_abi_version());
@@ -134,6 +137,7 @@ int main(int argc, char **argv) {
         else if (a == "-out") out = value("-out");
         else if (a == "-device") o.device = atoi(value("-device"));
         else if (a == "-gpu-decode") gpu_decode = true;
+        else if (a == "-host-decode") host_decode = true;
         else if (a == "-test-file") test = true;
         else if (a == "-verbose") verbose = atoi(value("-verbose"));
         else if (a == "-h" || a == "-help" || a == "--help") { usage(); return EXIT_SUCCESS; }
@@ -147,8 +151,40 @@ int main(int argc, char **argv) {
     auto seconds = [&]() { return std::chrono::duration<double>(std::chrono::steady_clock::now() - t_start).count(); };
     leon_file_stats s;
     if (decompress) {
+        bool auto_choice = false;
+        if (!gpu_decode && !host_decode) {
+            // Default of -d, from the measured cost of the two decoders (profiles/r1g_decode_bench_*.json, B200 + 16
+            // host cores): the device kernel runs one warp per block, all blocks side by side, ~50 us per read of the LARGEST block
+            // whatever the number of blocks, plus ~1 s to bring up a CUDA context in a fresh process; the host threads need ~5.6 us
+            // per read and thread.  92 blocks of 50000 reads: host (1.6 s vs 3.5 s); 920 blocks of 5000: device (0.3 + 1 s vs 1.6 s).
+            leon_container *ct = nullptr;
+            if (leon_container_open(in.c_str(), &ct) == LEON_OK) {
+                const uint8_t *bs = nullptr;
+                uint64_t nbytes = 0;
+                if (leon_container_dataset(ct, "leon/dna/blocksizes", &bs, &nbytes) == LEON_OK && nbytes >= 16) {
+                    const uint64_t nblocks = nbytes / 16;
+                    uint64_t total = 0, largest = 0;
+                    for (uint64_t b = 0; b < nblocks; b++) {
+                        uint64_t n;
+                        memcpy(&n, bs + 16 * b + 8, 8);
+                        total += n;
+                        if (n > largest) largest = n;
+                    }
+                    unsigned threads = o.nthreads > 0 ? (unsigned)o.nthreads : std::max(1u, std::thread::hardware_concurrency());
+                    const double t_dev = 1.0 + 50e-6 * (double)largest * (double)((nblocks + 4095) / 4096);
+                    const double t_host = 5.6e-6 * (double)total / threads;
+                    gpu_decode = t_dev < 0.8 * t_host;
+                    auto_choice = gpu_decode;
+                }
+                leon_container_close(ct);
+            }
+        }
         int rc = gpu_decode ? leon_decompress_file_device(in.c_str(), out.empty() ? nullptr : out.c_str(), o.nthreads, o.device, &s)
                             : leon_decompress_file(in.c_str(), out.empty() ? nullptr : out.c_str(), o.nthreads, &s);
+        if (rc == LEON_E_CUDA && auto_choice) {     // no usable device: the automatic choice (only) goes back to the host threads
+            gpu_decode = false;
+            rc = leon_decompress_file(in.c_str(), out.empty() ? nullptr : out.c_str(), o.nthreads, &s);
+        }
         if (rc) {
             fprintf(stderr, "EXCEPTION: %s\n", leon_last_error(nullptr));
             return EXIT_FAILURE;

@@ -190,6 +190,10 @@ struct leon_ctx {
     bool enc_partial_seen = false, stream_counting = false;
     uint64_t stream_reads_seen = 0;
     leon_block_out last_block_out = {};
+    // chunked upload of the one-shot path (do_upload): read ranges of the pieces, their events ([8] = qualities)
+    std::vector<std::pair<uint64_t, uint64_t>> up_chunks;
+    cudaEvent_t ev_up[10] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // [9] = offsets
+    bool up_quals_pending = false;
     // leon_stream_prefetch: spare read buffers and what is known about the batch in them
     DevBuf d_bases_next, d_offsets_next, d_quals_next;
     cudaStream_t st_copy = nullptr;
@@ -233,7 +237,12 @@ unsigned warp_grid(uint64_t nwarps_wanted)
     return (unsigned)blocks;
 }
 
-void do_upload(leon_ctx *c, const leon_reads *rd)
+constexpr int UP_CHUNKS = 8;
+
+// chunked = the one-shot path from host buffers (leon_compress): the bases travel in UP_CHUNKS pieces on the copy stream and
+// k_extract starts on each piece as it lands (count_add); the qualities follow the bases on the same stream, so the two copies
+// do not share the link, and k_quals waits for them on its own stream.
+void do_upload(leon_ctx *c, const leon_reads *rd, bool chunked = false)
 {
     if (!rd || !rd->offsets || (rd->nreads && !rd->bases)) throw LeonError(LEON_E_ARG, "leon_upload: null read set");
     if (rd->nreads >= 0xfffffff0ull) throw LeonError(LEON_E_ARG, "leon_upload: more than 2^32-16 reads in one set");
@@ -243,14 +252,44 @@ void do_upload(leon_ctx *c, const leon_reads *rd)
     CUDA_TRY(cudaEventRecord(c->ev[0], c->st));
     c->d_bases.reserve(c->nbases + 128);
     c->d_offsets.reserve((c->nreads + 1) * 8);
-    CUDA_TRY(cudaMemcpyAsync(c->d_bases.p, rd->bases, c->nbases, cudaMemcpyHostToDevice, c->st));
-    CUDA_TRY(cudaMemcpyAsync(c->d_offsets.p, rd->offsets, (c->nreads + 1) * 8, cudaMemcpyHostToDevice, c->st));
-    if (c->opts.has_qual) {
-        // Qualities are first needed by k_quals on the third stream, long after counting has started: their copy goes
-        // there, beside the counting kernels, instead of in front of them (one-shot calls from pinned memory: -9 ms).
-        c->d_quals.reserve(c->nbases + 128);
-        CUDA_TRY(cudaStreamWaitEvent(c->st3, c->ev[0], 0));
-        CUDA_TRY(cudaMemcpyAsync(c->d_quals.p, rd->quals, c->nbases, cudaMemcpyHostToDevice, c->st3));
+    c->up_chunks.clear();
+    c->up_quals_pending = false;
+    if (c->opts.has_qual) c->d_quals.reserve(c->nbases + 128);
+    static const uint64_t up_chunked = env_u64("LEON_B200_UPLOAD_CHUNKED", 1);
+    if (chunked && up_chunked && c->nreads >= 65536) {
+        if (!c->st_copy) {
+            CUDA_TRY(cudaStreamCreateWithFlags(&c->st_copy, cudaStreamNonBlocking));
+            CUDA_TRY(cudaEventCreateWithFlags(&c->ev_copy, cudaEventDisableTiming));
+        }
+        if (!c->ev_up[0])
+            for (int i = 0; i <= UP_CHUNKS + 1; i++) CUDA_TRY(cudaEventCreateWithFlags(&c->ev_up[i], cudaEventDisableTiming));
+        // the offsets FIRST and on the same stream as the rest: issued on the main stream they were measured to land only after
+        // everything queued on the copy stream (920 MB, 17 ms), holding up the whole counting stage
+        CUDA_TRY(cudaMemcpyAsync(c->d_offsets.p, rd->offsets, (c->nreads + 1) * 8, cudaMemcpyHostToDevice, c->st_copy));
+        CUDA_TRY(cudaEventRecord(c->ev_up[UP_CHUNKS + 1], c->st_copy));
+        CUDA_TRY(cudaStreamWaitEvent(c->st, c->ev_up[UP_CHUNKS + 1], 0));
+        const uint64_t per = ((c->nreads + UP_CHUNKS - 1) / UP_CHUNKS + 255) & ~255ull;       // whole 256-read tiles
+        int i = 0;
+        for (uint64_t r0 = 0; r0 < c->nreads; r0 += per, i++) {
+            const uint64_t r1 = std::min(c->nreads, r0 + per), b0 = rd->offsets[r0], b1 = rd->offsets[r1];
+            if (b1 > b0) CUDA_TRY(cudaMemcpyAsync(c->d_bases.as<uint8_t>() + b0, rd->bases + b0, b1 - b0, cudaMemcpyHostToDevice, c->st_copy));
+            CUDA_TRY(cudaEventRecord(c->ev_up[i], c->st_copy));
+            c->up_chunks.push_back({r0, r1});
+        }
+        if (c->opts.has_qual) {
+            CUDA_TRY(cudaMemcpyAsync(c->d_quals.p, rd->quals, c->nbases, cudaMemcpyHostToDevice, c->st_copy));
+            CUDA_TRY(cudaEventRecord(c->ev_up[UP_CHUNKS], c->st_copy));
+            c->up_quals_pending = true;
+        }
+    } else {
+        CUDA_TRY(cudaMemcpyAsync(c->d_bases.p, rd->bases, c->nbases, cudaMemcpyHostToDevice, c->st));
+        CUDA_TRY(cudaMemcpyAsync(c->d_offsets.p, rd->offsets, (c->nreads + 1) * 8, cudaMemcpyHostToDevice, c->st));
+        if (c->opts.has_qual) {
+            // Qualities are first needed by k_quals on the third stream, long after counting has started: their copy goes
+            // there, beside the counting kernels, instead of in front of them (one-shot calls from pinned memory: -9 ms).
+            CUDA_TRY(cudaStreamWaitEvent(c->st3, c->ev[0], 0));
+            CUDA_TRY(cudaMemcpyAsync(c->d_quals.p, rd->quals, c->nbases, cudaMemcpyHostToDevice, c->st3));
+        }
     }
     CUDA_TRY(cudaEventRecord(c->ev[1], c->st));
     // min / max read length for the metadata datasets (host side, offsets are already here)
@@ -401,8 +440,19 @@ template <typename K> void count_add(leon_ctx *c)
     if (c->count_npasses == 1) {
         if (c->keys_fill + nk > c->keys_cap) throw LeonError(LEON_E_OVERFLOW, "k-mer counting: more k-mers than the plan announced");
         K *keys = c->d_keys.as<K>() + c->keys_fill;
-        LB_TIMED(c->kt, "k_extract", st, LB_LAUNCH(c->lc, (k_extract<K>), cdiv_u(c->nreads, 256), 256, stage_bytes, st, c->d_bases.as<uint8_t>(),
-                  c->d_offsets.as<uint64_t>(), koff, c->nreads, k, keys, stage_bytes));
+        if (!c->up_chunks.empty()) {
+            // bases still arriving in pieces (do_upload, chunked): the k-mers of every piece as soon as it is there
+            for (size_t i = 0; i < c->up_chunks.size(); i++) {
+                const uint64_t r0 = c->up_chunks[i].first, r1 = c->up_chunks[i].second;
+                CUDA_TRY(cudaStreamWaitEvent(st, c->ev_up[i], 0));
+                LB_TIMED(c->kt, "k_extract", st, LB_LAUNCH(c->lc, (k_extract<K>), cdiv_u(r1 - r0, 256), 256, stage_bytes, st, c->d_bases.as<uint8_t>(),
+                          c->d_offsets.as<uint64_t>() + r0, koff + r0, r1 - r0, k, keys, stage_bytes));
+            }
+            c->up_chunks.clear();
+        } else {
+            LB_TIMED(c->kt, "k_extract", st, LB_LAUNCH(c->lc, (k_extract<K>), cdiv_u(c->nreads, 256), 256, stage_bytes, st, c->d_bases.as<uint8_t>(),
+                      c->d_offsets.as<uint64_t>(), koff, c->nreads, k, keys, stage_bytes));
+        }
         c->keys_fill += nk;
     } else {
         // all keys of the batch, then the ones of this pass appended to the pass buffer
@@ -694,70 +744,6 @@ namespace {
 // opts.dict_on_device = 1 runs it as a kernel instead (k_range_encode on the second stream); both produce the same bytes.
 constexpr uint64_t DICT_STAGE_SYMS = 1ull << 19;
 
-// One slice of records through the recurrence; same step as rc_step_spec (entropy.cuh): 0 or 1 output byte without a
-// data-dependent branch, the rare rest through the generic loop of RangeEncoder::encode.
-void dict_code_slice(const uint32_t *rec, const uint8_t *sh, uint64_t n, bool first, uint64_t &low, uint64_t &range,
-                     std::vector<uint8_t> &out)
-{
-    const uint64_t TOP = 1ull << 56, BOTTOM = 1ull << 48;
-    const size_t pos0 = out.size();
-    out.resize(pos0 + n * 2 + 64);          // the common step writes <= 1 byte per symbol; the rare path re-checks
-    uint8_t *op = out.data() + pos0;
-    const uint8_t *op_end = out.data() + out.size();
-    uint64_t j = 0;
-    if (first && n) {                       // first symbol: range = 2^64 - 1, range + inc needs 65 bits
-        const uint64_t m = ((uint64_t)rec[3] << 32) | rec[2];
-        const uint32_t s = sh[0];
-        const uint64_t q = (uint64_t)(((unsigned __int128)range * m + ((s & 0x80u) ? m : 0ull)) >> 64) >> (s & 63u);
-        low += (uint64_t)rec[0] * q;
-        range = q * (uint64_t)rec[1];
-        while ((low ^ (low + range)) < TOP || range < BOTTOM) {
-            if (range < BOTTOM && (low ^ (low + range)) >= TOP) range = (0 - low) & (BOTTOM - 1);
-            *op++ = (uint8_t)(low >> 56);
-            range <<= 8;
-            low <<= 8;
-        }
-        j = 1;
-    }
-    uint64_t rp = range + (j < n ? (sh[j] >> 7) : 0u);      // range + inc of symbol j
-    for (; j < n; j++) {
-        const uint32_t lo = rec[4 * j], w = rec[4 * j + 1];
-        const uint64_t m = ((uint64_t)rec[4 * j + 3] << 32) | rec[4 * j + 2];
-        const uint32_t inc_next = j + 1 < n ? (sh[j + 1] >> 7) : 0u;
-        const uint64_t q = (uint64_t)(((unsigned __int128)rp * m) >> 64) >> (sh[j] & 63u);   // == range / total
-        low += (uint64_t)lo * q;
-        range = q * (uint64_t)w;
-        const uint32_t x = (uint32_t)((low ^ (low + range)) >> 32), rh = (uint32_t)(range >> 32);
-        if (__builtin_expect((x < rh ? x : rh) < 65536u, 0)) {
-            while ((low ^ (low + range)) < TOP || range < BOTTOM) {
-                if (range < BOTTOM && (low ^ (low + range)) >= TOP) range = (0 - low) & (BOTTOM - 1);
-                *op++ = (uint8_t)(low >> 56);
-                range <<= 8;
-                low <<= 8;
-            }
-            if (op + (n - j) + 32 > op_end) {      // keep one byte per remaining symbol plus a rare step in reserve
-                const size_t used = op - out.data();
-                out.resize(out.size() * 2 + 64);
-                op = out.data() + used;
-                op_end = out.data() + out.size();
-            }
-            rp = range + inc_next;
-            continue;
-        }
-        // both candidates of (low, rp) beside the test, selected by conditional moves: the dependent chain of a step is
-        // multiply-high, shift, multiply, add, xor, compare, select
-        const bool one = x < (1u << 24);
-        const uint64_t rp0 = range + inc_next, rp1 = (range << 8) | inc_next;
-        const uint64_t low1 = low << 8;
-        *op = (uint8_t)(low >> 56);
-        op += one;
-        rp = one ? rp1 : rp0;
-        low = one ? low1 : low;
-    }
-    range = rp;      // inc_next of the last symbol is 0
-    out.resize(op - out.data());
-}
-
 template <typename K> void dict_host_worker(leon_ctx *c)
 {
     auto t0 = std::chrono::steady_clock::now();
@@ -823,7 +809,7 @@ template <typename K> void dict_host_worker(leon_ctx *c)
             auto w0 = std::chrono::steady_clock::now();
             CUDA_TRY(cudaEventSynchronize(c->ev_dstage[p.slot]));
             copy_wait += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - w0).count();
-            dict_code_slice(c->h_dstage_rec[p.slot].as<uint32_t>(), c->h_dstage_sh[p.slot].as<uint8_t>(), p.n * (uint64_t)k, first,
+            lbent::dict_code_slice(c->h_dstage_rec[p.slot].as<uint32_t>(), c->h_dstage_sh[p.slot].as<uint8_t>(), p.n * (uint64_t)k, first,
                             low, range, out);
             first = false;
         }
@@ -1394,6 +1380,10 @@ template <typename K> void encode_batch(leon_ctx *c)
         if (R) {
             CUDA_TRY(cudaEventRecord(c->ev_q[0], st));
             CUDA_TRY(cudaStreamWaitEvent(c->st3, c->ev_q[0], 0));
+            if (c->up_quals_pending) {      // qualities copied behind the bases on the copy stream (do_upload, chunked)
+                CUDA_TRY(cudaStreamWaitEvent(c->st3, c->ev_up[UP_CHUNKS], 0));
+                c->up_quals_pending = false;
+            }
             {
                 // bases and the output text of the QT reads of a CTA are staged in shared memory when they fit
                 uint64_t need = (((uint64_t)lbwalk::QT * (uint64_t)c->max_len + 31) & ~15ull) + 16;
@@ -1768,6 +1758,7 @@ void leon_destroy(leon_ctx *c)
     if (c->wk.st) cudaStreamDestroy(c->wk.st);
     if (c->st_copy) { cudaStreamSynchronize(c->st_copy); cudaStreamDestroy(c->st_copy); }
     if (c->ev_copy) cudaEventDestroy(c->ev_copy);
+    for (int i = 0; i < 10; i++) if (c->ev_up[i]) cudaEventDestroy(c->ev_up[i]);
     if (c->ev_user_in) cudaEventDestroy(c->ev_user_in);
     if (c->ev_user_out) cudaEventDestroy(c->ev_user_out);
     if (c->st2) { cudaStreamSynchronize(c->st2); cudaStreamDestroy(c->st2); }
@@ -1930,9 +1921,11 @@ template <typename K> static void stream_count_begin(leon_ctx *c, const leon_str
     if (np == 0) {
         size_t free_b = 0, total_b = 0;
         CUDA_TRY(cudaMemGetInfo(&free_b, &total_b));
-        // key buffer + its ping-pong twin (+ the receive buffer of the exchange with several ranks) within 70 % of what is free
+        // key buffer + its ping-pong twin (+ the receive buffer of the exchange with several ranks) within 30 % of what is free:
+        // the buffers stay allocated (grow-only, like every buffer of a context: freeing and re-allocating tens of GB per run
+        // cost more than a second counting pass), so they must leave room for the encoding stage
         const double per_key = (double)kb * (c->comm.n > 1 ? 3.2 : 2.1);
-        const double budget = 0.7 * (double)free_b;
+        const double budget = 0.3 * (double)(free_b + c->d_keys.cap + c->d_keys_alt.cap + c->d_keys_recv.cap + c->d_keys_batch.cap);
         np = (uint32_t)std::max(1.0, std::ceil((double)nk_bound * per_key / budget));
     }
     uint64_t cap = nk_bound;
@@ -2060,19 +2053,6 @@ int leon_count_finish(leon_ctx *c, leon_count_result *out)
     user_stream_in(c);
     count_finish(c);
     c->stream_counting = false;
-    {   // the key buffers of the counting passes are dead weight from here on: keep only the solid list
-        const size_t kb = c->opts.kmer_size <= 31 ? 8 : 16;
-        if (c->solid_keys != c->d_solid_keys.p) {
-            DevBuf compact;
-            compact.reserve((c->nsolid + 1) * kb);
-            if (c->nsolid) CUDA_TRY(cudaMemcpyAsync(compact.p, c->solid_keys, c->nsolid * kb, cudaMemcpyDeviceToDevice, c->st));
-            CUDA_TRY(cudaStreamSynchronize(c->st));
-            c->d_solid_keys.release();
-            std::swap(c->d_solid_keys.p, compact.p); std::swap(c->d_solid_keys.cap, compact.cap);
-            c->solid_keys = c->d_solid_keys.p;
-        }
-        c->d_keys.release(); c->d_keys_alt.release(); c->d_keys_batch.release(); c->d_keys_recv.release();
-    }
     if (out) *out = c->cres;
     user_stream_out(c);
     LB_API_END(c)
@@ -2181,11 +2161,27 @@ int leon_compress(leon_ctx *c, const leon_reads *reads, leon_result *out)
     LB_API_BEGIN
     CUDA_TRY(cudaSetDevice(c->opts.device));
     user_stream_in(c);
-    do_upload(c, reads);
-    LB_DISPATCH(c, do_count);
-    LB_DISPATCH(c, do_bloom);
-    LB_DISPATCH(c, do_encode);
+    static const bool trace = getenv("LEON_B200_TRACE") != nullptr;
+    auto now = []() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t0 = trace ? now() : 0;
+    double t1 = 0, t2 = 0, t3 = 0, t4 = 0;
+    try {
+        do_upload(c, reads, true);
+        if (trace) t1 = now();
+        LB_DISPATCH(c, do_count);
+        if (trace) t2 = now();
+        LB_DISPATCH(c, do_bloom);
+        if (trace) t3 = now();
+        LB_DISPATCH(c, do_encode);
+        if (trace) t4 = now();
+    } catch (...) {
+        if (c->st_copy) cudaStreamSynchronize(c->st_copy);      // the caller's buffers are free again when the call returns
+        cudaStreamSynchronize(c->st3);
+        throw;
+    }
     do_fetch(c, out);
+    if (trace) fprintf(stderr, "[leon_b200] leon_compress host clock: upload %.1f ms, count %.1f, bloom %.1f, encode %.1f, fetch %.1f\n",
+                       t1 - t0, t2 - t1, t3 - t2, t4 - t3, now() - t4);
     fill_timings(c);
     user_stream_out(c);
     LB_API_END(c)

@@ -1,6 +1,7 @@
 // Phase 3b — per-read de Bruijn walk (C/DnaCoder.cpp:599-757 encodeAnchorRead, :759-969 buildBifurcationList) and
-// the lossy quality smoothing (C/DnaCoder.cpp:428-516).  One warp per read; each extension step is one
-// warp-cooperative contains4 (28 probes = one gather, see bloom.cuh).
+// the lossy quality smoothing (C/DnaCoder.cpp:428-516).  One THREAD per read (the bases of a CTA's reads staged in shared
+// memory by one TMA bulk copy); each extension step is thread_contains4: 7 independent 64-bit probes (+ a predicated spill
+// load) that cover the 14-bit field of the four candidates of every hash.
 #pragma once
 #include "common.cuh"
 #include "kmer_math.cuh"

@@ -143,6 +143,120 @@ static int host_selftest(int streams, int reads)
     return (bad || badstreams) ? 1 : 0;
 }
 
+// ---- the host coder of the anchor dictionary stream (lbent::dict_code_slice) against the dividing coder, and its speed ----
+// REJECTED EXPERIMENT: next quotient formed for both outcomes of the renormalisation decision (see entropy.cuh)
+static void dict_slice_spec(const uint32_t *rec, const uint8_t *sh, uint64_t n, bool first, uint64_t &low, uint64_t &range,
+                     std::vector<uint8_t> &out)
+{
+    const uint64_t TOP = (1ull << 56), BOTTOM = (1ull << 48);
+    const size_t pos0 = out.size();
+    out.resize(pos0 + n * 2 + 64);          // the common step writes <= 1 byte per symbol; the rare path re-checks
+    uint8_t *op = out.data() + pos0;
+    const uint8_t *op_end = out.data() + out.size();
+    uint64_t j = 0;
+    if (first && n) {                       // first symbol: range = 2^64 - 1, range + inc needs 65 bits
+        const uint64_t m = ((uint64_t)rec[3] << 32) | rec[2];
+        const uint32_t s = sh[0];
+        const uint64_t q = (uint64_t)(((unsigned __int128)range * m + ((s & 0x80u) ? m : 0ull)) >> 64) >> (s & 63u);
+        low += (uint64_t)rec[0] * q;
+        range = q * (uint64_t)rec[1];
+        while ((low ^ (low + range)) < TOP || range < BOTTOM) {
+            if (range < BOTTOM && (low ^ (low + range)) >= TOP) range = (0 - low) & (BOTTOM - 1);
+            *op++ = (uint8_t)(low >> 56);
+            range <<= 8;
+            low <<= 8;
+        }
+        j = 1;
+    }
+    // The chain of a step on a CPU is latency, not issue: multiply-high (4-5 cycles), shift, multiply (3), add, xor, compare,
+    // select -- about 15 cycles when the next quotient can only start after the renormalisation decision.  So the quotient of
+    // the NEXT symbol is formed for both outcomes of that decision (no byte: range; one byte: range << 8) as soon as the
+    // new range exists, beside the computation of low and the decision itself, and the decision only selects one of them:
+    // the dependent chain shrinks to multiply, multiply-high, shift, select (~10 cycles).  State carried: (low, q) with
+    // q = range / total of the symbol to code.
+    auto quotient = [](uint64_t rp, uint64_t m, uint32_t s) { return (uint64_t)(((unsigned __int128)rp * m) >> 64) >> (s & 63u); };
+    auto magic = [&](uint64_t i) { return ((uint64_t)rec[4 * i + 3] << 32) | rec[4 * i + 2]; };
+    uint64_t q = j < n ? quotient(range + (sh[j] >> 7), magic(j), sh[j]) : 0;
+    for (; j < n; j++) {
+        const uint32_t lo = rec[4 * j], w = rec[4 * j + 1];
+        const bool more = j + 1 < n;
+        const uint64_t mn = more ? magic(j + 1) : 0ull;                 // record of the next symbol: independent of the chain
+        const uint32_t sn = more ? sh[j + 1] : 0u, inc_next = sn >> 7;
+        low += (uint64_t)lo * q;
+        range = q * (uint64_t)w;
+        const uint64_t qa = quotient(range + inc_next, mn, sn);          // next quotient if no byte leaves ...
+        const uint64_t qb = quotient((range << 8) | inc_next, mn, sn);   // ... and if exactly one does
+        const uint32_t x = (uint32_t)((low ^ (low + range)) >> 32), rh = (uint32_t)(range >> 32);
+        if (__builtin_expect((x < rh ? x : rh) < 65536u, 0)) {           // two bytes or more, or a range clamp: 1.4 % of the symbols
+            while ((low ^ (low + range)) < TOP || range < BOTTOM) {
+                if (range < BOTTOM && (low ^ (low + range)) >= TOP) range = (0 - low) & (BOTTOM - 1);
+                *op++ = (uint8_t)(low >> 56);
+                range <<= 8;
+                low <<= 8;
+            }
+            if (op + (n - j) + 32 > op_end) {      // keep one byte per remaining symbol plus a rare step in reserve
+                const size_t used = op - out.data();
+                out.resize(out.size() * 2 + 64);
+                op = out.data() + used;
+                op_end = out.data() + out.size();
+            }
+            q = quotient(range + inc_next, mn, sn);
+            continue;
+        }
+        const bool one = x < (1u << 24);
+        *op = (uint8_t)(low >> 56);
+        op += one;
+        q = one ? qb : qa;
+        range = one ? range << 8 : range;
+        low = one ? low << 8 : low;
+    }
+    out.resize(op - out.data());
+}
+
+
+
+static int dict_selftest(int anchors, int k)
+{
+    // a dictionary-shaped stream: one Order0Model(5), symbols 0..3, never reset
+    std::mt19937_64 rng(11);
+    HostModel model(5);
+    std::vector<Sym> syms;
+    for (int a = 0; a < anchors; a++)
+        for (int i = 0; i < k; i++) { Sym y; model.get((unsigned)(rng() % 4), y.lo, y.w, y.tot); syms.push_back(y); }
+    std::vector<uint8_t> want;
+    host_encode(syms, want);
+    std::vector<uint32_t> rec(4 * syms.size()); std::vector<uint8_t> sh(syms.size());
+    for (size_t i = 0; i < syms.size(); i++) {
+        uint64_t m; uint32_t s, inc; host_magic(syms[i].tot, m, s, inc);
+        rec[4 * i] = syms[i].lo; rec[4 * i + 1] = syms[i].w; rec[4 * i + 2] = (uint32_t)m; rec[4 * i + 3] = (uint32_t)(m >> 32);
+        sh[i] = (uint8_t)(s | (inc << 7));
+    }
+    int bad = 0;
+    double ns[2] = {0, 0};
+    for (int variant = 0; variant < 2; variant++) {
+        for (int rep = 0; rep < 3; rep++) {
+            std::vector<uint8_t> got;
+            uint64_t low = 0, range = ~0ull;
+            auto t0 = std::chrono::steady_clock::now();
+            size_t at = 0;
+            bool first = true;
+            while (at < syms.size()) {          // slices of uneven sizes, like the worker's
+                size_t nsl = std::min<size_t>(syms.size() - at, rep == 0 ? 1 + rng() % 5000 : (1u << 19));
+                if (variant == 0) lbent::dict_code_slice(rec.data() + 4 * at, sh.data() + at, nsl, first, low, range, got);
+                else dict_slice_spec(rec.data() + 4 * at, sh.data() + at, nsl, first, low, range, got);
+                first = false;
+                at += nsl;
+            }
+            double dt = std::chrono::duration<double, std::nano>(std::chrono::steady_clock::now() - t0).count() / syms.size();
+            if (rep == 0 || dt < ns[variant]) ns[variant] = dt;
+            for (int x = 0; x < 8; x++) { got.push_back((uint8_t)(low >> 56)); low <<= 8; }
+            if (got != want) bad++;
+        }
+    }
+    printf("host: dictionary coder, %zu symbols: library step %.2f ns/symbol, speculative-quotient experiment %.2f ns/symbol, mismatches %d\n", syms.size(), ns[0], ns[1], bad);
+    return bad;
+}
+
 __global__ void k_magic_check(uint32_t d0, uint32_t n, uint32_t stride, const uint64_t *want_m, const uint8_t *want_s, uint32_t *bad)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -157,6 +271,7 @@ __global__ void k_magic_check(uint32_t d0, uint32_t n, uint32_t stride, const ui
 
 int main(int argc, char **argv)
 {
+    if (argc > 1 && !strcmp(argv[1], "--dict")) return dict_selftest(argc > 2 ? atoi(argv[2]) : 300000, argc > 3 ? atoi(argv[3]) : 31);
     if (argc > 1 && !strcmp(argv[1], "--host")) return host_selftest(argc > 2 ? atoi(argv[2]) : 12, argc > 3 ? atoi(argv[3]) : 20000);
     int streams = argc > 1 ? atoi(argv[1]) : 92, reads = argc > 2 ? atoi(argv[2]) : 50000;
     using namespace lbent;
