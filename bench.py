@@ -501,10 +501,11 @@ def measure_large(args, torch, dist, world, rank, local_rank):
     gen_s = time.perf_counter() - t0
     local_reads = len(lens)
     # batches of M chunks per rank; every rank makes the same number of calls (empty batches at the end where it has run out)
+    from leon_b200 import shard
     M = max(1, args.large_batch_chunks)
-    max_chunks = (nchunks + world - 1) // world
-    ncalls = max(1, (max_chunks + M - 1) // M)
-    batches = [(min(local_reads, i * M * S), min(local_reads, (i + 1) * M * S)) for i in range(ncalls)]
+    batches = shard.stream_batches(total_reads, rank, world, S, M)
+    ncalls = len(batches)
+    assert local_reads == sum(hi - lo for lo, hi in shard.rank_read_ranges(total_reads, rank, world, S))
 
     torch.cuda.synchronize()
     free_start = torch.cuda.mem_get_info()[0]
@@ -545,21 +546,31 @@ def measure_large(args, torch, dist, world, rank, local_rank):
                 eng.count_batch(b, o, i == len(cuts) - 1)
         cnt = eng.count_finish()
         phases["count_s"] = time.perf_counter() - t
+        if keep:        # CUDA-event time per kernel of the counting pass(es), ms (the timers restart at count_begin)
+            phases["count_kernels_ms"] = {k: round(v[0], 2) for k, v in sorted(eng.kernel_times().items(), key=lambda kv: -kv[1][0])[:8]}
         t = time.perf_counter()
         eng.bloom_build()
         phases["bloom_s"] = time.perf_counter() - t
         t = time.perf_counter()
         first = 0
         outs = []
+        per_batch = []
         for i, (b, o, q) in enumerate(cuts):
             if i + 1 < len(cuts):
                 eng.prefetch(*cuts[i + 1])
+            tb = time.perf_counter()
             bo = eng.encode_block(first, b, o, q, copy=keep)
             first += bo["nblocks"]
             if keep:
                 outs.append(bo)
+                tmb = eng.timings()     # CUDA-event phases of this batch beside the wall clock of the call
+                per_batch.append({"call_ms": round((time.perf_counter() - tb) * 1e3, 1), "anchor_ms": round(tmb["anchor_ms"], 1),
+                                  "walk_entropy_ms": round(tmb["walk_ms"], 1), "reads": int(len(o) - 1)})
         res = eng.encode_finish(copy=keep)
         phases["encode_s"] = time.perf_counter() - t
+        if keep:        # phases of the LAST batch (CUDA events), main-stream kernels of the whole run + walk / entropy kernels of the last batch
+            phases["batches_ms"] = per_batch
+            phases["kernels_ms_cumulative_and_last_batch"] = {k: round(v[0], 2) for k, v in sorted(eng.kernel_times().items(), key=lambda kv: -kv[1][0])[:14]}
         tm = eng.timings()
         # the anchor dictionary is ONE never-reset range coder (C/Leon.cpp:1245-1260): a serial chain on a host thread of rank 0
         # that runs beside the whole encoding pass; dict_wait = how long the pass then still waited for it
@@ -601,11 +612,7 @@ def measure_large(args, torch, dist, world, rank, local_rank):
     with cf.ThreadPoolExecutor(threads) as ex:
         per = [h for lst in ex.map(block_hashes, outs) for h in lst]
     # local block j of chunk-round i on this rank is global block (i * world + rank) * (S / RPB) + j
-    bpc = S // RPB
-    gids = []
-    for i, ch in enumerate(mine):
-        n_in = min(S, total_reads - ch * S)
-        gids += [ch * bpc + j for j in range((n_in + RPB - 1) // RPB)]
+    gids = shard.global_block_ids(total_reads, rank, world, S, RPB)
     assert len(gids) == len(per), (len(gids), len(per))
     mem.stop = True
     mem.join()

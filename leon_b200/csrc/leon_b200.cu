@@ -207,7 +207,8 @@ struct leon_ctx {
     std::deque<SbState> sbs;
     uint64_t sbs_used = 0;
     std::atomic<uint64_t> sb_pub{0};
-    std::atomic<bool> sb_abort{false};
+    std::atomic<bool> sb_abort{false}, sb_walks_done{false}, sb_failed{false};
+    bool quals_late_active = false;      // this batch: quality kernels start after the last walk (encode_batch)
     std::thread sb_thread;
     std::string sb_err;
     int sb_err_code = 0;
@@ -1017,7 +1018,32 @@ template <typename K> void sb_prepare(leon_ctx *c, uint64_t g)
     CUDA_TRY(cudaEventRecord(sb.ev_records, st));
     // the chains of this super-block on their own stream: they do not hold up the next super-block's preparation
     CUDA_TRY(cudaEventSynchronize(sb.ev_records));
-    LB_TIMED(sb.kt, "k_range_encode", sb.rc_stream, LB_LAUNCH(ln.lc, k_range_encode, (unsigned)sb.nblocks, 32, 0, sb.rc_stream, sb.d_rec.as<uint4>(), sb.d_sh.as<uint8_t>(),
+    // The chains that are still running when the quality kernels start (quals_late: they start after the last walk) get an SM
+    // each to themselves: a CTA that claims all the shared memory of an SM shares it with no other CTA.  A lone warp per
+    // scheduler is what the chain's 130 cycles per symbol were measured with; beside the warps of k_quals it ran 31 % slower
+    // (153 against 138 cycles per symbol over the whole chain, +4.4 ms on the run).  Only the last RC_EXCLUSIVE super-blocks:
+    // earlier chains have that much slack before the last one ends, and their SMs stay open to the walks still to come.
+    static const uint64_t rc_exclusive = env_u64("LEON_B200_RC_EXCLUSIVE", 0);
+    size_t rc_smem = 0;
+    if (c->quals_late_active && g + rc_exclusive >= c->sbs_used) {
+        static std::mutex mu;
+        static int optin[64];                 // per device: 0 = not asked yet, -1 = refused
+        std::lock_guard<std::mutex> lk(mu);
+        int &max_optin = optin[c->opts.device & 63];
+        if (max_optin == 0) {
+            int v = 0;
+            cudaFuncAttributes fa{};
+            cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, c->opts.device);
+            if (cudaFuncGetAttributes(&fa, k_range_encode) == cudaSuccess) v -= (int)fa.sharedSizeBytes;    // its own static arrays
+            if (v <= 0 || cudaFuncSetAttribute(k_range_encode, cudaFuncAttributeMaxDynamicSharedMemorySize, v) != cudaSuccess) {
+                cudaGetLastError();
+                v = -1;
+            }
+            max_optin = v;
+        }
+        rc_smem = max_optin > 0 ? (size_t)max_optin : 0;
+    }
+    LB_TIMED(sb.kt, "k_range_encode", sb.rc_stream, LB_LAUNCH(ln.lc, k_range_encode, (unsigned)sb.nblocks, 32, rc_smem, sb.rc_stream, sb.d_rec.as<uint4>(), sb.d_sh.as<uint8_t>(),
               sb.d_descs.as<StreamDesc>(), sb.d_outall.as<uint8_t>(), sb.d_outsize.as<uint64_t>(), 0, c->d_counters.as<uint32_t>() + 2));
     sb.h_sizes.reserve(sb.nblocks * 8 + 8);
     CUDA_TRY(cudaMemcpyAsync(sb.h_sizes.p, sb.d_outsize.p, sb.nblocks * 8, cudaMemcpyDeviceToHost, sb.rc_stream));
@@ -1065,6 +1091,11 @@ void sb_finish(leon_ctx *c, uint64_t g)
 }
 
 constexpr uint64_t SB_PIPELINE_MIN_DEFAULT = 16;
+static uint64_t sb_pipeline_min()
+{
+    static const uint64_t v = env_u64("LEON_B200_SB_PIPELINE_MIN", SB_PIPELINE_MIN_DEFAULT);
+    return v;
+}
 
 
 template <typename K> void stage_b_worker(leon_ctx *c)
@@ -1077,24 +1108,27 @@ template <typename K> void stage_b_worker(leon_ctx *c)
         // 4.6 M reads (10 super-blocks): the bulk kernels take the SMs from the small latency-critical anchor kernels
         // (anchor stage 8.6 -> 15.5 ms) and that costs what the overlap gains (72.4 vs 72.2 ms; FASTQ 87.4 vs 82.8 ms), since
         // the run ends one chain length (40 ms) after the LAST chain is launched either way.  Larger sets are pipelined.
-        static const uint64_t SB_PIPELINE_MIN = env_u64("LEON_B200_SB_PIPELINE_MIN", SB_PIPELINE_MIN_DEFAULT);
-        const uint64_t gate = nsb <= SB_PIPELINE_MIN ? nsb - 1 : 0;
+        const uint64_t gate = nsb <= sb_pipeline_min() ? nsb - 1 : 0;
         for (uint64_t g = 0; g < nsb; g++) {
             while (c->sb_pub.load(std::memory_order_acquire) <= std::max(g, gate)) {
-                if (c->sb_abort.load()) return;
+                if (c->sb_abort.load()) { c->sb_walks_done.store(true); return; }
                 std::this_thread::sleep_for(std::chrono::microseconds(10));
             }
             sb_prepare<K>(c, g);
         }
+        // sb_prepare returns once the records of its super-block are made (it waits for them before it launches the chains):
+        // from here on only range coder chains run
+        c->sb_walks_done.store(true, std::memory_order_release);
         // outputs in file order; by the time the last super-block is launched the first chains have long finished
         for (uint64_t g = 0; g < nsb; g++) sb_finish(c, g);
         for (uint64_t g = 0; g < nsb; g++)
             if (c->sbs[g].fetched) CUDA_TRY(cudaEventSynchronize(c->sbs[g].ev_coded));
     } catch (const LeonError &e) {
-        c->sb_err = e.msg; c->sb_err_code = e.code;
+        c->sb_err = e.msg; c->sb_err_code = e.code; c->sb_failed.store(true);
     } catch (const std::exception &e) {
-        c->sb_err = e.what(); c->sb_err_code = LEON_E_NOMEM;
+        c->sb_err = e.what(); c->sb_err_code = LEON_E_NOMEM; c->sb_failed.store(true);
     }
+    c->sb_walks_done.store(true, std::memory_order_release);       // also after an error: nobody waits for ever
 }
 
 // Start of the encoding pass over a read set of R_total reads (all ranks): empty anchor dictionary, the list the anchors
@@ -1372,32 +1406,41 @@ template <typename K> void encode_batch(leon_ctx *c)
     const uint8_t *bases = c->d_bases.as<uint8_t>();
     const uint64_t *offsets = c->d_offsets.as<uint64_t>();
 
-    // Quality smoothing only needs the Bloom filter: it runs on a third (low priority) stream beside everything else;
-    // the run ends when its zlib streams are written too.
+    // Quality smoothing only needs the Bloom filter: it runs on a third (low priority) stream; the run ends when its zlib
+    // streams are written too.  WHEN it starts: with up to SB_PIPELINE_MIN super-blocks (deferred start of the walk / entropy
+    // stage, see stage_b_worker) the run ends one range coder chain (38 ms of ~100 lone warps on an otherwise idle GPU) after
+    // the last walk, so the quality kernels (8 ms + 5 ms of deflate at configs[2]) go THERE; started beside the anchor stage
+    // they took the SMs from its small latency-critical kernels (k_quals 7.9 ms alone, 15 ms beside them, and the anchor
+    // stage as much longer).  Larger sets (pipelined stage) have no idle tail to speak of: the kernels start at once.
+    // LEON_B200_QUALS_LATE=0 restores the early start.
     c->qz_done = false;
-    if (c->opts.has_qual) {
+    static const uint64_t quals_late_knob = env_u64("LEON_B200_QUALS_LATE", 1);
+    auto launch_quals = [&]() {
+        if (!c->opts.has_qual) return;
         c->d_qout.reserve(c->nbases + R + 16);
-        if (R) {
-            CUDA_TRY(cudaEventRecord(c->ev_q[0], st));
-            CUDA_TRY(cudaStreamWaitEvent(c->st3, c->ev_q[0], 0));
-            if (c->up_quals_pending) {      // qualities copied behind the bases on the copy stream (do_upload, chunked)
-                CUDA_TRY(cudaStreamWaitEvent(c->st3, c->ev_up[UP_CHUNKS], 0));
-                c->up_quals_pending = false;
-            }
-            {
-                // bases and the output text of the QT reads of a CTA are staged in shared memory when they fit
-                uint64_t need = (((uint64_t)lbwalk::QT * (uint64_t)c->max_len + 31) & ~15ull) + 16;
-                uint32_t stage_bytes = need <= 100000 ? (uint32_t)need : 16u;
-                size_t smem = 2 * (size_t)stage_bytes + lbwalk::QT + 32;
-                // 4 k-mers in flight per thread, 4 CTAs per SM: the best of the (2..8, 2..8) combinations measured on the B200
-                CUDA_TRY(cudaFuncSetAttribute(lbwalk::k_quals<K, 4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 100000 + lbwalk::QT + 32));
-                LB_TIMED(c->kt, "k_quals", c->st3, LB_LAUNCH(c->lc, (lbwalk::k_quals<K, 4, 4>), cdiv_u(R, lbwalk::QT), lbwalk::QT, smem, c->st3, bases,
-                          c->d_quals.as<uint8_t>(), offsets, R, c->bloom, c->d_tbl.as<uint64_t>(), c->opts.lossless, c->d_qout.as<uint8_t>(), stage_bytes));
-            }
-            CUDA_TRY(cudaEventRecord(c->ev_q[1], c->st3));
-            if (c->opts.qual_zlib_on_device) deflate_quals(c);
+        if (!R) return;
+        CUDA_TRY(cudaEventRecord(c->ev_q[0], st));
+        CUDA_TRY(cudaStreamWaitEvent(c->st3, c->ev_q[0], 0));
+        if (c->up_quals_pending) {      // qualities copied behind the bases on the copy stream (do_upload, chunked)
+            CUDA_TRY(cudaStreamWaitEvent(c->st3, c->ev_up[UP_CHUNKS], 0));
+            c->up_quals_pending = false;
         }
-    }
+        {
+            // bases and the output text of the QT reads of a CTA are staged in shared memory when they fit
+            uint64_t need = (((uint64_t)lbwalk::QT * (uint64_t)c->max_len + 31) & ~15ull) + 16;
+            uint32_t stage_bytes = need <= 100000 ? (uint32_t)need : 16u;
+            size_t smem = 2 * (size_t)stage_bytes + lbwalk::QT + 32;
+            // 4 k-mers in flight per thread, 4 CTAs per SM: the best of the (2..8, 2..8) combinations measured on the B200
+            CUDA_TRY(cudaFuncSetAttribute(lbwalk::k_quals<K, 4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 100000 + lbwalk::QT + 32));
+            LB_TIMED(c->kt, "k_quals", c->st3, LB_LAUNCH(c->lc, (lbwalk::k_quals<K, 4, 4>), cdiv_u(R, lbwalk::QT), lbwalk::QT, smem, c->st3, bases,
+                      c->d_quals.as<uint8_t>(), offsets, R, c->bloom, c->d_tbl.as<uint64_t>(), c->opts.lossless, c->d_qout.as<uint8_t>(), stage_bytes));
+        }
+        CUDA_TRY(cudaEventRecord(c->ev_q[1], c->st3));
+        if (c->opts.qual_zlib_on_device) deflate_quals(c);
+    };
+    const bool quals_late = quals_late_knob && c->opts.has_qual && R && (R + superblock_reads(c) - 1) / superblock_reads(c) <= sb_pipeline_min();
+    c->quals_late_active = quals_late;
+    if (!quals_late) launch_quals();
 
     // ---- super-blocks of the walk / entropy stage
     c->d_apos.reserve((R + 1) * 4);
@@ -1441,6 +1484,8 @@ template <typename K> void encode_batch(leon_ctx *c)
     c->sb_abort.store(false);
     c->sb_err.clear();
     if (c->sb_thread.joinable()) c->sb_thread.join();
+    c->sb_walks_done.store(nsb == 0);
+    c->sb_failed.store(false);
     if (nsb) c->sb_thread = std::thread(stage_b_worker<K>, c);
 
     do_anchors<K>(c);
@@ -1454,6 +1499,11 @@ template <typename K> void encode_batch(leon_ctx *c)
         if (R) LB_LAUNCH(c->lc, k_count_noanchor, (unsigned)std::min<uint64_t>((R + 255) / 256, 1024), 256, 0, st, apos, R, cnt);
         c->enc_noanchor += fetch_scalar(c, cnt);
         c->reads_without_anchor = c->enc_noanchor;
+    }
+    if (quals_late) {
+        // the last walk has finished (or the stage has failed): the quality kernels run beside the tail of range coder chains
+        while (!c->sb_walks_done.load(std::memory_order_acquire)) std::this_thread::sleep_for(std::chrono::microseconds(20));
+        if (!c->sb_failed.load()) launch_quals();
     }
     // join the walk / entropy stage: every block is coded and on the host
     if (c->sb_thread.joinable()) c->sb_thread.join();
@@ -1912,6 +1962,12 @@ static void stream_upload(leon_ctx *c, const leon_reads *rd, bool with_quals, bo
     c->max_len = first_of_set ? bmx : std::max(c->max_len, bmx);
 }
 
+static double count_budget_frac()
+{
+    static const uint64_t pct = std::min<uint64_t>(90, std::max<uint64_t>(5, env_u64("LEON_B200_COUNT_BUDGET", 50)));
+    return (double)pct / 100.0;
+}
+
 template <typename K> static void stream_count_begin(leon_ctx *c, const leon_stream_plan *plan, uint32_t *npasses_out)
 {
     const uint64_t kb = sizeof(K);
@@ -1921,11 +1977,13 @@ template <typename K> static void stream_count_begin(leon_ctx *c, const leon_str
     if (np == 0) {
         size_t free_b = 0, total_b = 0;
         CUDA_TRY(cudaMemGetInfo(&free_b, &total_b));
-        // key buffer + its ping-pong twin (+ the receive buffer of the exchange with several ranks) within 30 % of what is free:
-        // the buffers stay allocated (grow-only, like every buffer of a context: freeing and re-allocating tens of GB per run
-        // cost more than a second counting pass), so they must leave room for the encoding stage
+        // key buffer + its ping-pong twin (+ the receive buffer of the exchange with several ranks) within half of what is free
+        // (LEON_B200_COUNT_BUDGET, per cent): the buffers stay allocated (grow-only, like every buffer of a context: freeing and
+        // re-allocating tens of GB per run cost more than a second counting pass), so they must leave room for the encoding
+        // stage, whose buffers grow with the caller's batch (5 KB per read of 150 bp measured: 43 GB for batches of 8 M reads).
+        // Measured on configs[3], 1 GPU: 70 % with release 1.65 s, 30 % = two passes 0.82 s, one pass with the buffers kept 0.48 s.
         const double per_key = (double)kb * (c->comm.n > 1 ? 3.2 : 2.1);
-        const double budget = 0.3 * (double)(free_b + c->d_keys.cap + c->d_keys_alt.cap + c->d_keys_recv.cap + c->d_keys_batch.cap);
+        const double budget = count_budget_frac() * (double)(free_b + c->d_keys.cap + c->d_keys_alt.cap + c->d_keys_recv.cap + c->d_keys_batch.cap);
         np = (uint32_t)std::max(1.0, std::ceil((double)nk_bound * per_key / budget));
     }
     uint64_t cap = nk_bound;

@@ -50,6 +50,18 @@ def global_block_ids(nreads, rank, nranks, S, reads_per_block):
     return ids
 
 
+def stream_batches(nreads, rank, nranks, S, chunks_per_batch):
+    """Streaming path on several ranks (leon_count / leon_encode_block, include/leon_b200.h): the (first, last) LOCAL read
+    indices of the batches `rank` feeds, `chunks_per_batch` rounds of S reads at a time.  Every rank makes the same number of
+    calls -- the anchor exchange of a round is a collective -- so a rank that has run out of reads goes on with empty batches."""
+    local = sum(hi - lo for lo, hi in rank_read_ranges(nreads, rank, nranks, S))
+    nchunks = (nreads + S - 1) // S
+    max_chunks = (nchunks + nranks - 1) // nranks
+    M = max(1, int(chunks_per_batch))
+    ncalls = max(1, (max_chunks + M - 1) // M)
+    return [(min(local, i * M * S), min(local, (i + 1) * M * S)) for i in range(ncalls)]
+
+
 def merge_results(results, nreads, nranks, S, reads_per_block):
     """Reassembles the per-rank result dicts (Leon._result) into the single-GPU layout: blocks in file order, per-read
     arrays in file order; whole-set fields (Bloom, counts, anchor dictionary) come from rank 0."""

@@ -103,3 +103,54 @@ def test_choose_batch_reads_balances():
         per = [sum(hi - lo for lo, hi in shard.rank_read_ranges(4_600_000, r, n, S)) for r in range(n)]
         assert sum(per) == 4_600_000
         assert max(per) <= 1.35 * 4_600_000 / n
+
+
+def _stream_worker(rank, world, port, nreads, S, rpb, M, out_path):
+    import sys
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    from leon_b200 import shard
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    batches = shard.stream_batches(nreads, rank, world, S, M)
+    ranges = shard.rank_read_ranges(nreads, rank, world, S)
+    local = sum(hi - lo for lo, hi in ranges)
+    ok = batches[0][0] == 0 and batches[-1][1] == local and all(a[1] == b[0] for a, b in zip(batches, batches[1:]))
+    # every rank makes the same number of calls (the anchor exchange of a round is a collective)
+    t = torch.tensor([len(batches)])
+    lo_t, hi_t = t.clone(), t.clone()
+    dist.all_reduce(lo_t, op=dist.ReduceOp.MIN)
+    dist.all_reduce(hi_t, op=dist.ReduceOp.MAX)
+    ok &= int(lo_t) == int(hi_t)
+    # the engine numbers the reads of local round i of rank r from (i * world + r) * S (leon_b200.cu encode_batch, delta0):
+    # walking the batches round by round must give back exactly this rank's global ranges
+    seen = []
+    done_rounds = 0
+    for lo, hi in batches:
+        at = lo
+        while at < hi:
+            n = min(S, hi - at)
+            g0 = (done_rounds * world + rank) * S
+            seen.append((g0, g0 + n))
+            at += n
+            done_rounds += 1
+    ok &= seen == ranges
+    mine = dict(ids=shard.global_block_ids(nreads, rank, world, S, rpb), ok=bool(ok))
+    allr = [None] * world
+    dist.all_gather_object(allr, mine)
+    if rank == 0:
+        ids = sorted(i for r in allr for i in r["ids"])
+        good = all(r["ok"] for r in allr) and ids == list(range((nreads + rpb - 1) // rpb))
+        open(out_path, "w").write("OK" if good else "FAILED")
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("nreads,S,rpb,M", [(2300, 300, 100, 2), (1750, 250, 50, 1), (90, 200, 100, 4), (4000, 500, 100, 3)])
+def test_two_gloo_ranks_streaming_batches(tmp_path, nreads, S, rpb, M):
+    import torch.multiprocessing as mp
+    out = str(tmp_path / "result.txt")
+    mp.spawn(_stream_worker, args=(2, _free_port(), nreads, S, rpb, M, out), nprocs=2, join=True)
+    assert open(out).read() == "OK"
