@@ -184,6 +184,77 @@ __global__ void __launch_bounds__(256) k_extract(const uint8_t *__restrict__ bas
     (void)n;
 }
 
+// The same for read sets of VARIABLE length (the host knows: min != max).  koff[r] + p is then the only layout there is, and a
+// thread that stores its own read's keys one by one makes every store instruction of its warp touch 32 lines (measured on
+// configs[3], 2 % trimmed reads so that hardly any CTA is uniform: 0.69 TB/s against 4.4 TB/s of the position-major stores
+// above).  Here every warp transposes through shared memory: XT positions of its 32 reads are rolled into a tile
+// [32 reads][XT + 1], then each group of XT lanes writes one read's XT consecutive keys (128 contiguous bytes per group).
+template <typename K> struct ExtractRagged { static constexpr int XT = sizeof(K) == 8 ? 16 : 8; };
+template <typename K> LB_HD constexpr uint32_t extract_ragged_tile_bytes() { return 8u * 32u * (ExtractRagged<K>::XT + 1) * (uint32_t)sizeof(K); }
+
+template <typename K>
+__global__ void __launch_bounds__(256) k_extract_ragged(const uint8_t *__restrict__ bases, const uint64_t *__restrict__ offsets,
+                                                        const uint64_t *__restrict__ koff, uint64_t nreads, int k, K *__restrict__ keys,
+                                                        uint32_t stage_bytes)
+{
+    constexpr int XT = ExtractRagged<K>::XT;
+    extern __shared__ __align__(128) uint8_t stage[];          // [tiles of the 8 warps][staged bases]
+    __shared__ __align__(8) uint64_t bar;
+    K *tile = reinterpret_cast<K *>(stage) + (size_t)(threadIdx.x >> 5) * 32 * (XT + 1);
+    uint8_t *sbytes = stage + extract_ragged_tile_bytes<K>();
+    const uint64_t r0 = (uint64_t)blockIdx.x * 256;
+    const uint64_t r1 = r0 + 256 < nreads ? r0 + 256 : nreads;
+    const uint64_t o0 = offsets[r0];
+    const uint8_t *sbase = stage_reads(bases, o0, offsets[r1], sbytes, stage_bytes, &bar);
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const uint64_t r = r0 + threadIdx.x;
+    const bool have = r < nreads;
+    const uint64_t o = have ? offsets[r] : 0, L = have ? offsets[r + 1] - o : 0;
+    const uint64_t n = L >= (uint64_t)k ? L - k + 1 : 0;
+    const uint64_t kbase = have ? koff[r] : 0;
+    // the warp walks to the end of its longest read (reads of 2^32 bases and more do not exist here: leon_upload checks)
+    const uint32_t nmax = __reduce_max_sync(0xffffffffu, (uint32_t)n);
+    if (!nmax) return;
+    const uint8_t *s = sbase ? sbase + (o - o0) : bases + o;
+    const K mask = kmer_mask(K(0), k);
+    const int top = 2 * (k - 1);
+    K fwd = K(0), rc = K(0);
+    uint32_t clean = 0;
+    const uint32_t steps = nmax + (uint32_t)k - 1;
+    const int row0 = lane / XT, j = lane % XT;
+    for (uint32_t i = 0; i < steps; i++) {
+        if (i < L) {
+            const uint8_t c = s[i];
+            const unsigned code = base_code(c);
+            fwd = ((fwd << 2) | K((uint64_t)code)) & mask;
+            rc = (rc >> 2) | (K((uint64_t)(code ^ 2u)) << top);
+            clean = base_invalid(c) ? 0u : (clean < (uint32_t)k ? clean + 1 : clean);
+            if (i + 1 >= (uint32_t)k) {
+                const uint32_t p = i + 1 - k;
+                K key;
+                if (clean >= (uint32_t)k) key = rc < fwd ? rc : fwd;
+                else kmer_make_invalid(key, (r << 24) ^ (uint64_t)p);
+                tile[lane * (XT + 1) + (p % XT)] = key;
+            }
+        }
+        if (i + 1 >= (uint32_t)k) {
+            const uint32_t p = i + 1 - k;                      // warp-uniform
+            if (p % XT == XT - 1 || i + 1 == steps) {
+                const uint32_t pbase = p - p % XT;
+                __syncwarp();
+#pragma unroll 4
+                for (int row = row0; row < 32; row += 32 / XT) {
+                    const uint64_t n_row = __shfl_sync(0xffffffffu, n, row);
+                    const uint64_t k_row = __shfl_sync(0xffffffffu, kbase, row);
+                    if ((uint64_t)pbase + j < n_row) keys[k_row + pbase + j] = tile[row * (XT + 1) + j];
+                }
+                __syncwarp();
+            }
+        }
+    }
+}
+
 // ---- partition pass (also the LSD radix sort pass of entropy.cuh) ------------------------------------------------
 constexpr int RS_THREADS = 256;
 constexpr int RS_WARPS = RS_THREADS / 32;

@@ -78,6 +78,32 @@ static uint64_t env_u64(const char *name, uint64_t dflt)
 
 // One host thread's private launch context: stream, scratch of the scan / partition helpers, pinned scalar slot,
 // launch counter and kernel timer (none of them is shared between threads).
+// LEON_B200_TRACE: host-clock marks of the sections of a call, printed to stderr (no extra synchronisation: a mark shows when
+// the HOST got there)
+struct TraceClock {
+    bool on;
+    std::chrono::steady_clock::time_point t0, last;
+    std::string line;
+    explicit TraceClock(const char *what) : on(getenv("LEON_B200_TRACE") != nullptr)
+    {
+        if (on) { t0 = last = std::chrono::steady_clock::now(); line = std::string("[leon_b200 trace] ") + what + ":"; }
+    }
+    void mark(const char *name)
+    {
+        if (!on) return;
+        auto t = std::chrono::steady_clock::now();
+        char b[96];
+        snprintf(b, sizeof b, " %s %.2f", name, std::chrono::duration<double, std::milli>(t - last).count());
+        line += b;
+        last = t;
+    }
+    ~TraceClock()
+    {
+        if (!on) return;
+        fprintf(stderr, "%s | total %.2f ms\n", line.c_str(), std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+    }
+};
+
 struct Lane {
     cudaStream_t st = nullptr;
     DevBuf d_scan, d_tile_hist, d_tile_off;
@@ -438,6 +464,20 @@ template <typename K> void count_add(leon_ctx *c)
     // bases of the 256 reads of a CTA are staged in shared memory when they fit (40 KB), else read from global
     uint64_t need = ((256ull * (uint64_t)c->max_len + 31) & ~15ull) + 16;
     uint32_t stage_bytes = need <= 40960 ? (uint32_t)need : 16u;
+    // reads of one length: position-major stores; variable lengths: per-warp transposition (k_extract_ragged)
+    static const uint64_t ragged_knob = env_u64("LEON_B200_EXTRACT_RAGGED", 1);
+    const bool ragged = ragged_knob && c->min_len != c->max_len;
+    auto extract = [&](uint64_t r0, uint64_t nr, K *keys) {
+        if (ragged) {
+            const uint32_t smem = extract_ragged_tile_bytes<K>() + stage_bytes;
+            CUDA_TRY(cudaFuncSetAttribute(k_extract_ragged<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(extract_ragged_tile_bytes<K>() + 40960 + 16)));
+            LB_TIMED(c->kt, "k_extract", st, LB_LAUNCH(c->lc, (k_extract_ragged<K>), cdiv_u(nr, 256), 256, smem, st, c->d_bases.as<uint8_t>(),
+                      c->d_offsets.as<uint64_t>() + r0, koff + r0, nr, k, keys, stage_bytes));
+        } else {
+            LB_TIMED(c->kt, "k_extract", st, LB_LAUNCH(c->lc, (k_extract<K>), cdiv_u(nr, 256), 256, stage_bytes, st, c->d_bases.as<uint8_t>(),
+                      c->d_offsets.as<uint64_t>() + r0, koff + r0, nr, k, keys, stage_bytes));
+        }
+    };
     if (c->count_npasses == 1) {
         if (c->keys_fill + nk > c->keys_cap) throw LeonError(LEON_E_OVERFLOW, "k-mer counting: more k-mers than the plan announced");
         K *keys = c->d_keys.as<K>() + c->keys_fill;
@@ -446,21 +486,18 @@ template <typename K> void count_add(leon_ctx *c)
             for (size_t i = 0; i < c->up_chunks.size(); i++) {
                 const uint64_t r0 = c->up_chunks[i].first, r1 = c->up_chunks[i].second;
                 CUDA_TRY(cudaStreamWaitEvent(st, c->ev_up[i], 0));
-                LB_TIMED(c->kt, "k_extract", st, LB_LAUNCH(c->lc, (k_extract<K>), cdiv_u(r1 - r0, 256), 256, stage_bytes, st, c->d_bases.as<uint8_t>(),
-                          c->d_offsets.as<uint64_t>() + r0, koff + r0, r1 - r0, k, keys, stage_bytes));
+                extract(r0, r1 - r0, keys);
             }
             c->up_chunks.clear();
         } else {
-            LB_TIMED(c->kt, "k_extract", st, LB_LAUNCH(c->lc, (k_extract<K>), cdiv_u(c->nreads, 256), 256, stage_bytes, st, c->d_bases.as<uint8_t>(),
-                      c->d_offsets.as<uint64_t>(), koff, c->nreads, k, keys, stage_bytes));
+            extract(0, c->nreads, keys);
         }
         c->keys_fill += nk;
     } else {
         // all keys of the batch, then the ones of this pass appended to the pass buffer
         c->d_keys_batch.reserve((nk + 1) * sizeof(K));
         K *tmp = c->d_keys_batch.as<K>();
-        LB_TIMED(c->kt, "k_extract", st, LB_LAUNCH(c->lc, (k_extract<K>), cdiv_u(c->nreads, 256), 256, stage_bytes, st, c->d_bases.as<uint8_t>(),
-                  c->d_offsets.as<uint64_t>(), koff, c->nreads, k, tmp, stage_bytes));
+        extract(0, c->nreads, tmp);
         unsigned long long *fill = (unsigned long long *)(c->d_stats.as<uint8_t>() + sizeof(CountStats) + 8);
         LB_TIMED(c->kt, "k_select_pass", st, LB_LAUNCH(c->lc, (k_select_pass<K>), cdiv_u(nk, 2048), 256, 0, st, tmp, nk, c->count_npasses, c->count_pass,
                   c->d_keys.as<K>(), fill));
@@ -1021,9 +1058,10 @@ template <typename K> void sb_prepare(leon_ctx *c, uint64_t g)
     // The chains that are still running when the quality kernels start (quals_late: they start after the last walk) get an SM
     // each to themselves: a CTA that claims all the shared memory of an SM shares it with no other CTA.  A lone warp per
     // scheduler is what the chain's 130 cycles per symbol were measured with; beside the warps of k_quals it ran 31 % slower
-    // (153 against 138 cycles per symbol over the whole chain, +4.4 ms on the run).  Only the last RC_EXCLUSIVE super-blocks:
+    // (153 against 138 cycles per symbol over the whole chain, +4.4 ms on the run).  Only the last RC_EXCLUSIVE super-blocks
+    // (configs[2], 10 super-blocks: 0 -> 74.4 ms, 3 -> 72.8, 5 -> 71.9, 10 -> 74.5 with the walks slowed from 9.4 to 11.9 ms):
     // earlier chains have that much slack before the last one ends, and their SMs stay open to the walks still to come.
-    static const uint64_t rc_exclusive = env_u64("LEON_B200_RC_EXCLUSIVE", 0);
+    static const uint64_t rc_exclusive = env_u64("LEON_B200_RC_EXCLUSIVE", 5);
     size_t rc_smem = 0;
     if (c->quals_late_active && g + rc_exclusive >= c->sbs_used) {
         static std::mutex mu;
@@ -1200,6 +1238,18 @@ template <typename K> void do_anchors(leon_ctx *c)
     const uint64_t delta0 = N > 1 ? c->enc_rounds_done * (uint64_t)N * S + (uint64_t)me * S : c->enc_reads_done;
     std::vector<uint32_t> m_all(N, 0), m_off(N, 0);
     uint64_t sb_next = 0;                                    // first super-block not handed over yet
+    // LEON_B200_TRACE: host clock per section of the batches (the stream is drained at every mark, so the run is slower)
+    static const bool trace = getenv("LEON_B200_TRACE") != nullptr;
+    double tsec[6] = {0, 0, 0, 0, 0, 0};
+    uint64_t m_sum = 0, ins_sum = 0, rounds0 = (uint64_t)c->tm.anchor_rounds;
+    auto tnow = std::chrono::steady_clock::now();
+    auto mark = [&](int i) {
+        if (!trace) return;
+        cudaStreamSynchronize(st);
+        auto t = std::chrono::steady_clock::now();
+        tsec[i] += std::chrono::duration<double, std::milli>(t - tnow).count();
+        tnow = t;
+    };
 
     for (uint64_t g = 0; g < nbatches; g++) {
         const uint64_t lo = std::min(R, g * S), hi = std::min(R, (g + 1) * S);
@@ -1210,6 +1260,7 @@ template <typename K> void do_anchors(leon_ctx *c)
         if (c->dict_count && nb)
             LB_LAUNCH(c->lc, (k_anchor_lookup<K>), cdiv_u(nb, 256), 256, look_stage, st, bases, offsets, lo, hi, delta, k,
                       dict_view<K>(c, c->dict_cur), apos, aaddr, (const uint8_t *)nullptr, look_stage);
+        mark(0);
         // P: no-hit reads in order
         c->d_plist.reserve((nb + 1) * 4);
         uint32_t *plist = c->d_plist.as<uint32_t>();
@@ -1232,6 +1283,8 @@ template <typename K> void do_anchors(leon_ctx *c)
             joff = m_off[me];
         }
         uint32_t nins = 0;
+        mark(1);
+        m_sum += m;
         if (m) {
             c->d_cand_pos.reserve((uint64_t)m * 4);
             c->d_cand_key.reserve((uint64_t)m * sizeof(K));
@@ -1278,6 +1331,7 @@ template <typename K> void do_anchors(leon_ctx *c)
             // A round after the last undecided read changes nothing, so rounds are launched in groups and the "undecided"
             // counter is only read once per group: fewer host round trips than one per round.
             const int group = N > 1 ? 1 : 3;
+            mark(2);
             while (true) {
                 for (int it = 0; it < group; it++) {
                     c->tm.anchor_rounds++;
@@ -1295,6 +1349,7 @@ template <typename K> void do_anchors(leon_ctx *c)
                 }
                 if (!fetch_scalar(c, counters + 1)) break;
             }
+            mark(3);
             // I: addresses in read order, insertion into D (every rank inserts every new anchor)
             dict_ensure<K>(c, c->dict_count + m);
             if (c->dict_count + m + 1 > anchors_cap) throw LeonError(LEON_E_OVERFLOW, "anchor list: more anchors than reads");
@@ -1303,12 +1358,15 @@ template <typename K> void do_anchors(leon_ctx *c)
             uint32_t *itot = lbscan::exclusive_scan<uint32_t>(m, InsIn{state}, io, c->d_scan, st, c->lc);
             nins = fetch_scalar(c, itot);
             c->dict_count += nins;
+            ins_sum += nins;
+            mark(4);
             if (dict_thread_on) c->dict_pub.store(c->dict_count, std::memory_order_release);   // the stream is idle: the new anchors are in HBM
             // B: anchors of this batch can pre-empt later reads of the batch at earlier positions
             if (nins && nb)
                 LB_LAUNCH(c->lc, (k_anchor_lookup<K>), cdiv_u(nb, 256), 256, look_stage, st, bases, offsets, lo, hi, delta, k,
                           dict_view<K>(c, c->dict_cur), apos, aaddr, (const uint8_t *)insflag, look_stage);
         }
+        mark(5);
         // hand over every super-block whose reads are all anchored now
         while (sb_next < c->sbs_used && (c->sbs[sb_next].hi <= hi || g + 1 == nbatches)) {
             CUDA_TRY(cudaEventRecord(c->sbs[sb_next].ev_anchored, st));
@@ -1323,6 +1381,12 @@ template <typename K> void do_anchors(leon_ctx *c)
     }
     c->enc_rounds_done += nbatches;
     c->enc_reads_done += R;
+    if (trace)
+        fprintf(stderr, "[leon_b200 trace] anchors: %llu reads, %llu batches, %llu rounds, %llu no-hit reads, %llu inserted, dictionary %llu | ms: "
+                        "lookup A %.2f, no-hit list %.2f, candidates+table %.2f, rounds %.2f, insert %.2f, lookup B %.2f\n",
+                (unsigned long long)R, (unsigned long long)nbatches, (unsigned long long)((uint64_t)c->tm.anchor_rounds - rounds0),
+                (unsigned long long)m_sum, (unsigned long long)ins_sum, (unsigned long long)c->dict_count,
+                tsec[0], tsec[1], tsec[2], tsec[3], tsec[4], tsec[5]);
     CUDA_TRY(cudaEventRecord(c->ev[7], st));
 }
 
@@ -1440,7 +1504,9 @@ template <typename K> void encode_batch(leon_ctx *c)
     };
     const bool quals_late = quals_late_knob && c->opts.has_qual && R && (R + superblock_reads(c) - 1) / superblock_reads(c) <= sb_pipeline_min();
     c->quals_late_active = quals_late;
+    TraceClock tc("encode_batch");
     if (!quals_late) launch_quals();
+    tc.mark("quals_early");
 
     // ---- super-blocks of the walk / entropy stage
     c->d_apos.reserve((R + 1) * 4);
@@ -1487,8 +1553,10 @@ template <typename K> void encode_batch(leon_ctx *c)
     c->sb_walks_done.store(nsb == 0);
     c->sb_failed.store(false);
     if (nsb) c->sb_thread = std::thread(stage_b_worker<K>, c);
+    tc.mark("prepare");
 
     do_anchors<K>(c);
+    tc.mark("anchors");
     int32_t *apos = c->d_apos.as<int32_t>();
     uint32_t *ovf = c->d_counters.as<uint32_t>() + 2;
     CUDA_TRY(cudaEventRecord(c->ev[8], st));
@@ -1500,19 +1568,25 @@ template <typename K> void encode_batch(leon_ctx *c)
         c->enc_noanchor += fetch_scalar(c, cnt);
         c->reads_without_anchor = c->enc_noanchor;
     }
+    tc.mark("noanchor");
     if (quals_late) {
         // the last walk has finished (or the stage has failed): the quality kernels run beside the tail of range coder chains
         while (!c->sb_walks_done.load(std::memory_order_acquire)) std::this_thread::sleep_for(std::chrono::microseconds(20));
+        tc.mark("walks");
         if (!c->sb_failed.load()) launch_quals();
+        tc.mark("quals_late");
     }
     // join the walk / entropy stage: every block is coded and on the host
     if (c->sb_thread.joinable()) c->sb_thread.join();
+    tc.mark("join");
     if (!c->sb_err.empty()) throw LeonError(c->sb_err_code, "walk / entropy stage: " + c->sb_err);
     for (uint64_t g = 0; g < nsb; g++) c->nsym_total += c->sbs[g].nsym;
     CUDA_TRY(cudaEventRecord(c->ev[9], st));
     if (fetch_scalar(c, ovf)) throw LeonError(LEON_E_OVERFLOW, "range coder output exceeded its capacity bound");
+    tc.mark("ovf");
     if (c->qz_done) CUDA_TRY(cudaEventSynchronize(c->ev_qz));   // the run ends when the quality streams are written too
     else if (c->opts.has_qual && R) CUDA_TRY(cudaEventSynchronize(c->ev_q[1]));
+    tc.mark("quals_wait");
     c->enc_blocks_done += c->nblocks;
 }
 
@@ -1906,7 +1980,9 @@ static void batch_check(const leon_reads *rd, bool with_quals)
 // leon_stream_prefetch: the NEXT batch on its way into the spare read buffers while the current one is being processed
 static void stream_prefetch(leon_ctx *c, const leon_reads *rd, bool with_quals)
 {
+    TraceClock tc("leon_stream_prefetch");
     batch_check(rd, with_quals);
+    tc.mark("check");
     if (!c->st_copy) {
         CUDA_TRY(cudaStreamCreateWithFlags(&c->st_copy, cudaStreamNonBlocking));
         CUDA_TRY(cudaEventCreateWithFlags(&c->ev_copy, cudaEventDisableTiming));
@@ -1922,7 +1998,9 @@ static void stream_prefetch(leon_ctx *c, const leon_reads *rd, bool with_quals)
         CUDA_TRY(cudaMemcpyAsync(c->d_quals_next.p, rd->quals, nbases, cudaMemcpyHostToDevice, c->st_copy));
     }
     CUDA_TRY(cudaEventRecord(c->ev_copy, c->st_copy));
+    tc.mark("enqueue");
     batch_host_scan(rd, (uint64_t)c->opts.reads_per_block, with_quals, c->pf_min, c->pf_max, c->pf_qsizes);   // while the copies run
+    tc.mark("host_scan");
     c->pf_reads = *rd;
     c->pf_quals = with_quals;
     c->pf_valid = true;
@@ -2029,13 +2107,18 @@ template <typename K> static void stream_encode_block(leon_ctx *c, uint64_t firs
     if (batch->nreads % (uint64_t)c->opts.reads_per_block) c->enc_partial_seen = true;
     if (c->comm.n > 1 && batch->nreads % anchor_batch_reads(c)) c->enc_partial_seen = true;
     const int32_t mn = c->min_len, mx = c->max_len;
+    TraceClock tc("leon_encode_block");
     stream_upload(c, batch, c->opts.has_qual != 0, false);
+    tc.mark("upload");
     c->min_len = std::min(mn, c->min_len); c->max_len = std::max(mx, c->max_len);     // of the whole set (counting pass)
     count_koff(c);
+    tc.mark("koff");
     encode_batch<K>(c);
+    tc.mark("encode_batch");
     c->enc_total_bases += c->nbases;
     leon_result r;
     do_fetch(c, &r, false);
+    tc.mark("fetch");
     memset(out, 0, sizeof *out);
     out->first_block = first_block; out->nblocks = r.nblocks; out->read_count = r.read_count;
     out->blocksizes = r.blocksizes; out->dna = r.dna; out->dna_nbytes = r.dna_nbytes;
