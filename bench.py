@@ -539,10 +539,14 @@ def measure_large(args, torch, dist, world, rank, local_rank):
         phases = {}
         t = time.perf_counter()
         npass = eng.count_begin(local_reads, nb, args.large_passes)
-        for _ in range(npass):
+        for ps in range(npass):
             for i, (b, o, _q) in enumerate(cuts):
                 if i + 1 < len(cuts):
                     eng.prefetch(cuts[i + 1][0], cuts[i + 1][1])
+                elif ps + 1 < npass:
+                    eng.prefetch(cuts[0][0], cuts[0][1])        # first batch of the next counting pass
+                else:
+                    eng.prefetch(*cuts[0])                      # first batch of the encoding pass (with its qualities)
                 eng.count_batch(b, o, i == len(cuts) - 1)
         cnt = eng.count_finish()
         phases["count_s"] = time.perf_counter() - t

@@ -190,8 +190,11 @@ int leon_count_finish(leon_ctx *ctx, leon_count_result *out);
 /* Optional, any time between two leon_count / leon_encode_block calls: starts copying the batch that will be submitted NEXT
  * into spare device buffers, so that its upload runs beside the work on the current one (the reference's bank iterator
  * reads ahead the same way, DP/api/ICommand.hpp:304-331 hands chunks to free threads).  The batch's memory must stay
- * valid and unchanged until the call it is then submitted to returns; a prefetched batch that is not the next one
- * submitted is ignored. */
+ * valid and unchanged until the call it is then submitted to returns.  Since submissions are synchronous, the usual order is
+ * "announce batch i + 1, submit batch i": two announcements may be open at a time -- the second one's copy starts the moment
+ * the first one is swapped in by its submission and runs beside that call (a third announcement replaces the second).  A batch
+ * that was not announced is uploaded by its submission; an announced batch that is never submitted is dropped by
+ * leon_count_begin. */
 int leon_stream_prefetch(leon_ctx *ctx, const leon_reads *next_batch, int with_quals);
 /* Codes the blocks of `batch`; first_block must be the number of blocks this rank has coded so far.  The outputs are on
  * the host when it returns and stay valid until the next leon_encode_block / leon_encode_finish on the context. */

@@ -599,9 +599,11 @@ class Leon:
         self._check(self.L.leon_encode_finish(self.ctx, C.byref(r)))
         return self._result(r, copy)
 
-    def compress_stream(self, bases, offsets, quals=None, batch_reads=None, count_passes=0, batches=None):
+    def compress_stream(self, bases, offsets, quals=None, batch_reads=None, count_passes=0, batches=None, prefetch="alternate"):
         """The whole set through the streaming entry points, `batch_reads` reads at a time (or the explicit list of (lo, hi) read
-        ranges `batches`); returns the result dict of compress() assembled from the per-batch outputs, plus `count_passes`."""
+        ranges `batches`); returns the result dict of compress() assembled from the per-batch outputs, plus `count_passes`.
+        `prefetch`: "all" announces every next batch before the current one is submitted (what a caller after speed does),
+        "alternate" every other one in the encoding pass (both upload paths of the library stay exercised), "none" never."""
         offsets = np.ascontiguousarray(offsets, np.uint64)
         n = len(offsets) - 1
         if batches is None:
@@ -615,10 +617,15 @@ class Leon:
             cuts.append((bases[b0:b1], np.ascontiguousarray(offsets[lo:hi + 1] - offsets[lo]), quals[b0:b1] if quals is not None else None))
 
         npass = self.count_begin(n, int(offsets[-1]), count_passes)
-        for _ in range(npass):
+        for ps in range(npass):
             for i, (b, o, _q) in enumerate(cuts):
-                if i + 1 < len(cuts):
+                if i + 1 < len(cuts) and prefetch != "none":
                     self.prefetch(cuts[i + 1][0], cuts[i + 1][1])
+                elif prefetch == "all":     # behind the last batch of a pass: the first one of the next pass / of the encoding pass
+                    if ps + 1 < npass:
+                        self.prefetch(cuts[0][0], cuts[0][1])
+                    else:
+                        self.prefetch(*cuts[0])
                 self.count_batch(b, o, i == len(cuts) - 1)
         self.count_finish()
         self.bloom_build()
@@ -626,7 +633,7 @@ class Leon:
         parts = {k: [] for k in keys}
         first = 0
         for i, (b, o, q) in enumerate(cuts):
-            if i + 1 < len(cuts) and i % 2 == 0:      # every other batch prefetched: both upload paths stay exercised
+            if i + 1 < len(cuts) and (prefetch == "all" or (prefetch == "alternate" and i % 2 == 0)):
                 self.prefetch(*cuts[i + 1])
             bo = self.encode_block(first, b, o, q)
             for k in keys:

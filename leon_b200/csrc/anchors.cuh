@@ -32,10 +32,15 @@ template <typename K> struct DictDev {
     K *keys;
     uint32_t *addr;
     uint32_t *time;      // LB_EMPTY32 = free slot
+    uint8_t *tag;        // 0 = free slot, else dict_tag of the key: one byte per slot, the only array a failed probe touches
     uint64_t mask;       // capacity - 1 (power of two)
 };
 
 template <typename K> LB_HD uint64_t dict_hash(K key) { return hash64(kmer_fold64(key), 0x9E3779B97F4A7C15ULL); }
+// The lookups probe every k-mer of a read until the first hit, so most probes fail, and at the scale of configs[3] (2.8 M
+// anchors, 16 M slots) the 4-byte and 8-byte arrays of the table are 64 + 128 MB: every failed probe was a DRAM access.  The
+// tags of the same table are 16 MB and stay in L2; keys and times are only read behind a matching tag (1 in 255 by chance).
+LB_HD uint8_t dict_tag(uint64_t h) { uint8_t t = (uint8_t)(h >> 56); return t ? t : (uint8_t)1; }
 
 // forward-strand k-mers of positions [start, end) of a read, 32 per step, N read as A (C/DnaCoder.cpp:519-535).
 // f(p, kmer, active) is called by all 32 lanes together and returns a warp-uniform "stop".
@@ -58,12 +63,14 @@ LB_D void warp_for_kmers(const uint8_t *__restrict__ s, uint64_t L, int k, uint6
 
 template <typename K> LB_D bool dict_find(const DictDev<K> &d, K key, uint32_t before, uint32_t *addr)
 {
-    uint64_t s = dict_hash(key) & d.mask;
+    const uint64_t h = dict_hash(key);
+    const uint8_t tg = dict_tag(h);
+    uint64_t s = h & d.mask;
     while (true) {
-        uint32_t t = d.time[s];
-        if (t == LB_EMPTY32) return false;
-        if (d.keys[s] == key) {
-            if (t < before) { *addr = d.addr[s]; return true; }
+        const uint8_t t8 = d.tag[s];
+        if (t8 == 0) return false;
+        if (t8 == tg && d.keys[s] == key) {
+            if (d.time[s] < before) { *addr = d.addr[s]; return true; }
             return false;   // keys are unique in D
         }
         s = (s + 1) & d.mask;
@@ -335,10 +342,12 @@ template <typename K> struct InsOut {
             aaddr[r] = a;
             inserter[r] = 1;
         }
-        uint64_t s = dict_hash(key) & d.mask;
+        const uint64_t h = dict_hash(key);
+        uint64_t s = h & d.mask;
         while (atomicCAS(&d.time[s], LB_EMPTY32, g) != LB_EMPTY32) s = (s + 1) & d.mask;   // keys are distinct
         d.keys[s] = key;
         d.addr[s] = a;
+        d.tag[s] = dict_tag(h);        // lookups run in later kernels
     }
 };
 
@@ -350,10 +359,12 @@ template <typename K> __global__ void k_dict_rehash(DictDev<K> from, DictDev<K> 
     uint32_t t = from.time[i];
     if (t == LB_EMPTY32) return;
     K key = from.keys[i];
-    uint64_t s = dict_hash(key) & to.mask;
+    const uint64_t h = dict_hash(key);
+    uint64_t s = h & to.mask;
     while (atomicCAS(&to.time[s], LB_EMPTY32, t) != LB_EMPTY32) s = (s + 1) & to.mask;
     to.keys[s] = key;
     to.addr[s] = from.addr[i];
+    to.tag[s] = dict_tag(h);
 }
 
 }  // namespace lbanchor

@@ -450,12 +450,15 @@ extern "C" int leon_compress_file(const char *in_path, const char *out_path, con
             uint32_t npasses = 1;
             rc = leon_count_begin(ctx, &plan, &npasses);
             leon_reads b, nextb;
+            batch_of(0, b);
             for (uint32_t p = 0; !rc && p < npasses; p++) {
                 uint64_t r0 = 0;
-                batch_of(0, b);
                 do {
                     r0 += batch_reads;
-                    if (r0 < nreads) { batch_of(r0, nextb); leon_stream_prefetch(ctx, &nextb, 0); }    // upload beside the counting of b
+                    // the next batch is announced before this one is submitted: its upload runs beside the counting of b.  Behind
+                    // the last batch of a pass that is the first batch again, of the next pass or (with qualities) of the encoding pass
+                    if (r0 < nreads) { batch_of(r0, nextb); leon_stream_prefetch(ctx, &nextb, 0); }
+                    else { batch_of(0, nextb); leon_stream_prefetch(ctx, &nextb, p + 1 < npasses ? 0 : 1); }
                     rc = leon_count(ctx, &b, r0 >= nreads);
                     b = nextb;
                 } while (!rc && r0 < nreads);
@@ -464,7 +467,6 @@ extern "C" int leon_compress_file(const char *in_path, const char *out_path, con
             if (!rc) rc = leon_count_finish(ctx, &cr);
             if (!rc) rc = leon_bloom_build(ctx, nullptr, nullptr, nullptr);
             uint64_t first_block = 0, r0 = 0;
-            batch_of(0, b);
             do {
                 if (rc) break;
                 r0 += batch_reads;

@@ -298,11 +298,14 @@ def test_streaming_equals_one_shot(k, fastq, lossless, passes, batch_blocks, see
     r = eng.compress_stream(bases, offs, quals, batch_reads=batch_blocks * rpb, count_passes=passes)
     assert r["count_passes"] == passes
     _same(r, ref, fastq)
-    # a second set on the same context, other batching, passes chosen by the library (1 at this size)
-    r2 = eng.compress_stream(bases, offs, quals, batch_reads=4 * rpb, count_passes=0)
-    eng.close()
+    # a second set on the same context, other batching, passes chosen by the library (1 at this size); every next batch
+    # announced before the current one is submitted (two announcements open at a time: include/leon_b200.h, leon_stream_prefetch)
+    r2 = eng.compress_stream(bases, offs, quals, batch_reads=4 * rpb, count_passes=0, prefetch="all")
     assert r2["count_passes"] == 1
     _same(r2, ref, fastq)
+    r3 = eng.compress_stream(bases, offs, quals, batch_reads=2 * rpb, count_passes=2, prefetch="all" if seed % 2 else "none")
+    eng.close()
+    _same(r3, ref, fastq)
 
 
 def test_streaming_device_memory_is_independent_of_the_number_of_reads():
