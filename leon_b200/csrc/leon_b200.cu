@@ -240,6 +240,7 @@ struct leon_ctx {
     uint64_t sbs_used = 0;
     std::atomic<uint64_t> sb_pub{0};
     std::atomic<bool> sb_abort{false}, sb_walks_done{false}, sb_failed{false};
+    std::atomic<uint64_t> sb_walked{0};     // super-blocks whose records are made (sb_prepare returned)
     bool quals_late_active = false;      // this batch: quality kernels start after the last walk (encode_batch)
     std::thread sb_thread;
     std::string sb_err;
@@ -1162,6 +1163,7 @@ template <typename K> void stage_b_worker(leon_ctx *c)
                 std::this_thread::sleep_for(std::chrono::microseconds(10));
             }
             sb_prepare<K>(c, g);
+            c->sb_walked.store(g + 1, std::memory_order_release);
         }
         // sb_prepare returns once the records of its super-block are made (it waits for them before it launches the chains):
         // from here on only range coder chains run
@@ -1511,8 +1513,15 @@ template <typename K> void encode_batch(leon_ctx *c)
         CUDA_TRY(cudaEventRecord(c->ev_q[1], c->st3));
         if (c->opts.qual_zlib_on_device) deflate_quals(c);
     };
-    const bool quals_late = quals_late_knob && c->opts.has_qual && R && (R + superblock_reads(c) - 1) / superblock_reads(c) <= sb_pipeline_min();
-    c->quals_late_active = quals_late;
+    const uint64_t nsb_q = R ? (R + superblock_reads(c) - 1) / superblock_reads(c) : 0;
+    const bool deferred = nsb_q <= sb_pipeline_min();
+    // pipelined stage (LEON_B200_QUALS_LATE_PIPE, per cent of the super-blocks walked before the quality kernels start; 0 = at
+    // once): the GPU is busy with anchors + walks until the last walk and idle under the last chains, and the quality kernels
+    // take longer than one chain, so they start when about a quarter of the walks is still to come
+    static const uint64_t late_pipe_pct = std::min<uint64_t>(100, env_u64("LEON_B200_QUALS_LATE_PIPE", 75));
+    const bool quals_late = quals_late_knob && c->opts.has_qual && R && (deferred || late_pipe_pct > 0);
+    const uint64_t quals_after = deferred ? nsb_q : nsb_q * late_pipe_pct / 100;      // super-blocks walked before they start
+    c->quals_late_active = quals_late && deferred;
     TraceClock tc("encode_batch");
     if (!quals_late) launch_quals();
     tc.mark("quals_early");
@@ -1560,6 +1569,7 @@ template <typename K> void encode_batch(leon_ctx *c)
     c->sb_err.clear();
     if (c->sb_thread.joinable()) c->sb_thread.join();
     c->sb_walks_done.store(nsb == 0);
+    c->sb_walked.store(0);
     c->sb_failed.store(false);
     if (nsb) c->sb_thread = std::thread(stage_b_worker<K>, c);
     tc.mark("prepare");
@@ -1580,7 +1590,8 @@ template <typename K> void encode_batch(leon_ctx *c)
     tc.mark("noanchor");
     if (quals_late) {
         // the last walk has finished (or the stage has failed): the quality kernels run beside the tail of range coder chains
-        while (!c->sb_walks_done.load(std::memory_order_acquire)) std::this_thread::sleep_for(std::chrono::microseconds(20));
+        while (!c->sb_walks_done.load(std::memory_order_acquire) && c->sb_walked.load(std::memory_order_acquire) < quals_after)
+            std::this_thread::sleep_for(std::chrono::microseconds(20));
         tc.mark("walks");
         if (!c->sb_failed.load()) launch_quals();
         tc.mark("quals_late");
