@@ -125,6 +125,8 @@ __global__ void __launch_bounds__(256) k_anchor_lookup(const uint8_t *__restrict
     const int top = 2 * (k - 1);
     const uint32_t before = (uint32_t)(r + delta);      // index of the read in the whole set
     K fwd = K(0), rc = K(0);
+    // (rolling LU = 4 positions and requesting their tags together before looking at them in order was measured: anchor stage
+    // 8.8 -> 9.5 ms at configs[2], no change at configs[3] -- the probes are not what the threads wait for; profiles/r3b_*)
     for (uint64_t i = 0; i < lim + k - 1; i++) {
         const unsigned code = base_code_n_as_a(s[i]);
         fwd = ((fwd << 2) | K((uint64_t)code)) & mask;

@@ -463,12 +463,18 @@ __global__ void __launch_bounds__(RS_THREADS) k_msd_hist(const K *__restrict__ k
     if (threadIdx.x <= lv.mask && h[threadIdx.x]) atomicAdd(&cnt[(sp << lv.wbits) + threadIdx.x], (unsigned long long)h[threadIdx.x]);
 }
 
-template <typename K>
-__global__ void __launch_bounds__(RS_THREADS, 4) k_msd_scatter(const K *__restrict__ in, K *__restrict__ out, const MsdLevel lv,
-                                                            unsigned long long *__restrict__ cursor)
+// THREADS = 256: 16 keys per thread (64 registers, 4 CTAs = 32 warps per SM); THREADS = 512: 8 keys per thread, 40 registers,
+// 3 CTAs = 48 warps per SM over the same 4096-key tile (the kernel is latency-bound: three barrier-separated phases and one
+// global atomic round trip per tile; ncu: dram 27 %, issue 27 %, occupancy 49 % with 256 threads).  Measured at configs[2]
+// (2 x 322 M keys): 4.84 ms with 256 threads, 3.99 ms with 512, 4.47 ms with 1024 (2 CTAs, 32 registers; profiles/r3c_msd_threads.txt):
+// 512 is the default.
+template <typename K, int THREADS>
+__global__ void __launch_bounds__(THREADS, THREADS == 256 ? 4 : 3) k_msd_scatter(const K *__restrict__ in, K *__restrict__ out, const MsdLevel lv,
+                                                                               unsigned long long *__restrict__ cursor)
 {
-    constexpr int ITEMS = RsCfg<K>::ITEMS, TILE = RsCfg<K>::TILE;
-    __shared__ uint32_t h[256], dstart[256], wsum[RS_WARPS];
+    constexpr int TILE = RsCfg<K>::TILE, ITEMS = TILE / THREADS, WARPS = THREADS / 32;
+    static_assert(WARPS >= 8, "the digit scan runs on the first 8 warps");
+    __shared__ uint32_t h[256], dstart[256], wsum[8];
     __shared__ uint64_t gbase[256];
     __shared__ K stage[TILE];
     __shared__ uint8_t sdig[TILE];
@@ -480,7 +486,7 @@ __global__ void __launch_bounds__(RS_THREADS, 4) k_msd_scatter(const K *__restri
         live = msd_locate(lv, blockIdx.x, TILE, p, b, e);
         sp = p; sbeg = b; send = e;
     }
-    h[threadIdx.x] = 0;
+    if (threadIdx.x < 256) h[threadIdx.x] = 0;
     __syncthreads();
     if (!live) return;
     const uint64_t beg = sbeg, end = send;
@@ -489,7 +495,7 @@ __global__ void __launch_bounds__(RS_THREADS, 4) k_msd_scatter(const K *__restri
     uint8_t dig[ITEMS];
 #pragma unroll
     for (int j = 0; j < ITEMS; j++) {
-        uint64_t i = beg + (uint64_t)j * RS_THREADS + threadIdx.x;
+        uint64_t i = beg + (uint64_t)j * THREADS + threadIdx.x;
         if (i < end) {
             key[j] = in[i];
             unsigned d = (unsigned)(key_mix(key[j]) >> lv.shift) & lv.mask;
@@ -499,25 +505,28 @@ __global__ void __launch_bounds__(RS_THREADS, 4) k_msd_scatter(const K *__restri
     }
     __syncthreads();
     {
-        const unsigned d = threadIdx.x;
-        const uint32_t tot = h[d];
+        const unsigned d = threadIdx.x & 255u;
+        const bool scanner = threadIdx.x < 256;
+        const uint32_t tot = scanner ? h[d] : 0u;
         uint32_t incl = tot;
 #pragma unroll
         for (int s = 1; s < 32; s <<= 1) {
             uint32_t o = __shfl_up_sync(0xffffffffu, incl, s);
             if (lane >= s) incl += o;
         }
-        if (lane == 31) wsum[warp] = incl;
+        if (scanner && lane == 31) wsum[warp] = incl;
         __syncthreads();
-        uint32_t base = 0;
-        for (int w = 0; w < warp; w++) base += wsum[w];
-        dstart[d] = base + incl - tot;
-        gbase[d] = tot ? atomicAdd(&cursor[(sp << lv.wbits) + d], (unsigned long long)tot) : 0ull;
+        if (scanner) {
+            uint32_t base = 0;
+            for (int w = 0; w < warp; w++) base += wsum[w];
+            dstart[d] = base + incl - tot;
+            gbase[d] = tot ? atomicAdd(&cursor[(sp << lv.wbits) + d], (unsigned long long)tot) : 0ull;
+        }
     }
     __syncthreads();
 #pragma unroll
     for (int j = 0; j < ITEMS; j++) {
-        uint64_t i = beg + (uint64_t)j * RS_THREADS + threadIdx.x;
+        uint64_t i = beg + (uint64_t)j * THREADS + threadIdx.x;
         if (i < end) {
             uint32_t pos = dstart[dig[j]] + rank[j];
             stage[pos] = key[j];
@@ -526,7 +535,7 @@ __global__ void __launch_bounds__(RS_THREADS, 4) k_msd_scatter(const K *__restri
     }
     __syncthreads();
     const uint32_t nt = (uint32_t)(end - beg);
-    for (uint32_t i = threadIdx.x; i < nt; i += RS_THREADS) {
+    for (uint32_t i = threadIdx.x; i < nt; i += THREADS) {
         unsigned d = sdig[i];
         out[gbase[d] + (i - dstart[d])] = stage[i];
     }
@@ -653,6 +662,8 @@ __global__ void __launch_bounds__(BC_THREADS) k_bucket_count(const K *__restrict
             uint64_t tag = table_tag<K>(key, salt);
             uint32_t slot = (uint32_t)(mx ^ (mx >> 37)) & (BC_SLOTS - 1);
             for (int probe = 0; probe < BC_SLOTS; probe++) {
+                // (a plain load of the tag before the compare-and-swap, for the keys that repeat one already in the table, was
+                // measured: 2.10 -> 2.14 ms; the kernel is bound by shared-memory wavefronts, not by the atomic's latency)
                 unsigned long long old = atomicCAS((unsigned long long *)&tags[slot], ~0ull, (unsigned long long)tag);
                 if (old == ~0ull) {
                     if (sizeof(K) > 8) full[slot] = key;

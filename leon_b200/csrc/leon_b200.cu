@@ -110,6 +110,9 @@ struct Lane {
     PinBuf h_small;
     LaunchCounter lc;
     KernelTimer kt;
+    // transient buffers of the walk / entropy stage of the SECOND lane (the first one uses the context's, which the debug
+    // fetches read)
+    DevBuf d_bif, d_err, d_recs, d_symoff, d_srec, d_srec_alt, d_segstart, d_chunkoff, d_chist;
 };
 
 // A super-block of the walk / entropy stage: whole blocks [first_block, first_block + nblocks) = reads [lo, hi) of this
@@ -236,6 +239,9 @@ struct leon_ctx {
     cudaEvent_t ev_pf_guard = nullptr;
     // walk / entropy stage (stage_b_worker)
     Lane wk;
+    Lane wk2;                            // second lane: super-blocks are prepared alternately on two streams by two threads
+    std::atomic<bool> lane_abort{false};
+    std::string sb_err2; int sb_err2_code = 0;
     std::deque<SbState> sbs;
     uint64_t sbs_used = 0;
     std::atomic<uint64_t> sb_pub{0};
@@ -573,7 +579,12 @@ template <typename K> void count_close(leon_ctx *c)
             LB_TIMED(c->kt, "k_msd_hist", st, LB_LAUNCH(c->lc, (k_msd_hist<K>), grid, RS_THREADS, 0, st, keys, lv, cnt));
             uint64_t *ptot = lbscan::exclusive_scan<uint64_t>(P << w, MsdCntIn{cnt}, MsdCntOut{pnext, cur}, c->d_scan, st, c->lc);
             CUDA_TRY(cudaMemcpyAsync(pnext + (P << w), ptot, 8, cudaMemcpyDeviceToDevice, st));
-            LB_TIMED(c->kt, "k_msd_scatter", st, LB_LAUNCH(c->lc, (k_msd_scatter<K>), grid, RS_THREADS, 0, st, keys, alt, lv, cur));
+            static const uint64_t msd_threads = env_u64("LEON_B200_MSD_THREADS", 512);
+            if (msd_threads == 512) {
+                LB_TIMED(c->kt, "k_msd_scatter", st, LB_LAUNCH(c->lc, (k_msd_scatter<K, 512>), grid, 512, 0, st, keys, alt, lv, cur));
+            } else {
+                LB_TIMED(c->kt, "k_msd_scatter", st, LB_LAUNCH(c->lc, (k_msd_scatter<K, 256>), grid, 256, 0, st, keys, alt, lv, cur));
+            }
             std::swap(keys, alt);
             std::swap(pcur, pnext);
             P <<= w;
@@ -977,10 +988,14 @@ __global__ void k_sb_info(const uint64_t *__restrict__ offsets, const uint64_t *
 }
 
 // Walk, symbol records, per-(block, model) ranks and the launch of the range coder for super-block g.
-template <typename K> void sb_prepare(leon_ctx *c, uint64_t g)
+template <typename K> void sb_prepare(leon_ctx *c, uint64_t g, int lane = 0)
 {
     using namespace lbent;
-    Lane &ln = c->wk;
+    Lane &ln = lane ? c->wk2 : c->wk;
+    // transient buffers: the context's on lane 0, the lane's own on lane 1
+    DevBuf &d_bif = lane ? ln.d_bif : c->d_bif, &d_err = lane ? ln.d_err : c->d_err, &d_recs = lane ? ln.d_recs : c->d_recs;
+    DevBuf &d_symoff = lane ? ln.d_symoff : c->d_symoff, &d_srec = lane ? ln.d_srec : c->d_srec, &d_srec_alt = lane ? ln.d_srec_alt : c->d_srec_alt;
+    DevBuf &d_segstart = lane ? ln.d_segstart : c->d_segstart, &d_chunkoff = lane ? ln.d_chunkoff : c->d_chunkoff, &d_chist = lane ? ln.d_chist : c->d_chist;
     cudaStream_t st = ln.st;
     SbState &sb = c->sbs[g];
     const int k = c->opts.kmer_size;
@@ -997,10 +1012,10 @@ template <typename K> void sb_prepare(leon_ctx *c, uint64_t g)
     // (measured: the anchor kernels and the chains of other super-blocks queued behind such waits, 83 -> 199 ms per run).
     CUDA_TRY(cudaEventSynchronize(sb.ev_anchored));
     // the transient buffers of the stage are reused by the next super-block: in stream order on this lane
-    c->d_bif.reserve(sb.nk + 1);
-    c->d_err.reserve((sb.nk + 1) * 4);
-    c->d_recs.reserve((R + 1) * sizeof(lbwalk::ReadRec));
-    ReadRec *recs = c->d_recs.as<ReadRec>();
+    d_bif.reserve(sb.nk + 1);
+    d_err.reserve((sb.nk + 1) * 4);
+    d_recs.reserve((R + 1) * sizeof(lbwalk::ReadRec));
+    ReadRec *recs = d_recs.as<ReadRec>();
     {
         // bases of the 256 reads of a CTA are staged in shared memory when they fit (40 KB), else read from global
         uint64_t need = ((256ull * (uint64_t)c->max_len + 31) & ~15ull) + 16;
@@ -1011,32 +1026,32 @@ template <typename K> void sb_prepare(leon_ctx *c, uint64_t g)
         size_t smem_claim = std::max<size_t>(stage_bytes, walk_smem);
         if (walk_smem) CUDA_TRY(cudaFuncSetAttribute(lbwalk::k_walk<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_claim));
         LB_TIMED(ln.kt, "k_walk", st, LB_LAUNCH(ln.lc, (lbwalk::k_walk<K>), cdiv_u(R, 256), 256, smem_claim, st, bases, offsets, koff, R, c->bloom,
-                  c->d_tbl.as<uint64_t>(), apos, c->d_bif.as<uint8_t>(), c->d_err.as<uint32_t>(), recs, stage_bytes));
+                  c->d_tbl.as<uint64_t>(), apos, d_bif.as<uint8_t>(), d_err.as<uint32_t>(), recs, stage_bytes));
     }
     sb.nblocks = (R + rpb - 1) / rpb;
     if (sb.nblocks >= (1ull << 18)) throw LeonError(LEON_E_OVERFLOW, "more than 2^18 blocks in one super-block");
-    c->d_symoff.reserve((R + 2) * 8);
-    uint64_t *symoff = c->d_symoff.as<uint64_t>();
-    SymCountIn cin{bases, offsets, koff, apos, aaddr, recs, c->d_bif.as<uint8_t>(), c->d_err.as<uint32_t>()};
+    d_symoff.reserve((R + 2) * 8);
+    uint64_t *symoff = d_symoff.as<uint64_t>();
+    SymCountIn cin{bases, offsets, koff, apos, aaddr, recs, d_bif.as<uint8_t>(), d_err.as<uint32_t>()};
     uint64_t *symtot = lbscan::exclusive_scan<uint64_t>(R, cin, SymOffOut{symoff}, ln.d_scan, st, ln.lc);
     CUDA_TRY(cudaMemcpyAsync(symoff + R, symtot, 8, cudaMemcpyDeviceToDevice, st));
     const uint64_t nsym = fetch_scalar_on(ln, symtot);
     if (nsym >= 0xffffff00ull) throw LeonError(LEON_E_OVERFLOW, "more than 2^32 symbols in one super-block");
     sb.nsym = nsym;
-    c->d_srec.reserve((nsym + 1) * 8);
-    c->d_srec_alt.reserve((nsym + 1) * 8);
-    uint64_t *srec = c->d_srec.as<uint64_t>(), *salt = c->d_srec_alt.as<uint64_t>();
+    d_srec.reserve((nsym + 1) * 8);
+    d_srec_alt.reserve((nsym + 1) * 8);
+    uint64_t *srec = d_srec.as<uint64_t>(), *salt = d_srec_alt.as<uint64_t>();
     LB_TIMED(ln.kt, "k_emit_syms", st, LB_LAUNCH(ln.lc, k_emit_syms, cdiv_u(R, 256), 256, 0, st, bases, offsets, koff, R, rpb, apos, aaddr, recs,
-              c->d_bif.as<uint8_t>(), c->d_err.as<uint32_t>(), symoff, srec));
+              d_bif.as<uint8_t>(), d_err.as<uint32_t>(), symoff, srec));
     // stable sort by (block, model): key bits [40, 46 + bits(nblocks - 1))
     int keybits = REC_MODEL_BITS;
     while (keybits < 24 && ((sb.nblocks - 1) >> (keybits - REC_MODEL_BITS))) keybits++;
     for (int p = 0; p < (keybits + 7) / 8 && nsym > 1; p++)
         partition_pass_on(ln, srec, salt, nsym, lbcount::ShiftDigit<uint64_t>{REC_KEY_SHIFT + 8 * p});
     // segments and chunks
-    c->d_segstart.reserve((sb.nblocks * NUM_MODELS + 2) * 8);
-    c->d_chunkoff.reserve((sb.nblocks * NUM_MODELS + 2) * 8);
-    uint64_t *segstart = c->d_segstart.as<uint64_t>(), *chunkoff = c->d_chunkoff.as<uint64_t>();
+    d_segstart.reserve((sb.nblocks * NUM_MODELS + 2) * 8);
+    d_chunkoff.reserve((sb.nblocks * NUM_MODELS + 2) * 8);
+    uint64_t *segstart = d_segstart.as<uint64_t>(), *chunkoff = d_chunkoff.as<uint64_t>();
     uint64_t nseg = 0, nchunks = 0;
     if (nsym) {
         uint64_t *segtot = lbscan::exclusive_scan<uint64_t>(nsym, SegHeadIn{srec}, SegHeadOut{segstart}, ln.d_scan, st, ln.lc);
@@ -1049,8 +1064,8 @@ template <typename K> void sb_prepare(leon_ctx *c, uint64_t g)
     sb.d_rec.reserve((nsym + 1) * sizeof(uint4));
     sb.d_sh.reserve(nsym + 1);
     if (nchunks) {
-        c->d_chist.reserve(nchunks * 256 * 4);
-        uint32_t *H = c->d_chist.as<uint32_t>();
+        d_chist.reserve(nchunks * 256 * 4);
+        uint32_t *H = d_chist.as<uint32_t>();
         LB_TIMED(ln.kt, "k_chunk_hist", st, LB_LAUNCH(ln.lc, k_chunk_hist, (unsigned)nchunks, 256, 0, st, srec, segstart, chunkoff, nseg, H));
         LB_TIMED(ln.kt, "k_seg_scan", st, LB_LAUNCH(ln.lc, k_seg_scan, (unsigned)nseg, 256, 0, st, chunkoff, nseg, nchunks, H));
         LB_TIMED(ln.kt, "k_chunk_ranks", st, LB_LAUNCH(ln.lc, k_chunk_ranks, (unsigned)nchunks, CHUNK, 0, st, srec, segstart, chunkoff, nseg, H,
@@ -1146,8 +1161,24 @@ static uint64_t sb_pipeline_min()
 }
 
 
+// super-blocks lane, lane + nlanes, ... in turn: each waits for its anchors (all anchors when the stage is deferred)
+template <typename K> void stage_b_lane(leon_ctx *c, int lane, int nlanes, uint64_t gate)
+{
+    const uint64_t nsb = c->sbs_used;
+    for (uint64_t g = (uint64_t)lane; g < nsb; g += (uint64_t)nlanes) {
+        while (c->sb_pub.load(std::memory_order_acquire) <= std::max(g, gate)) {
+            if (c->sb_abort.load() || c->lane_abort.load()) return;
+            std::this_thread::sleep_for(std::chrono::microseconds(10));
+        }
+        if (c->lane_abort.load()) return;
+        sb_prepare<K>(c, g, lane);
+        c->sb_walked.fetch_add(1, std::memory_order_acq_rel);
+    }
+}
+
 template <typename K> void stage_b_worker(leon_ctx *c)
 {
+    std::thread helper;
     try {
         CUDA_TRY(cudaSetDevice(c->opts.device));
         const uint64_t nsb = c->sbs_used;
@@ -1157,14 +1188,30 @@ template <typename K> void stage_b_worker(leon_ctx *c)
         // (anchor stage 8.6 -> 15.5 ms) and that costs what the overlap gains (72.4 vs 72.2 ms; FASTQ 87.4 vs 82.8 ms), since
         // the run ends one chain length (40 ms) after the LAST chain is launched either way.  Larger sets are pipelined.
         const uint64_t gate = nsb <= sb_pipeline_min() ? nsb - 1 : 0;
-        for (uint64_t g = 0; g < nsb; g++) {
-            while (c->sb_pub.load(std::memory_order_acquire) <= std::max(g, gate)) {
-                if (c->sb_abort.load()) { c->sb_walks_done.store(true); return; }
-                std::this_thread::sleep_for(std::chrono::microseconds(10));
-            }
-            sb_prepare<K>(c, g);
-            c->sb_walked.store(g + 1, std::memory_order_release);
-        }
+        // Two lanes (LEON_B200_WALK_LANES=2; default 1): a super-block's preparation is a walk (0.8 ms at configs[2]) and a dozen
+        // small kernels with four host round trips (0.4 ms); on two streams, driven by two threads, the walk of one super-block
+        // runs beside the small kernels of the other.  Measured (profiles/r3b_walk_lanes.txt): configs[2] 72.2 -> 93.0 ms -- the
+        // chains that claim a whole SM cannot start while the other lane's walk holds every SM -- and the configs[3] encode pass
+        // 1.21 -> 1.23 s (the GPU is busy either way), so one lane it is.
+        static const uint64_t lanes_knob = env_u64("LEON_B200_WALK_LANES", 1);
+        const int nlanes = (lanes_knob >= 2 && nsb >= 2 && c->wk2.st) ? 2 : 1;
+        c->lane_abort.store(false);
+        c->sb_err2.clear();
+        if (nlanes == 2)
+            helper = std::thread([c, gate]() {
+                try {
+                    CUDA_TRY(cudaSetDevice(c->opts.device));
+                    stage_b_lane<K>(c, 1, 2, gate);
+                } catch (const LeonError &e) {
+                    c->sb_err2 = e.msg; c->sb_err2_code = e.code; c->lane_abort.store(true);
+                } catch (const std::exception &e) {
+                    c->sb_err2 = e.what(); c->sb_err2_code = LEON_E_NOMEM; c->lane_abort.store(true);
+                }
+            });
+        stage_b_lane<K>(c, 0, nlanes, gate);
+        if (helper.joinable()) helper.join();
+        if (!c->sb_err2.empty()) throw LeonError(c->sb_err2_code, c->sb_err2);
+        if (c->sb_abort.load()) { c->sb_walks_done.store(true); return; }
         // sb_prepare returns once the records of its super-block are made (it waits for them before it launches the chains):
         // from here on only range coder chains run
         c->sb_walks_done.store(true, std::memory_order_release);
@@ -1177,6 +1224,7 @@ template <typename K> void stage_b_worker(leon_ctx *c)
     } catch (const std::exception &e) {
         c->sb_err = e.what(); c->sb_err_code = LEON_E_NOMEM; c->sb_failed.store(true);
     }
+    if (helper.joinable()) { c->lane_abort.store(true); helper.join(); }
     c->sb_walks_done.store(true, std::memory_order_release);       // also after an error: nobody waits for ever
 }
 
@@ -1564,6 +1612,7 @@ template <typename K> void encode_batch(leon_ctx *c)
     c->h_dna.reserve(c->nbases / 16 + 8 * R + 1024 * c->nblocks + 4096);
     c->h_bs.reserve(c->nblocks * 16 + 16);
     c->wk.kt.reset();
+    c->wk2.kt.reset();
     c->sb_pub.store(0);
     c->sb_abort.store(false);
     c->sb_err.clear();
@@ -1806,8 +1855,9 @@ static void fill_timings(leon_ctx *c)
     c->tm.dict_wait_ms = c->opts.dict_on_device ? 0.f : el(15, 14);
     c->kt.resolve();
     c->wk.kt.resolve();
+    c->wk2.kt.resolve();
     for (uint64_t g = 0; g < c->sbs_used; g++) c->sbs[g].kt.resolve();
-    c->tm.kernel_launches += c->wk.lc.n;
+    c->tm.kernel_launches += c->wk.lc.n + c->wk2.lc.n;
     c->tm.nsym_total = c->nsym_total;
     c->tm.sort_pass_ms = 0;
     for (auto &sl : c->kt.slots)
@@ -1851,6 +1901,7 @@ int leon_create(const leon_opts *opts, leon_ctx **out)
             CUDA_TRY(cudaStreamCreateWithPriority(&c->st2, cudaStreamNonBlocking, hi_pri));
             CUDA_TRY(cudaStreamCreateWithPriority(&c->st3, cudaStreamNonBlocking, mid_pri));   // quality kernels: issued first, so they run first and are out of the way of the last chains
             CUDA_TRY(cudaStreamCreateWithPriority(&c->wk.st, cudaStreamNonBlocking, mid_pri));
+            CUDA_TRY(cudaStreamCreateWithPriority(&c->wk2.st, cudaStreamNonBlocking, mid_pri));
         }
         CUDA_TRY(cudaEventCreateWithFlags(&c->ev_user_in, cudaEventDisableTiming));
         CUDA_TRY(cudaEventCreateWithFlags(&c->ev_user_out, cudaEventDisableTiming));
@@ -1878,8 +1929,10 @@ void leon_destroy(leon_ctx *c)
     if (c->sb_thread.joinable()) c->sb_thread.join();
     if (c->st) cudaStreamSynchronize(c->st);
     if (c->wk.st) { cudaStreamSynchronize(c->wk.st); }
+    if (c->wk2.st) { cudaStreamSynchronize(c->wk2.st); }
     for (auto &sb : c->sbs) sb.destroy();
     c->wk.kt.release();
+    c->wk2.kt.release();
     if (c->comm.comm) nccl_api().CommDestroy(c->comm.comm);
     DevBuf *dev[] = {&c->d_retry, &c->d_pstart_alt, &c->d_tstart, &c->d_mcnt, &c->d_mcur, &c->d_bases, &c->d_offsets, &c->d_quals, &c->d_koff, &c->d_keys, &c->d_keys_alt, &c->d_tile_hist, &c->d_tile_off,
                      &c->d_scan, &c->d_bstart, &c->d_solid_cnt, &c->d_bstart_all, &c->d_keys_recv, &c->d_solid_keys, &c->d_pick,
@@ -1900,6 +1953,7 @@ void leon_destroy(leon_ctx *c)
     if (c->ev_dtot) cudaEventDestroy(c->ev_dtot);
     if (c->st) cudaStreamDestroy(c->st);
     if (c->wk.st) cudaStreamDestroy(c->wk.st);
+    if (c->wk2.st) cudaStreamDestroy(c->wk2.st);
     if (c->st_copy) { cudaStreamSynchronize(c->st_copy); cudaStreamDestroy(c->st_copy); }
     if (c->ev_copy) cudaEventDestroy(c->ev_copy);
     if (c->ev_pf_guard) cudaEventDestroy(c->ev_pf_guard);
@@ -2454,6 +2508,7 @@ int leon_get_kernel_times(const leon_ctx *c, leon_kernel_time *out, int cap, int
     };
     add(c->kt);
     add(c->wk.kt);
+    add(c->wk2.kt);
     for (uint64_t g = 0; g < c->sbs_used && g < c->sbs.size(); g++) add(c->sbs[g].kt);
     int m = 0;
     for (auto &sl : all) {
