@@ -36,7 +36,15 @@ template <typename K> struct DictDev {
     uint64_t mask;       // capacity - 1 (power of two)
 };
 
-template <typename K> LB_HD uint64_t dict_hash(K key) { return hash64(kmer_fold64(key), 0x9E3779B97F4A7C15ULL); }
+// The dictionary is private to this implementation (the reference keeps a std::unordered_map-like container,
+// C/Leon.cpp:1105-1243), so its hash is free: one multiply, the high half folded into the low one (slot = low bits, tag = top
+// byte).  The reference's hash64 used here at first cost ~60 of the ~120 instructions the lookups spend per position, and the
+// lookups are issue-bound (ncu: sm 76 %, dram 4 %; profiles/r3e_ncu_full.csv).
+template <typename K> LB_HD uint64_t dict_hash(K key)
+{
+    const uint64_t x = kmer_fold64(key) * 0x9E3779B97F4A7C15ULL;
+    return x ^ (x >> 32);
+}
 // The lookups probe every k-mer of a read until the first hit, so most probes fail, and at the scale of configs[3] (2.8 M
 // anchors, 16 M slots) the 4-byte and 8-byte arrays of the table are 64 + 128 MB: every failed probe was a DRAM access.  The
 // tags of the same table are 16 MB and stay in L2; keys and times are only read behind a matching tag (1 in 255 by chance).
