@@ -221,7 +221,9 @@ int leon_get_kernel_times(const leon_ctx *ctx, leon_kernel_time *out, int cap, i
  * file order.  Counting exchanges k-mers by hash owner (all-to-all), the Bloom filter is the OR of the ranks' parts
  * (all-gather), anchor candidates are all-gathered per batch so that addresses equal the serial reference's.  Each
  * rank returns its own blocks (block j of round g on rank r is block (g * nranks + r) * S / reads_per_block + j of the
- * file); the Bloom filter, the counts and (on rank 0) the anchor dictionary are those of the whole set. */
+ * file); the Bloom filter, the counts and (on rank 0) the anchor dictionary are those of the whole set.
+ * 1 <= nranks <= 8 (one NVSwitch node; the per-bucket source table of the counting kernel is sized for it): more ranks are
+ * refused with LEON_E_ARG and a message, nothing is capped silently. */
 int leon_comm_unique_id(void *id128);
 int leon_comm_init(leon_ctx *ctx, int rank, int nranks, const void *id128);
 int leon_comm_batch_reads(const leon_ctx *ctx, uint64_t *reads);
