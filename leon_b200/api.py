@@ -563,7 +563,7 @@ class Leon:
         """Starts the upload of the batch that will be submitted next (leon_stream_prefetch); the arrays must be the very
         ones passed to the next count_batch / encode_block call."""
         rd, keep = self._batch(bases, offsets, quals)
-        self._pf_keep = keep
+        self._pf_keep = (getattr(self, "_pf_keep", ()) + (keep,))[-3:]      # two announcements may be open + the batch in work
         self._check(self.L.leon_stream_prefetch(self.ctx, C.byref(rd), int(quals is not None)))
 
     def count_batch(self, bases, offsets, last):
